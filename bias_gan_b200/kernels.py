@@ -1,0 +1,70 @@
+"""Thin Python wrappers over the C ABI (include/bgr.h): raw pointers in, status out.
+
+Tensors here are bf16 NHWC views `[N, H, W, C]` whose last dim is contiguous; a view may be a
+channel slice of a wider buffer (pixel stride = `stride(2)`), which is how concatenations are
+written in place.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import check, int_array, ptr, stream_ptr
+
+
+def taps_for(kernel_size, dilation=1):
+    """(dy, dx) input offsets of a `kernel_size` x `kernel_size` conv with 'same' padding
+    (fixed_padding, deeplab.py:66-72, and padding=dilation for the dense 3x3 convs)."""
+    if kernel_size == 1:
+        return [0], [0]
+    r = (kernel_size - 1) // 2
+    dy, dx = [], []
+    for i in range(kernel_size):
+        for j in range(kernel_size):
+            dy.append((i - r) * dilation)
+            dx.append((j - r) * dilation)
+    return dy, dx
+
+
+def _nhwc_view(t):
+    assert t.dim() == 4 and t.dtype == torch.bfloat16 and t.is_cuda, "expected a bf16 NHWC cuda view"
+    N, H, W, C = t.shape
+    ld = t.stride(2)
+    assert t.stride(3) == 1 and t.stride(1) == W * ld and t.stride(0) == H * W * ld, \
+        "expected dense pixels with a uniform pixel stride"
+    return N, H, W, C, ld
+
+
+def conv_fprop(x, w, dy, dx, out=None, bias=None, s2d=False):
+    """y = conv(x, w).  x: [N,H,W,Cin] bf16 NHWC; w: [Cout, ntaps, Cin] bf16; out: [N,H,W,Cout]."""
+    N, H, W, Cin, ldx = _nhwc_view(x)
+    if s2d:
+        assert H % 2 == 0 and W % 2 == 0
+        H, W, Cin = H // 2, W // 2, Cin * 4
+    Cout, ntaps, wc = w.shape
+    assert wc == Cin and w.is_contiguous() and w.dtype == torch.bfloat16 and ntaps == len(dy)
+    if out is None:
+        out = torch.empty((N, H, W, Cout), dtype=torch.bfloat16, device=x.device)
+    No, Ho, Wo, Co, ldy = _nhwc_view(out)
+    assert (No, Ho, Wo, Co) == (N, H, W, Cout)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() == Cout
+    check(_lib.lib().bgr_conv_fprop(ptr(x), N, H, W, Cin, ldx, ptr(w), Cout, ntaps, int_array(dy),
+                                    int_array(dx), ptr(out), ldy, ptr(bias), int(s2d), stream_ptr()))
+    return out
+
+
+def conv_wgrad(x, gy, dy, dx, dw=None, s2d=False):
+    """dw[Cout, ntaps, Cin] (fp32) += sum_pixels gy[p, co] * x[p + tap, ci]."""
+    N, H, W, Cin, ldx = _nhwc_view(x)
+    if s2d:
+        H, W, Cin = H // 2, W // 2, Cin * 4
+    Ng, Hg, Wg, Cout, ldy = _nhwc_view(gy)
+    assert (Ng, Hg, Wg) == (N, H, W)
+    ntaps = len(dy)
+    if dw is None:
+        dw = torch.zeros((Cout, ntaps, Cin), dtype=torch.float32, device=x.device)
+    assert dw.is_contiguous() and dw.dtype == torch.float32 and tuple(dw.shape) == (Cout, ntaps, Cin)
+    check(_lib.lib().bgr_conv_wgrad(ptr(x), N, H, W, Cin, ldx, ptr(gy), Cout, ldy, ntaps,
+                                    int_array(dy), int_array(dx), ptr(dw), int(s2d), stream_ptr()))
+    return dw
