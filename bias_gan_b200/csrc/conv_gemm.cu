@@ -39,7 +39,7 @@ template <int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(192, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   __nv_bfloat16* __restrict__ out, const float* __restrict__ bias,
-                  const ConvParams p) {
+                  const __grid_constant__ ConvParams p) {
   constexpr uint32_t A_BYTES = kBlockM * kBlockK * 2;
   constexpr uint32_t B_BYTES = BLOCK_N * kBlockK * 2;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -155,7 +155,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 template <int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(192, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
-                  float* __restrict__ dw, const ConvParams p) {
+                  float* __restrict__ dw, const __grid_constant__ ConvParams p) {
   constexpr uint32_t BOX_BYTES = 64 * kBlockK * 2;           // one 64-channel x 64-pixel box
   constexpr uint32_t A_BYTES = (kBlockM / 64) * BOX_BYTES;   // dY^T : 128 couts
   constexpr uint32_t B_BYTES = (BLOCK_N / 64) * BOX_BYTES;   // X^T  : BLOCK_N cins
@@ -278,41 +278,23 @@ static void pick_rect(int H, int W, int pixels, int* BW, int* BH) {
   }
 }
 
-// 5-D activation map (c, d1, x, y, n).  Plain NHWC: d1 == 1.  s2d: the tensor is [N,2H,2W,C4]
-// and (c, d1) = ((px, c4) = 2*C4 contiguous elements, py) so that one pixel of the H x W grid is
-// a 2x2 block = 4*C4 channels landing contiguously in shared memory.
+// 5-D activation map (c, 1, x, y, n) over a bf16 NHWC view with pixel stride ld.
 static int make_act_map(CUtensorMap* m, const void* base, int N, int H, int W, int C, int ld,
-                        int BW, int BH, int s2d) {
-  uint64_t dims[5], strides[4];
-  uint32_t box[5];
-  if (!s2d) {
-    dims[0] = C; dims[1] = 1; dims[2] = W; dims[3] = H; dims[4] = N;
-    strides[0] = uint64_t(ld) * 2;                 // d1 (unused)
-    strides[1] = uint64_t(ld) * 2;                 // x
-    strides[2] = uint64_t(W) * ld * 2;             // y
-    strides[3] = uint64_t(H) * W * ld * 2;         // n
-    box[0] = 64; box[1] = 1;
-  } else {
-    const int C4 = C / 4;  // channels of the full-resolution tensor
-    dims[0] = 2 * C4; dims[1] = 2; dims[2] = W; dims[3] = H; dims[4] = N;
-    strides[0] = uint64_t(2 * W) * ld * 2;         // py: next full-res row
-    strides[1] = uint64_t(2) * ld * 2;             // block x
-    strides[2] = uint64_t(2) * (2 * W) * ld * 2;   // block y
-    strides[3] = uint64_t(2 * H) * (2 * W) * ld * 2;
-    box[0] = 2 * C4; box[1] = 2;
-  }
-  box[2] = BW; box[3] = BH; box[4] = 1;
+                        int BW, int BH) {
+  uint64_t dims[5] = {uint64_t(C), 1, uint64_t(W), uint64_t(H), uint64_t(N)};
+  uint64_t strides[4] = {uint64_t(ld) * 2, uint64_t(ld) * 2, uint64_t(W) * ld * 2,
+                         uint64_t(H) * W * ld * 2};
+  uint32_t box[5] = {64, 1, uint32_t(BW), uint32_t(BH), 1};
   return encode_tmap_bf16(m, base, 5, dims, strides, box);
 }
 
 static int check_conv_args(const void* x, const void* w, const void* y, int Cin, int ldx, int Cout,
-                           int ldy, int ntaps, int s2d) {
+                           int ldy, int ntaps) {
   if (ntaps < 1 || ntaps > kMaxTaps) return fail(BGR_ERR_ARG, "conv: ntaps must be in [1,9]");
   if ((Cin % 8) || (Cout % 8) || (ldx % 8) || (ldy % 8))
     return fail(BGR_ERR_ARG, "conv: channel counts and pixel strides must be multiples of 8");
   if ((uintptr_t(x) | uintptr_t(w) | uintptr_t(y)) & 15)
     return fail(BGR_ERR_ARG, "conv: pointers must be 16-byte aligned");
-  if (s2d && Cin != 64) return fail(BGR_ERR_ARG, "conv: s2d needs Cin == 64 (16-channel fields)");
   return BGR_OK;
 }
 
@@ -363,8 +345,8 @@ using namespace bgr;
 
 extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w,
                               int Cout, int ntaps, const int* dy, const int* dx, void* y, int ldy,
-                              const float* bias, int s2d, void* stream) {
-  if (int rc = check_conv_args(x, w, y, Cin, ldx, Cout, ldy, ntaps, s2d)) return rc;
+                              const float* bias, void* stream) {
+  if (int rc = check_conv_args(x, w, y, Cin, ldx, Cout, ldy, ntaps)) return rc;
   ConvParams p{};
   p.N = N; p.H = H; p.W = W;
   pick_rect(H, W, kBlockM, &p.BW, &p.BH);
@@ -375,7 +357,7 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
   p.Cout = Cout; p.Cin = Cin; p.ld_out = ldy;
   for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
   CUtensorMap tmA, tmB;
-  if (int rc = make_act_map(&tmA, x, N, H, W, Cin, ldx, p.BW, p.BH, s2d)) return rc;
+  if (int rc = make_act_map(&tmA, x, N, H, W, Cin, ldx, p.BW, p.BH)) return rc;
   const int bn = Cout <= 64 ? 64 : 128;
   {
     uint64_t dims[3] = {uint64_t(Cin), uint64_t(ntaps), uint64_t(Cout)};
@@ -390,8 +372,8 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
 
 extern "C" int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx,
                               const void* dy_, int Cout, int ldy, int ntaps, const int* dy,
-                              const int* dx, float* dw, int s2d, void* stream) {
-  if (int rc = check_conv_args(x, dw, dy_, Cin, ldx, Cout, ldy, ntaps, s2d)) return rc;
+                              const int* dx, float* dw, void* stream) {
+  if (int rc = check_conv_args(x, dw, dy_, Cin, ldx, Cout, ldy, ntaps)) return rc;
   ConvParams p{};
   p.N = N; p.H = H; p.W = W;
   pick_rect(H, W, kBlockK, &p.BW, &p.BH);
@@ -402,8 +384,8 @@ extern "C" int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int l
   p.Cout = Cout; p.Cin = Cin;
   for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
   CUtensorMap tmDY, tmX;
-  if (int rc = make_act_map(&tmDY, dy_, N, H, W, Cout, ldy, p.BW, p.BH, 0)) return rc;
-  if (int rc = make_act_map(&tmX, x, N, H, W, Cin, ldx, p.BW, p.BH, s2d)) return rc;
+  if (int rc = make_act_map(&tmDY, dy_, N, H, W, Cout, ldy, p.BW, p.BH)) return rc;
+  if (int rc = make_act_map(&tmX, x, N, H, W, Cin, ldx, p.BW, p.BH)) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (Cin <= 64) return launch_wgrad<64, 6>(tmDY, tmX, dw, p, st);
   return launch_wgrad<128, 6>(tmDY, tmX, dw, p, st);

@@ -35,12 +35,9 @@ def _nhwc_view(t):
     return N, H, W, C, ld
 
 
-def conv_fprop(x, w, dy, dx, out=None, bias=None, s2d=False):
+def conv_fprop(x, w, dy, dx, out=None, bias=None):
     """y = conv(x, w).  x: [N,H,W,Cin] bf16 NHWC; w: [Cout, ntaps, Cin] bf16; out: [N,H,W,Cout]."""
     N, H, W, Cin, ldx = _nhwc_view(x)
-    if s2d:
-        assert H % 2 == 0 and W % 2 == 0
-        H, W, Cin = H // 2, W // 2, Cin * 4
     Cout, ntaps, wc = w.shape
     assert wc == Cin and w.is_contiguous() and w.dtype == torch.bfloat16 and ntaps == len(dy)
     if out is None:
@@ -50,15 +47,13 @@ def conv_fprop(x, w, dy, dx, out=None, bias=None, s2d=False):
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == Cout
     check(_lib.lib().bgr_conv_fprop(ptr(x), N, H, W, Cin, ldx, ptr(w), Cout, ntaps, int_array(dy),
-                                    int_array(dx), ptr(out), ldy, ptr(bias), int(s2d), stream_ptr()))
+                                    int_array(dx), ptr(out), ldy, ptr(bias), stream_ptr()))
     return out
 
 
-def conv_wgrad(x, gy, dy, dx, dw=None, s2d=False):
+def conv_wgrad(x, gy, dy, dx, dw=None):
     """dw[Cout, ntaps, Cin] (fp32) += sum_pixels gy[p, co] * x[p + tap, ci]."""
     N, H, W, Cin, ldx = _nhwc_view(x)
-    if s2d:
-        H, W, Cin = H // 2, W // 2, Cin * 4
     Ng, Hg, Wg, Cout, ldy = _nhwc_view(gy)
     assert (Ng, Hg, Wg) == (N, H, W)
     ntaps = len(dy)
@@ -66,5 +61,5 @@ def conv_wgrad(x, gy, dy, dx, dw=None, s2d=False):
         dw = torch.zeros((Cout, ntaps, Cin), dtype=torch.float32, device=x.device)
     assert dw.is_contiguous() and dw.dtype == torch.float32 and tuple(dw.shape) == (Cout, ntaps, Cin)
     check(_lib.lib().bgr_conv_wgrad(ptr(x), N, H, W, Cin, ldx, ptr(gy), Cout, ldy, ntaps,
-                                    int_array(dy), int_array(dx), ptr(dw), int(s2d), stream_ptr()))
+                                    int_array(dy), int_array(dx), ptr(dw), stream_ptr()))
     return dw

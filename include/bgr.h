@@ -39,6 +39,34 @@ extern "C" {
 const char* bgr_last_error(void);
 int bgr_version(void);
 
+/* ---- .npy reader (numpy_reader.cpp:501-536) ---------------------------------------------- */
+
+/* numpy_reader(split_axis, device) constructor (numpy_reader.h:54-95); device -1 = host. */
+int bgr_reader_create(int split_axis, int device, void** handle);
+int bgr_reader_destroy(void* handle);
+/* NumpyReader::ParseFile (numpy_reader.cpp:58-185): header -> dtype/order/shape/strides. */
+int bgr_reader_parse(void* handle, const char* filename);
+/* NumpyReader::InitFile / FinalizeFile (numpy_reader.cpp:342-380). */
+int bgr_reader_init_file(void* handle, const char* filename);
+int bgr_reader_finalize_file(void* handle);
+/* NumpyReader::SetBatchsize (numpy_reader.cpp:228-247); range errors -> BGR_ERR_INDEX. */
+int bgr_reader_set_batchsize(void* handle, int64_t batch_size);
+/* num_inter_threads / num_intra_threads setters (numpy_reader.h:135-159). */
+int bgr_reader_set_threads(void* handle, int inter, int intra);
+/* shape/strides/num_samples properties; shape and stride hold up to 8 entries. */
+int bgr_reader_info(void* handle, int* ndim, int64_t* shape, int64_t* stride, int* dtype,
+                    int64_t* num_samples, int* fortran_order, int64_t* payload_offset,
+                    int64_t* batchsize, int* inter, int* intra);
+/* getSample / getBatch (numpy_reader.cpp:434-497): read n == batchsize samples (negative ids
+ * wrap) into dst, sample-major.  dst_device < 0: dst is host memory; else device memory on
+ * cuda:dst_device, filled by chunked pinned-staging copies enqueued on `stream`. */
+int bgr_reader_read(void* handle, const int64_t* ids, int n, void* dst, int dst_device,
+                    void* stream);
+int64_t bgr_reader_bytes_read(void* handle);
+/* EnableP2P / DisableP2P (numpy_reader.cpp:17-56). */
+int bgr_reader_enable_p2p(void);
+int bgr_reader_disable_p2p(void);
+
 /* ---- implicit-GEMM convolution (tcgen05 / TMEM / TMA) ------------------------------------ */
 
 /* y[n,h,w,co] = bias[co] + sum_{t,ci} x[n, h+dy[t], w+dx[t], ci] * w[co,t,ci]   (zero outside)
@@ -46,17 +74,16 @@ int bgr_version(void);
  * y: bf16 NHWC view, pixel stride ldy.  Cin, Cout, ldx, ldy multiples of 8; pointers 16-byte
  * aligned.  Covers nn.Conv2d 1x1 / 3x3 / atrous stride 1 (deeplab.py:58,81,95,182,331,363,366,
  * 622,626,630) and, with transposed+flipped weights, their data gradients.
- * s2d != 0: x is the full-resolution [N,2H,2W,Cin/4] tensor read as 2x2 space-to-depth blocks
- * (Cin must be 64): the stride-2 3x3 entry conv (deeplab.py:178) as a 2x2-tap conv. */
+ * The stride-2 3x3 entry conv (deeplab.py:178) runs through the same entry point as a 2x2-tap
+ * stride-1 conv over fields stored as 2x2 space-to-depth blocks (see bgr_stage_normalize). */
 int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w, int Cout,
                    int ntaps, const int* dy, const int* dx, void* y, int ldy, const float* bias,
-                   int s2d, void* stream);
+                   void* stream);
 
 /* dw[co,t,ci] += sum_{n,h,w} dy_[n,h,w,co] * x[n, h+dy[t], w+dx[t], ci]   (fp32, accumulated:
  * zero dw first).  Same views as bgr_conv_fprop. */
 int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx, const void* dy_, int Cout,
-                   int ldy, int ntaps, const int* dy, const int* dx, float* dw, int s2d,
-                   void* stream);
+                   int ldy, int ntaps, const int* dy, const int* dx, float* dw, void* stream);
 
 #ifdef __cplusplus
 }
