@@ -1,0 +1,281 @@
+// Training-mode BatchNorm + LeakyReLU(0.2) + residual kernels on bf16 NHWC tensors viewed as
+// [M pixels][C channels] with a pixel stride (ld) so they can read/write channel slices.
+// Replaces nn.BatchNorm2d / nn.LeakyReLU / `x += skip` call sites of the reference
+// (src/deepCam/architecture/gpsro/deeplab.py:100,141,179-183,334-338,365-368,623-631).
+//
+// All kernels are HBM-bound: 128-bit accesses (8 bf16 per thread), per-channel reductions via
+// per-thread fp32 partials -> shared-memory fp32 atomics -> one fp64 global atomic per
+// channel per block (warp-shuffle-free because each thread owns fixed channels).
+#include <cuda_bf16.h>
+
+#include "bgr_internal.h"
+
+namespace bgr {
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+
+// Thread -> (row lane r, channel group g) mapping shared by the reduction kernels:
+// G = C/8 groups.  If G <= 256 a block covers R = 256/G rows at a time, else each thread loops
+// over groups g = tid, tid+256, ...
+struct RowGroupMap {
+  int G, R;
+  __device__ RowGroupMap(int C) : G(C >> 3) { R = G >= 256 ? 1 : 256 / G; }
+};
+
+// ---------------------------------------------------------------- statistics: sum, sum of squares
+__global__ void __launch_bounds__(256)
+bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long M, int C, int ld, int rows_per_block,
+                double* __restrict__ sums /* [2][C] */) {
+  extern __shared__ float sh[];  // [2][C]
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const RowGroupMap m(C);
+  const long r0 = long(blockIdx.x) * rows_per_block;
+  const long r1 = min(r0 + rows_per_block, M);
+  for (int g = threadIdx.x % m.G; g < m.G; g += (m.G >= 256 ? 256 : m.G)) {
+    const int r = m.G >= 256 ? 0 : threadIdx.x / m.G;
+    if (r >= m.R) break;
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long row = r0 + r; row < r1; row += m.R) {
+      float f[8];
+      unpack8(*reinterpret_cast<const uint4*>(x + row * ld + g * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] += f[j] * f[j]; }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&sh[g * 8 + j], s[j]);
+      atomicAdd(&sh[C + g * 8 + j], q[j]);
+    }
+    if (m.G < 256) break;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&sums[i], double(sh[i]));
+}
+
+// mean / invstd / fused affine (a, b) / running statistics (momentum, unbiased variance)
+__global__ void bn_finalize_kernel(const double* __restrict__ sums, long M, int C,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   float eps, float momentum, float* __restrict__ mean,
+                                   float* __restrict__ invstd, float* __restrict__ a,
+                                   float* __restrict__ b, float* __restrict__ running_mean,
+                                   float* __restrict__ running_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double mu = sums[c] / double(M);
+  double var = sums[C + c] / double(M) - mu * mu;
+  if (var < 0) var = 0;
+  const float is = float(1.0 / sqrt(var + double(eps)));
+  mean[c] = float(mu);
+  invstd[c] = is;
+  const float ga = gamma ? gamma[c] : 1.f;
+  a[c] = ga * is;
+  b[c] = (beta ? beta[c] : 0.f) - float(mu) * ga * is;
+  if (running_mean) {
+    const double unbiased = M > 1 ? var * double(M) / double(M - 1) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * float(mu);
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * float(unbiased);
+  }
+}
+
+// ---------------------------------------------------------------- apply: out = act(a*x + b [+ res])
+template <bool ACT, bool RES>
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __restrict__ a,
+                const float* __restrict__ b, const __nv_bfloat16* __restrict__ res, int ldr,
+                __nv_bfloat16* __restrict__ out, int ldo, long M, int C, float slope) {
+  const int G = C >> 3;
+  const long total = M * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int g = int(i % G);
+    const long row = i / G;
+    float f[8], r[8];
+    unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + g * 8), f);
+    if (RES) unpack8(*reinterpret_cast<const uint4*>(res + row * ldr + g * 8), r);
+    const float4 a0 = *reinterpret_cast<const float4*>(a + g * 8), a1 = *reinterpret_cast<const float4*>(a + g * 8 + 4);
+    const float4 b0 = *reinterpret_cast<const float4*>(b + g * 8), b1 = *reinterpret_cast<const float4*>(b + g * 8 + 4);
+    const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = fmaf(av[j], f[j], bv[j]);
+      if (RES) v += r[j];
+      if (ACT) v = v > 0.f ? v : slope * v;
+      f[j] = v;
+    }
+    *reinterpret_cast<uint4*>(out + row * ldo + g * 8) = pack8(f);
+  }
+}
+
+// ---------------------------------------------------------------- backward, pass 1:
+// dyh = g * act'(out) (bf16, = gradient of the residual input too) and per-channel
+// sums s1 = sum dyh, s2 = sum dyh * xhat  with xhat = (x - mean) * invstd.
+template <bool ACT>
+__global__ void __launch_bounds__(256)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ out,
+                     int ldo, const __nv_bfloat16* __restrict__ x, int ldx,
+                     const float* __restrict__ mean, const float* __restrict__ invstd,
+                     __nv_bfloat16* __restrict__ dyh, long M, int C, int rows_per_block, float slope,
+                     double* __restrict__ sums /* [2][C] */) {
+  extern __shared__ float sh[];
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const RowGroupMap m(C);
+  const long r0 = long(blockIdx.x) * rows_per_block;
+  const long r1 = min(r0 + rows_per_block, M);
+  for (int gi = threadIdx.x % m.G; gi < m.G; gi += (m.G >= 256 ? 256 : m.G)) {
+    const int r = m.G >= 256 ? 0 : threadIdx.x / m.G;
+    if (r >= m.R) break;
+    float mu[8], is[8], s1[8], s2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { mu[j] = mean[gi * 8 + j]; is[j] = invstd[gi * 8 + j]; s1[j] = 0.f; s2[j] = 0.f; }
+    for (long row = r0 + r; row < r1; row += m.R) {
+      float gv[8], xv[8], ov[8];
+      unpack8(*reinterpret_cast<const uint4*>(g + row * ldg + gi * 8), gv);
+      unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + gi * 8), xv);
+      if (ACT) unpack8(*reinterpret_cast<const uint4*>(out + row * ldo + gi * 8), ov);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float d = gv[j];
+        if (ACT) d = ov[j] > 0.f ? d : slope * d;
+        gv[j] = d;
+        s1[j] += d;
+        s2[j] += d * (xv[j] - mu[j]) * is[j];
+      }
+      *reinterpret_cast<uint4*>(dyh + row * C + gi * 8) = pack8(gv);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&sh[gi * 8 + j], s1[j]);
+      atomicAdd(&sh[C + gi * 8 + j], s2[j]);
+    }
+    if (m.G < 256) break;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&sums[i], double(sh[i]));
+}
+
+// backward, pass 2: dx = gamma*invstd * (dyh - s1/M - xhat * s2/M)
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* __restrict__ x, int ldx,
+                    const float* __restrict__ mean, const float* __restrict__ invstd,
+                    const float* __restrict__ gamma, const double* __restrict__ sums,
+                    __nv_bfloat16* __restrict__ dx, long M, int C) {
+  const int G = C >> 3;
+  const long total = M * G;
+  const float invM = 1.f / float(M);
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int g = int(i % G);
+    const long row = i / G;
+    float d[8], xv[8];
+    unpack8(*reinterpret_cast<const uint4*>(dyh + row * C + g * 8), d);
+    unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + g * 8), xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      const float is = invstd[c];
+      const float xh = (xv[j] - mean[c]) * is;
+      const float k1 = float(sums[c]) * invM, k2 = float(sums[C + c]) * invM;
+      d[j] = (gamma ? gamma[c] : 1.f) * is * (d[j] - k1 - xh * k2);
+    }
+    *reinterpret_cast<uint4*>(dx + row * C + g * 8) = pack8(d);
+  }
+}
+
+static int reduce_grid(long M, int C, int* rows_per_block) {
+  const int G = C / 8;
+  const int R = G >= 256 ? 1 : 256 / G;
+  long blocks = (M + long(R) * 8 - 1) / (long(R) * 8);  // >= 8 row iterations per thread
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  *rows_per_block = int((M + blocks - 1) / blocks);
+  return int((M + *rows_per_block - 1) / *rows_per_block);
+}
+
+static int elementwise_grid(long total) {
+  long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  return int(blocks < 1 ? 1 : blocks);
+}
+
+}  // namespace bgr
+
+using namespace bgr;
+
+#define BGR_CHECK_C8(C) \
+  if ((C) % 8 || (C) < 8) return fail(BGR_ERR_ARG, "channel count must be a multiple of 8")
+
+extern "C" int bgr_bn_stats(const void* x, long M, int C, int ld, double* sums, void* stream) {
+  BGR_CHECK_C8(C);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
+  int rpb;
+  const int grid = reduce_grid(M, C, &rpb);
+  bn_stats_kernel<<<grid, 256, 2 * C * sizeof(float), st>>>(static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, sums);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const float* beta,
+                               float eps, float momentum, float* mean, float* invstd, float* a, float* b,
+                               float* running_mean, float* running_var, void* stream) {
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      sums, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float* b, const void* res, int ldr,
+                            void* out, int ldo, long M, int C, int act, float slope, void* stream) {
+  BGR_CHECK_C8(C);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = elementwise_grid(M * (C / 8));
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto R = static_cast<const __nv_bfloat16*>(res);
+  auto O = static_cast<__nv_bfloat16*>(out);
+  if (act && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  else if (act) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
+                               const float* mean, const float* invstd, const float* gamma, int act,
+                               float slope, long M, int C, void* dyh, void* dx, double* sums,
+                               void* stream) {
+  BGR_CHECK_C8(C);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
+  int rpb;
+  const int grid = reduce_grid(M, C, &rpb);
+  auto G = static_cast<const __nv_bfloat16*>(g);
+  auto O = static_cast<const __nv_bfloat16*>(out);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto D = static_cast<__nv_bfloat16*>(dyh);
+  if (act) bn_bwd_reduce_kernel<true><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
+  else bn_bwd_reduce_kernel<false><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
+  BGR_CUDA_OK(cudaGetLastError());
+  bn_bwd_apply_kernel<<<elementwise_grid(M * (C / 8)), 256, 0, st>>>(D, X, ldx, mean, invstd, gamma, sums,
+                                                                    static_cast<__nv_bfloat16*>(dx), M, C);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}

@@ -63,3 +63,31 @@ def conv_wgrad(x, gy, dy, dx, dw=None):
     check(_lib.lib().bgr_conv_wgrad(ptr(x), N, H, W, Cin, ldx, ptr(gy), Cout, ldy, ntaps,
                                     int_array(dy), int_array(dx), ptr(dw), stream_ptr()))
     return dw
+
+
+_SRC_DTYPES = {torch.int64: 0, torch.int32: 1, torch.float64: 2, torch.float32: 3}
+
+
+def stage_normalize(src, layout, channels, shift, scale, crop=None, flip=(False, False), s2d=False, out=None):
+    """Fused standardise/crop/flip/bf16 staging.  src: [B,Cf,H,W] ('NCHW') or [B,H,W,Cf] ('NHWC')
+    device tensor straight from the reader; shift/scale: fp32 device [C]; returns bf16
+    [B,h,w,C] or the space-to-depth field layout [B,h/2,w/2,4C]."""
+    assert src.is_cuda and src.is_contiguous() and src.dim() == 4
+    if layout == "NCHW":
+        B, Cf, H, W = src.shape
+        lay = 0
+    else:
+        B, H, W, Cf = src.shape
+        lay = 1
+    channels = list(range(Cf)) if channels is None else [int(c) for c in channels]
+    C = len(channels)
+    y0, x0, h, w = crop if crop is not None else (0, 0, H, W)
+    shape = (B, h // 2, w // 2, 4 * C) if s2d else (B, h, w, C)
+    if out is None:
+        out = torch.empty(shape, dtype=torch.bfloat16, device=src.device)
+    assert tuple(out.shape) == shape and out.is_contiguous() and out.dtype == torch.bfloat16
+    assert shift.dtype == torch.float32 and scale.dtype == torch.float32 and shift.numel() == C == scale.numel()
+    check(_lib.lib().bgr_stage_normalize(ptr(src), _SRC_DTYPES[src.dtype], lay, B, Cf, H, W, int_array(channels), C,
+                                         ptr(shift), ptr(scale), y0, x0, h, w, int(flip[0]), int(flip[1]),
+                                         ptr(out), int(s2d), stream_ptr()))
+    return out

@@ -67,6 +67,20 @@ int64_t bgr_reader_bytes_read(void* handle);
 int bgr_reader_enable_p2p(void);
 int bgr_reader_disable_p2p(void);
 
+/* ---- decode / standardise / crop / flip / stage (gpsro_dataset.py:169-170,
+ *      cam_numpy_singlefile_dataset.py:200) ------------------------------------------------ */
+
+/* dst[b, y, x, i] = bf16_rne(scale[i] * (float(src[b, channels[i], y0+y', x0+x']) - shift[i]))
+ * with y' = flip_v ? h-1-y : y and x' = flip_h ? w-1-x : x.
+ * src: device payload of B samples, dtype BGR_*, layout BGR_NCHW [B,Cf,H,W] or BGR_NHWC
+ * [B,H,W,Cf].  channels: HOST array of C source-channel indices (NULL = identity); shift/scale:
+ * DEVICE fp32 [C].  dst: device bf16 [B,h,w,C], or with s2d != 0 the 2x2 space-to-depth layout
+ * [B,h/2,w/2,4C] with channel (py*2+px)*C + i.  C multiple of 8 (<= 64), w multiple of 4. */
+int bgr_stage_normalize(const void* src, int src_dtype, int src_layout, int B, int Cf, int H, int W,
+                        const int* channels, int C, const float* shift, const float* scale, int y0,
+                        int x0, int h, int w, int flip_h, int flip_v, void* dst, int s2d,
+                        void* stream);
+
 /* ---- implicit-GEMM convolution (tcgen05 / TMEM / TMA) ------------------------------------ */
 
 /* y[n,h,w,co] = bias[co] + sum_{t,ci} x[n, h+dy[t], w+dx[t], ci] * w[co,t,ci]   (zero outside)
