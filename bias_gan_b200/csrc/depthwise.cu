@@ -1,0 +1,282 @@
+// Depthwise 3x3 convolution with the reference's "fixed padding" (pad = dilation on every side,
+// src/deepCam/architecture/gpsro/deeplab.py:66-72,75-87), stride 1 or 2, bf16 NHWC.
+//   fwd   : y[n,oy,ox,c] = sum_k x[n, oy*s + (ky-1)*d, ox*s + (kx-1)*d, c] * w[k][c]
+//   dgrad : adjoint gather over the taps
+//   wgrad : dw[k][c] = sum_pixels dy * x_shifted   (per-channel reduction)
+// plus the stride-2 pixel subsample used in front of the 1x1 stride-2 skip convs (deeplab.py:95)
+// and its adjoint.  CUDA-core, HBM/L2-bound: 8 channels (128 bit) per thread.
+#include <cuda_bf16.h>
+
+#include "bgr_internal.h"
+
+namespace bgr {
+
+__device__ __forceinline__ void dw_unpack8(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 dw_pack8(const float (&f)[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+
+struct DwGeom {
+  int N, H, W, C;     // input
+  int Ho, Wo;         // output
+  int stride, dil;
+  int ldx, ldy;       // pixel strides (elements)
+};
+
+// w: fp32 [9][C]
+__global__ void __launch_bounds__(256)
+dw_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+              __nv_bfloat16* __restrict__ y, const DwGeom g) {
+  const int G = g.C >> 3;
+  const long total = long(g.N) * g.Ho * g.Wo * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int ox = int(r % g.Wo); r /= g.Wo;
+    const int oy = int(r % g.Ho);
+    const int n = int(r / g.Ho);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int iy = oy * g.stride + (ky - 1) * g.dil;
+      if (iy < 0 || iy >= g.H) continue;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int ix = ox * g.stride + (kx - 1) * g.dil;
+        if (ix < 0 || ix >= g.W) continue;
+        float xv[8];
+        dw_unpack8(*reinterpret_cast<const uint4*>(x + (size_t(size_t(n) * g.H + iy) * g.W + ix) * g.ldx + cg * 8), xv);
+        const float4 w0 = *reinterpret_cast<const float4*>(w + (ky * 3 + kx) * g.C + cg * 8);
+        const float4 w1 = *reinterpret_cast<const float4*>(w + (ky * 3 + kx) * g.C + cg * 8 + 4);
+        acc[0] = fmaf(xv[0], w0.x, acc[0]); acc[1] = fmaf(xv[1], w0.y, acc[1]);
+        acc[2] = fmaf(xv[2], w0.z, acc[2]); acc[3] = fmaf(xv[3], w0.w, acc[3]);
+        acc[4] = fmaf(xv[4], w1.x, acc[4]); acc[5] = fmaf(xv[5], w1.y, acc[5]);
+        acc[6] = fmaf(xv[6], w1.z, acc[6]); acc[7] = fmaf(xv[7], w1.w, acc[7]);
+      }
+    }
+    *reinterpret_cast<uint4*>(y + (size_t(size_t(n) * g.Ho + oy) * g.Wo + ox) * g.ldy + cg * 8) = dw_pack8(acc);
+  }
+}
+
+// dx[n,iy,ix,c] = sum_k dy[n,(iy-(ky-1)d)/s,(ix-(kx-1)d)/s,c] * w[k][c]  where divisible/in range
+__global__ void __launch_bounds__(256)
+dw_dgrad_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ w,
+                __nv_bfloat16* __restrict__ dx, const DwGeom g) {
+  const int G = g.C >> 3;
+  const long total = long(g.N) * g.H * g.W * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int ix = int(r % g.W); r /= g.W;
+    const int iy = int(r % g.H);
+    const int n = int(r / g.H);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int ty = iy - (ky - 1) * g.dil;
+      if (ty < 0 || (ty % g.stride)) continue;
+      const int oy = ty / g.stride;
+      if (oy >= g.Ho) continue;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int tx = ix - (kx - 1) * g.dil;
+        if (tx < 0 || (tx % g.stride)) continue;
+        const int ox = tx / g.stride;
+        if (ox >= g.Wo) continue;
+        float gv[8];
+        dw_unpack8(*reinterpret_cast<const uint4*>(dy + (size_t(size_t(n) * g.Ho + oy) * g.Wo + ox) * g.ldy + cg * 8), gv);
+        const float4 w0 = *reinterpret_cast<const float4*>(w + (ky * 3 + kx) * g.C + cg * 8);
+        const float4 w1 = *reinterpret_cast<const float4*>(w + (ky * 3 + kx) * g.C + cg * 8 + 4);
+        acc[0] = fmaf(gv[0], w0.x, acc[0]); acc[1] = fmaf(gv[1], w0.y, acc[1]);
+        acc[2] = fmaf(gv[2], w0.z, acc[2]); acc[3] = fmaf(gv[3], w0.w, acc[3]);
+        acc[4] = fmaf(gv[4], w1.x, acc[4]); acc[5] = fmaf(gv[5], w1.y, acc[5]);
+        acc[6] = fmaf(gv[6], w1.z, acc[6]); acc[7] = fmaf(gv[7], w1.w, acc[7]);
+      }
+    }
+    *reinterpret_cast<uint4*>(dx + (size_t(size_t(n) * g.H + iy) * g.W + ix) * g.ldx + cg * 8) = dw_pack8(acc);
+  }
+}
+
+// dw[k][c] += sum over output pixels.  Thread = (pixel lane, 8-channel group); each block walks a
+// contiguous range of output pixels; 72 fp32 partials per thread -> smem atomics -> global atomics.
+__global__ void __launch_bounds__(256)
+dw_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                float* __restrict__ dw, const DwGeom g, long pix_per_block) {
+  extern __shared__ float sh[];  // [9][C]
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int G = g.C >> 3;
+  const int R = G >= 256 ? 1 : 256 / G;
+  const long P = long(g.N) * g.Ho * g.Wo;
+  const long p0 = long(blockIdx.x) * pix_per_block, p1 = min(p0 + pix_per_block, P);
+  for (int cg = threadIdx.x % G; cg < G; cg += (G >= 256 ? 256 : G)) {
+    const int r = G >= 256 ? 0 : threadIdx.x / G;
+    if (r >= R) break;
+    float acc[9][8];
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
+    for (long p = p0 + r; p < p1; p += R) {
+      const int ox = int(p % g.Wo);
+      const int oy = int((p / g.Wo) % g.Ho);
+      const int n = int(p / (long(g.Wo) * g.Ho));
+      float gv[8];
+      dw_unpack8(*reinterpret_cast<const uint4*>(dy + size_t(p) * g.ldy + cg * 8), gv);
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const int iy = oy * g.stride + (ky - 1) * g.dil;
+        if (iy < 0 || iy >= g.H) continue;
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          const int ix = ox * g.stride + (kx - 1) * g.dil;
+          if (ix < 0 || ix >= g.W) continue;
+          float xv[8];
+          dw_unpack8(*reinterpret_cast<const uint4*>(x + (size_t(size_t(n) * g.H + iy) * g.W + ix) * g.ldx + cg * 8), xv);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[ky * 3 + kx][j] = fmaf(gv[j], xv[j], acc[ky * 3 + kx][j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(&sh[k * g.C + cg * 8 + j], acc[k][j]);
+    if (G < 256) break;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
+}
+
+// y[n,oy,ox,:] = x[n,2oy,2ox,:]  /  adjoint: dx = 0 except dx[n,2oy,2ox,:] = dy[n,oy,ox,:]
+__global__ void __launch_bounds__(256)
+subsample2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, const DwGeom g) {
+  const int G = g.C >> 3;
+  const long total = long(g.N) * g.Ho * g.Wo * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int ox = int(r % g.Wo); r /= g.Wo;
+    const int oy = int(r % g.Ho);
+    const int n = int(r / g.Ho);
+    *reinterpret_cast<uint4*>(y + (size_t(size_t(n) * g.Ho + oy) * g.Wo + ox) * g.ldy + cg * 8) =
+        *reinterpret_cast<const uint4*>(x + (size_t(size_t(n) * g.H + 2 * oy) * g.W + 2 * ox) * g.ldx + cg * 8);
+  }
+}
+__global__ void __launch_bounds__(256)
+subsample2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, const DwGeom g) {
+  const int G = g.C >> 3;
+  const long total = long(g.N) * g.H * g.W * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int ix = int(r % g.W); r /= g.W;
+    const int iy = int(r % g.H);
+    const int n = int(r / g.H);
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (!(ix & 1) && !(iy & 1))
+      v = *reinterpret_cast<const uint4*>(dy + (size_t(size_t(n) * g.Ho + (iy >> 1)) * g.Wo + (ix >> 1)) * g.ldy + cg * 8);
+    *reinterpret_cast<uint4*>(dx + (size_t(size_t(n) * g.H + iy) * g.W + ix) * g.ldx + cg * 8) = v;
+  }
+}
+
+static int ew_grid(long total) {
+  long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  return int(blocks < 1 ? 1 : blocks);
+}
+
+static int make_geom(DwGeom* g, int N, int H, int W, int C, int stride, int dil, int ldx, int ldy) {
+  if (C % 8 || C < 8) return fail(BGR_ERR_ARG, "depthwise: channel count must be a multiple of 8");
+  if (stride != 1 && stride != 2) return fail(BGR_ERR_ARG, "depthwise: stride must be 1 or 2");
+  g->N = N; g->H = H; g->W = W; g->C = C;
+  g->Ho = (H - 1) / stride + 1;
+  g->Wo = (W - 1) / stride + 1;
+  g->stride = stride; g->dil = dil; g->ldx = ldx; g->ldy = ldy;
+  return BGR_OK;
+}
+
+}  // namespace bgr
+
+using namespace bgr;
+
+extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* w, int stride,
+                          int dil, void* y, int ldy, void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
+  dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), w, static_cast<__nv_bfloat16*>(y), g);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy, const float* w, int stride,
+                            int dil, void* dx, int ldx, void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
+  dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), w, static_cast<__nv_bfloat16*>(dx), g);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, const void* dy, int ldy,
+                            int stride, int dil, float* dw, void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * C, st));
+  const long P = long(N) * g.Ho * g.Wo;
+  const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
+  long blocks = (P + long(R) * 4 - 1) / (long(R) * 4);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks < 1) blocks = 1;
+  const long ppb = (P + blocks - 1) / blocks;
+  blocks = (P + ppb - 1) / ppb;
+  static bool configured = false;
+  if (!configured) {
+    BGR_CUDA_OK(cudaFuncSetAttribute(dw_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    configured = true;
+  }
+  if (9 * C * sizeof(float) > 160 * 1024) return fail(BGR_ERR_ARG, "depthwise wgrad: too many channels");
+  dw_wgrad_kernel<<<int(blocks), 256, 9 * C * sizeof(float), st>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), dw, g, ppb);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_subsample2(const void* x, int N, int H, int W, int C, int ldx, void* y, int ldy,
+                              void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, 2, 1, ldx, ldy)) return rc;
+  subsample2_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_subsample2_bwd(const void* dy, int N, int H, int W, int C, int ldy, void* dx, int ldx,
+                                  void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, 2, 1, ldx, ldy)) return rc;
+  subsample2_bwd_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), g);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}

@@ -1,0 +1,376 @@
+// Spatial helpers of the DeepLabv3+ decoder / discriminator head on bf16 NHWC tensors:
+//   bilinear align_corners=True up-sampling + adjoint   (deeplab.py:375-379,663)
+//   global average pool + adjoint                         (deeplab.py:621)
+//   flatten + Linear(->1) head fwd / bwd                   (deeplab_gan.py:32-36)
+//   fused L1 loss + gradient                               (train_gan.py:146,281)
+//   field layout conversions (2x2 space-to-depth bf16 <-> NCHW fp32)
+// All HBM-bound, 128-bit accesses where the layout allows.
+#include <cuda_bf16.h>
+
+#include "bgr_internal.h"
+
+namespace bgr {
+
+__device__ __forceinline__ void sp_unpack8(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 sp_pack8(const float (&f)[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+
+static int sp_grid(long total) {
+  long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  return int(blocks < 1 ? 1 : blocks);
+}
+
+// Source index/weights as ATen's upsample_bilinear2d with align_corners=True:
+// scale = (in-1)/(out-1) (0 if out == 1), src = scale*dst, i0 = floor(src), l1 = src - i0.
+__device__ __forceinline__ void bil_coord(int o, float scale, int in, int* i0, int* i1, float* l1) {
+  const float s = scale * float(o);
+  int a = int(s);
+  if (a > in - 1) a = in - 1;
+  *i0 = a;
+  *i1 = a + (a < in - 1 ? 1 : 0);
+  *l1 = s - float(a);
+}
+
+struct BilGeom {
+  int N, h, w, H, W, C;
+  int ldx, ldy;
+  int s2d;           // output (or incoming gradient) stored as 2x2 space-to-depth blocks [N,H/2,W/2,4C]
+  float sy, sx;
+};
+
+__device__ __forceinline__ size_t bil_out_index(const BilGeom& g, int n, int y, int x) {
+  if (!g.s2d) return (size_t(size_t(n) * g.H + y) * g.W + x) * g.ldy;
+  return (size_t(size_t(n) * (g.H >> 1) + (y >> 1)) * (g.W >> 1) + (x >> 1)) * (4 * g.C) +
+         size_t(((y & 1) * 2 + (x & 1)) * g.C);
+}
+
+__global__ void __launch_bounds__(256)
+bilinear_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, const BilGeom g) {
+  const int G = g.C >> 3;
+  const long total = long(g.N) * g.H * g.W * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int ox = int(r % g.W); r /= g.W;
+    const int oy = int(r % g.H);
+    const int n = int(r / g.H);
+    int y0, y1, x0, x1;
+    float ly, lx;
+    bil_coord(oy, g.sy, g.h, &y0, &y1, &ly);
+    bil_coord(ox, g.sx, g.w, &x0, &x1, &lx);
+    const __nv_bfloat16* base = x + size_t(n) * g.h * g.w * g.ldx + cg * 8;
+    float a[8], b[8], c[8], d[8], o[8];
+    sp_unpack8(*reinterpret_cast<const uint4*>(base + (size_t(y0) * g.w + x0) * g.ldx), a);
+    sp_unpack8(*reinterpret_cast<const uint4*>(base + (size_t(y0) * g.w + x1) * g.ldx), b);
+    sp_unpack8(*reinterpret_cast<const uint4*>(base + (size_t(y1) * g.w + x0) * g.ldx), c);
+    sp_unpack8(*reinterpret_cast<const uint4*>(base + (size_t(y1) * g.w + x1) * g.ldx), d);
+    const float hy = 1.f - ly, hx = 1.f - lx;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = hy * (hx * a[j] + lx * b[j]) + ly * (hx * c[j] + lx * d[j]);
+    *reinterpret_cast<uint4*>(y + bil_out_index(g, n, oy, ox) + cg * 8) = sp_pack8(o);
+  }
+}
+
+// adjoint: scatter the output gradient into an fp32 [N,h,w,C] buffer (zeroed by the caller).
+__global__ void __launch_bounds__(256)
+bilinear_bwd_kernel(const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx, const BilGeom g) {
+  const int G = g.C >> 3;
+  const long total = long(g.N) * g.H * g.W * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int ox = int(r % g.W); r /= g.W;
+    const int oy = int(r % g.H);
+    const int n = int(r / g.H);
+    int y0, y1, x0, x1;
+    float ly, lx;
+    bil_coord(oy, g.sy, g.h, &y0, &y1, &ly);
+    bil_coord(ox, g.sx, g.w, &x0, &x1, &lx);
+    float v[8];
+    sp_unpack8(*reinterpret_cast<const uint4*>(gy + bil_out_index(g, n, oy, ox) + cg * 8), v);
+    float* base = gx + size_t(n) * g.h * g.w * g.C + cg * 8;
+    const float hy = 1.f - ly, hx = 1.f - lx;
+    float* p00 = base + (size_t(y0) * g.w + x0) * g.C;
+    float* p01 = base + (size_t(y0) * g.w + x1) * g.C;
+    float* p10 = base + (size_t(y1) * g.w + x0) * g.C;
+    float* p11 = base + (size_t(y1) * g.w + x1) * g.C;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(p00 + j, hy * hx * v[j]);
+      if (lx != 0.f) atomicAdd(p01 + j, hy * lx * v[j]);
+      if (ly != 0.f) atomicAdd(p10 + j, ly * hx * v[j]);
+      if (lx != 0.f && ly != 0.f) atomicAdd(p11 + j, ly * lx * v[j]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- global average pool
+// x [N][P][C] (ld) -> out fp32 sums [N][C] (zeroed by caller); caller scales by 1/P.
+__global__ void __launch_bounds__(256)
+gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int ld, long P, int C, long pix_per_block,
+               float* __restrict__ out) {
+  const int n = blockIdx.y;
+  const int G = C >> 3;
+  const int R = G >= 256 ? 1 : 256 / G;
+  const long p0 = long(blockIdx.x) * pix_per_block, p1 = min(p0 + pix_per_block, P);
+  for (int cg = threadIdx.x % G; cg < G; cg += (G >= 256 ? 256 : G)) {
+    const int r = G >= 256 ? 0 : threadIdx.x / G;
+    if (r >= R) break;
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long p = p0 + r; p < p1; p += R) {
+      float f[8];
+      sp_unpack8(*reinterpret_cast<const uint4*>(x + (size_t(n) * P + p) * ld + cg * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += f[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(out + size_t(n) * C + cg * 8 + j, s[j]);
+    if (G < 256) break;
+  }
+}
+
+// dx[n,p,c] = g[n,c] * inv_p   (g bf16 [N][C])
+__global__ void __launch_bounds__(256)
+gap_bwd_kernel(const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ dx, long P, int C, int N,
+               float inv_p) {
+  const int G = C >> 3;
+  const long total = long(N) * P * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    const long row = i / G;
+    const int n = int(row / P);
+    float f[8];
+    sp_unpack8(*reinterpret_cast<const uint4*>(g + size_t(n) * C + cg * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= inv_p;
+    *reinterpret_cast<uint4*>(dx + row * C + cg * 8) = sp_pack8(f);
+  }
+}
+
+// ---------------------------------------------------------------- linear head (K -> 1)
+// logits[n] += sum_i x[n,i] * w[i]     x bf16 [N][K], w bf16 [K]; logits pre-set to the bias.
+__global__ void __launch_bounds__(256)
+head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w, long K,
+                float* __restrict__ logits) {
+  const int n = blockIdx.y;
+  const long K8 = K >> 3;
+  float acc = 0.f;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < K8; i += long(gridDim.x) * blockDim.x) {
+    float a[8], b[8];
+    sp_unpack8(*reinterpret_cast<const uint4*>(x + size_t(n) * K + i * 8), a);
+    sp_unpack8(*reinterpret_cast<const uint4*>(w + i * 8), b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc = fmaf(a[j], b[j], acc);
+  }
+  __shared__ float red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    atomicAdd(logits + n, t);
+  }
+}
+
+// dx[n,i] = g[n] * w[i] (bf16, optional);  dw[i] = sum_n g[n] * x[n,i] (fp32, optional)
+__global__ void __launch_bounds__(256)
+head_bwd_kernel(const float* __restrict__ g, const __nv_bfloat16* __restrict__ x,
+                const __nv_bfloat16* __restrict__ w, long K, int N, __nv_bfloat16* __restrict__ dx,
+                float* __restrict__ dw) {
+  const long K8 = K >> 3;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < K8; i += long(gridDim.x) * blockDim.x) {
+    float wv[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    sp_unpack8(*reinterpret_cast<const uint4*>(w + i * 8), wv);
+    for (int n = 0; n < N; ++n) {
+      const float gn = g[n];
+      if (dw) {
+        float xv[8];
+        sp_unpack8(*reinterpret_cast<const uint4*>(x + size_t(n) * K + i * 8), xv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(gn, xv[j], acc[j]);
+      }
+      if (dx) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = gn * wv[j];
+        *reinterpret_cast<uint4*>(dx + size_t(n) * K + i * 8) = sp_pack8(o);
+      }
+    }
+    if (dw) {
+      *reinterpret_cast<float4*>(dw + i * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      *reinterpret_cast<float4*>(dw + i * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- fused L1 loss + gradient
+// sum += sum |a - b| (fp64 atomic);  grad = sign(a - b) * gscale (bf16)
+__global__ void __launch_bounds__(256)
+l1_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, long n8,
+                    float gscale, __nv_bfloat16* __restrict__ grad, double* __restrict__ sum) {
+  float acc = 0.f;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += long(gridDim.x) * blockDim.x) {
+    float x[8], y[8], o[8];
+    sp_unpack8(*reinterpret_cast<const uint4*>(a + i * 8), x);
+    sp_unpack8(*reinterpret_cast<const uint4*>(b + i * 8), y);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = x[j] - y[j];
+      acc += fabsf(d);
+      o[j] = d > 0.f ? gscale : (d < 0.f ? -gscale : 0.f);
+    }
+    if (grad) *reinterpret_cast<uint4*>(grad + i * 8) = sp_pack8(o);
+  }
+  __shared__ float red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    atomicAdd(sum, double(t));
+  }
+}
+
+// ---------------------------------------------------------------- field layout conversions
+// field = bf16 [N, H/2, W/2, (py, px, c)];  nchw = fp32 [N, C, H, W]
+template <bool TO_NCHW>
+__global__ void __launch_bounds__(256)
+field_convert_kernel(__nv_bfloat16* __restrict__ field, float* __restrict__ nchw, int N, int C, int H, int W) {
+  const long total = long(N) * C * H * W;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int x = int(i % W);
+    long r = i / W;
+    const int y = int(r % H); r /= H;
+    const int c = int(r % C);
+    const int n = int(r / C);
+    const size_t f = (size_t(size_t(n) * (H >> 1) + (y >> 1)) * (W >> 1) + (x >> 1)) * (4 * C) +
+                     size_t(((y & 1) * 2 + (x & 1)) * C + c);
+    if (TO_NCHW) nchw[i] = __bfloat162float(field[f]);
+    else field[f] = __float2bfloat16_rn(nchw[i]);
+  }
+}
+
+}  // namespace bgr
+
+using namespace bgr;
+
+static int make_bil(BilGeom* g, int N, int h, int w, int H, int W, int C, int ldx, int ldy, int s2d) {
+  if (C % 8 || C < 8) return fail(BGR_ERR_ARG, "bilinear: channel count must be a multiple of 8");
+  if (s2d && ((H | W) & 1)) return fail(BGR_ERR_ARG, "bilinear: space-to-depth output needs even size");
+  g->N = N; g->h = h; g->w = w; g->H = H; g->W = W; g->C = C; g->ldx = ldx; g->ldy = ldy; g->s2d = s2d;
+  g->sy = H > 1 ? float(h - 1) / float(H - 1) : 0.f;
+  g->sx = W > 1 ? float(w - 1) / float(W - 1) : 0.f;
+  return BGR_OK;
+}
+
+extern "C" int bgr_bilinear_fwd(const void* x, int N, int h, int w, int C, int ldx, void* y, int H, int W,
+                                int ldy, int s2d, void* stream) {
+  BilGeom g;
+  if (int rc = make_bil(&g, N, h, w, H, W, C, ldx, ldy, s2d)) return rc;
+  bilinear_fwd_kernel<<<sp_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_bilinear_bwd(const void* gy, int N, int h, int w, int C, int H, int W, int ldy, int s2d,
+                                float* gx, void* stream) {
+  BilGeom g;
+  if (int rc = make_bil(&g, N, h, w, H, W, C, C, ldy, s2d)) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(gx, 0, sizeof(float) * size_t(N) * h * w * C, st));
+  bilinear_bwd_kernel<<<sp_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(gy), gx, g);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* out_sums, void* stream) {
+  if (C % 8) return fail(BGR_ERR_ARG, "gap: channel count must be a multiple of 8");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(out_sums, 0, sizeof(float) * size_t(N) * C, st));
+  const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
+  long blocks = (P + long(R) * 4 - 1) / (long(R) * 4);
+  if (blocks > 64) blocks = 64;
+  if (blocks < 1) blocks = 1;
+  const long ppb = (P + blocks - 1) / blocks;
+  blocks = (P + ppb - 1) / ppb;
+  gap_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld, P, C, ppb, out_sums);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_gap_bwd(const void* g, int N, long P, int C, void* dx, void* stream) {
+  if (C % 8) return fail(BGR_ERR_ARG, "gap: channel count must be a multiple of 8");
+  gap_bwd_kernel<<<sp_grid(long(N) * P * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(g), static_cast<__nv_bfloat16*>(dx), P, C, N, 1.f / float(P));
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_head_fwd(const void* x, const void* w, int N, long K, float* logits, void* stream) {
+  if (K % 8) return fail(BGR_ERR_ARG, "head: K must be a multiple of 8");
+  long blocks = (K / 8 + 255) / 256;
+  if (blocks > 148 * 2) blocks = 148 * 2;
+  head_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, logits);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_head_bwd(const float* g, const void* x, const void* w, int N, long K, void* dx, float* dw,
+                            void* stream) {
+  if (K % 8) return fail(BGR_ERR_ARG, "head: K must be a multiple of 8");
+  head_bwd_kernel<<<sp_grid(K / 8), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      g, static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, N,
+      static_cast<__nv_bfloat16*>(dx), dw);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_l1_loss_grad(const void* a, const void* b, long n, float gscale, void* grad, double* sum,
+                                void* stream) {
+  if (n % 8) return fail(BGR_ERR_ARG, "l1: element count must be a multiple of 8");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(sum, 0, sizeof(double), st));
+  l1_loss_grad_kernel<<<sp_grid(n / 8), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(a),
+                                                      static_cast<const __nv_bfloat16*>(b), n / 8, gscale,
+                                                      static_cast<__nv_bfloat16*>(grad), sum);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream) {
+  field_convert_kernel<true><<<sp_grid(long(N) * C * H * W), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(field)), nchw, N, C, H, W);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
+
+extern "C" int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W, void* stream) {
+  field_convert_kernel<false><<<sp_grid(long(N) * C * H * W), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<__nv_bfloat16*>(field), const_cast<float*>(nchw), N, C, H, W);
+  BGR_CUDA_OK(cudaGetLastError());
+  return BGR_OK;
+}
