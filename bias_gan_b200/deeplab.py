@@ -1,0 +1,258 @@
+"""DeepLabv3+ / modified aligned Xception on the sm_100a kernels.
+
+Module and parameter names mirror src/deepCam/architecture/gpsro/deeplab.py so state dicts
+interchange with the reference (`xception_features.block4.rep.1.conv1.weight`, ...).  nn.Conv2d /
+nn.BatchNorm2d objects are used only as parameter holders with the reference's shapes; the
+arithmetic is the C-ABI kernels through functional.py on bf16 NHWC activations.
+
+In-place LeakyReLU semantics of the reference (deeplab.py:100,137-141: the first `rep` element
+mutates the block input, so the skip path and `low_level_feat` see the activated tensor) are
+reproduced by fusing that activation into the producer of each block input.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import functional as F_
+
+
+def _hold_conv(cin, cout, k, groups=1, bias=False):
+    return nn.Conv2d(cin, cout, k, groups=groups, bias=bias)
+
+
+class SeparableConv2d_same(nn.Module):
+    """fixed_padding + depthwise 3x3 + pointwise 1x1 (deeplab.py:75-87)."""
+
+    def __init__(self, inplanes, planes, kernel_size=3, stride=1, dilation=1, bias=False):
+        super().__init__()
+        assert kernel_size == 3 and not bias
+        self.conv1 = _hold_conv(inplanes, inplanes, 3, groups=inplanes)
+        self.pointwise = _hold_conv(inplanes, planes, 1)
+        self.stride, self.dilation = stride, dilation
+
+    def forward(self, x):
+        x = F_.depthwise3x3(x, self.conv1.weight, self.stride, self.dilation)
+        return F_.conv2d(x, self.pointwise.weight)
+
+
+class Block(nn.Module):
+    """Xception block (deeplab.py:90-143).  `forward(a)` takes the already-activated block input
+    when start_with_relu (the reference's in-place relu) and returns the pre-activation sum's
+    fused result: act_out=True applies the *next* block's in-place LeakyReLU."""
+
+    def __init__(self, inplanes, planes, reps, stride=1, dilation=1, start_with_relu=True, grow_first=True,
+                 is_last=False, normalizer=nn.BatchNorm2d):
+        super().__init__()
+        if planes != inplanes or stride != 1:
+            self.skip = _hold_conv(inplanes, planes, 1)
+            self.skipbn = normalizer(planes)
+        else:
+            self.skip = None
+        self.relu = nn.Identity()
+        self.stride = stride
+        rep = []
+        filters = inplanes
+        if grow_first:
+            rep += [nn.Identity(), SeparableConv2d_same(inplanes, planes, 3, 1, dilation), normalizer(planes)]
+            filters = planes
+        for _ in range(reps - 1):
+            rep += [nn.Identity(), SeparableConv2d_same(filters, filters, 3, 1, dilation), normalizer(filters)]
+        if not grow_first:
+            rep += [nn.Identity(), SeparableConv2d_same(inplanes, planes, 3, 1, dilation), normalizer(planes)]
+        if not start_with_relu:
+            rep = rep[1:]
+        if stride != 1:
+            rep.append(SeparableConv2d_same(planes, planes, 3, stride=2))
+        if stride == 1 and is_last:
+            rep.append(SeparableConv2d_same(planes, planes, 3, stride=1))
+        self.rep = nn.Sequential(*rep)
+
+    def forward(self, a, act_out):
+        mods = list(self.rep)
+        x = a
+        i = 0
+        pending = None  # (raw conv output, bn) waiting for its fused BN(+act)
+        tail_bn = None
+        while i < len(mods):
+            m = mods[i]
+            if isinstance(m, SeparableConv2d_same):
+                if pending is not None:  # BN followed directly by a conv: no activation between
+                    x = F_.bn_act(pending[0], pending[1], act=False)
+                    pending = None
+                y = m(x)
+                if i + 1 < len(mods) and isinstance(mods[i + 1], nn.BatchNorm2d):
+                    pending = (y, mods[i + 1])
+                    i += 2
+                    # is this BN followed by the (identity-held) relu?
+                    if i < len(mods) and isinstance(mods[i], nn.Identity):
+                        x = F_.bn_act(pending[0], pending[1], act=True)
+                        pending = None
+                        i += 1
+                    continue
+                x = y
+            i += 1
+        if pending is not None:
+            tail_bn = pending  # last rep element is a BN: fuse with the residual add
+        if self.skip is not None:
+            s_in = F_.subsample2(a) if self.stride == 2 else a
+            s = F_.conv2d(s_in, self.skip.weight)
+            if tail_bn is not None:
+                x = F_.bn_act(tail_bn[0], tail_bn[1], act=False)
+            return F_.bn_act(s, self.skipbn, res=x, act=act_out)
+        if tail_bn is not None:
+            return F_.bn_act(tail_bn[0], tail_bn[1], res=a, act=act_out)
+        raise NotImplementedError("identity-skip block ending in a convolution does not occur in Xception")
+
+
+class Xception(nn.Module):
+    """Modified aligned Xception trunk (deeplab.py:146-278), os=16 or 8."""
+
+    def __init__(self, inplanes=3, os=16, pretrained=False, normalizer=nn.BatchNorm2d):
+        super().__init__()
+        assert not pretrained, "pretrained weights need network access"
+        if os == 16:
+            b3s, mid_rate, exit_rates = 2, 1, (1, 2)
+        elif os == 8:
+            b3s, mid_rate, exit_rates = 1, 2, (2, 4)
+        else:
+            raise NotImplementedError
+        self.inplanes = inplanes
+        self.conv1 = nn.Conv2d(inplanes, 128, 3, stride=2, padding=1, bias=False)
+        self.bn1 = normalizer(128)
+        self.relu = nn.Identity()
+        self.conv2 = nn.Conv2d(128, 128, 3, stride=1, padding=1, bias=False)
+        self.bn2 = normalizer(128)
+        self.block1 = Block(128, 128, reps=2, stride=2, start_with_relu=False, normalizer=normalizer)
+        self.block2 = Block(128, 256, reps=2, stride=2, normalizer=normalizer)
+        self.block3 = Block(256, 728, reps=2, stride=b3s, is_last=True, normalizer=normalizer)
+        for i in range(4, 20):
+            setattr(self, "block%d" % i, Block(728, 728, reps=3, dilation=mid_rate, normalizer=normalizer))
+        self.block20 = Block(728, 1024, reps=2, dilation=exit_rates[0], grow_first=False, is_last=True,
+                             normalizer=normalizer)
+        self.conv3 = SeparableConv2d_same(1024, 1536, 3, dilation=exit_rates[1])
+        self.bn3 = normalizer(1536)
+        self.conv4 = SeparableConv2d_same(1536, 1536, 3, dilation=exit_rates[1])
+        self.bn4 = normalizer(1536)
+        self.conv5 = SeparableConv2d_same(1536, 2048, 3, dilation=exit_rates[1])
+        self.bn5 = normalizer(2048)
+        self._init_weight()
+
+    def _init_weight(self):
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight)
+            elif isinstance(m, nn.BatchNorm2d):
+                nn.init.ones_(m.weight)
+                nn.init.zeros_(m.bias)
+
+    def forward(self, field):
+        """field: bf16 [N, H/2, W/2, 4*inplanes] (2x2 space-to-depth).  Returns (features
+        [N,H/16,W/16,2048], low_level [N,H/4,W/4,128]) — both activated, as the reference's
+        in-place LeakyReLUs leave them."""
+        x = F_.bn_act(F_.conv_s2d(field, self.conv1.weight), self.bn1, act=True)
+        x = F_.bn_act(F_.conv2d(x, self.conv2.weight), self.bn2, act=True)
+        x = self.block1(x, act_out=True)
+        low = x
+        x = self.block2(x, act_out=True)
+        x = self.block3(x, act_out=True)
+        for i in range(4, 20):
+            x = getattr(self, "block%d" % i)(x, act_out=True)
+        x = self.block20(x, act_out=False)
+        x = F_.bn_act(self.conv3(x), self.bn3, act=True)
+        x = F_.bn_act(self.conv4(x), self.bn4, act=True)
+        x = F_.bn_act(self.conv5(x), self.bn5, act=True)
+        return x, low
+
+
+def _init_decoder(mod):
+    gain = nn.init.calculate_gain("leaky_relu", 0.2)
+    for m in mod.modules():
+        if isinstance(m, nn.Conv2d):
+            n = m.kernel_size[0] * m.kernel_size[1] * m.out_channels
+            nn.init.normal_(m.weight, mean=0.0, std=gain / math.sqrt(n))
+        elif isinstance(m, nn.BatchNorm2d):
+            nn.init.ones_(m.weight)
+            nn.init.zeros_(m.bias)
+
+
+class ASPP_module(nn.Module):
+    """deeplab.py:322-355."""
+
+    def __init__(self, inplanes, planes, rate, normalizer=nn.BatchNorm2d):
+        super().__init__()
+        k = 1 if rate == 1 else 3
+        self.atrous_convolution = nn.Conv2d(inplanes, planes, k, padding=0 if rate == 1 else rate,
+                                            dilation=rate, bias=False)
+        self.bn = normalizer(planes)
+        self.relu = nn.Identity()
+        self.rate = rate
+        nn.init.kaiming_normal_(self.atrous_convolution.weight)
+
+    def forward(self, x):
+        return F_.bn_act(F_.conv2d(x, self.atrous_convolution.weight, dilation=self.rate), self.bn, act=True)
+
+
+class InterpolationUpsampler(nn.Module):
+    """deeplab.py:358-381; returns the output field (2x2 space-to-depth bf16)."""
+
+    def __init__(self, n_output, normalizer=nn.BatchNorm2d):
+        super().__init__()
+        self.last_conv = nn.Sequential(nn.Conv2d(304, 256, 3, padding=1, bias=False), normalizer(256), nn.Identity(),
+                                       nn.Conv2d(256, 256, 3, padding=1, bias=False), normalizer(256), nn.Identity(),
+                                       nn.Conv2d(256, n_output, 1))
+        _init_decoder(self)
+
+    def forward(self, x, low_level_features, H, W):
+        x = F_.bilinear(x, int(math.ceil(H / 4)), int(math.ceil(W / 4)))
+        x = torch.cat((x, low_level_features), dim=3)
+        lc = self.last_conv
+        x = F_.bn_act(F_.conv2d(x, lc[0].weight), lc[1], act=True)
+        x = F_.bn_act(F_.conv2d(x, lc[3].weight), lc[4], act=True)
+        x = F_.conv2d(x, lc[6].weight, lc[6].bias)
+        return F_.bilinear(x, H, W, s2d=True)
+
+
+class DeepLabv3_plus(nn.Module):
+    """deeplab.py:583-684 with upsampler_type='Interpolate' (the only shape-generic one)."""
+
+    def __init__(self, n_input=3, n_output=21, os=16, upsampler_type="Interpolate", pretrained=False, _print=False,
+                 normalizer=nn.BatchNorm2d, nn_pooling=True):
+        super().__init__()
+        if upsampler_type != "Interpolate":
+            raise NotImplementedError("upsampler %s: only 'Interpolate' is built (SURVEY §8f rank 3)" % upsampler_type)
+        self.upsampler_type = upsampler_type
+        self.n_output = n_output
+        self.xception_features = Xception(n_input, os, pretrained, normalizer)
+        rates = [1, 6, 12, 18] if os == 16 else [1, 12, 24, 36]
+        self.aspp1 = ASPP_module(2048, 256, rates[0], normalizer)
+        self.aspp2 = ASPP_module(2048, 256, rates[1], normalizer)
+        self.aspp3 = ASPP_module(2048, 256, rates[2], normalizer)
+        self.aspp4 = ASPP_module(2048, 256, rates[3], normalizer)
+        self.relu = nn.Identity()
+        self.global_avg_pool = nn.Sequential(nn.Identity(), nn.Conv2d(2048, 256, 1, bias=False), normalizer(256),
+                                             nn.Identity())
+        self.conv1 = nn.Conv2d(1280, 256, 1, bias=False)
+        self.bn1 = normalizer(256)
+        self.conv2 = nn.Conv2d(128, 48, 1, bias=False)
+        self.bn2 = normalizer(48)
+        self.upsample = InterpolationUpsampler(n_output, normalizer)
+
+    def forward(self, field):
+        N, H2, W2, _ = field.shape
+        H, W = 2 * H2, 2 * W2
+        x, low = self.xception_features(field)
+        h, w = x.shape[1], x.shape[2]
+        x1, x2, x3, x4 = self.aspp1(x), self.aspp2(x), self.aspp3(x), self.aspp4(x)
+        gp = self.global_avg_pool
+        x5 = F_.bn_act(F_.conv2d(F_.global_avg_pool(x), gp[1].weight), gp[2], act=True)
+        x5 = F_.bilinear(x5, h, w)
+        x = torch.cat((x1, x2, x3, x4, x5), dim=3)
+        x = F_.bn_act(F_.conv2d(x, self.conv1.weight), self.bn1, act=True)
+        low = F_.bn_act(F_.conv2d(low, self.conv2.weight), self.bn2, act=True)
+        return self.upsample(x, low, H, W)
+
+    def freeze_bn(self):
+        for m in self.modules():
+            if isinstance(m, nn.BatchNorm2d):
+                m.eval()

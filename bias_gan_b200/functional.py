@@ -1,0 +1,279 @@
+"""Autograd bindings of the sm_100a kernels (bf16 NHWC activations, fp32 master parameters).
+
+Each Function's forward/backward is one or a few C-ABI launches (kernels.py); PyTorch's autograd
+only orders them.  Parameter tensors keep the reference's shapes ([Cout,Cin,kh,kw] etc.) so that
+state dicts interchange; GEMM-layout bf16 copies are derived per call (tiny tensors).
+"""
+import torch
+
+from . import kernels as K
+from . import layouts as L
+
+SLOPE = 0.2  # nn.LeakyReLU(0.2) everywhere in the reference (deeplab.py:100,180,334,365)
+
+
+def _bf16c(t):
+    return t if (t.dtype == torch.bfloat16 and t.is_contiguous()) else t.to(torch.bfloat16).contiguous()
+
+
+class _Conv(torch.autograd.Function):
+    """Dense conv (1x1 / 3x3 / atrous, stride 1) as tcgen05 implicit GEMM."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, dil):
+        ks = weight.shape[-1]
+        dy, dx = K.taps_for(ks, dil)
+        ctx.save_for_backward(x, weight)
+        ctx.taps = (dy, dx)
+        ctx.has_bias = bias is not None
+        return K.conv_fprop(x, L.gemm_weight(weight), dy, dx, bias=bias)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, weight = ctx.saved_tensors
+        dy, dx = ctx.taps
+        g = _bf16c(g)
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            gx = K.conv_fprop(g, L.gemm_weight_t(weight), [-v for v in dy], [-v for v in dx])
+        if ctx.needs_input_grad[1]:
+            gw = L.from_gemm_grad(K.conv_wgrad(x, g, dy, dx), weight.shape)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = K.bn_stats(g)[: g.shape[-1]].float()
+        return gx, gw, gb, None
+
+
+def conv2d(x, weight, bias=None, dilation=1):
+    return _Conv.apply(x, weight, bias, dilation)
+
+
+class _ConvS2D(torch.autograd.Function):
+    """3x3 stride-2 pad-1 entry conv (deeplab.py:178) on a field stored as 2x2 space-to-depth
+    blocks: a 2x2-tap stride-1 implicit GEMM with K = 4 taps x 4*C channels."""
+
+    @staticmethod
+    def forward(ctx, field, weight):
+        ctx.save_for_backward(field, weight)
+        w2 = L.s2d_weight(weight).to(torch.bfloat16).contiguous()
+        return K.conv_fprop(field, w2, L.S2D_DY, L.S2D_DX)
+
+    @staticmethod
+    def backward(ctx, g):
+        field, weight = ctx.saved_tensors
+        g = _bf16c(g)
+        gf = gw = None
+        if ctx.needs_input_grad[0]:
+            w2t = L.s2d_weight(weight).permute(2, 1, 0).to(torch.bfloat16).contiguous()
+            gf = K.conv_fprop(g, w2t, [-v for v in L.S2D_DY], [-v for v in L.S2D_DX])
+        if ctx.needs_input_grad[1]:
+            gw = L.s2d_weight_grad(K.conv_wgrad(field, g, L.S2D_DY, L.S2D_DX), weight.shape)
+        return gf, gw
+
+
+def conv_s2d(field, weight):
+    return _ConvS2D.apply(field, weight)
+
+
+class _Depthwise(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, stride, dil):
+        C = weight.shape[0]
+        w9 = weight.reshape(C, 9).t().contiguous().float()
+        ctx.save_for_backward(x, w9)
+        ctx.cfg = (stride, dil, tuple(x.shape))
+        return K.dw_fwd(x, w9, stride, dil)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w9 = ctx.saved_tensors
+        stride, dil, shape = ctx.cfg
+        g = _bf16c(g)
+        gx = gw = None
+        if ctx.needs_input_grad[0]:
+            gx = K.dw_dgrad(g, w9, stride, dil, shape)
+        if ctx.needs_input_grad[1]:
+            gw = K.dw_wgrad(x, g, stride, dil).t().reshape(shape[3], 1, 3, 3)
+        return gx, gw, None, None
+
+
+def depthwise3x3(x, weight, stride=1, dilation=1):
+    return _Depthwise.apply(x, weight, stride, dilation)
+
+
+class _BNAct(torch.autograd.Function):
+    """out = act(BatchNorm_train(y) [+ res]) with batch statistics (nn.BatchNorm2d training mode)."""
+
+    @staticmethod
+    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act):
+        M = y.numel() // y.shape[-1]
+        sums = K.bn_stats(y)
+        mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var)
+        out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
+        ctx.save_for_backward(y, out if act else None, mean, invstd, gamma)
+        ctx.act = act
+        ctx.has_res = res is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        y, out, mean, invstd, gamma = ctx.saved_tensors
+        g = _bf16c(g)
+        C = y.shape[-1]
+        dx, dyh, sums = K.bn_backward(g, out, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
+        ggamma = sums[C:].float() if ctx.needs_input_grad[1] else None
+        gbeta = sums[:C].float() if ctx.needs_input_grad[2] else None
+        gres = dyh if (ctx.has_res and ctx.needs_input_grad[3]) else None
+        return dx, ggamma, gbeta, gres, None, None, None, None, None
+
+
+class _AffineAct(torch.autograd.Function):
+    """Eval-mode BatchNorm (running statistics folded into a, b) + activation; forward only."""
+
+    @staticmethod
+    def forward(ctx, y, a, b, res, act):
+        return K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
+
+    @staticmethod
+    def backward(ctx, g):
+        raise NotImplementedError("eval-mode BatchNorm backward is not on the training hot path")
+
+
+def bn_act(y, bn, res=None, act=True):
+    """`bn` is a torch.nn.BatchNorm2d-compatible module (weight, bias, running_*, eps, momentum)."""
+    if bn.training:
+        if bn.num_batches_tracked is not None:
+            bn.num_batches_tracked += 1
+        return _BNAct.apply(y, bn.weight, bn.bias, res, bn.running_mean, bn.running_var, bn.eps,
+                            bn.momentum, act)
+    a = (bn.weight * torch.rsqrt(bn.running_var + bn.eps)).float().contiguous()
+    b = (bn.bias - bn.running_mean * a).float().contiguous()
+    return _AffineAct.apply(y, a, b, res, act)
+
+
+class _Subsample2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.shape = tuple(x.shape)
+        return K.subsample2(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return K.subsample2_bwd(_bf16c(g), ctx.shape)
+
+
+def subsample2(x):
+    return _Subsample2.apply(x)
+
+
+class _Bilinear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, H, W, s2d):
+        ctx.cfg = (tuple(x.shape), H, W, s2d)
+        return K.bilinear_fwd(x, H, W, s2d=s2d)
+
+    @staticmethod
+    def backward(ctx, g):
+        shape, H, W, s2d = ctx.cfg
+        return K.bilinear_bwd(_bf16c(g), shape, H, W, s2d=s2d).to(torch.bfloat16), None, None, None
+
+
+def bilinear(x, H, W, s2d=False):
+    """F.interpolate(x, (H, W), mode='bilinear', align_corners=True) on NHWC; s2d=True writes the
+    2x2 space-to-depth field layout [N, H/2, W/2, 4C]."""
+    return _Bilinear.apply(x, H, W, s2d)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        N, H, W, C = x.shape
+        ctx.shape = (N, H, W, C)
+        return (K.gap_fwd(x) * (1.0 / (H * W))).to(torch.bfloat16).view(N, 1, 1, C)
+
+    @staticmethod
+    def backward(ctx, g):
+        N, H, W, C = ctx.shape
+        return K.gap_bwd(_bf16c(g).view(N, C), N, H, W, C)
+
+
+def global_avg_pool(x):
+    return _GlobalAvgPool.apply(x)
+
+
+class _Head(torch.autograd.Function):
+    """flatten (C,H,W order of the reference) + Linear(K, 1) on an NHWC feature map."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        N, H, W, C = x.shape
+        w_hwc = weight.view(C, H, W).permute(1, 2, 0).reshape(-1).to(torch.bfloat16).contiguous()
+        logits = bias.detach().float().repeat(N).contiguous()
+        K.head_fwd(x, w_hwc, logits)
+        ctx.save_for_backward(x, w_hwc)
+        return logits.view(N, 1)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w_hwc = ctx.saved_tensors
+        N, H, W, C = x.shape
+        g = g.reshape(N).float().contiguous()
+        gx, gw = K.head_bwd(g, x, w_hwc, need_dx=ctx.needs_input_grad[0], need_dw=ctx.needs_input_grad[1])
+        if gw is not None:
+            gw = gw.view(H, W, C).permute(2, 0, 1).reshape(1, -1)
+        gb = g.sum().view(1) if ctx.needs_input_grad[2] else None
+        return gx, gw, gb
+
+
+def linear_head(x, weight, bias):
+    return _Head.apply(x, weight, bias)
+
+
+class _L1(torch.autograd.Function):
+    """mean |a - b| with the sign gradient produced in the same pass (train_gan.py:146,281)."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        n = a.numel()
+        s, grad = K.l1_loss_grad(a, b, 1.0 / n, need_grad=ctx.needs_input_grad[0])
+        ctx.save_for_backward(grad)
+        return (s / n).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return (grad * g.to(grad.dtype)), None
+
+
+def l1_loss(a, b):
+    return _L1.apply(a, b)
+
+
+class _ToField(torch.autograd.Function):
+    """fp32 NCHW -> bf16 field layout [N, H/2, W/2, (py, px, c)] (and back in backward)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.C = x.shape[1]
+        return K.nchw_to_field(x.float().contiguous())
+
+    @staticmethod
+    def backward(ctx, g):
+        return K.field_to_nchw(_bf16c(g), ctx.C)
+
+
+class _FromField(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, field, C):
+        return K.field_to_nchw(field, C)
+
+    @staticmethod
+    def backward(ctx, g):
+        return K.nchw_to_field(g.float().contiguous()), None
+
+
+def to_field(x_nchw):
+    return _ToField.apply(x_nchw)
+
+
+def from_field(field, C):
+    return _FromField.apply(field, C)

@@ -91,3 +91,193 @@ def stage_normalize(src, layout, channels, shift, scale, crop=None, flip=(False,
                                          ptr(shift), ptr(scale), y0, x0, h, w, int(flip[0]), int(flip[1]),
                                          ptr(out), int(s2d), stream_ptr()))
     return out
+
+
+# ---------------------------------------------------------------------------------------------
+# BatchNorm / activation / depthwise / decoder helpers.  Tensors are bf16 [..., C] whose leading
+# dims are dense with a uniform pixel stride (channel slices of wider buffers are fine).
+# ---------------------------------------------------------------------------------------------
+c_long, c_float = ctypes.c_long, ctypes.c_float
+
+
+def _rows(t):
+    """(M, C, ld) of a bf16 [..., C] view with uniform pixel stride."""
+    assert t.dtype == torch.bfloat16 and t.is_cuda and t.stride(-1) == 1
+    C = t.shape[-1]
+    ld = t.stride(-2) if t.dim() > 1 else C
+    M = t.numel() // C
+    exp = ld
+    for d in range(t.dim() - 2, -1, -1):
+        assert t.shape[d] == 1 or t.stride(d) == exp, "non-uniform pixel stride"
+        exp *= t.shape[d]
+    return M, C, ld
+
+
+def bn_stats(x, sums=None):
+    M, C, ld = _rows(x)
+    if sums is None:
+        sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+    check(_lib.lib().bgr_bn_stats(ptr(x), c_long(M), C, ld, ptr(sums), stream_ptr()))
+    return sums
+
+
+def bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var):
+    C = sums.numel() // 2
+    dev = sums.device
+    mean, invstd, a, b = (torch.empty(C, dtype=torch.float32, device=dev) for _ in range(4))
+    check(_lib.lib().bgr_bn_finalize(ptr(sums), c_long(M), C, ptr(gamma), ptr(beta), c_float(eps), c_float(momentum),
+                                     ptr(mean), ptr(invstd), ptr(a), ptr(b), ptr(running_mean),
+                                     ptr(running_var), stream_ptr()))
+    return mean, invstd, a, b
+
+
+def bn_apply(x, a, b, res=None, act=True, slope=0.2, out=None):
+    M, C, ldx = _rows(x)
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    Mo, Co, ldo = _rows(out)
+    assert (Mo, Co) == (M, C)
+    ldr = 0
+    if res is not None:
+        Mr, Cr, ldr = _rows(res)
+        assert (Mr, Cr) == (M, C)
+    check(_lib.lib().bgr_bn_apply(ptr(x), ldx, ptr(a), ptr(b), ptr(res), ldr, ptr(out), ldo, c_long(M), C,
+                                  int(act), c_float(slope), stream_ptr()))
+    return out
+
+
+def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2):
+    """Returns (dx, dyh, sums) — dyh is also the gradient of the residual input."""
+    M, C, ldx = _rows(x)
+    Mg, Cg, ldg = _rows(g)
+    assert (Mg, Cg) == (M, C)
+    ldo = 0
+    if act:
+        Mo, Co, ldo = _rows(out)
+        assert (Mo, Co) == (M, C)
+    dyh = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+    check(_lib.lib().bgr_bn_backward(ptr(g), ldg, ptr(out) if act else ctypes.c_void_p(0), ldo, ptr(x), ldx,
+                                     ptr(mean), ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
+                                     ptr(dyh), ptr(dx), ptr(sums), stream_ptr()))
+    return dx, dyh, sums
+
+
+def dw_fwd(x, w9, stride, dil, out=None):
+    N, H, W, C, ldx = _nhwc_view(x)
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    if out is None:
+        out = torch.empty((N, Ho, Wo, C), dtype=torch.bfloat16, device=x.device)
+    _, _, _, _, ldy = _nhwc_view(out)
+    assert w9.dtype == torch.float32 and tuple(w9.shape) == (9, C) and w9.is_contiguous()
+    check(_lib.lib().bgr_dw_fwd(ptr(x), N, H, W, C, ldx, ptr(w9), stride, dil, ptr(out), ldy, stream_ptr()))
+    return out
+
+
+def dw_dgrad(gy, w9, stride, dil, in_shape):
+    N, H, W, C = in_shape
+    _, _, _, _, ldy = _nhwc_view(gy)
+    dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=gy.device)
+    check(_lib.lib().bgr_dw_dgrad(ptr(gy), N, H, W, C, ldy, ptr(w9), stride, dil, ptr(dx), C, stream_ptr()))
+    return dx
+
+
+def dw_wgrad(x, gy, stride, dil):
+    N, H, W, C, ldx = _nhwc_view(x)
+    _, _, _, _, ldy = _nhwc_view(gy)
+    dw = torch.empty((9, C), dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_dw_wgrad(ptr(x), N, H, W, C, ldx, ptr(gy), ldy, stride, dil, ptr(dw), stream_ptr()))
+    return dw
+
+
+def subsample2(x):
+    N, H, W, C, ldx = _nhwc_view(x)
+    out = torch.empty((N, (H + 1) // 2, (W + 1) // 2, C), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().bgr_subsample2(ptr(x), N, H, W, C, ldx, ptr(out), C, stream_ptr()))
+    return out
+
+
+def subsample2_bwd(gy, in_shape):
+    N, H, W, C = in_shape
+    _, _, _, _, ldy = _nhwc_view(gy)
+    dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=gy.device)
+    check(_lib.lib().bgr_subsample2_bwd(ptr(gy), N, H, W, C, ldy, ptr(dx), C, stream_ptr()))
+    return dx
+
+
+def bilinear_fwd(x, H, W, out=None, s2d=False):
+    N, h, w, C, ldx = _nhwc_view(x)
+    if out is None:
+        shape = (N, H // 2, W // 2, 4 * C) if s2d else (N, H, W, C)
+        out = torch.empty(shape, dtype=torch.bfloat16, device=x.device)
+    ldy = 4 * C if s2d else _nhwc_view(out)[4]
+    check(_lib.lib().bgr_bilinear_fwd(ptr(x), N, h, w, C, ldx, ptr(out), H, W, ldy, int(s2d), stream_ptr()))
+    return out
+
+
+def bilinear_bwd(gy, in_shape, H, W, s2d=False):
+    N, h, w, C = in_shape
+    ldy = 4 * C if s2d else _nhwc_view(gy)[4]
+    assert gy.dtype == torch.bfloat16
+    gx = torch.empty((N, h, w, C), dtype=torch.float32, device=gy.device)
+    check(_lib.lib().bgr_bilinear_bwd(ptr(gy), N, h, w, C, H, W, ldy, int(s2d), ptr(gx), stream_ptr()))
+    return gx
+
+
+def gap_fwd(x):
+    N, H, W, C, ld = _nhwc_view(x)
+    sums = torch.empty((N, C), dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_gap_fwd(ptr(x), N, c_long(H * W), C, ld, ptr(sums), stream_ptr()))
+    return sums
+
+
+def gap_bwd(g, N, H, W, C):
+    assert g.dtype == torch.bfloat16 and g.is_contiguous()
+    dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=g.device)
+    check(_lib.lib().bgr_gap_bwd(ptr(g), N, c_long(H * W), C, ptr(dx), stream_ptr()))
+    return dx
+
+
+def head_fwd(x, w, logits):
+    """logits (fp32 [N], pre-set to the bias) += x.view(N,-1) @ w."""
+    N = x.shape[0]
+    K = x.numel() // N
+    assert x.is_contiguous() and w.is_contiguous() and w.numel() == K and logits.dtype == torch.float32
+    check(_lib.lib().bgr_head_fwd(ptr(x), ptr(w), N, c_long(K), ptr(logits), stream_ptr()))
+    return logits
+
+
+def head_bwd(g, x, w, need_dx=True, need_dw=True):
+    N = x.shape[0]
+    K = x.numel() // N
+    assert g.dtype == torch.float32 and g.numel() == N and g.is_contiguous()
+    dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if need_dx else None
+    dw = torch.empty(K, dtype=torch.float32, device=x.device) if need_dw else None
+    check(_lib.lib().bgr_head_bwd(ptr(g), ptr(x), ptr(w), N, c_long(K), ptr(dx), ptr(dw), stream_ptr()))
+    return dx, dw
+
+
+def l1_loss_grad(a, b, gscale, need_grad=True):
+    """Returns (sum|a-b| as fp64 0-d tensor, grad bf16 or None)."""
+    assert a.shape == b.shape and a.is_contiguous() and b.is_contiguous() and a.dtype == b.dtype == torch.bfloat16
+    s = torch.empty((), dtype=torch.float64, device=a.device)
+    grad = torch.empty(a.shape, dtype=torch.bfloat16, device=a.device) if need_grad else None
+    check(_lib.lib().bgr_l1_loss_grad(ptr(a), ptr(b), c_long(a.numel()), c_float(gscale), ptr(grad), ptr(s), stream_ptr()))
+    return s, grad
+
+
+def field_to_nchw(field, C):
+    N, H2, W2, C4 = field.shape
+    assert C4 == 4 * C and field.is_contiguous() and field.dtype == torch.bfloat16
+    out = torch.empty((N, C, 2 * H2, 2 * W2), dtype=torch.float32, device=field.device)
+    check(_lib.lib().bgr_field_to_nchw(ptr(field), ptr(out), N, C, 2 * H2, 2 * W2, stream_ptr()))
+    return out
+
+
+def nchw_to_field(x):
+    N, C, H, W = x.shape
+    assert x.dtype == torch.float32 and x.is_contiguous() and H % 2 == 0 and W % 2 == 0
+    out = torch.empty((N, H // 2, W // 2, 4 * C), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().bgr_nchw_to_field(ptr(x), ptr(out), N, C, H, W, stream_ptr()))
+    return out

@@ -1,0 +1,49 @@
+"""GANLoss with the reference's interface (src/deepCam/utils/losses.py:129-172) and the fused
+reconstruction loss.  The adversarial terms act on [B,1] logits (a handful of scalars, plain torch);
+label noise and the 5 % swap are drawn on the CPU generator in the reference's order so seeded
+runs reproduce the same labels.  The reconstruction loss over the full fields is the fused
+loss-and-gradient kernel (functional.l1_loss).
+"""
+import torch
+import torch.nn as nn
+
+from . import functional as F_
+
+
+class GANLoss:
+    def __init__(self, mode, batch_size, device):
+        self.mode = mode
+        self.batch_size = batch_size
+        self.device = device
+        if mode == "ModifiedMinMax":
+            self.criterion = nn.BCEWithLogitsLoss()
+            self.label_real = torch.ones((batch_size, 1)).to(device)
+            self.label_fake = torch.zeros((batch_size, 1)).to(device)
+            self.dist_real = torch.distributions.uniform.Uniform(0.8, 1.0)
+            self.dist_fake = torch.distributions.uniform.Uniform(0.0, 0.2)
+            self.dist_swap = torch.distributions.uniform.Uniform(0.0, 1.0)
+        elif mode == "Wasserstein":
+            pass
+        else:
+            raise NotImplementedError("Error, {} loss not implemented".format(mode))
+
+    def d_loss(self, logits_real, logits_fake):
+        if self.mode == "Wasserstein":
+            return torch.mean(logits_fake - logits_real)
+        label_fake = self.dist_fake.rsample(self.label_fake.shape).to(self.device, non_blocking=True)
+        label_real = self.dist_real.rsample(self.label_real.shape).to(self.device, non_blocking=True)
+        if self.dist_swap.sample() < 0.05:
+            label_fake, label_real = label_real, label_fake
+        return 0.5 * (self.criterion(logits_fake, label_fake) + self.criterion(logits_real, label_real))
+
+    def g_loss(self, logits_fake):
+        if self.mode == "Wasserstein":
+            return -1.0 * torch.mean(logits_fake)
+        return self.criterion(logits_fake, self.label_real)
+
+
+class L1LossField(nn.Module):
+    """nn.L1Loss (train_gan.py:146) on two fields in the same (space-to-depth bf16) layout."""
+
+    def forward(self, fake_field, real_field):
+        return F_.l1_loss(fake_field, real_field)

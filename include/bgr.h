@@ -99,6 +99,64 @@ int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const v
 int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx, const void* dy_, int Cout,
                    int ldy, int ntaps, const int* dy, const int* dx, float* dw, void* stream);
 
+/* ---- BatchNorm (training mode) + LeakyReLU + residual (deeplab.py:100,141,179-183,334-338) --
+ * Tensors are bf16 [M pixels][C] with pixel strides ld*; C multiple of 8. */
+
+/* sums[0..C) = sum_m x, sums[C..2C) = sum_m x^2 (fp64, zeroed inside). */
+int bgr_bn_stats(const void* x, long M, int C, int ld, double* sums, void* stream);
+/* mean, invstd = 1/sqrt(var_biased+eps), a = gamma*invstd, b = beta - mean*a; running stats
+ * updated with `momentum` and the unbiased variance (nn.BatchNorm2d semantics); gamma/beta/
+ * running_* may be NULL. */
+int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const float* beta, float eps,
+                    float momentum, float* mean, float* invstd, float* a, float* b,
+                    float* running_mean, float* running_var, void* stream);
+/* out = act(a*x + b [+ res]); act != 0: LeakyReLU(slope). */
+int bgr_bn_apply(const void* x, int ldx, const float* a, const float* b, const void* res, int ldr,
+                 void* out, int ldo, long M, int C, int act, float slope, void* stream);
+/* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; dyh (dense [M][C]) receives
+ * g*act'(out), which is also dL/dres; dx (dense) receives dL/dx; sums (fp64 [2][C]) receives
+ * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat. */
+int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
+                    const float* mean, const float* invstd, const float* gamma, int act, float slope,
+                    long M, int C, void* dyh, void* dx, double* sums, void* stream);
+
+/* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
+ * w, dw: fp32 [9][C].  Output size ceil(H/stride) x ceil(W/stride). */
+int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* w, int stride, int dil,
+               void* y, int ldy, void* stream);
+int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy, const float* w, int stride, int dil,
+                 void* dx, int ldx, void* stream);
+int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, const void* dy, int ldy, int stride,
+                 int dil, float* dw, void* stream);
+/* y[n,oy,ox,:] = x[n,2oy,2ox,:] (input of the stride-2 1x1 skip convs, deeplab.py:95) + adjoint. */
+int bgr_subsample2(const void* x, int N, int H, int W, int C, int ldx, void* y, int ldy, void* stream);
+int bgr_subsample2_bwd(const void* dy, int N, int H, int W, int C, int ldy, void* dx, int ldx, void* stream);
+
+/* ---- decoder / head / loss helpers -------------------------------------------------------- */
+/* F.interpolate(mode='bilinear', align_corners=True) (deeplab.py:375-379,663): [N,h,w,C] ->
+ * [N,H,W,C] (pixel stride ldy) or, s2d != 0, the field layout [N,H/2,W/2,4C]. */
+int bgr_bilinear_fwd(const void* x, int N, int h, int w, int C, int ldx, void* y, int H, int W, int ldy,
+                     int s2d, void* stream);
+/* adjoint: gx fp32 dense [N,h,w,C] (zeroed inside) += scatter of gy. */
+int bgr_bilinear_bwd(const void* gy, int N, int h, int w, int C, int H, int W, int ldy, int s2d, float* gx,
+                     void* stream);
+/* nn.AdaptiveAvgPool2d(1) (deeplab.py:621): out_sums fp32 [N][C] = sum over P pixels (zeroed
+ * inside; caller scales by 1/P).  bwd: dx[n,p,:] = g[n,:]/P (g bf16 [N][C], dx dense). */
+int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* out_sums, void* stream);
+int bgr_gap_bwd(const void* g, int N, long P, int C, void* dx, void* stream);
+/* flatten + nn.Linear(K,1) (deeplab_gan.py:32-36): logits[n] += x[n,:].w (logits pre-set to
+ * the bias); bwd: dx[n,:] = g[n]*w (NULL to skip), dw = sum_n g[n]*x[n,:] (NULL to skip). */
+int bgr_head_fwd(const void* x, const void* w, int N, long K, float* logits, void* stream);
+int bgr_head_bwd(const float* g, const void* x, const void* w, int N, long K, void* dx, float* dw,
+                 void* stream);
+/* nn.L1Loss (train_gan.py:146,281) fused with its gradient: *sum = sum|a-b| (fp64, zeroed
+ * inside), grad = sign(a-b)*gscale (bf16, NULL to skip). */
+int bgr_l1_loss_grad(const void* a, const void* b, long n, float gscale, void* grad, double* sum,
+                     void* stream);
+/* field layout (bf16 [N,H/2,W/2,(py,px,c)]) <-> fp32 NCHW, the tensors the training script sees. */
+int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream);
+int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,81 @@
+"""Pins oracle/ref_model.py (the fp32 PyTorch restatement used as the model-parity checker):
+ * against tests/golden/model_golden.pt, generated from the reference's own modules
+   (tests/golden/make_model_golden.py), everywhere;
+ * state-dict key/shape identity with the product modules (so weights interchange).
+CPU only; a few seconds.
+"""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import ref_model as R
+from oracle.seeded import seed_state, seeded_fields
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "model_golden.pt")
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return torch.load(GOLD, weights_only=False)
+
+
+@pytest.fixture(scope="module")
+def oracle_run(golden):
+    m = golden["meta"]
+    B, C, H, W = m["B"], m["C"], m["H"], m["W"]
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    G = seed_state(R.GeneratorRef(C, C), 11).train()
+    D = seed_state(R.DiscriminatorRef(C, (H, W)), 12).train()
+    x, y = seeded_fields(5, B, C, H, W)
+    torch.manual_seed(333)
+    crit = R.GANLossRef("ModifiedMinMax", B, torch.device("cpu"))
+    out = {}
+    fake = G(x)
+    lr_, _ = D(y.clone())
+    lf_, _ = D(fake)
+    d_loss = crit.d_loss(lr_, lf_)
+    d_loss.backward()
+    out.update(fake_d=fake.detach(), logits_real=lr_.detach(), logits_fake=lf_.detach(), d_loss=d_loss.detach(),
+               d_grads={n: p.grad.clone() for n, p in D.named_parameters()})
+    G.zero_grad(); D.zero_grad()
+    fake = G(x)
+    lf_, _ = D(fake)
+    g_loss = crit.g_loss(lf_) + F.l1_loss(fake, y)
+    g_loss.backward()
+    out.update(fake_g=fake.detach(), g_loss=g_loss.detach(), logits_fake_g=lf_.detach(),
+               g_grads={n: p.grad.clone() for n, p in G.named_parameters()},
+               bn1_running_mean=G.model.xception_features.bn1.running_mean.clone(),
+               bn1_running_var=G.model.xception_features.bn1.running_var.clone())
+    return out
+
+
+def test_forward_matches_reference_golden(golden, oracle_run):
+    for k in ("logits_real", "logits_fake", "logits_fake_g", "d_loss", "g_loss", "bn1_running_mean",
+              "bn1_running_var"):
+        torch.testing.assert_close(oracle_run[k], golden[k], rtol=1e-4, atol=1e-5)
+    for k in ("fake_d", "fake_g"):  # stored at bf16 precision
+        torch.testing.assert_close(oracle_run[k].bfloat16().float(), golden[k].float(), rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("which", ["d_grads", "g_grads"])
+def test_gradients_match_reference_golden(golden, oracle_run, which):
+    gold, got = golden[which], oracle_run[which]
+    assert set(gold) == set(got)
+    for n, (norm, head) in gold.items():
+        g = got[n]
+        assert abs(float(g.double().norm()) - norm) <= 2e-3 * norm + 1e-7, n
+        torch.testing.assert_close(g.flatten()[:8], head, rtol=5e-3, atol=1e-6 + 1e-3 * norm / max(1, g.numel()) ** 0.5)
+
+
+def test_state_dict_keys_match_product():
+    """Product modules (bias_gan_b200) and oracle share key names and shapes."""
+    from bias_gan_b200 import deeplab_gan as P
+    C, H, W = 16, 64, 96
+    for prod, ref in ((P.Generator(C, C, "Interpolate", "Normal", 0), R.GeneratorRef(C, C)),
+                      (P.Discriminator(C, input_size=(H, W)), R.DiscriminatorRef(C, (H, W)))):
+        a, b = prod.state_dict(), ref.state_dict()
+        assert list(a.keys()) == list(b.keys())
+        for k in a:
+            assert a[k].shape == b[k].shape, k
