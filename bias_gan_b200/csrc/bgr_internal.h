@@ -22,6 +22,14 @@ int fail(int code, const std::string& msg);
       return ::bgr::fail(BGR_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
   } while (0)
 
+// every kernel launch of the library is counted (bench.py reports it as gpu_launches)
+extern unsigned long long g_launch_count;
+#define BGR_LAUNCH_OK()                          \
+  do {                                           \
+    ++::bgr::g_launch_count;                     \
+    BGR_CUDA_OK(cudaGetLastError());             \
+  } while (0)
+
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda at link time).
 // dims/strides innermost first; strides has rank-1 entries (bytes) for dims 1..rank-1.
 int encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,

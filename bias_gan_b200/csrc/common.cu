@@ -6,6 +6,7 @@
 namespace bgr {
 
 static thread_local std::string g_last_error;
+unsigned long long g_launch_count = 0;
 
 void set_error(const std::string& msg) { g_last_error = msg; }
 int fail(int code, const std::string& msg) {
@@ -63,3 +64,4 @@ int encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uint64_
 
 extern "C" const char* bgr_last_error(void) { return bgr::g_last_error.c_str(); }
 extern "C" int bgr_version(void) { return 100; }
+extern "C" unsigned long long bgr_launch_count(void) { return bgr::g_launch_count; }

@@ -311,7 +311,7 @@ static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y,
   }
   dim3 grid(p.N * p.tiles_x * p.tiles_y, (p.Cout + BLOCK_N - 1) / BLOCK_N);
   kern<<<grid, 192, smem, st>>>(tmA, tmB, reinterpret_cast<__nv_bfloat16*>(y), bias, p);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -335,7 +335,7 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* 
   splits = (p.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
   dim3 grid(tiles, splits);
   kern<<<grid, 192, smem, st>>>(tmDY, tmX, dw, p);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 

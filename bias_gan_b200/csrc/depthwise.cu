@@ -222,7 +222,7 @@ extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, co
   if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
   dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), w, static_cast<__nv_bfloat16*>(y), g);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -232,7 +232,7 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
   if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
   dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), w, static_cast<__nv_bfloat16*>(dx), g);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -257,7 +257,7 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
   if (9 * C * sizeof(float) > 160 * 1024) return fail(BGR_ERR_ARG, "depthwise wgrad: too many channels");
   dw_wgrad_kernel<<<int(blocks), 256, 9 * C * sizeof(float), st>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), dw, g, ppb);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -267,7 +267,7 @@ extern "C" int bgr_subsample2(const void* x, int N, int H, int W, int C, int ldx
   if (int rc = make_geom(&g, N, H, W, C, 2, 1, ldx, ldy)) return rc;
   subsample2_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -277,6 +277,6 @@ extern "C" int bgr_subsample2_bwd(const void* dy, int N, int H, int W, int C, in
   if (int rc = make_geom(&g, N, H, W, C, 2, 1, ldx, ldy)) return rc;
   subsample2_bwd_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), g);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }

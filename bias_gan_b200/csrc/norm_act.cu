@@ -229,7 +229,7 @@ extern "C" int bgr_bn_stats(const void* x, long M, int C, int ld, double* sums, 
   int rpb;
   const int grid = reduce_grid(M, C, &rpb);
   bn_stats_kernel<<<grid, 256, 2 * C * sizeof(float), st>>>(static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, sums);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -238,7 +238,7 @@ extern "C" int bgr_bn_finalize(const double* sums, long M, int C, const float* g
                                float* running_mean, float* running_var, void* stream) {
   bn_finalize_kernel<<<(C + 127) / 128, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       sums, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -254,7 +254,7 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
   else if (act) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
   else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
   else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -273,9 +273,9 @@ extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo,
   auto D = static_cast<__nv_bfloat16*>(dyh);
   if (act) bn_bwd_reduce_kernel<true><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
   else bn_bwd_reduce_kernel<false><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   bn_bwd_apply_kernel<<<elementwise_grid(M * (C / 8)), 256, 0, st>>>(D, X, ldx, mean, invstd, gamma, sums,
                                                                     static_cast<__nv_bfloat16*>(dx), M, C);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }

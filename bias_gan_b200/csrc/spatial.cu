@@ -291,7 +291,7 @@ extern "C" int bgr_bilinear_fwd(const void* x, int N, int h, int w, int C, int l
   if (int rc = make_bil(&g, N, h, w, H, W, C, ldx, ldy, s2d)) return rc;
   bilinear_fwd_kernel<<<sp_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -302,7 +302,7 @@ extern "C" int bgr_bilinear_bwd(const void* gy, int N, int h, int w, int C, int 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BGR_CUDA_OK(cudaMemsetAsync(gx, 0, sizeof(float) * size_t(N) * h * w * C, st));
   bilinear_bwd_kernel<<<sp_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(gy), gx, g);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -317,7 +317,7 @@ extern "C" int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* o
   const long ppb = (P + blocks - 1) / blocks;
   blocks = (P + ppb - 1) / ppb;
   gap_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld, P, C, ppb, out_sums);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -325,7 +325,7 @@ extern "C" int bgr_gap_bwd(const void* g, int N, long P, int C, void* dx, void* 
   if (C % 8) return fail(BGR_ERR_ARG, "gap: channel count must be a multiple of 8");
   gap_bwd_kernel<<<sp_grid(long(N) * P * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(g), static_cast<__nv_bfloat16*>(dx), P, C, N, 1.f / float(P));
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -335,7 +335,7 @@ extern "C" int bgr_head_fwd(const void* x, const void* w, int N, long K, float* 
   if (blocks > 148 * 2) blocks = 148 * 2;
   head_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, logits);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -345,7 +345,7 @@ extern "C" int bgr_head_bwd(const float* g, const void* x, const void* w, int N,
   head_bwd_kernel<<<sp_grid(K / 8), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       g, static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, N,
       static_cast<__nv_bfloat16*>(dx), dw);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
@@ -357,20 +357,20 @@ extern "C" int bgr_l1_loss_grad(const void* a, const void* b, long n, float gsca
   l1_loss_grad_kernel<<<sp_grid(n / 8), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(a),
                                                       static_cast<const __nv_bfloat16*>(b), n / 8, gscale,
                                                       static_cast<__nv_bfloat16*>(grad), sum);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
 extern "C" int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream) {
   field_convert_kernel<true><<<sp_grid(long(N) * C * H * W), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(field)), nchw, N, C, H, W);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
 extern "C" int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W, void* stream) {
   field_convert_kernel<false><<<sp_grid(long(N) * C * H * W), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       static_cast<__nv_bfloat16*>(field), const_cast<float*>(nchw), N, C, H, W);
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }

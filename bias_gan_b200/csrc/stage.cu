@@ -127,7 +127,7 @@ static int launch_stage(const void* src, int layout, bool vec, const float* shif
     if (vec) stage_kernel<T, BGR_NHWC, true><<<blocks, 256, 0, st>>>(s, shift, scale, d, p);
     else stage_kernel<T, BGR_NHWC, false><<<blocks, 256, 0, st>>>(s, shift, scale, d, p);
   }
-  BGR_CUDA_OK(cudaGetLastError());
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 

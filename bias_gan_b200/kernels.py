@@ -29,9 +29,11 @@ def taps_for(kernel_size, dilation=1):
 def _nhwc_view(t):
     assert t.dim() == 4 and t.dtype == torch.bfloat16 and t.is_cuda, "expected a bf16 NHWC cuda view"
     N, H, W, C = t.shape
-    ld = t.stride(2)
-    assert t.stride(3) == 1 and t.stride(1) == W * ld and t.stride(0) == H * W * ld, \
-        "expected dense pixels with a uniform pixel stride"
+    if t.is_contiguous():
+        return N, H, W, C, C
+    ld = t.stride(2) if W > 1 else (t.stride(1) if H > 1 else (t.stride(0) if N > 1 else C))
+    assert t.stride(3) == 1 and (W == 1 or t.stride(2) == ld) and (H == 1 or t.stride(1) == W * ld) \
+        and (N == 1 or t.stride(0) == H * W * ld), "expected dense pixels with a uniform pixel stride"
     return N, H, W, C, ld
 
 
@@ -104,8 +106,14 @@ def _rows(t):
     """(M, C, ld) of a bf16 [..., C] view with uniform pixel stride."""
     assert t.dtype == torch.bfloat16 and t.is_cuda and t.stride(-1) == 1
     C = t.shape[-1]
-    ld = t.stride(-2) if t.dim() > 1 else C
     M = t.numel() // C
+    if t.is_contiguous():
+        return M, C, C
+    ld = C
+    for d in range(t.dim() - 2, -1, -1):
+        if t.shape[d] > 1:
+            ld = t.stride(d)
+            break
     exp = ld
     for d in range(t.dim() - 2, -1, -1):
         assert t.shape[d] == 1 or t.stride(d) == exp, "non-uniform pixel stride"

@@ -26,6 +26,8 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
         d_loss = crit_gan.d_loss(logits_real, logits_fake)
         d_opt.zero_grad(set_to_none=True)
         d_loss.backward()
+        if hasattr(D, "grad_sync"):
+            D.grad_sync.finish()
         d_opt.step()
         del fake, logits_real, logits_fake
     if train_generator:
@@ -44,6 +46,8 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
             if lean:
                 for p in D.parameters():
                     p.requires_grad_(True)
+        if hasattr(G, "grad_sync"):
+            G.grad_sync.finish()
         g_opt.step()
     return (d_loss.detach() if d_loss is not None else None,
             g_loss.detach() if g_loss is not None else None)

@@ -38,6 +38,8 @@ extern "C" {
 
 const char* bgr_last_error(void);
 int bgr_version(void);
+/* number of CUDA kernels this library has launched in this process */
+unsigned long long bgr_launch_count(void);
 
 /* ---- .npy reader (numpy_reader.cpp:501-536) ---------------------------------------------- */
 

@@ -1,0 +1,252 @@
+"""GPU parity tests of the individual sm_100a kernels, called through the C ABI (ctypes wrappers in
+bias_gan_b200/kernels.py and the autograd bindings in functional.py).
+
+Byte/index work (stage layout, crop/flip indices, bf16 rounding) is checked bit-exact against
+oracle/npy_oracle.py; floating-point kernels against plain PyTorch fp32 ops of the same math on
+bf16-rounded inputs with rel-L2 <= 4e-3 unless stated.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.fixture(scope="module")
+def dev():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return torch.device("cuda", 0)
+
+
+def nhwc(x):
+    return x.permute(0, 2, 3, 1).contiguous()
+
+
+def nchw(x):
+    return x.permute(0, 3, 1, 2).contiguous()
+
+
+# --------------------------------------------------------------------------------- stage kernel
+@pytest.mark.parametrize("layout", ["NCHW", "NHWC"])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("crop,flip,s2d", [(None, (False, False), True), ((4, 8, 24, 40), (True, False), False),
+                                            ((2, 4, 20, 36), (True, True), True), ((1, 3, 10, 20), (False, True), False)])
+def test_stage_bit_exact(dev, layout, dtype, crop, flip, s2d):
+    from bias_gan_b200 import kernels as K
+    from oracle import npy_oracle as orc
+    rng = np.random.default_rng(3)
+    B, Cf, H, W = 2, 16, 32, 48
+    shape = (B, Cf, H, W) if layout == "NCHW" else (B, H, W, Cf)
+    src = (rng.standard_normal(shape) * 3 + 1).astype(dtype)
+    for channels in (list(range(16)), [3, 0, 7, 12, 1, 15, 9, 8]):
+        shift = rng.standard_normal(len(channels)).astype(np.float32)
+        scale = (0.5 + rng.random(len(channels))).astype(np.float32)
+        want = orc.stage_reference(src, layout, channels, shift, scale, crop, flip, s2d)
+        got = K.stage_normalize(torch.from_numpy(src).to(dev), layout, channels, torch.from_numpy(shift).to(dev),
+                                torch.from_numpy(scale).to(dev), crop, flip, s2d)
+        got = got.view(torch.int16).cpu().numpy().view(np.uint16)
+        np.testing.assert_array_equal(got, want)
+
+
+def test_stage_full_size_roundtrip(dev):
+    """BASELINE size (16x768x1152): identity standardisation must reproduce bf16(x) exactly and the
+    s2d layout must be the permutation of the NHWC layout."""
+    from bias_gan_b200 import kernels as K
+    g = torch.Generator(device="cpu").manual_seed(0)
+    x = torch.randn(1, 16, 768, 1152, generator=g).to(dev)
+    zero, one = torch.zeros(16, device=dev), torch.ones(16, device=dev)
+    a = K.stage_normalize(x, "NCHW", None, zero, one, s2d=False)
+    assert torch.equal(a, nhwc(x).bfloat16())
+    b = K.stage_normalize(x, "NCHW", None, zero, one, s2d=True)
+    want = a.view(1, 384, 2, 576, 2, 16).permute(0, 1, 3, 2, 4, 5).reshape(1, 384, 576, 64)
+    assert torch.equal(b, want)
+    c = K.stage_normalize(nhwc(x), "NHWC", None, zero, one, s2d=True)
+    assert torch.equal(c, want)
+    # flip twice == identity (size-independent property)
+    f = K.stage_normalize(x, "NCHW", None, zero, one, flip=(True, True))
+    assert torch.equal(torch.flip(f, dims=(1, 2)), a)
+    assert torch.equal(K.field_to_nchw(b, 16), x.bfloat16().float())
+    assert torch.equal(K.nchw_to_field(x), b)
+
+
+# --------------------------------------------------------------------------------- conv kernels
+@pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil,bias", [
+    (1, 16, 8, 64, 128, 1, 1, False), (2, 48, 72, 728, 728, 1, 1, False), (2, 24, 40, 128, 48, 1, 1, False),
+    (1, 16, 24, 256, 16, 1, 1, True), (2, 32, 48, 128, 128, 3, 1, False), (1, 19, 37, 304, 256, 3, 1, False),
+    (1, 48, 72, 256, 256, 3, 6, False), (1, 12, 18, 192, 64, 3, 18, False), (8, 1, 1, 2048, 256, 1, 1, False)])
+def test_conv_fprop_dgrad_wgrad(dev, N, H, W, Cin, Cout, ks, dil, bias):
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(1)
+    x = torch.randn(N, Cin, H, W, generator=g).to(dev).bfloat16()
+    w = (torch.randn(Cout, Cin, ks, ks, generator=g) / (Cin * ks * ks) ** 0.5).to(dev).bfloat16().float()
+    b = torch.randn(Cout, generator=g).to(dev) if bias else None
+    gy = torch.randn(N, Cout, H, W, generator=g).to(dev).bfloat16()
+    xr, wr = x.float().requires_grad_(True), w.clone().requires_grad_(True)
+    br = b.clone().requires_grad_(True) if bias else None
+    ref = F.conv2d(xr, wr, br, padding=dil * (ks - 1) // 2, dilation=dil)
+    ref.backward(gy.float())
+    xp, wp = nhwc(x).requires_grad_(True), w.clone().requires_grad_(True)
+    bp = b.clone().requires_grad_(True) if bias else None
+    out = F_.conv2d(xp, wp, bp, dilation=dil)
+    out.backward(nhwc(gy))
+    assert rel(nchw(out), ref) < 4e-3
+    assert rel(nchw(xp.grad), xr.grad) < 4e-3
+    assert rel(wp.grad, wr.grad) < 1e-4
+    if bias:
+        assert rel(bp.grad, br.grad) < 1e-4
+
+
+@pytest.mark.parametrize("N,H,W", [(2, 64, 96), (1, 38, 74)])
+def test_entry_conv_s2d(dev, N, H, W):
+    from bias_gan_b200 import functional as F_, kernels as K
+    g = torch.Generator(device="cpu").manual_seed(2)
+    x = torch.randn(N, 16, H, W, generator=g).to(dev).bfloat16().float()
+    w = (torch.randn(128, 16, 3, 3, generator=g) / 12.0).to(dev).bfloat16().float()
+    gy = torch.randn(N, 128, H // 2, W // 2, generator=g).to(dev).bfloat16()
+    xr, wr = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    ref = F.conv2d(xr, wr, None, stride=2, padding=1)
+    ref.backward(gy.float())
+    field = K.nchw_to_field(x).requires_grad_(True)
+    wp = w.clone().requires_grad_(True)
+    out = F_.conv_s2d(field, wp)
+    out.backward(nhwc(gy))
+    assert rel(nchw(out), ref) < 4e-3
+    assert rel(wp.grad, wr.grad) < 1e-4
+    assert rel(K.field_to_nchw(field.grad, 16), xr.grad) < 4e-3
+
+
+# --------------------------------------------------------------------------------- BN + act
+@pytest.mark.parametrize("C,M_shape", [(128, (2, 24, 36)), (728, (2, 6, 9)), (2048, (2, 3, 5)), (48, (1, 16, 24)), (256, (8, 1, 1))])
+@pytest.mark.parametrize("act,with_res", [(True, False), (True, True), (False, True), (False, False)])
+def test_bn_act_train(dev, C, M_shape, act, with_res):
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(4)
+    N, H, W = M_shape
+    y = (torch.randn(N, C, H, W, generator=g) * 2 + 0.5).to(dev).bfloat16()
+    r = torch.randn(N, C, H, W, generator=g).to(dev).bfloat16() if with_res else None
+    go = torch.randn(N, C, H, W, generator=g).to(dev).bfloat16()
+    bn_ref = torch.nn.BatchNorm2d(C).to(dev).train()
+    bn_p = torch.nn.BatchNorm2d(C).to(dev).train()
+    with torch.no_grad():
+        bn_ref.weight.copy_(1 + 0.1 * torch.randn(C, generator=g)); bn_ref.bias.copy_(0.1 * torch.randn(C, generator=g))
+        bn_p.load_state_dict(bn_ref.state_dict())
+    yr = y.float().requires_grad_(True)
+    rr = r.float().requires_grad_(True) if with_res else None
+    o = bn_ref(yr)
+    if with_res:
+        o = o + rr
+    if act:
+        o = F.leaky_relu(o, 0.2)
+    o.backward(go.float())
+    yp = nhwc(y).requires_grad_(True)
+    rp = nhwc(r).requires_grad_(True) if with_res else None
+    op = F_.bn_act(yp, bn_p, res=rp, act=act)
+    op.backward(nhwc(go))
+    assert rel(nchw(op), o) < 4e-3
+    assert rel(nchw(yp.grad), yr.grad) < 1e-2
+    assert rel(bn_p.weight.grad, bn_ref.weight.grad) < 5e-3
+    assert rel(bn_p.bias.grad, bn_ref.bias.grad) < 5e-3
+    if with_res:
+        assert rel(nchw(rp.grad), rr.grad) < 4e-3
+    torch.testing.assert_close(bn_p.running_mean, bn_ref.running_mean, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(bn_p.running_var, bn_ref.running_var, rtol=1e-3, atol=1e-4)
+    assert int(bn_p.num_batches_tracked) == 1
+
+
+# --------------------------------------------------------------------------------- depthwise
+@pytest.mark.parametrize("C,H,W,stride,dil", [(128, 24, 36, 1, 1), (128, 25, 37, 2, 1), (728, 6, 9, 1, 1),
+                                              (1536, 5, 7, 1, 2), (256, 12, 18, 2, 1)])
+def test_depthwise(dev, C, H, W, stride, dil):
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(5)
+    x = torch.randn(2, C, H, W, generator=g).to(dev).bfloat16()
+    w = (torch.randn(C, 1, 3, 3, generator=g) / 3).to(dev)
+    xr, wr = x.float().requires_grad_(True), w.clone().requires_grad_(True)
+    ref = F.conv2d(F.pad(xr, (dil,) * 4), wr, None, stride=stride, dilation=dil, groups=C)
+    gy = torch.randn(ref.shape, generator=g).to(dev).bfloat16()
+    ref.backward(gy.float())
+    xp, wp = nhwc(x).requires_grad_(True), w.clone().requires_grad_(True)
+    out = F_.depthwise3x3(xp, wp, stride, dil)
+    assert tuple(out.shape) == (2, ref.shape[2], ref.shape[3], C)
+    out.backward(nhwc(gy))
+    assert rel(nchw(out), ref) < 4e-3
+    assert rel(nchw(xp.grad), xr.grad) < 4e-3
+    assert rel(wp.grad, wr.grad) < 1e-4
+
+
+def test_subsample2(dev):
+    from bias_gan_b200 import functional as F_
+    x = torch.randn(2, 9, 13, 64, device=dev).bfloat16().requires_grad_(True)
+    y = F_.subsample2(x)
+    assert torch.equal(y, x[:, ::2, ::2, :])
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    want = torch.zeros_like(x)
+    want[:, ::2, ::2, :] = gy
+    assert torch.equal(x.grad, want)
+
+
+# --------------------------------------------------------------------------------- decoder helpers
+@pytest.mark.parametrize("h,w,H,W,C,s2d", [(4, 6, 16, 24, 256, False), (16, 24, 64, 96, 16, True), (1, 1, 4, 6, 256, False),
+                                           (5, 10, 19, 37, 48, False)])
+def test_bilinear(dev, h, w, H, W, C, s2d):
+    from bias_gan_b200 import functional as F_, kernels as K
+    g = torch.Generator(device="cpu").manual_seed(6)
+    x = torch.randn(2, C, h, w, generator=g).to(dev).bfloat16()
+    gy = torch.randn(2, C, H, W, generator=g).to(dev).bfloat16()
+    xr = x.float().requires_grad_(True)
+    ref = F.interpolate(xr, size=(H, W), mode="bilinear", align_corners=True)
+    ref.backward(gy.float())
+    xp = nhwc(x).requires_grad_(True)
+    out = F_.bilinear(xp, H, W, s2d=s2d)
+    out.backward(K.nchw_to_field(gy.float()) if s2d else nhwc(gy))
+    got = K.field_to_nchw(out, C) if s2d else nchw(out)
+    assert rel(got, ref) < 4e-3
+    assert rel(nchw(xp.grad), xr.grad) < 4e-3
+
+
+def test_gap_head_l1(dev):
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(7)
+    x = torch.randn(2, 2048, 3, 5, generator=g).to(dev).bfloat16()
+    xr = x.float().requires_grad_(True)
+    ref = F.adaptive_avg_pool2d(xr, 1)
+    go = torch.randn(2, 2048, 1, 1, generator=g).to(dev).bfloat16()
+    ref.backward(go.float())
+    xp = nhwc(x).requires_grad_(True)
+    out = F_.global_avg_pool(xp)
+    out.backward(nhwc(go))
+    assert rel(nchw(out), ref) < 4e-3 and rel(nchw(xp.grad), xr.grad) < 4e-3
+    # linear head with the reference's (C,H,W) flatten order
+    lin = torch.nn.Linear(2048 * 15, 1).to(dev)
+    with torch.no_grad():
+        lin.weight.copy_(lin.weight.bfloat16().float())
+    xr = x.float().requires_grad_(True)
+    ref = lin(xr.reshape(2, -1))
+    gl = torch.tensor([[0.3], [-1.2]], device=dev)
+    ref.backward(gl)
+    wr_grad, br_grad = lin.weight.grad.clone(), lin.bias.grad.clone()
+    lin.zero_grad()
+    xp = nhwc(x).requires_grad_(True)
+    out = F_.linear_head(xp, lin.weight, lin.bias)
+    out.backward(gl)
+    assert rel(out, ref) < 2e-3 and rel(nchw(xp.grad), xr.grad) < 4e-3
+    assert rel(lin.weight.grad, wr_grad) < 1e-4 and rel(lin.bias.grad, br_grad) < 1e-5
+    # fused L1 loss + gradient
+    a = torch.randn(2, 8, 12, 64, generator=g).to(dev).bfloat16()
+    b = torch.randn(2, 8, 12, 64, generator=g).to(dev).bfloat16()
+    ar = a.float().requires_grad_(True)
+    ref = F.l1_loss(ar, b.float())
+    (2.5 * ref).backward()
+    ap = a.clone().requires_grad_(True)
+    out = F_.l1_loss(ap, b)
+    (2.5 * out).backward()
+    assert abs(float(out) - float(ref)) < 1e-5 * abs(float(ref))
+    assert rel(ap.grad, ar.grad) < 4e-3
