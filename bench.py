@@ -42,10 +42,10 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop = index, [], threading.Event()
+        self.index, self.rows, self._halt = index, [], threading.Event()
 
     def run(self):
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
@@ -54,10 +54,10 @@ class ClockSampler(threading.Thread):
                     self.rows.append(f)
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._halt.wait(0.2)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=6)
         if not self.rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -150,6 +150,9 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="local batch per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--faithful", action="store_true", help="reference-faithful schedule (no lean shortcuts)")
+    ap.add_argument("--profile", action="store_true",
+                    help="warm up, then run --steps steps between cudaProfilerStart/Stop and exit (for ncu "
+                         "--profile-from-start off); prints no bench value")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -226,6 +229,16 @@ def main():
 
     for _ in range(max(args.warmup, 3)):
         step(False)
+    if args.profile:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        for _ in range(args.steps):
+            step(False)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        if rank == 0:
+            print(json.dumps({"profile_only": True, "steps": args.steps}), flush=True)
+        return
     sampler = ClockSampler(lrank)
     if rank == 0:
         sampler.start()

@@ -196,6 +196,138 @@ subsample2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __res
   }
 }
 
+// ---------------------------------------------------------------- strip-mined variants
+// One thread = 8 channels x T consecutive output columns: the 72 weights live in registers and
+// every input column of the window is loaded once per row (18 loads per 4 outputs instead of 36
+// for stride 1), which moves these kernels from LSU-bound to HBM/L2-bound.
+// REVERSE applies the taps mirrored (w[8-k]): the stride-1 data gradient.
+template <int S, int D, int T, bool REVERSE>
+__global__ void __launch_bounds__(256)
+dw_fwd_strip_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                    __nv_bfloat16* __restrict__ y, const DwGeom g) {
+  constexpr int SPAN = (T - 1) * S + 2 * D + 1;
+  const int G = g.C >> 3;
+  const int strips = (g.Wo + T - 1) / T;
+  const long total = long(g.N) * g.Ho * strips * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int sx = int(r % strips); r /= strips;
+    const int oy = int(r % g.Ho);
+    const int n = int(r / g.Ho);
+    const int ox0 = sx * T;
+    float wr[9][8];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const int kk = REVERSE ? 8 - k : k;
+      const float4 w0 = *reinterpret_cast<const float4*>(w + kk * g.C + cg * 8);
+      const float4 w1 = *reinterpret_cast<const float4*>(w + kk * g.C + cg * 8 + 4);
+      wr[k][0] = w0.x; wr[k][1] = w0.y; wr[k][2] = w0.z; wr[k][3] = w0.w;
+      wr[k][4] = w1.x; wr[k][5] = w1.y; wr[k][6] = w1.z; wr[k][7] = w1.w;
+    }
+    float acc[T][8];
+#pragma unroll
+    for (int j = 0; j < T; ++j)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[j][c] = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int iy = oy * S + (ky - 1) * D;
+      if (iy < 0 || iy >= g.H) continue;
+      const __nv_bfloat16* row = x + (size_t(size_t(n) * g.H + iy) * g.W) * g.ldx + cg * 8;
+#pragma unroll
+      for (int c = 0; c < SPAN; ++c) {
+        const int ix = ox0 * S - D + c;
+        if (ix < 0 || ix >= g.W) continue;
+        float xv[8];
+        dw_unpack8(*reinterpret_cast<const uint4*>(row + size_t(ix) * g.ldx), xv);
+#pragma unroll
+        for (int j = 0; j < T; ++j)
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx)
+            if (j * S + kx * D == c) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) acc[j][e] = fmaf(xv[e], wr[ky * 3 + kx][e], acc[j][e]);
+            }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < T; ++j)
+      if (ox0 + j < g.Wo)
+        *reinterpret_cast<uint4*>(y + (size_t(size_t(n) * g.Ho + oy) * g.Wo + ox0 + j) * g.ldy + cg * 8) = dw_pack8(acc[j]);
+  }
+}
+
+// dw[k][c] += sum over output pixels, strip-mined like the forward kernel.  Each block walks a
+// contiguous range of (row, strip) items for all channel groups.
+template <int S, int D, int T>
+__global__ void __launch_bounds__(256)
+dw_wgrad_strip_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                      float* __restrict__ dw, const DwGeom g, long items_per_block) {
+  constexpr int SPAN = (T - 1) * S + 2 * D + 1;
+  extern __shared__ float sh[];  // [9][C]
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int G = g.C >> 3;
+  const int R = G >= 256 ? 1 : 256 / G;
+  const int strips = (g.Wo + T - 1) / T;
+  const long items = long(g.N) * g.Ho * strips;
+  const long i0 = long(blockIdx.x) * items_per_block, i1 = min(i0 + items_per_block, items);
+  for (int cg = threadIdx.x % G; cg < G; cg += (G >= 256 ? 256 : G)) {
+    const int r = G >= 256 ? 0 : threadIdx.x / G;
+    if (r >= R) break;
+    float acc[9][8];
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[k][e] = 0.f;
+    for (long it = i0 + r; it < i1; it += R) {
+      const int sx = int(it % strips);
+      const int oy = int((it / strips) % g.Ho);
+      const int n = int(it / (long(strips) * g.Ho));
+      const int ox0 = sx * T;
+      float gv[T][8];
+#pragma unroll
+      for (int j = 0; j < T; ++j) {
+        if (ox0 + j < g.Wo)
+          dw_unpack8(*reinterpret_cast<const uint4*>(dy + (size_t(size_t(n) * g.Ho + oy) * g.Wo + ox0 + j) * g.ldy + cg * 8), gv[j]);
+        else
+#pragma unroll
+          for (int e = 0; e < 8; ++e) gv[j][e] = 0.f;
+      }
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const int iy = oy * S + (ky - 1) * D;
+        if (iy < 0 || iy >= g.H) continue;
+        const __nv_bfloat16* row = x + (size_t(size_t(n) * g.H + iy) * g.W) * g.ldx + cg * 8;
+#pragma unroll
+        for (int c = 0; c < SPAN; ++c) {
+          const int ix = ox0 * S - D + c;
+          if (ix < 0 || ix >= g.W) continue;
+          float xv[8];
+          dw_unpack8(*reinterpret_cast<const uint4*>(row + size_t(ix) * g.ldx), xv);
+#pragma unroll
+          for (int j = 0; j < T; ++j)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx)
+              if (j * S + kx * D == c) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[ky * 3 + kx][e] = fmaf(gv[j][e], xv[e], acc[ky * 3 + kx][e]);
+              }
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) atomicAdd(&sh[k * g.C + cg * 8 + e], acc[k][e]);
+    if (G < 256) break;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
+}
+
 static int ew_grid(long total) {
   long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
@@ -216,12 +348,30 @@ static int make_geom(DwGeom* g, int N, int H, int W, int C, int stride, int dil,
 
 using namespace bgr;
 
+constexpr int kStripT = 4;
+
+// strip-mined forward for the (stride, dilation) pairs of the os=16 trunk; generic kernel otherwise
+template <bool REVERSE>
+static bool launch_fwd_strip(const __nv_bfloat16* x, const float* w, __nv_bfloat16* y, const DwGeom& g,
+                             cudaStream_t st) {
+  const long total = long(g.N) * g.Ho * ((g.Wo + kStripT - 1) / kStripT) * (g.C / 8);
+  const int grid = ew_grid(total);
+  if (g.stride == 1 && g.dil == 1) dw_fwd_strip_kernel<1, 1, kStripT, REVERSE><<<grid, 256, 0, st>>>(x, w, y, g);
+  else if (g.stride == 1 && g.dil == 2) dw_fwd_strip_kernel<1, 2, kStripT, REVERSE><<<grid, 256, 0, st>>>(x, w, y, g);
+  else if (g.stride == 2 && g.dil == 1 && !REVERSE) dw_fwd_strip_kernel<2, 1, kStripT, false><<<grid, 256, 0, st>>>(x, w, y, g);
+  else return false;
+  return true;
+}
+
 extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* w, int stride,
                           int dil, void* y, int ldy, void* stream) {
   DwGeom g;
   if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
-  dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), w, static_cast<__nv_bfloat16*>(y), g);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto Y = static_cast<__nv_bfloat16*>(y);
+  if (!launch_fwd_strip<false>(X, w, Y, g, st))
+    dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, st>>>(X, w, Y, g);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -230,9 +380,39 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
                             int dil, void* dx, int ldx, void* stream) {
   DwGeom g;
   if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
-  dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dy), w, static_cast<__nv_bfloat16*>(dx), g);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  auto DY = static_cast<const __nv_bfloat16*>(dy);
+  auto DX = static_cast<__nv_bfloat16*>(dx);
+  bool done = false;
+  if (stride == 1) {
+    // stride-1 data gradient = the same stencil with mirrored taps, reading dy and writing dx
+    DwGeom r = g;
+    r.ldx = ldy;
+    r.ldy = ldx;
+    done = launch_fwd_strip<true>(DY, w, DX, r, st);
+  }
+  if (!done) dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
   BGR_LAUNCH_OK();
+  return BGR_OK;
+}
+
+template <int S, int D>
+static int launch_wgrad_strip(const __nv_bfloat16* x, const __nv_bfloat16* dy, float* dw, const DwGeom& g,
+                              cudaStream_t st) {
+  auto kern = dw_wgrad_strip_kernel<S, D, kStripT>;
+  static bool configured = false;
+  if (!configured) {
+    BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    configured = true;
+  }
+  const long items = long(g.N) * g.Ho * ((g.Wo + kStripT - 1) / kStripT);
+  const int G = g.C / 8, R = G >= 256 ? 1 : 256 / G;
+  long blocks = (items + long(R) * 2 - 1) / (long(R) * 2);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks < 1) blocks = 1;
+  const long ipb = (items + blocks - 1) / blocks;
+  blocks = (items + ipb - 1) / ipb;
+  kern<<<int(blocks), 256, 9 * g.C * sizeof(float), st>>>(x, dy, dw, g, ipb);
   return BGR_OK;
 }
 
@@ -242,21 +422,29 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
   if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BGR_CUDA_OK(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * C, st));
-  const long P = long(N) * g.Ho * g.Wo;
-  const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
-  long blocks = (P + long(R) * 4 - 1) / (long(R) * 4);
-  if (blocks > 148 * 4) blocks = 148 * 4;
-  if (blocks < 1) blocks = 1;
-  const long ppb = (P + blocks - 1) / blocks;
-  blocks = (P + ppb - 1) / ppb;
-  static bool configured = false;
-  if (!configured) {
-    BGR_CUDA_OK(cudaFuncSetAttribute(dw_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    configured = true;
-  }
   if (9 * C * sizeof(float) > 160 * 1024) return fail(BGR_ERR_ARG, "depthwise wgrad: too many channels");
-  dw_wgrad_kernel<<<int(blocks), 256, 9 * C * sizeof(float), st>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy), dw, g, ppb);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto DY = static_cast<const __nv_bfloat16*>(dy);
+  int rc = BGR_OK;
+  if (stride == 1 && dil == 1) rc = launch_wgrad_strip<1, 1>(X, DY, dw, g, st);
+  else if (stride == 1 && dil == 2) rc = launch_wgrad_strip<1, 2>(X, DY, dw, g, st);
+  else if (stride == 2 && dil == 1) rc = launch_wgrad_strip<2, 1>(X, DY, dw, g, st);
+  else {
+    const long P = long(N) * g.Ho * g.Wo;
+    const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
+    long blocks = (P + long(R) * 4 - 1) / (long(R) * 4);
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    const long ppb = (P + blocks - 1) / blocks;
+    blocks = (P + ppb - 1) / ppb;
+    static bool configured = false;
+    if (!configured) {
+      BGR_CUDA_OK(cudaFuncSetAttribute(dw_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      configured = true;
+    }
+    dw_wgrad_kernel<<<int(blocks), 256, 9 * C * sizeof(float), st>>>(X, DY, dw, g, ppb);
+  }
+  if (rc != BGR_OK) return rc;
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

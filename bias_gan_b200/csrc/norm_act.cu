@@ -154,6 +154,9 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
       for (int j = 0; j < 8; ++j) {
         float d = gv[j];
         if (ACT) d = ov[j] > 0.f ? d : slope * d;
+        // statistics are taken from the bf16-rounded value pass 2 will read back, so that the
+        // mean subtraction cancels exactly (matters when M is tiny, e.g. the image-pool branch)
+        d = __bfloat162float(__float2bfloat16_rn(d));
         gv[j] = d;
         s1[j] += d;
         s2[j] += d * (xv[j] - mu[j]) * is[j];
@@ -171,30 +174,45 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&sums[i], double(sh[i]));
 }
 
-// backward, pass 2: dx = gamma*invstd * (dyh - s1/M - xhat * s2/M)
+// backward, pass 2: dx = gamma*invstd * (dyh - s1/M - xhat * s2/M), xhat = (x - mean)*invstd.
+// Per-channel fp32 coefficients (c0 = gamma*invstd, k1 = s1/M, k2 = s2/M, mean, invstd) are
+// prepared by a tiny kernel so the streaming pass has no fp64 and only vector loads.
+__global__ void bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ invstd,
+                                   const float* __restrict__ gamma, const double* __restrict__ sums,
+                                   long M, int C, float* __restrict__ coef /* [5][C] */) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  coef[c] = (gamma ? gamma[c] : 1.f) * invstd[c];
+  coef[C + c] = float(sums[c] / double(M));
+  coef[2 * C + c] = float(sums[C + c] / double(M));
+  coef[3 * C + c] = mean[c];
+  coef[4 * C + c] = invstd[c];
+}
+
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+  *reinterpret_cast<float4*>(f) = *reinterpret_cast<const float4*>(p);
+  *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(p + 4);
+}
+
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* __restrict__ x, int ldx,
-                    const float* __restrict__ mean, const float* __restrict__ invstd,
-                    const float* __restrict__ gamma, const double* __restrict__ sums,
-                    __nv_bfloat16* __restrict__ dx, long M, int C) {
+                    const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, long M, int C) {
   const int G = C >> 3;
   const long total = M * G;
-  const float invM = 1.f / float(M);
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += long(gridDim.x) * blockDim.x) {
     const int g = int(i % G);
     const long row = i / G;
-    float d[8], xv[8];
+    float d[8], xv[8], c0[8], k1[8], k2[8], mu[8], is[8];
     unpack8(*reinterpret_cast<const uint4*>(dyh + row * C + g * 8), d);
     unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + g * 8), xv);
+    load8f(coef + g * 8, c0);
+    load8f(coef + C + g * 8, k1);
+    load8f(coef + 2 * C + g * 8, k2);
+    load8f(coef + 3 * C + g * 8, mu);
+    load8f(coef + 4 * C + g * 8, is);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = g * 8 + j;
-      const float is = invstd[c];
-      const float xh = (xv[j] - mean[c]) * is;
-      const float k1 = float(sums[c]) * invM, k2 = float(sums[C + c]) * invM;
-      d[j] = (gamma ? gamma[c] : 1.f) * is * (d[j] - k1 - xh * k2);
-    }
+    for (int j = 0; j < 8; ++j) d[j] = c0[j] * (d[j] - k1[j] - (xv[j] - mu[j]) * is[j] * k2[j]);
     *reinterpret_cast<uint4*>(dx + row * C + g * 8) = pack8(d);
   }
 }
@@ -261,7 +279,7 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
 extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
                                const float* mean, const float* invstd, const float* gamma, int act,
                                float slope, long M, int C, void* dyh, void* dx, double* sums,
-                               void* stream) {
+                               float* coef_ws, void* stream) {
   BGR_CHECK_C8(C);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BGR_CUDA_OK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
@@ -274,7 +292,9 @@ extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo,
   if (act) bn_bwd_reduce_kernel<true><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
   else bn_bwd_reduce_kernel<false><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
   BGR_LAUNCH_OK();
-  bn_bwd_apply_kernel<<<elementwise_grid(M * (C / 8)), 256, 0, st>>>(D, X, ldx, mean, invstd, gamma, sums,
+  bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
+  BGR_LAUNCH_OK();
+  bn_bwd_apply_kernel<<<elementwise_grid(M * (C / 8)), 256, 0, st>>>(D, X, ldx, coef_ws,
                                                                     static_cast<__nv_bfloat16*>(dx), M, C);
   BGR_LAUNCH_OK();
   return BGR_OK;

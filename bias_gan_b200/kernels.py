@@ -166,9 +166,10 @@ def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2):
     dyh = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
     dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
     sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+    coef = torch.empty(5 * C, dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_bn_backward(ptr(g), ldg, ptr(out) if act else ctypes.c_void_p(0), ldo, ptr(x), ldx,
                                      ptr(mean), ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
-                                     ptr(dyh), ptr(dx), ptr(sums), stream_ptr()))
+                                     ptr(dyh), ptr(dx), ptr(sums), ptr(coef), stream_ptr()))
     return dx, dyh, sums
 
 

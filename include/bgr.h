@@ -117,10 +117,10 @@ int bgr_bn_apply(const void* x, int ldx, const float* a, const float* b, const v
                  void* out, int ldo, long M, int C, int act, float slope, void* stream);
 /* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; dyh (dense [M][C]) receives
  * g*act'(out), which is also dL/dres; dx (dense) receives dL/dx; sums (fp64 [2][C]) receives
- * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat. */
+ * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat; coef_ws: fp32 [5][C] workspace. */
 int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
                     const float* mean, const float* invstd, const float* gamma, int act, float slope,
-                    long M, int C, void* dyh, void* dx, double* sums, void* stream);
+                    long M, int C, void* dyh, void* dx, double* sums, float* coef_ws, void* stream);
 
 /* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
  * w, dw: fp32 [9][C].  Output size ceil(H/stride) x ceil(W/stride). */
