@@ -328,6 +328,209 @@ dw_wgrad_strip_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
   for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
 }
 
+// ---------------------------------------------------------------- column-marching variants
+// stride 1, dilation 1 (57 of the 63 depthwise layers of a trunk).  One thread = 4 channels x 4
+// output columns, marching down a segment of rows.  Every input row is loaded once (6 column
+// vectors, issued together and one row ahead of the arithmetic so that DRAM latency overlaps
+// the FMAs) and scattered into three rolling accumulator rows: 1.5 loads per output vector
+// instead of 9, weights in registers for the whole march, index arithmetic once per thread.
+constexpr int kCpt = 4;  // channels per thread
+
+__device__ __forceinline__ void dw_unpack4(const uint2& u, float (&f)[4]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+  const float2 a = __bfloat1622float2(h[0]), b = __bfloat1622float2(h[1]);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+__device__ __forceinline__ uint2 dw_pack4(const float (&f)[4]) {
+  uint2 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+  h[0] = __floats2bfloat162_rn(f[0], f[1]);
+  h[1] = __floats2bfloat162_rn(f[2], f[3]);
+  return u;
+}
+
+struct MarchItem {
+  int c0, ox0, oy0, oy1, n;
+};
+__device__ __forceinline__ bool march_item(const DwGeom& g, int segs, int RY, MarchItem* it) {
+  const int G = g.C / kCpt;
+  const int strips = (g.W + 3) >> 2;
+  const unsigned total = unsigned(g.N) * segs * strips * G;
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return false;
+  it->c0 = (i % G) * kCpt;
+  unsigned t = i / G;
+  it->ox0 = (t % strips) * 4;
+  t /= strips;
+  it->oy0 = (t % segs) * RY;
+  it->n = t / segs;
+  it->oy1 = min(it->oy0 + RY, g.H);
+  return true;
+}
+
+// six column vectors of input row iy (zeros outside the image), all loads independent
+__device__ __forceinline__ void march_load_row(const __nv_bfloat16* base, const DwGeom& g, int ld, int iy,
+                                               int ox0, uint2 (&r)[6]) {
+  const bool rv = iy >= 0 && iy < g.H;
+  const __nv_bfloat16* row = base + size_t(rv ? iy : 0) * g.W * ld;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const int ix = ox0 - 1 + c;
+    r[c] = make_uint2(0, 0);
+    if (rv && ix >= 0 && ix < g.W) r[c] = __ldg(reinterpret_cast<const uint2*>(row + size_t(ix) * ld));
+  }
+}
+
+template <bool REVERSE>
+__global__ void __launch_bounds__(128)
+dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                    __nv_bfloat16* __restrict__ y, const DwGeom g, int segs, int RY) {
+  MarchItem it;
+  if (!march_item(g, segs, RY, &it)) return;
+  float wr[9][kCpt];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const float4 w0 = *reinterpret_cast<const float4*>(w + (REVERSE ? 8 - k : k) * g.C + it.c0);
+    wr[k][0] = w0.x; wr[k][1] = w0.y; wr[k][2] = w0.z; wr[k][3] = w0.w;
+  }
+  float a0[4][kCpt], a1[4][kCpt], a2[4][kCpt];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int e = 0; e < kCpt; ++e) { a0[j][e] = 0.f; a1[j][e] = 0.f; a2[j][e] = 0.f; }
+  const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + it.c0;
+  __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + it.c0;
+  // input row iy adds to output rows iy+1 (ky=0), iy (ky=1), iy-1 (ky=2); then row iy-1 is complete
+  auto phase = [&](int iy, const uint2 (&rc)[6], uint2 (&rn)[6], float (&prev)[4][kCpt],
+                   float (&cur)[4][kCpt], float (&next)[4][kCpt]) {
+    if (iy + 1 <= it.oy1) march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);  // prefetch next row
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      float xv[kCpt];
+      dw_unpack4(rc[c], xv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int kx = c - j;
+        if (kx < 0 || kx > 2) continue;
+#pragma unroll
+        for (int e = 0; e < kCpt; ++e) {
+          next[j][e] = fmaf(xv[e], wr[0 + kx][e], next[j][e]);
+          cur[j][e] = fmaf(xv[e], wr[3 + kx][e], cur[j][e]);
+          prev[j][e] = fmaf(xv[e], wr[6 + kx][e], prev[j][e]);
+        }
+      }
+    }
+    const int oy = iy - 1;
+    if (oy >= it.oy0 && oy < it.oy1) {
+      __nv_bfloat16* orow = yout + size_t(oy) * g.W * g.ldy;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + size_t(it.ox0 + j) * g.ldy) = dw_pack4(prev[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < kCpt; ++e) prev[j][e] = 0.f;
+  };
+  uint2 rA[6], rB[6];
+  march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
+  for (int iy = it.oy0 - 1; iy <= it.oy1; iy += 6) {
+    phase(iy, rA, rB, a0, a1, a2);
+    if (iy + 1 <= it.oy1) phase(iy + 1, rB, rA, a1, a2, a0);
+    if (iy + 2 <= it.oy1) phase(iy + 2, rA, rB, a2, a0, a1);
+    if (iy + 3 <= it.oy1) phase(iy + 3, rB, rA, a0, a1, a2);
+    if (iy + 4 <= it.oy1) phase(iy + 4, rA, rB, a1, a2, a0);
+    if (iy + 5 <= it.oy1) phase(iy + 5, rB, rA, a2, a0, a1);
+  }
+}
+
+// dw[ky][kx][c] += sum dy[oy][ox] * x[oy+ky-1][ox+kx-1]; marching over input rows with the three
+// neighbouring dy rows kept (packed) in registers.  Rows of dy outside the segment count as zero.
+__global__ void __launch_bounds__(128)
+dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                      float* __restrict__ dw, const DwGeom g, int segs, int RY) {
+  extern __shared__ float sh[];  // [9][C]
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  MarchItem it;
+  if (march_item(g, segs, RY, &it)) {
+    float acc[9][kCpt];
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+#pragma unroll
+      for (int e = 0; e < kCpt; ++e) acc[k][e] = 0.f;
+    const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + it.c0;
+    const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + it.c0;
+    auto load_dy = [&](int oy, uint2 (&d)[4]) {
+      const bool ok = oy >= it.oy0 && oy < it.oy1;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        d[j] = make_uint2(0, 0);
+        if (ok && it.ox0 + j < g.W)
+          d[j] = __ldg(reinterpret_cast<const uint2*>(gin + (size_t(oy) * g.W + it.ox0 + j) * g.ldy));
+      }
+    };
+    // at input row iy: prev/cur/next = dy rows iy-1 / iy / iy+1 ; rn / dnn = prefetch for row iy+1
+    auto phase = [&](int iy, const uint2 (&rc)[6], uint2 (&rn)[6], const uint2 (&prev)[4], const uint2 (&cur)[4],
+                     const uint2 (&next)[4], uint2 (&dnn)[4]) {
+      if (iy + 1 <= it.oy1) {
+        march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);
+        load_dy(iy + 2, dnn);
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        float xv[kCpt];
+        dw_unpack4(rc[c], xv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int kx = c - j;
+          if (kx < 0 || kx > 2) continue;
+          float gp[kCpt], gc[kCpt], gn[kCpt];
+          dw_unpack4(prev[j], gp);  // oy = iy-1 -> ky = 2
+          dw_unpack4(cur[j], gc);   // oy = iy   -> ky = 1
+          dw_unpack4(next[j], gn);  // oy = iy+1 -> ky = 0
+#pragma unroll
+          for (int e = 0; e < kCpt; ++e) {
+            acc[0 + kx][e] = fmaf(gn[e], xv[e], acc[0 + kx][e]);
+            acc[3 + kx][e] = fmaf(gc[e], xv[e], acc[3 + kx][e]);
+            acc[6 + kx][e] = fmaf(gp[e], xv[e], acc[6 + kx][e]);
+          }
+        }
+      }
+    };
+    uint2 rA[6], rB[6], d0[4], d1[4], d2[4], d3[4];
+    march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
+    load_dy(it.oy0 - 2, d0);
+    load_dy(it.oy0 - 1, d1);
+    load_dy(it.oy0, d2);
+    for (int iy = it.oy0 - 1; iy <= it.oy1; iy += 4) {
+      phase(iy, rA, rB, d0, d1, d2, d3);
+      if (iy + 1 <= it.oy1) phase(iy + 1, rB, rA, d1, d2, d3, d0);
+      if (iy + 2 <= it.oy1) phase(iy + 2, rA, rB, d2, d3, d0, d1);
+      if (iy + 3 <= it.oy1) phase(iy + 3, rB, rA, d3, d0, d1, d2);
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+#pragma unroll
+      for (int e = 0; e < kCpt; ++e) atomicAdd(&sh[k * g.C + it.c0 + e], acc[k][e]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
+}
+
+// rows per segment so that the launch has >= ~200k threads (several resident 128-thread blocks per SM)
+static void march_plan(const DwGeom& g, int* segs, int* RY, unsigned* blocks) {
+  const long per_seg = long(g.N) * ((g.W + 3) / 4) * (g.C / kCpt);
+  long s = (200000 + per_seg - 1) / per_seg;
+  if (s < 1) s = 1;
+  long ry = (g.H + s - 1) / s;
+  if (ry < 6) ry = 6;
+  if (ry > g.H) ry = g.H;
+  *RY = int(ry);
+  *segs = int((g.H + ry - 1) / ry);
+  *blocks = unsigned((per_seg * *segs + 127) / 128);
+}
+
 static int ew_grid(long total) {
   long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
@@ -370,7 +573,12 @@ extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, co
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto Y = static_cast<__nv_bfloat16*>(y);
-  if (!launch_fwd_strip<false>(X, w, Y, g, st))
+  if (stride == 1 && dil == 1) {
+    int segs, RY;
+    unsigned blocks;
+    march_plan(g, &segs, &RY, &blocks);
+    dw_march_fwd_kernel<false><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY);
+  } else if (!launch_fwd_strip<false>(X, w, Y, g, st))
     dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, st>>>(X, w, Y, g);
   BGR_LAUNCH_OK();
   return BGR_OK;
@@ -389,7 +597,15 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
     DwGeom r = g;
     r.ldx = ldy;
     r.ldy = ldx;
-    done = launch_fwd_strip<true>(DY, w, DX, r, st);
+    if (dil == 1) {
+      int segs, RY;
+      unsigned blocks;
+      march_plan(r, &segs, &RY, &blocks);
+      dw_march_fwd_kernel<true><<<blocks, 128, 0, st>>>(DY, w, DX, r, segs, RY);
+      done = true;
+    } else {
+      done = launch_fwd_strip<true>(DY, w, DX, r, st);
+    }
   }
   if (!done) dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
   BGR_LAUNCH_OK();
@@ -426,7 +642,17 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto DY = static_cast<const __nv_bfloat16*>(dy);
   int rc = BGR_OK;
-  if (stride == 1 && dil == 1) rc = launch_wgrad_strip<1, 1>(X, DY, dw, g, st);
+  if (stride == 1 && dil == 1) {
+    static bool configured = false;
+    if (!configured) {
+      BGR_CUDA_OK(cudaFuncSetAttribute(dw_march_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      configured = true;
+    }
+    int segs, RY;
+    unsigned blocks;
+    march_plan(g, &segs, &RY, &blocks);
+    dw_march_wgrad_kernel<<<blocks, 128, 9 * C * sizeof(float), st>>>(X, DY, dw, g, segs, RY);
+  }
   else if (stride == 1 && dil == 2) rc = launch_wgrad_strip<1, 2>(X, DY, dw, g, st);
   else if (stride == 2 && dil == 1) rc = launch_wgrad_strip<2, 1>(X, DY, dw, g, st);
   else {

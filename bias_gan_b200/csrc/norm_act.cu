@@ -221,7 +221,7 @@ static int reduce_grid(long M, int C, int* rows_per_block) {
   const int G = C / 8;
   const int R = G >= 256 ? 1 : 256 / G;
   long blocks = (M + long(R) * 8 - 1) / (long(R) * 8);  // >= 8 row iterations per thread
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > 148 * 2) blocks = 148 * 2;  // two CTAs per SM: keeps the per-channel global atomics few
   if (blocks < 1) blocks = 1;
   *rows_per_block = int((M + blocks - 1) / blocks);
   return int((M + *rows_per_block - 1) / *rows_per_block);

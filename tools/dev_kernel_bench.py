@@ -1,0 +1,45 @@
+"""GPU micro-benchmark of the HBM-bound kernels at the trunk's dominant shapes (CUDA events,
+L2 flushed between iterations)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from bias_gan_b200 import kernels as K
+
+dev = torch.device("cuda")
+flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+
+def timeit(fn, n=5):
+    fn(); torch.cuda.synchronize()
+    ts = []
+    for _ in range(n):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return min(ts) * 1e3  # us
+
+
+for (N, H, W, C) in [(8, 384, 576, 128), (8, 192, 288, 256), (8, 96, 144, 728), (8, 48, 72, 728), (8, 48, 72, 1536)]:
+    x = torch.randn(N, H, W, C, device=dev).bfloat16()
+    g = torch.randn(N, H, W, C, device=dev).bfloat16()
+    w9 = torch.randn(9, C, device=dev)
+    nbytes = x.numel() * 2
+    rows = []
+    rows.append(("dw_fwd s1d1", timeit(lambda: K.dw_fwd(x, w9, 1, 1)), 2 * nbytes))
+    rows.append(("dw_fwd s1d2", timeit(lambda: K.dw_fwd(x, w9, 1, 2)), 2 * nbytes))
+    rows.append(("dw_fwd s2d1", timeit(lambda: K.dw_fwd(x, w9, 2, 1)), 1.25 * nbytes))
+    rows.append(("dw_dgrad s1d1", timeit(lambda: K.dw_dgrad(g, w9, 1, 1, tuple(x.shape))), 2 * nbytes))
+    rows.append(("dw_wgrad s1d1", timeit(lambda: K.dw_wgrad(x, g, 1, 1)), 2 * nbytes))
+    rows.append(("dw_wgrad s1d2", timeit(lambda: K.dw_wgrad(x, g, 1, 2)), 2 * nbytes))
+    sums = torch.empty(2 * C, dtype=torch.float64, device=dev)
+    rows.append(("bn_stats", timeit(lambda: K.bn_stats(x, sums)), nbytes))
+    a = torch.ones(C, device=dev); b = torch.zeros(C, device=dev)
+    out = torch.empty_like(x)
+    rows.append(("bn_apply act", timeit(lambda: K.bn_apply(x, a, b, act=True, out=out)), 2 * nbytes))
+    rows.append(("bn_apply act+res", timeit(lambda: K.bn_apply(x, a, b, res=g, act=True, out=out)), 3 * nbytes))
+    mean = torch.zeros(C, device=dev); inv = torch.ones(C, device=dev)
+    rows.append(("bn_backward (2 kernels)", timeit(lambda: K.bn_backward(g, out, x, mean, inv, a, act=True)), 7 * nbytes))
+    print("shape N%d %dx%d C%d  (%.1f MB per tensor)" % (N, H, W, C, nbytes / 1e6))
+    for name, us, by in rows:
+        print("   %-26s %9.1f us   %7.0f GB/s" % (name, us, by / us / 1e3))
