@@ -1,0 +1,80 @@
+"""Host-side data-parallel logic on CPU: world size 2, gloo backend.  Checks that
+the bucketed, hook-driven gradient all-reduce yields the mean of the per-rank gradients, that
+parameters are broadcast from rank 0, and metric_average's sum/average semantics
+(comm/distributed.py:12-34,195-199)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    from bias_gan_b200.comm import comm as Comm
+    cm = Comm(backend="gloo")
+    try:
+        assert cm.size() == world and cm.rank() == rank
+        torch.manual_seed(100 + rank)  # different init per rank: broadcast must equalise
+        model = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.Tanh(), torch.nn.Linear(32, 8),
+                                    torch.nn.Linear(8, 1))
+        cm.DistributedModel(model, bucket_mb=0)  # tiny buckets: one per parameter, exercised from hooks
+        ref = [p.detach().clone() for p in model.parameters()]
+        gathered = [torch.zeros_like(ref[0]) for _ in range(world)]
+        dist.all_gather(gathered, ref[0])
+        assert torch.equal(gathered[0], gathered[1]), "parameters were not broadcast from rank 0"
+        torch.manual_seed(7 + rank)
+        x = torch.randn(4, 16)
+        loss = model(x).pow(2).mean()
+        local = torch.autograd.grad(loss, list(model.parameters()), retain_graph=True)
+        loss.backward()
+        model.grad_sync.finish()
+        for p, g in zip(model.parameters(), local):
+            parts = [torch.zeros_like(g) for _ in range(world)]
+            dist.all_gather(parts, g.contiguous())
+            torch.testing.assert_close(p.grad, sum(parts) / world, rtol=1e-6, atol=1e-7)
+        # second backward re-arms the buckets
+        model.zero_grad()
+        model(x).sum().backward()
+        model.grad_sync.finish()
+        assert all(p.grad is not None for p in model.parameters())
+        s = cm.metric_average(torch.tensor(float(rank + 1)))
+        a = cm.metric_average(torch.tensor(float(rank + 1)), op_name="average")
+        assert s == 3.0 and a == 1.5
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        q.put((rank, repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+def test_bucketed_allreduce_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=150) for _ in procs]
+    for p in procs:
+        p.join(timeout=30)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], res
+
+
+def test_dummy_mode_single_process():
+    from bias_gan_b200.comm import comm as Comm
+    cm = Comm(mode="dummy")
+    assert cm.size() == 1 and cm.rank() == 0
+    assert cm.metric_average(torch.tensor(2.5)) == 2.5
