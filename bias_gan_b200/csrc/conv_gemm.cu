@@ -27,51 +27,92 @@ struct ConvParams {
   int tiles_x, tiles_y;
   int ntaps, kblocks;       // taps and 64-channel blocks per tap
   int Cout, Cin, ld_out;    // valid channels, output row stride (elements)
+  int m_tiles, n_tiles;     // fprop only: pixel tiles, Cout tiles
   int chunks_per_split;     // wgrad only
   int total_chunks;         // wgrad only
   int dy[kMaxTaps], dx[kMaxTaps];
 };
 
 // ------------------------------------------------------------------------------------------
-// fprop: grid = (pixel tiles, Cout tiles), 192 threads: warp0 = TMA, warp1 = MMA, warps2-5 = epilogue
+// fprop: persistent, one CTA per SM, tiles (pixel tile, Cout tile) round-robin with the Cout
+// tile fastest (neighbouring CTAs share the activation tile through L2).  192 threads:
+//   warp 0    TMA producer   (smem ring of STAGES x {A 128x64, B BLOCK_Nx64}, runs across tiles)
+//   warp 1    tcgen05.mma issuer, accumulators double-buffered in TMEM (2 x BLOCK_N columns)
+//   warps 2-5 epilogue: tcgen05.ld -> (+bias) -> bf16 -> 128B-swizzled smem -> TMA store in
+//             64-channel chunks (two staging buffers), overlapped with the next tile's MMAs.
+//             Optional fused BatchNorm statistics: per-channel sum / sum-of-squares of the
+//             bf16-rounded outputs by a lane-transposing butterfly, smem atomics, then one fp64
+//             global atomic per channel and tile.
 // ------------------------------------------------------------------------------------------
-template <int BLOCK_N, int STAGES>
+// Sum v[0..31] over the 32 lanes of a warp: lane l ends with column l's total in v[0].
+__device__ __forceinline__ void warp_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < n / 2; ++i) {
+      const float send = upper ? v[i] : v[i + n / 2];
+      const float keep = upper ? v[i + n / 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+}
+
+template <int BLOCK_N, int STAGES, bool STATS>
 __global__ void __launch_bounds__(192, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  __nv_bfloat16* __restrict__ out, const float* __restrict__ bias,
-                  const __grid_constant__ ConvParams p) {
+                  const __grid_constant__ CUtensorMap tmO, const float* __restrict__ bias,
+                  double* __restrict__ stats, const __grid_constant__ ConvParams p) {
   constexpr uint32_t A_BYTES = kBlockM * kBlockK * 2;
   constexpr uint32_t B_BYTES = BLOCK_N * kBlockK * 2;
+  constexpr uint32_t O_BYTES = kBlockM * 64 * 2;       // one 64-channel output chunk
+  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;
+  constexpr uint32_t NEEDED = STAGES * (A_BYTES + B_BYTES) + 2 * O_BYTES + 2 * BLOCK_N * 4 +
+                              (2 * STAGES + 4) * 8 + 16;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
+  if (threadIdx.x == 0 && (smem - smem_raw) + NEEDED > dynamic_smem_size()) {
+    printf("bgr: conv_fprop shared memory window too small\n");
+    __trap();
+  }
   uint8_t* sA = smem;
-  uint8_t* sB = smem + STAGES * A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
+  uint8_t* sB = sA + STAGES * A_BYTES;
+  uint8_t* sO = sB + STAGES * B_BYTES;
+  float* s_stats = reinterpret_cast<float*>(sO + 2 * O_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(s_stats + 2 * BLOCK_N);
   uint64_t* empty = full + STAGES;
-  uint64_t* tmem_full = empty + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tfull = empty + STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tile = blockIdx.x;
-  const int tx = tile % p.tiles_x;
-  const int ty = (tile / p.tiles_x) % p.tiles_y;
-  const int n = tile / (p.tiles_x * p.tiles_y);
-  const int n0 = blockIdx.y * BLOCK_N;
-  const int x0 = tx * p.BW, y0 = ty * p.BH;
   const int iters = p.ntaps * p.kblocks;
+  // gridDim.x is a multiple of n_tiles: this CTA keeps one Cout tile (so its BatchNorm partial sums
+  // stay in shared memory for the whole kernel) and strides over the pixel tiles; the n_tiles CTAs
+  // of one group work on the same activation tile at the same time (shared through L2).
+  const int nt = blockIdx.x % p.n_tiles;
+  const int mt_first = blockIdx.x / p.n_tiles, mt_step = gridDim.x / p.n_tiles;
+  const int n0 = nt * BLOCK_N;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tfull[b], 1);
+      mbar_init(&tempty[b], 4);
+    }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<BLOCK_N>(tmem_slot);
+  if (STATS) {
+    for (int i = threadIdx.x; i < 2 * BLOCK_N; i += blockDim.x) s_stats[i] = 0.f;
+  }
+  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -79,73 +120,147 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int it = 0; it < iters; ++it) {
-        const int s = it % STAGES;
-        const uint32_t ph = (it / STAGES) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        const int t = it / p.kblocks, kb = it - t * p.kblocks;
-        mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
-        tma_load_5d(sA + s * A_BYTES, &tmA, &full[s], kb * kBlockK, 0, x0 + p.dx[t],
-                    y0 + p.dy[t], n);
-        tma_load_3d(sB + s * B_BYTES, &tmB, &full[s], kb * kBlockK, t, n0);
+      uint32_t it = 0;
+      for (int mt = mt_first; mt < p.m_tiles; mt += mt_step) {
+        const int tx = mt % p.tiles_x;
+        const int ty = (mt / p.tiles_x) % p.tiles_y;
+        const int n = mt / (p.tiles_x * p.tiles_y);
+        const int x0 = tx * p.BW, y0 = ty * p.BH;
+        for (int t = 0; t < p.ntaps; ++t) {
+          for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+            const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+            mbar_wait(&empty[s], ph ^ 1);
+            mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
+            tma_load_5d(sA + s * A_BYTES, &tmA, &full[s], kb * kBlockK, 0, x0 + p.dx[t],
+                        y0 + p.dy[t], n);
+            tma_load_3d(sB + s * B_BYTES, &tmB, &full[s], kb * kBlockK, t, n0);
+          }
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
-      for (int it = 0; it < iters; ++it) {
-        const int s = it % STAGES;
-        const uint32_t ph = (it / STAGES) & 1;
-        mbar_wait(&full[s], ph);
+      uint32_t it = 0, lt = 0;
+      for (int mt = mt_first; mt < p.m_tiles; mt += mt_step, ++lt) {
+        const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+        mbar_wait(&tempty[acc], aph ^ 1);
         tc_fence_after();
-        const uint64_t da = umma_desc_sw128(smem_u32(sA + s * A_BYTES), 16, 1024);
-        const uint64_t db = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
+        const uint32_t d = tmem + acc * BLOCK_N;
+        for (int i = 0; i < iters; ++i, ++it) {
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint64_t da = umma_desc_sw128(smem_u32(sA + s * A_BYTES), 16, 1024);
+          const uint64_t db = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
 #pragma unroll
-        for (int k = 0; k < kBlockK / 16; ++k)
-          umma_bf16(tmem, da + uint64_t(k * 2), db + uint64_t(k * 2), idesc, (it | k) != 0);
-        umma_commit(&empty[s]);
+          for (int k = 0; k < kBlockK / 16; ++k)
+            umma_bf16(d, da + uint64_t(k * 2), db + uint64_t(k * 2), idesc, (i | k) != 0);
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&tfull[acc]);
       }
-      umma_commit(tmem_full);
     }
   } else {
-    const int q = warp & 3;  // TMEM lane quadrant this warp may access
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    const int row = q * 32 + lane;
-    const int y = y0 + row / p.BW, x = x0 + row % p.BW;
-    const bool row_ok = (y < p.H) && (x < p.W);
-    __nv_bfloat16* orow = out + (size_t(size_t(n) * p.H + y) * p.W + x) * p.ld_out + n0;
-#pragma unroll 1
-    for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
-      uint32_t v[16];
-      tmem_ld16(tmem + (uint32_t(q * 32) << 16) + c0, v);
-      tmem_ld_wait();
-      if (row_ok) {
+    const int q = warp & 3;                  // TMEM lane quadrant this warp may access
+    const int row = q * 32 + lane;           // tile row = pixel (row % BW, row / BW) of the rectangle
+    const int epi_tid = threadIdx.x - 64;    // 0..127
+    const int ly = row / p.BW, lx = row - ly * p.BW;
+    uint8_t* my_row = nullptr;
+    uint32_t lt = 0, chunk_ctr = 0;
+    // BatchNorm partial sums of this CTA's Cout tile: lane l keeps channels c*64 + h*32 + l
+    float st_sum[BLOCK_N / 32], st_sq[BLOCK_N / 32];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int c = c0 + h * 8;
-          if (n0 + c < p.Cout) {
-            float f[8];
+    for (int i = 0; i < BLOCK_N / 32; ++i) st_sum[i] = st_sq[i] = 0.f;
+    for (int mt = mt_first; mt < p.m_tiles; mt += mt_step, ++lt) {
+      const int tx = mt % p.tiles_x;
+      const int ty = (mt / p.tiles_x) % p.tiles_y;
+      const int n = mt / (p.tiles_x * p.tiles_y);
+      const int x0 = tx * p.BW, y0 = ty * p.BH;
+      const bool row_ok = (y0 + ly < p.H) && (x0 + lx < p.W);
+      const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+      mbar_wait(&tfull[acc], aph);
+      tc_fence_after();
 #pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[h * 8 + j]);
-            if (bias != nullptr) {
+      for (int c = 0; c < BLOCK_N / 64; ++c) {
+        const int ch0 = n0 + c * 64;
+        if (ch0 >= p.Cout) break;
+        uint8_t* buf = sO + (chunk_ctr & 1) * O_BYTES;
+        if (epi_tid == 0) bulk_wait_group_read<1>();   // the store issued two chunks ago has left smem
+        named_bar_sync(1, 128);
+        uint32_t v[64];
+        const uint32_t taddr = tmem + (uint32_t(q * 32) << 16) + acc * BLOCK_N + c * 64;
+        tmem_ld32(taddr, v);
+        tmem_ld32(taddr + 32, v + 32);
+        tmem_ld_wait();
+        if (bias != nullptr) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) f[j] += __ldg(bias + n0 + c + j);
-            }
-            uint4 o;
-            o.x = pack_bf16(f[0], f[1]);
-            o.y = pack_bf16(f[2], f[3]);
-            o.z = pack_bf16(f[4], f[5]);
-            o.w = pack_bf16(f[6], f[7]);
-            *reinterpret_cast<uint4*>(orow + c) = o;
+          for (int j = 0; j < 64; ++j)
+            if (ch0 + j < p.Cout) v[j] = __float_as_uint(__uint_as_float(v[j]) + __ldg(bias + ch0 + j));
+        }
+        my_row = buf + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          uint4 o;
+          o.x = pack_bf16(__uint_as_float(v[j * 8 + 0]), __uint_as_float(v[j * 8 + 1]));
+          o.y = pack_bf16(__uint_as_float(v[j * 8 + 2]), __uint_as_float(v[j * 8 + 3]));
+          o.z = pack_bf16(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5]));
+          o.w = pack_bf16(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7]));
+          *reinterpret_cast<uint4*>(my_row + ((j ^ (row & 7)) << 4)) = o;
+          if (STATS) {  // keep the rounded values for the statistics
+            v[j * 8 + 0] = o.x << 16; v[j * 8 + 1] = o.x & 0xffff0000u;
+            v[j * 8 + 2] = o.y << 16; v[j * 8 + 3] = o.y & 0xffff0000u;
+            v[j * 8 + 4] = o.z << 16; v[j * 8 + 5] = o.z & 0xffff0000u;
+            v[j * 8 + 6] = o.w << 16; v[j * 8 + 7] = o.w & 0xffff0000u;
           }
+        }
+        fence_proxy_async();
+        named_bar_sync(1, 128);
+        if (epi_tid == 0) {
+          tma_store_5d(&tmO, buf, ch0, 0, x0, y0, n);
+          bulk_commit_group();
+        }
+        if (STATS) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            float a[32], b[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float f = row_ok ? __uint_as_float(v[h * 32 + j]) : 0.f;
+              a[j] = f;
+              b[j] = f * f;
+            }
+            warp_transpose_reduce32(a, lane);
+            warp_transpose_reduce32(b, lane);
+            st_sum[c * 2 + h] += a[0];
+            st_sq[c * 2 + h] += b[0];
+          }
+        }
+        ++chunk_ctr;
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+    }
+    if (STATS) {  // combine the four warps in shared memory, then one fp64 atomic per channel and CTA
+#pragma unroll
+      for (int i = 0; i < BLOCK_N / 32; ++i) {
+        atomicAdd(&s_stats[i * 32 + lane], st_sum[i]);
+        atomicAdd(&s_stats[BLOCK_N + i * 32 + lane], st_sq[i]);
+      }
+      named_bar_sync(2, 128);
+      for (int i = epi_tid; i < BLOCK_N; i += 128) {
+        if (n0 + i < p.Cout) {
+          atomicAdd(stats + n0 + i, double(s_stats[i]));
+          atomicAdd(stats + p.Cout + n0 + i, double(s_stats[BLOCK_N + i]));
         }
       }
     }
+    if (epi_tid == 0) bulk_wait_group_read<0>();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<BLOCK_N>(tmem);
+  if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -248,8 +363,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
         tmem_ld_wait();
         if (co < p.Cout) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (n0 + c0 + j < p.Cin) atomicAdd(drow + c0 + j, __uint_as_float(v[j]));
+          for (int j = 0; j < 16; j += 4)   // Cin % 8 == 0: a group of 4 is entirely in or out
+            if (n0 + c0 + j < p.Cin)
+              red_add_v4(drow + c0 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                         __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
         }
       }
     }
@@ -298,19 +415,38 @@ static int check_conv_args(const void* x, const void* w, const void* y, int Cin,
   return BGR_OK;
 }
 
-template <int BLOCK_N, int STAGES>
-static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, void* y, const float* bias,
-                        const ConvParams& p, cudaStream_t st) {
-  constexpr size_t smem = size_t(STAGES) * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) +
-                          (2 * STAGES + 1) * 8 + 16 + 1024;
-  auto kern = conv_fprop_kernel<BLOCK_N, STAGES>;
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+constexpr size_t kMaxDynSmem = 232448;  // 227 KB per CTA on sm_100
+
+template <int BLOCK_N, int STAGES, bool STATS>
+static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
+                        const float* bias, double* stats, const ConvParams& p, cudaStream_t st) {
+  constexpr size_t needed = size_t(STAGES) * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) +
+                            2 * (kBlockM * 64 * 2) + 2 * BLOCK_N * 4 + (2 * STAGES + 4) * 8 + 16;
+  // the kernel aligns its window to 1024 B itself and traps if the slack does not suffice
+  constexpr size_t smem = needed + 1024 > kMaxDynSmem ? kMaxDynSmem : needed + 1024;
+  static_assert(needed <= kMaxDynSmem, "fprop stage ring does not fit");
+  auto kern = conv_fprop_kernel<BLOCK_N, STAGES, STATS>;
   static bool configured = false;
   if (!configured) {
     BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     configured = true;
   }
-  dim3 grid(p.N * p.tiles_x * p.tiles_y, (p.Cout + BLOCK_N - 1) / BLOCK_N);
-  kern<<<grid, 192, smem, st>>>(tmA, tmB, reinterpret_cast<__nv_bfloat16*>(y), bias, p);
+  int groups = sm_count() / p.n_tiles;   // CTAs per Cout tile
+  if (groups < 1) groups = 1;            // more Cout tiles than SMs: the surplus CTAs queue
+  if (groups > p.m_tiles) groups = p.m_tiles;
+  dim3 grid(groups * p.n_tiles);
+  kern<<<grid, 192, smem, st>>>(tmA, tmB, tmO, bias, stats, p);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -327,10 +463,20 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* 
     configured = true;
   }
   const int tiles = ((p.Cout + kBlockM - 1) / kBlockM) * ((p.Cin + BLOCK_N - 1) / BLOCK_N) * p.ntaps;
-  // split the pixel reduction so that the grid covers the 148 SMs about twice
-  int splits = (2 * 148 + tiles - 1) / tiles;
-  if (splits > p.total_chunks) splits = p.total_chunks;
-  if (splits < 1) splits = 1;
+  // Split the pixel reduction over `splits` CTAs per tile.  Every split costs a prologue and a
+  // Cout x Cin pass of fp32 reductions through L2 (about 32 chunks' worth of MMA time), and the
+  // grid runs in rounds of one CTA per SM: take the split count with the cheapest schedule.
+  const int sms = sm_count();
+  int splits = 1;
+  long best = -1;
+  for (int sp = 1; sp <= 64 && sp <= p.total_chunks; ++sp) {
+    const long rounds = (long(tiles) * sp + sms - 1) / sms;
+    const long cost = rounds * ((p.total_chunks + sp - 1) / sp + 32);
+    if (best < 0 || cost < best) {
+      best = cost;
+      splits = sp;
+    }
+  }
   p.chunks_per_split = (p.total_chunks + splits - 1) / splits;
   splits = (p.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
   dim3 grid(tiles, splits);
@@ -343,31 +489,61 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* 
 
 using namespace bgr;
 
+static int g_force_block_n = 0;
+extern "C" void bgr_debug_conv_block_n(int bn) { g_force_block_n = bn; }
+
+// Cout tile width: 256 halves the activation re-reads and the shared-memory operand traffic per
+// FLOP, 128 quantises better onto the SMs; compare the number of SM rounds each needs.
+static int pick_block_n(int m_tiles, int Cout) {
+  if (Cout <= 64) return 64;
+  if (Cout <= 128) return 128;
+  if (g_force_block_n == 128 || g_force_block_n == 256) return g_force_block_n;
+  const int sms = sm_count();
+  auto rounds = [&](int n_tiles) {
+    const int groups = sms / n_tiles > 0 ? sms / n_tiles : 1;
+    return long((m_tiles + groups - 1) / groups);
+  };
+  const long r128 = rounds((Cout + 127) / 128), r256 = rounds((Cout + 255) / 256);
+  return (r256 * 18 <= r128 * 10) ? 256 : 128;
+}
+
 extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w,
-                              int Cout, int ntaps, const int* dy, const int* dx, void* y, int ldy,
-                              const float* bias, void* stream) {
+                              int ldw, int Cout, int ntaps, const int* dy, const int* dx, void* y,
+                              int ldy, const float* bias, double* bn_sums, void* stream) {
   if (int rc = check_conv_args(x, w, y, Cin, ldx, Cout, ldy, ntaps)) return rc;
+  if (ldw < Cin || (ldw % 8)) return fail(BGR_ERR_ARG, "conv: ldw must be >= Cin and a multiple of 8");
   ConvParams p{};
   p.N = N; p.H = H; p.W = W;
   pick_rect(H, W, kBlockM, &p.BW, &p.BH);
   p.tiles_x = (W + p.BW - 1) / p.BW;
   p.tiles_y = (H + p.BH - 1) / p.BH;
+  p.m_tiles = N * p.tiles_x * p.tiles_y;
   p.ntaps = ntaps;
   p.kblocks = (Cin + kBlockK - 1) / kBlockK;
   p.Cout = Cout; p.Cin = Cin; p.ld_out = ldy;
   for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
-  CUtensorMap tmA, tmB;
+  const int bn = pick_block_n(p.m_tiles, Cout);
+  p.n_tiles = (Cout + bn - 1) / bn;
+  CUtensorMap tmA, tmB, tmO;
   if (int rc = make_act_map(&tmA, x, N, H, W, Cin, ldx, p.BW, p.BH)) return rc;
-  const int bn = Cout <= 64 ? 64 : 128;
+  if (int rc = make_act_map(&tmO, y, N, H, W, Cout, ldy, p.BW, p.BH)) return rc;
   {
     uint64_t dims[3] = {uint64_t(Cin), uint64_t(ntaps), uint64_t(Cout)};
-    uint64_t strides[2] = {uint64_t(Cin) * 2, uint64_t(Cin) * ntaps * 2};
+    uint64_t strides[2] = {uint64_t(ldw) * 2, uint64_t(ldw) * ntaps * 2};
     uint32_t box[3] = {64, 1, uint32_t(bn)};
     if (int rc = encode_tmap_bf16(&tmB, w, 3, dims, strides, box)) return rc;
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (bn == 64) return launch_fprop<64, 6>(tmA, tmB, y, bias, p, st);
-  return launch_fprop<128, 6>(tmA, tmB, y, bias, p, st);
+  if (bn_sums != nullptr) {
+    if (bias != nullptr) return fail(BGR_ERR_ARG, "conv: fused BatchNorm statistics exclude a bias");
+    BGR_CUDA_OK(cudaMemsetAsync(bn_sums, 0, sizeof(double) * 2 * Cout, st));
+    if (bn == 64) return launch_fprop<64, 6, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
+    if (bn == 128) return launch_fprop<128, 6, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
+    return launch_fprop<256, 4, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
+  }
+  if (bn == 64) return launch_fprop<64, 6, false>(tmA, tmB, tmO, bias, nullptr, p, st);
+  if (bn == 128) return launch_fprop<128, 6, false>(tmA, tmB, tmO, bias, nullptr, p, st);
+  return launch_fprop<256, 4, false>(tmA, tmB, tmO, bias, nullptr, p, st);
 }
 
 extern "C" int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx,
@@ -388,5 +564,9 @@ extern "C" int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int l
   if (int rc = make_act_map(&tmX, x, N, H, W, Cin, ldx, p.BW, p.BH)) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (Cin <= 64) return launch_wgrad<64, 6>(tmDY, tmX, dw, p, st);
+  // Cin tile 256 halves the shared-memory operand traffic per FLOP; weigh it against the padding
+  const int pad128 = (Cin + 127) / 128 * 128, pad256 = (Cin + 255) / 256 * 256;
+  const bool wide = g_force_block_n ? g_force_block_n == 256 : (Cin > 128 && pad256 * 13 <= pad128 * 20);
+  if (wide) return launch_wgrad<256, 4>(tmDY, tmX, dw, p, st);
   return launch_wgrad<128, 6>(tmDY, tmX, dw, p, st);
 }

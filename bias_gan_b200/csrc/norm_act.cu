@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ out,
                      int ldo, const __nv_bfloat16* __restrict__ x, int ldx,
                      const float* __restrict__ mean, const float* __restrict__ invstd,
-                     __nv_bfloat16* __restrict__ dyh, long M, int C, int rows_per_block, float slope,
+                     __nv_bfloat16* __restrict__ dyh, int ldd, long M, int C, int rows_per_block, float slope,
                      double* __restrict__ sums /* [2][C] */) {
   extern __shared__ float sh[];
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
@@ -161,7 +161,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
         s1[j] += d;
         s2[j] += d * (xv[j] - mu[j]) * is[j];
       }
-      *reinterpret_cast<uint4*>(dyh + row * C + gi * 8) = pack8(gv);
+      *reinterpret_cast<uint4*>(dyh + row * ldd + gi * 8) = pack8(gv);
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -196,7 +196,8 @@ __device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
 
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* __restrict__ x, int ldx,
-                    const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, long M, int C) {
+                    const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, int ldd, long M,
+                    int C) {
   const int G = C >> 3;
   const long total = M * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -204,7 +205,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* 
     const int g = int(i % G);
     const long row = i / G;
     float d[8], xv[8], c0[8], k1[8], k2[8], mu[8], is[8];
-    unpack8(*reinterpret_cast<const uint4*>(dyh + row * C + g * 8), d);
+    unpack8(*reinterpret_cast<const uint4*>(dyh + row * ldd + g * 8), d);
     unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + g * 8), xv);
     load8f(coef + g * 8, c0);
     load8f(coef + C + g * 8, k1);
@@ -213,7 +214,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* 
     load8f(coef + 4 * C + g * 8, is);
 #pragma unroll
     for (int j = 0; j < 8; ++j) d[j] = c0[j] * (d[j] - k1[j] - (xv[j] - mu[j]) * is[j] * k2[j]);
-    *reinterpret_cast<uint4*>(dx + row * C + g * 8) = pack8(d);
+    *reinterpret_cast<uint4*>(dx + row * ldd + g * 8) = pack8(d);
   }
 }
 
@@ -278,7 +279,7 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
 
 extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
                                const float* mean, const float* invstd, const float* gamma, int act,
-                               float slope, long M, int C, void* dyh, void* dx, double* sums,
+                               float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
                                float* coef_ws, void* stream) {
   BGR_CHECK_C8(C);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -289,13 +290,13 @@ extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo,
   auto O = static_cast<const __nv_bfloat16*>(out);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto D = static_cast<__nv_bfloat16*>(dyh);
-  if (act) bn_bwd_reduce_kernel<true><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
-  else bn_bwd_reduce_kernel<false><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, M, C, rpb, slope, sums);
+  if (act) bn_bwd_reduce_kernel<true><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  else bn_bwd_reduce_kernel<false><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
   BGR_LAUNCH_OK();
   bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
   BGR_LAUNCH_OK();
   bn_bwd_apply_kernel<<<elementwise_grid(M * (C / 8)), 256, 0, st>>>(D, X, ldx, coef_ws,
-                                                                    static_cast<__nv_bfloat16*>(dx), M, C);
+                                                                    static_cast<__nv_bfloat16*>(dx), ldd, M, C);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

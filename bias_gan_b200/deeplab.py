@@ -31,9 +31,10 @@ class SeparableConv2d_same(nn.Module):
         self.pointwise = _hold_conv(inplanes, planes, 1)
         self.stride, self.dilation = stride, dilation
 
-    def forward(self, x):
+    def forward(self, x, want_stats=False):
+        """want_stats=True returns (y, sums): the BatchNorm sums of y from the 1x1 conv's epilogue."""
         x = F_.depthwise3x3(x, self.conv1.weight, self.stride, self.dilation)
-        return F_.conv2d(x, self.pointwise.weight)
+        return F_.conv2d(x, self.pointwise.weight, want_stats=want_stats)
 
 
 class Block(nn.Module):
@@ -80,8 +81,9 @@ class Block(nn.Module):
                 if pending is not None:  # BN followed directly by a conv: no activation between
                     x = F_.bn_act(pending[0], pending[1], act=False)
                     pending = None
-                y = m(x)
-                if i + 1 < len(mods) and isinstance(mods[i + 1], nn.BatchNorm2d):
+                has_bn = i + 1 < len(mods) and isinstance(mods[i + 1], nn.BatchNorm2d)
+                y = m(x, want_stats=has_bn and mods[i + 1].training)
+                if has_bn:
                     pending = (y, mods[i + 1])
                     i += 2
                     # is this BN followed by the (identity-held) relu?
@@ -96,7 +98,7 @@ class Block(nn.Module):
             tail_bn = pending  # last rep element is a BN: fuse with the residual add
         if self.skip is not None:
             s_in = F_.subsample2(a) if self.stride == 2 else a
-            s = F_.conv2d(s_in, self.skip.weight)
+            s = F_.conv2d(s_in, self.skip.weight, want_stats=self.skipbn.training)
             if tail_bn is not None:
                 x = F_.bn_act(tail_bn[0], tail_bn[1], act=False)
             return F_.bn_act(s, self.skipbn, res=x, act=act_out)
@@ -150,8 +152,8 @@ class Xception(nn.Module):
         """field: bf16 [N, H/2, W/2, 4*inplanes] (2x2 space-to-depth).  Returns (features
         [N,H/16,W/16,2048], low_level [N,H/4,W/4,128]) — both activated, as the reference's
         in-place LeakyReLUs leave them."""
-        x = F_.bn_act(F_.conv_s2d(field, self.conv1.weight), self.bn1, act=True)
-        x = F_.bn_act(F_.conv2d(x, self.conv2.weight), self.bn2, act=True)
+        x = F_.bn_act(F_.conv_s2d(field, self.conv1.weight, self.bn1.training), self.bn1, act=True)
+        x = F_.bn_act(F_.conv2d(x, self.conv2.weight, want_stats=self.bn2.training), self.bn2, act=True)
         x = self.block1(x, act_out=True)
         low = x
         x = self.block2(x, act_out=True)
@@ -159,9 +161,9 @@ class Xception(nn.Module):
         for i in range(4, 20):
             x = getattr(self, "block%d" % i)(x, act_out=True)
         x = self.block20(x, act_out=False)
-        x = F_.bn_act(self.conv3(x), self.bn3, act=True)
-        x = F_.bn_act(self.conv4(x), self.bn4, act=True)
-        x = F_.bn_act(self.conv5(x), self.bn5, act=True)
+        x = F_.bn_act(self.conv3(x, self.bn3.training), self.bn3, act=True)
+        x = F_.bn_act(self.conv4(x, self.bn4.training), self.bn4, act=True)
+        x = F_.bn_act(self.conv5(x, self.bn5.training), self.bn5, act=True)
         return x, low
 
 
@@ -190,7 +192,8 @@ class ASPP_module(nn.Module):
         nn.init.kaiming_normal_(self.atrous_convolution.weight)
 
     def forward(self, x):
-        return F_.bn_act(F_.conv2d(x, self.atrous_convolution.weight, dilation=self.rate), self.bn, act=True)
+        return F_.bn_act(F_.conv2d(x, self.atrous_convolution.weight, dilation=self.rate,
+                                   want_stats=self.bn.training), self.bn, act=True)
 
 
 class InterpolationUpsampler(nn.Module):
@@ -207,8 +210,8 @@ class InterpolationUpsampler(nn.Module):
         x = F_.bilinear(x, int(math.ceil(H / 4)), int(math.ceil(W / 4)))
         x = torch.cat((x, low_level_features), dim=3)
         lc = self.last_conv
-        x = F_.bn_act(F_.conv2d(x, lc[0].weight), lc[1], act=True)
-        x = F_.bn_act(F_.conv2d(x, lc[3].weight), lc[4], act=True)
+        x = F_.bn_act(F_.conv2d(x, lc[0].weight, want_stats=lc[1].training), lc[1], act=True)
+        x = F_.bn_act(F_.conv2d(x, lc[3].weight, want_stats=lc[4].training), lc[4], act=True)
         x = F_.conv2d(x, lc[6].weight, lc[6].bias)
         return F_.bilinear(x, H, W, s2d=True)
 
@@ -245,11 +248,11 @@ class DeepLabv3_plus(nn.Module):
         h, w = x.shape[1], x.shape[2]
         x1, x2, x3, x4 = self.aspp1(x), self.aspp2(x), self.aspp3(x), self.aspp4(x)
         gp = self.global_avg_pool
-        x5 = F_.bn_act(F_.conv2d(F_.global_avg_pool(x), gp[1].weight), gp[2], act=True)
+        x5 = F_.bn_act(F_.conv2d(F_.global_avg_pool(x), gp[1].weight, want_stats=gp[2].training), gp[2], act=True)
         x5 = F_.bilinear(x5, h, w)
         x = torch.cat((x1, x2, x3, x4, x5), dim=3)
-        x = F_.bn_act(F_.conv2d(x, self.conv1.weight), self.bn1, act=True)
-        low = F_.bn_act(F_.conv2d(low, self.conv2.weight), self.bn2, act=True)
+        x = F_.bn_act(F_.conv2d(x, self.conv1.weight, want_stats=self.bn1.training), self.bn1, act=True)
+        low = F_.bn_act(F_.conv2d(low, self.conv2.weight, want_stats=self.bn2.training), self.bn2, act=True)
         return self.upsample(x, low, H, W)
 
     def freeze_bn(self):

@@ -13,38 +13,47 @@ SLOPE = 0.2  # nn.LeakyReLU(0.2) everywhere in the reference (deeplab.py:100,180
 
 
 def _bf16c(t):
-    return t if (t.dtype == torch.bfloat16 and t.is_contiguous()) else t.to(torch.bfloat16).contiguous()
+    """Incoming gradient as a bf16 activation view (padded pixel strides are kept as they are)."""
+    return t if K.is_act_view(t) else t.to(torch.bfloat16).contiguous()
 
 
 class _Conv(torch.autograd.Function):
     """Dense conv (1x1 / 3x3 / atrous, stride 1) as tcgen05 implicit GEMM."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, dil):
+    def forward(ctx, x, weight, bias, dil, want_stats):
         ks = weight.shape[-1]
         dy, dx = K.taps_for(ks, dil)
         ctx.save_for_backward(x, weight)
         ctx.taps = (dy, dx)
         ctx.has_bias = bias is not None
-        return K.conv_fprop(x, L.gemm_weight(weight), dy, dx, bias=bias)
+        sums = None
+        if want_stats:  # BatchNorm statistics of y from the conv epilogue (no second pass over y)
+            sums = torch.empty(2 * weight.shape[0], dtype=torch.float64, device=x.device)
+        y = K.conv_fprop(x, L.cached(weight, "gemm", L.gemm_weight), dy, dx, bias=bias, bn_sums=sums)
+        if want_stats:
+            ctx.mark_non_differentiable(sums)
+            return y, sums
+        return y
 
     @staticmethod
-    def backward(ctx, g):
+    def backward(ctx, g, *unused):
         x, weight = ctx.saved_tensors
         dy, dx = ctx.taps
         g = _bf16c(g)
         gx = gw = gb = None
         if ctx.needs_input_grad[0]:
-            gx = K.conv_fprop(g, L.gemm_weight_t(weight), [-v for v in dy], [-v for v in dx])
+            gx = K.conv_fprop(g, L.cached(weight, "gemm_t", L.gemm_weight_t), [-v for v in dy], [-v for v in dx])
         if ctx.needs_input_grad[1]:
             gw = L.from_gemm_grad(K.conv_wgrad(x, g, dy, dx), weight.shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = K.bn_stats(g)[: g.shape[-1]].float()
-        return gx, gw, gb, None
+        return gx, gw, gb, None, None
 
 
-def conv2d(x, weight, bias=None, dilation=1):
-    return _Conv.apply(x, weight, bias, dilation)
+def conv2d(x, weight, bias=None, dilation=1, want_stats=False):
+    """want_stats=True returns (y, sums) with the fp64 [2*Cout] BatchNorm sums of y."""
+    return _Conv.apply(x, weight, bias, dilation, want_stats)
 
 
 class _ConvS2D(torch.autograd.Function):
@@ -52,33 +61,40 @@ class _ConvS2D(torch.autograd.Function):
     blocks: a 2x2-tap stride-1 implicit GEMM with K = 4 taps x 4*C channels."""
 
     @staticmethod
-    def forward(ctx, field, weight):
+    def forward(ctx, field, weight, want_stats):
         ctx.save_for_backward(field, weight)
-        w2 = L.s2d_weight(weight).to(torch.bfloat16).contiguous()
-        return K.conv_fprop(field, w2, L.S2D_DY, L.S2D_DX)
+        w2 = L.cached(weight, "s2d", lambda w: L.s2d_weight(w).to(torch.bfloat16).contiguous())
+        sums = None
+        if want_stats:
+            sums = torch.empty(2 * weight.shape[0], dtype=torch.float64, device=field.device)
+        y = K.conv_fprop(field, w2, L.S2D_DY, L.S2D_DX, bn_sums=sums)
+        if want_stats:
+            ctx.mark_non_differentiable(sums)
+            return y, sums
+        return y
 
     @staticmethod
-    def backward(ctx, g):
+    def backward(ctx, g, *unused):
         field, weight = ctx.saved_tensors
         g = _bf16c(g)
         gf = gw = None
         if ctx.needs_input_grad[0]:
-            w2t = L.s2d_weight(weight).permute(2, 1, 0).to(torch.bfloat16).contiguous()
+            w2t = L.cached(weight, "s2d_t", lambda w: L.s2d_weight(w).permute(2, 1, 0).to(torch.bfloat16).contiguous())
             gf = K.conv_fprop(g, w2t, [-v for v in L.S2D_DY], [-v for v in L.S2D_DX])
         if ctx.needs_input_grad[1]:
             gw = L.s2d_weight_grad(K.conv_wgrad(field, g, L.S2D_DY, L.S2D_DX), weight.shape)
-        return gf, gw
+        return gf, gw, None
 
 
-def conv_s2d(field, weight):
-    return _ConvS2D.apply(field, weight)
+def conv_s2d(field, weight, want_stats=False):
+    return _ConvS2D.apply(field, weight, want_stats)
 
 
 class _Depthwise(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, stride, dil):
         C = weight.shape[0]
-        w9 = weight.reshape(C, 9).t().contiguous().float()
+        w9 = L.cached(weight, "dw9", lambda w: w.reshape(C, 9).t().contiguous().float())
         ctx.save_for_backward(x, w9)
         ctx.cfg = (stride, dil, tuple(x.shape))
         return K.dw_fwd(x, w9, stride, dil)
@@ -104,9 +120,10 @@ class _BNAct(torch.autograd.Function):
     """out = act(BatchNorm_train(y) [+ res]) with batch statistics (nn.BatchNorm2d training mode)."""
 
     @staticmethod
-    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act):
+    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act, sums):
         M = y.numel() // y.shape[-1]
-        sums = K.bn_stats(y)
+        if sums is None:
+            sums = K.bn_stats(y)
         mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var)
         out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
         ctx.save_for_backward(y, out if act else None, mean, invstd, gamma)
@@ -123,7 +140,7 @@ class _BNAct(torch.autograd.Function):
         ggamma = sums[C:].float() if ctx.needs_input_grad[1] else None
         gbeta = sums[:C].float() if ctx.needs_input_grad[2] else None
         gres = dyh if (ctx.has_res and ctx.needs_input_grad[3]) else None
-        return dx, ggamma, gbeta, gres, None, None, None, None, None
+        return dx, ggamma, gbeta, gres, None, None, None, None, None, None
 
 
 class _AffineAct(torch.autograd.Function):
@@ -138,13 +155,16 @@ class _AffineAct(torch.autograd.Function):
         raise NotImplementedError("eval-mode BatchNorm backward is not on the training hot path")
 
 
-def bn_act(y, bn, res=None, act=True):
-    """`bn` is a torch.nn.BatchNorm2d-compatible module (weight, bias, running_*, eps, momentum)."""
+def bn_act(y, bn, res=None, act=True, sums=None):
+    """`bn` is a torch.nn.BatchNorm2d-compatible module (weight, bias, running_*, eps, momentum).
+    `y` may be the (y, sums) pair of a conv called with want_stats=True."""
+    if isinstance(y, tuple):
+        y, sums = y
     if bn.training:
         if bn.num_batches_tracked is not None:
             bn.num_batches_tracked += 1
         return _BNAct.apply(y, bn.weight, bn.bias, res, bn.running_mean, bn.running_var, bn.eps,
-                            bn.momentum, act)
+                            bn.momentum, act, sums)
     a = (bn.weight * torch.rsqrt(bn.running_var + bn.eps)).float().contiguous()
     b = (bn.bias - bn.running_mean * a).float().contiguous()
     return _AffineAct.apply(y, a, b, res, act)
@@ -206,7 +226,7 @@ class _Head(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias):
         N, H, W, C = x.shape
-        w_hwc = weight.view(C, H, W).permute(1, 2, 0).reshape(-1).to(torch.bfloat16).contiguous()
+        w_hwc = L.cached(weight, "head", lambda w: w.view(C, H, W).permute(1, 2, 0).reshape(-1).to(torch.bfloat16).contiguous())
         logits = bias.detach().float().repeat(N).contiguous()
         K.head_fwd(x, w_hwc, logits)
         ctx.save_for_backward(x, w_hwc)

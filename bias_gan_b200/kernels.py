@@ -26,6 +26,41 @@ def taps_for(kernel_size, dilation=1):
     return dy, dx
 
 
+def pad_channels(C):
+    """Channel stride of an activation with C channels: TMA and the vector kernels move 128-byte
+    lines, so wide tensors whose rows would straddle lines (728 channels) are stored with the
+    pixel stride rounded up to 64 elements (include/bgr.h, bgr_conv_fprop)."""
+    return C if (C <= 64 or C % 64 == 0) else (C + 63) // 64 * 64
+
+
+def act_empty(shape, device):
+    """Uninitialised bf16 [..., C] activation view with the padded pixel stride."""
+    C = shape[-1]
+    Cp = pad_channels(C)
+    t = torch.empty(tuple(shape[:-1]) + (Cp,), dtype=torch.bfloat16, device=device)
+    return t if Cp == C else t[..., :C]
+
+
+def is_act_view(t):
+    """bf16 [..., C] view with unit channel stride and one uniform pixel stride."""
+    if t.dtype != torch.bfloat16 or t.stride(-1) != 1:
+        return False
+    if t.is_contiguous():
+        return True
+    exp = None
+    for d in range(t.dim() - 2, -1, -1):
+        if t.shape[d] == 1:
+            continue
+        if exp is None:
+            exp = t.stride(d)
+            if exp < t.shape[-1]:
+                return False
+        elif t.stride(d) != exp:
+            return False
+        exp *= t.shape[d]
+    return True
+
+
 def _nhwc_view(t):
     assert t.dim() == 4 and t.dtype == torch.bfloat16 and t.is_cuda, "expected a bf16 NHWC cuda view"
     N, H, W, C = t.shape
@@ -37,19 +72,24 @@ def _nhwc_view(t):
     return N, H, W, C, ld
 
 
-def conv_fprop(x, w, dy, dx, out=None, bias=None):
-    """y = conv(x, w).  x: [N,H,W,Cin] bf16 NHWC; w: [Cout, ntaps, Cin] bf16; out: [N,H,W,Cout]."""
+def conv_fprop(x, w, dy, dx, out=None, bias=None, bn_sums=None):
+    """y = conv(x, w).  x: [N,H,W,Cin] bf16 NHWC; w: [Cout, ntaps, Cin] bf16; out: [N,H,W,Cout].
+    bn_sums: optional fp64 [2*Cout] filled with the per-channel sum / sum of squares of y."""
     N, H, W, Cin, ldx = _nhwc_view(x)
     Cout, ntaps, wc = w.shape
-    assert wc == Cin and w.is_contiguous() and w.dtype == torch.bfloat16 and ntaps == len(dy)
+    ldw = w.stride(1) if ntaps > 1 else w.stride(0)
+    assert wc == Cin and w.stride(2) == 1 and w.stride(0) == ntaps * ldw and w.dtype == torch.bfloat16 \
+        and ntaps == len(dy), "expected bf16 [Cout, ntaps, Cin] weights with a uniform row pitch"
     if out is None:
-        out = torch.empty((N, H, W, Cout), dtype=torch.bfloat16, device=x.device)
+        out = act_empty((N, H, W, Cout), x.device)
     No, Ho, Wo, Co, ldy = _nhwc_view(out)
     assert (No, Ho, Wo, Co) == (N, H, W, Cout)
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == Cout
-    check(_lib.lib().bgr_conv_fprop(ptr(x), N, H, W, Cin, ldx, ptr(w), Cout, ntaps, int_array(dy),
-                                    int_array(dx), ptr(out), ldy, ptr(bias), stream_ptr()))
+    if bn_sums is not None:
+        assert bn_sums.dtype == torch.float64 and bn_sums.numel() == 2 * Cout and bn_sums.is_contiguous()
+    check(_lib.lib().bgr_conv_fprop(ptr(x), N, H, W, Cin, ldx, ptr(w), ldw, Cout, ntaps, int_array(dy),
+                                    int_array(dx), ptr(out), ldy, ptr(bias), ptr(bn_sums), stream_ptr()))
     return out
 
 
@@ -142,7 +182,7 @@ def bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var):
 def bn_apply(x, a, b, res=None, act=True, slope=0.2, out=None):
     M, C, ldx = _rows(x)
     if out is None:
-        out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+        out = act_empty(x.shape, x.device)
     Mo, Co, ldo = _rows(out)
     assert (Mo, Co) == (M, C)
     ldr = 0
@@ -163,13 +203,13 @@ def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2):
     if act:
         Mo, Co, ldo = _rows(out)
         assert (Mo, Co) == (M, C)
-    dyh = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
-    dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    dyh = act_empty(x.shape, x.device)
+    dx = act_empty(x.shape, x.device)
     sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
     coef = torch.empty(5 * C, dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_bn_backward(ptr(g), ldg, ptr(out) if act else ctypes.c_void_p(0), ldo, ptr(x), ldx,
                                      ptr(mean), ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
-                                     ptr(dyh), ptr(dx), ptr(sums), ptr(coef), stream_ptr()))
+                                     ptr(dyh), ptr(dx), _rows(dx)[2], ptr(sums), ptr(coef), stream_ptr()))
     return dx, dyh, sums
 
 
@@ -177,7 +217,7 @@ def dw_fwd(x, w9, stride, dil, out=None):
     N, H, W, C, ldx = _nhwc_view(x)
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     if out is None:
-        out = torch.empty((N, Ho, Wo, C), dtype=torch.bfloat16, device=x.device)
+        out = act_empty((N, Ho, Wo, C), x.device)
     _, _, _, _, ldy = _nhwc_view(out)
     assert w9.dtype == torch.float32 and tuple(w9.shape) == (9, C) and w9.is_contiguous()
     check(_lib.lib().bgr_dw_fwd(ptr(x), N, H, W, C, ldx, ptr(w9), stride, dil, ptr(out), ldy, stream_ptr()))
@@ -187,8 +227,9 @@ def dw_fwd(x, w9, stride, dil, out=None):
 def dw_dgrad(gy, w9, stride, dil, in_shape):
     N, H, W, C = in_shape
     _, _, _, _, ldy = _nhwc_view(gy)
-    dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=gy.device)
-    check(_lib.lib().bgr_dw_dgrad(ptr(gy), N, H, W, C, ldy, ptr(w9), stride, dil, ptr(dx), C, stream_ptr()))
+    dx = act_empty((N, H, W, C), gy.device)
+    check(_lib.lib().bgr_dw_dgrad(ptr(gy), N, H, W, C, ldy, ptr(w9), stride, dil, ptr(dx), _nhwc_view(dx)[4],
+                                  stream_ptr()))
     return dx
 
 
@@ -202,16 +243,16 @@ def dw_wgrad(x, gy, stride, dil):
 
 def subsample2(x):
     N, H, W, C, ldx = _nhwc_view(x)
-    out = torch.empty((N, (H + 1) // 2, (W + 1) // 2, C), dtype=torch.bfloat16, device=x.device)
-    check(_lib.lib().bgr_subsample2(ptr(x), N, H, W, C, ldx, ptr(out), C, stream_ptr()))
+    out = act_empty((N, (H + 1) // 2, (W + 1) // 2, C), x.device)
+    check(_lib.lib().bgr_subsample2(ptr(x), N, H, W, C, ldx, ptr(out), _nhwc_view(out)[4], stream_ptr()))
     return out
 
 
 def subsample2_bwd(gy, in_shape):
     N, H, W, C = in_shape
     _, _, _, _, ldy = _nhwc_view(gy)
-    dx = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=gy.device)
-    check(_lib.lib().bgr_subsample2_bwd(ptr(gy), N, H, W, C, ldy, ptr(dx), C, stream_ptr()))
+    dx = act_empty((N, H, W, C), gy.device)
+    check(_lib.lib().bgr_subsample2_bwd(ptr(gy), N, H, W, C, ldy, ptr(dx), _nhwc_view(dx)[4], stream_ptr()))
     return dx
 
 

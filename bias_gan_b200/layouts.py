@@ -1,19 +1,66 @@
 """Weight-layout transforms between PyTorch's [Cout, Cin, kh, kw] parameters (the state-dict
 contract, deeplab.py) and the GEMM layouts the tcgen05 kernels consume.  Tiny tensors; plain torch.
 """
+import weakref
+
 import torch
+
+# Derived GEMM-layout copies are cached per parameter and reused until the parameter changes
+# (optimizer steps / load_state_dict / .to() bump `_version` or move the storage).  A CUDA-graph
+# replay changes parameters behind Python's back: GraphedGanStep calls invalidate_cache().
+_cache = {}   # id(param) -> (weakref to param, {kind: ((data_ptr, version), derived tensor)})
+
+
+def cached(param, kind, fn):
+    """fn(param) memoised until the parameter's storage or version changes."""
+    ent = _cache.get(id(param))
+    if ent is None or ent[0]() is not param:
+        pid = id(param)
+        ent = _cache[pid] = (weakref.ref(param, lambda _r, pid=pid: _cache.pop(pid, None)), {})
+    key = (param.data_ptr(), param._version)
+    hit = ent[1].get(kind)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    with torch.no_grad():
+        val = fn(param)
+    ent[1][kind] = (key, val)
+    return val
+
+
+def invalidate_cache(module=None):
+    """Drop the derived copies of `module`'s parameters (all parameters if None)."""
+    if module is None:
+        _cache.clear()
+        return
+    for p in module.parameters():
+        _cache.pop(id(p), None)
+
+
+def _row_pitch(K):
+    """GEMM-K row pitch of a weight matrix: rounded up to 64 elements (128-byte lines for TMA)."""
+    return K if K % 64 == 0 else (K + 63) // 64 * 64
+
+
+def _padded_rows(src, rows, taps, K):
+    """bf16 [rows, taps, K] view of a [rows, taps, pitch] buffer filled from `src` (same logical shape)."""
+    pitch = _row_pitch(K)
+    if pitch == K:
+        return src.to(torch.bfloat16).contiguous()
+    buf = torch.zeros((rows, taps, pitch), dtype=torch.bfloat16, device=src.device)
+    buf[..., :K].copy_(src)
+    return buf[..., :K]
 
 
 def gemm_weight(w):
-    """[Cout, Cin, kh, kw] -> bf16 [Cout, kh*kw, Cin] (tap-major, Cin contiguous)."""
+    """[Cout, Cin, kh, kw] -> bf16 [Cout, kh*kw, Cin] (tap-major, Cin contiguous, padded row pitch)."""
     Cout, Cin, kh, kw = w.shape
-    return w.permute(0, 2, 3, 1).reshape(Cout, kh * kw, Cin).to(torch.bfloat16).contiguous()
+    return _padded_rows(w.permute(0, 2, 3, 1).reshape(Cout, kh * kw, Cin), Cout, kh * kw, Cin)
 
 
 def gemm_weight_t(w):
     """Data-gradient weights: bf16 [Cin, kh*kw, Cout]; used with negated tap offsets."""
     Cout, Cin, kh, kw = w.shape
-    return w.permute(1, 2, 3, 0).reshape(Cin, kh * kw, Cout).to(torch.bfloat16).contiguous()
+    return _padded_rows(w.permute(1, 2, 3, 0).reshape(Cin, kh * kw, Cout), Cin, kh * kw, Cout)
 
 
 def from_gemm_grad(dw, shape):

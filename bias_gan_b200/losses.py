@@ -26,10 +26,33 @@ class GANLoss:
             pass
         else:
             raise NotImplementedError("Error, {} loss not implemented".format(mode))
+        self._static = None   # (label_for_fake, label_for_real) device buffers once draw_labels() is used
+
+    def draw_labels(self):
+        """Draw this step's noisy labels and the 5 % swap on the CPU generator — the same three
+        draws in the same order as d_loss (losses.py:146-153) — into persistent device buffers.
+        After the first call d_loss() reads those buffers instead of drawing, which keeps host RNG
+        and host->device copies out of a captured CUDA graph (step.GraphedGanStep)."""
+        if self.mode != "ModifiedMinMax":
+            return
+        label_fake = self.dist_fake.rsample(self.label_fake.shape)
+        label_real = self.dist_real.rsample(self.label_real.shape)
+        if self.dist_swap.sample() < 0.05:
+            label_fake, label_real = label_real, label_fake
+        if self._static is None:
+            pin = torch.cuda.is_available() and torch.device(self.device).type == "cuda"
+            self._host = tuple(torch.empty(self.label_fake.shape, pin_memory=pin) for _ in range(2))
+            self._static = tuple(torch.empty_like(self.label_fake) for _ in range(2))
+        for host, dev, val in zip(self._host, self._static, (label_fake, label_real)):
+            host.copy_(val)
+            dev.copy_(host, non_blocking=True)
 
     def d_loss(self, logits_real, logits_fake):
         if self.mode == "Wasserstein":
             return torch.mean(logits_fake - logits_real)
+        if self._static is not None:
+            label_fake, label_real = self._static
+            return 0.5 * (self.criterion(logits_fake, label_fake) + self.criterion(logits_real, label_real))
         label_fake = self.dist_fake.rsample(self.label_fake.shape).to(self.device, non_blocking=True)
         label_real = self.dist_real.rsample(self.label_real.shape).to(self.device, non_blocking=True)
         if self.dist_swap.sample() < 0.05:

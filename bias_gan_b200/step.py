@@ -9,6 +9,8 @@ are identical to the reference-faithful schedule (`lean=False`).
 """
 import torch
 
+from . import layouts as L
+
 
 def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_reg=1.0, lean=True,
              train_discriminator=True, train_generator=True, warmup=False):
@@ -29,6 +31,7 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
         if hasattr(D, "grad_sync"):
             D.grad_sync.finish()
         d_opt.step()
+        L.invalidate_cache(D)
         del fake, logits_real, logits_fake
     if train_generator:
         fake = G.forward_field(inputs)
@@ -49,5 +52,77 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
         if hasattr(G, "grad_sync"):
             G.grad_sync.finish()
         g_opt.step()
+        L.invalidate_cache(G)
     return (d_loss.detach() if d_loss is not None else None,
             g_loss.detach() if g_loss is not None else None)
+
+
+class GraphedGanStep:
+    """gan_step captured once into a CUDA graph and replayed: the ~6000 kernel launches of a step
+    (and PyTorch's autograd bookkeeping between them) collapse into one graph launch, so the GPU is
+    never waiting for the host.  Inputs are copied (or staged directly, see `inputs`/`real`) into
+    static field buffers; the adversarial labels are drawn on the host before each replay
+    (GANLoss.draw_labels) so the captured region has no host RNG and no host->device copy.
+
+    Optimizers must be capturable (torch.optim.AdamW(..., capturable=True)).  Model, BatchNorm and
+    optimizer state are snapshotted before the warm-up iterations that capture needs and restored
+    in place afterwards, so constructing this object does not advance training.
+    """
+
+    def __init__(self, G, D, g_opt, d_opt, crit_gan, crit_reg, field_shape, device, warmup_iters=2, **step_kw):
+        self.G, self.D, self.g_opt, self.d_opt = G, D, g_opt, d_opt
+        self.crit_gan, self.crit_reg, self.step_kw = crit_gan, crit_reg, step_kw
+        self.inputs = torch.zeros(field_shape, dtype=torch.bfloat16, device=device)
+        self.real = torch.zeros(field_shape, dtype=torch.bfloat16, device=device)
+        cpu_rng = torch.get_rng_state()
+        crit_gan.draw_labels()
+        torch.set_rng_state(cpu_rng)      # the capture-time draws must not advance the label stream
+        # state that the warm-up steps touch: parameters, buffers, optimizer moments
+        tensors = [t for m in (G, D) for t in list(m.parameters()) + list(m.buffers())]
+        side = torch.cuda.Stream(device=device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        def opt_tensors():
+            return [t for o in (g_opt, d_opt) for st in o.state.values() for t in st.values() if torch.is_tensor(t)]
+
+        with torch.cuda.stream(side):
+            snap = [t.detach().clone() for t in tensors]
+            opt_before = {id(t): t.detach().clone() for t in opt_tensors()}
+            opt_snap = None
+            for i in range(max(1, warmup_iters)):
+                self._run()
+                if i == 0:  # lazily created optimizer state: its value before the first step is zero
+                    opt_snap = [(t, opt_before.get(id(t), None)) for t in opt_tensors()]
+                    opt_snap = [(t, torch.zeros_like(t) if s0 is None else s0) for t, s0 in opt_snap]
+            L.invalidate_cache()
+        torch.cuda.current_stream(device).wait_stream(side)
+        torch.cuda.synchronize(device)
+        from . import _lib
+        lib = _lib.lib()
+        lib.bgr_launch_count.restype = __import__("ctypes").c_ulonglong
+        c0 = lib.bgr_launch_count()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.d_loss, self.g_loss = self._run()
+        self.launches_per_step = int(lib.bgr_launch_count() - c0)   # kernels of libbgr.so in the graph
+        L.invalidate_cache()
+        with torch.no_grad():
+            for t, s0 in zip(tensors, snap):
+                t.copy_(s0)
+            for t, z in opt_snap:
+                t.copy_(z)
+        torch.cuda.synchronize(device)
+
+    def _run(self):
+        return gan_step(self.G, self.D, self.g_opt, self.d_opt, self.crit_gan, self.crit_reg, self.inputs, self.real,
+                        **self.step_kw)
+
+    def __call__(self, inputs=None, real=None):
+        """One training step.  inputs/real: bf16 fields to copy into the static buffers; pass None
+        when the caller has staged straight into `self.inputs` / `self.real`."""
+        if inputs is not None:
+            self.inputs.copy_(inputs)
+        if real is not None:
+            self.real.copy_(real)
+        self.crit_gan.draw_labels()
+        self.graph.replay()
+        return self.d_loss, self.g_loss

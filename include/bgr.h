@@ -86,15 +86,22 @@ int bgr_stage_normalize(const void* src, int src_dtype, int src_layout, int B, i
 /* ---- implicit-GEMM convolution (tcgen05 / TMEM / TMA) ------------------------------------ */
 
 /* y[n,h,w,co] = bias[co] + sum_{t,ci} x[n, h+dy[t], w+dx[t], ci] * w[co,t,ci]   (zero outside)
- * x: bf16 NHWC view [N,H,W,Cin] with pixel stride ldx elements; w: bf16 [Cout][ntaps][Cin];
+ * x: bf16 NHWC view [N,H,W,Cin] with pixel stride ldx elements; w: bf16 [Cout][ntaps][ldw];
  * y: bf16 NHWC view, pixel stride ldy.  Cin, Cout, ldx, ldy multiples of 8; pointers 16-byte
  * aligned.  Covers nn.Conv2d 1x1 / 3x3 / atrous stride 1 (deeplab.py:58,81,95,182,331,363,366,
  * 622,626,630) and, with transposed+flipped weights, their data gradients.
  * The stride-2 3x3 entry conv (deeplab.py:178) runs through the same entry point as a 2x2-tap
  * stride-1 conv over fields stored as 2x2 space-to-depth blocks (see bgr_stage_normalize). */
-int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w, int Cout,
-                   int ntaps, const int* dy, const int* dx, void* y, int ldy, const float* bias,
-                   void* stream);
+int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w, int ldw,
+                   int Cout, int ntaps, const int* dy, const int* dx, void* y, int ldy,
+                   const float* bias, double* bn_sums, void* stream);
+/* ldw: elements between consecutive (cout, tap) rows of w (>= Cin, multiple of 8).  TMA moves whole
+ * 128-byte lines: keep ldx, ldy and ldw multiples of 64 elements where the channel count is not
+ * (728 -> 768) so that no pixel row straddles a line — measured 1.65x on the 728-channel layers. */
+/* bn_sums (optional, NULL to skip; excludes bias): fp64 [2*Cout], zeroed inside and filled by the
+ * conv epilogue with sum_m y and sum_m y^2 of the bf16-rounded outputs — the statistics pass of
+ * the nn.BatchNorm2d that follows every such conv in the reference (deeplab.py:179,183,334,...)
+ * without re-reading y (same contract as bgr_bn_stats). */
 
 /* dw[co,t,ci] += sum_{n,h,w} dy_[n,h,w,co] * x[n, h+dy[t], w+dx[t], ci]   (fp32, accumulated:
  * zero dw first).  Same views as bgr_conv_fprop. */
@@ -115,12 +122,13 @@ int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const
 /* out = act(a*x + b [+ res]); act != 0: LeakyReLU(slope). */
 int bgr_bn_apply(const void* x, int ldx, const float* a, const float* b, const void* res, int ldr,
                  void* out, int ldo, long M, int C, int act, float slope, void* stream);
-/* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; dyh (dense [M][C]) receives
- * g*act'(out), which is also dL/dres; dx (dense) receives dL/dx; sums (fp64 [2][C]) receives
+/* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; dyh ([M][C], pixel stride ldd) receives
+ * g*act'(out), which is also dL/dres; dx (same stride) receives dL/dx; sums (fp64 [2][C]) receives
  * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat; coef_ws: fp32 [5][C] workspace. */
 int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
                     const float* mean, const float* invstd, const float* gamma, int act, float slope,
-                    long M, int C, void* dyh, void* dx, double* sums, float* coef_ws, void* stream);
+                    long M, int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
+                    void* stream);
 
 /* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
  * w, dw: fp32 [9][C].  Output size ceil(H/stride) x ceil(W/stride). */

@@ -103,6 +103,53 @@ def test_conv_fprop_dgrad_wgrad(dev, N, H, W, Cin, Cout, ks, dil, bias):
         assert rel(bp.grad, br.grad) < 1e-4
 
 
+@pytest.mark.parametrize("block_n", [0, 128, 256])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil", [
+    (2, 48, 72, 728, 728, 1, 1), (1, 19, 37, 304, 256, 3, 1), (3, 40, 56, 128, 1536, 1, 1), (1, 24, 40, 128, 48, 1, 1),
+    (2, 12, 18, 264, 320, 3, 2)])
+def test_conv_fused_bn_stats(dev, block_n, N, H, W, Cin, Cout, ks, dil):
+    """The persistent fprop kernel at every Cout tile width (many tiles per CTA, ragged pixel and
+    channel tiles): output equals the separate-statistics path bit for bit, and the epilogue's
+    BatchNorm sums equal bn_stats over the stored bf16 output (fp64 accumulation of fp32 tile sums)."""
+    from bias_gan_b200 import _lib, kernels as K, layouts as L
+    g = torch.Generator(device="cpu").manual_seed(5)
+    x = nhwc(torch.randn(N, Cin, H, W, generator=g).to(dev).bfloat16())
+    w = (torch.randn(Cout, Cin, ks, ks, generator=g) / (Cin * ks * ks) ** 0.5).to(dev)
+    dy, dx = K.taps_for(ks, dil)
+    ref = F.conv2d(nchw(x).float(), w.bfloat16().float(), padding=dil * (ks - 1) // 2, dilation=dil)
+    _lib.lib().bgr_debug_conv_block_n(block_n)
+    try:
+        sums = torch.full((2 * Cout,), 7.0, dtype=torch.float64, device=dev)
+        y = K.conv_fprop(x, L.gemm_weight(w), dy, dx, bn_sums=sums)
+        y0 = K.conv_fprop(x, L.gemm_weight(w), dy, dx)
+        gy = nhwc(torch.randn(N, Cout, H, W, generator=g).to(dev).bfloat16())
+        dw = K.conv_wgrad(x, gy, dy, dx)
+    finally:
+        _lib.lib().bgr_debug_conv_block_n(0)
+    assert rel(nchw(y), ref) < 4e-3
+    assert torch.equal(y, y0)
+    want = K.bn_stats(y)
+    yd = y.double().reshape(-1, Cout)
+    assert torch.allclose(want, torch.cat((yd.sum(0), (yd * yd).sum(0))), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(sums, want, rtol=1e-5, atol=1e-3)
+    wr = w.bfloat16().float().requires_grad_(True)
+    F.conv2d(nchw(x).float(), wr, padding=dil * (ks - 1) // 2, dilation=dil).backward(nchw(gy).float())
+    assert rel(L.from_gemm_grad(dw, w.shape), wr.grad) < 1e-4
+
+
+def test_conv_fprop_into_channel_slice(dev):
+    """TMA-store epilogue into a channel slice of a wider NHWC buffer (in-place concatenation)."""
+    from bias_gan_b200 import kernels as K, layouts as L
+    g = torch.Generator(device="cpu").manual_seed(6)
+    x = nhwc(torch.randn(2, 128, 20, 28, generator=g).to(dev).bfloat16())
+    w = (torch.randn(48, 128, 1, 1, generator=g) / 128 ** 0.5).to(dev)
+    buf = torch.full((2, 20, 28, 304), 3.0, dtype=torch.bfloat16, device=dev)
+    K.conv_fprop(x, L.gemm_weight(w), [0], [0], out=buf[..., 256:])
+    ref = F.conv2d(nchw(x).float(), w.bfloat16().float())
+    assert rel(nchw(buf[..., 256:]), ref) < 4e-3
+    assert torch.equal(buf[..., :256], torch.full_like(buf[..., :256], 3.0))
+
+
 @pytest.mark.parametrize("N,H,W", [(2, 64, 96), (1, 38, 74)])
 def test_entry_conv_s2d(dev, N, H, W):
     from bias_gan_b200 import functional as F_, kernels as K

@@ -14,6 +14,7 @@ caps that catch semantic errors (early-trunk activations within 2e-2, gradient c
 """
 import os
 
+import numpy as np
 import pytest
 import torch
 import torch.nn.functional as F
@@ -183,3 +184,60 @@ def test_gan_step_matches_oracle_step(setup):
                 assert rel(sp[k], sr[k]) <= 0.1, k
             if k.endswith("num_batches_tracked"):
                 assert int(sp[k]) == int(sr[k]), k
+
+
+def test_graphed_step_matches_eager():
+    """step.GraphedGanStep (one CUDA-graph replay per step, labels pre-drawn on the host, cached GEMM
+    weight copies) against the kernel-by-kernel gan_step from the same state.  The 70-layer train-mode
+    network amplifies the last-bit run-to-run differences of fp32 atomics (BatchNorm sums, wgrad) to
+    ~10 % at the losses of this tiny configuration, so: (1) quantities upstream of the amplification
+    (entry-layer BatchNorm running statistics after the step's three D and two G forwards) must agree
+    tightly, (2) the losses must agree within the measured eager run-to-run spread, (3) constructing
+    the graphed step must not advance training, (4) replays must update parameters and Adam state."""
+    import copy
+    dev = torch.device("cuda", 0)
+    from bias_gan_b200 import kernels as K
+    from bias_gan_b200.deeplab_gan import Discriminator, Generator
+    from bias_gan_b200.losses import GANLoss, L1LossField
+    from bias_gan_b200.step import GraphedGanStep, gan_step
+    from oracle.seeded import seed_state, seeded_fields
+    B, C, H, W = 4, 16, 64, 96
+    x, y = seeded_fields(3, B, C, H, W)
+    xf, yf = K.nchw_to_field(x.to(dev)), K.nchw_to_field(y.to(dev))
+    opt = lambda m: torch.optim.AdamW(m.parameters(), lr=1e-4, eps=1e-8, weight_decay=1e-5, fused=True, capturable=True)
+
+    def build():
+        G = seed_state(Generator(C, C, "Interpolate", "Normal", 0), 21).to(dev).train()
+        D = seed_state(Discriminator(C, input_size=(H, W)), 22).to(dev).train()
+        return G, D, opt(G), opt(D)
+
+    def eager():
+        G0, D0, go0, do0 = build()
+        torch.manual_seed(5)
+        dl, gl = gan_step(G0, D0, go0, do0, GANLoss("ModifiedMinMax", B, dev), L1LossField(), xf, yf)
+        return G0, D0, (float(dl), float(gl))
+
+    runs = [eager() for _ in range(3)]
+    G0, D0, ref = runs[0]
+    spread = [max(abs(r[2][i] - q[2][i]) for r in runs for q in runs) for i in range(2)]
+    G1, D1, go1, do1 = build()
+    before = copy.deepcopy(G1.state_dict())
+    torch.manual_seed(5)
+    gs = GraphedGanStep(G1, D1, go1, do1, GANLoss("ModifiedMinMax", B, dev), L1LossField(), tuple(xf.shape), dev)
+    for k, v in G1.state_dict().items():
+        assert torch.equal(v, before[k]), "constructing the graphed step changed " + k
+    assert all(int(st["step"]) == 0 for st in go1.state.values())
+    got = tuple(float(t) for t in gs(xf, yf))
+    for i in range(2):
+        assert abs(got[i] - ref[i]) <= max(4 * spread[i], 5e-3 * abs(ref[i])), (ref, spread, got)
+    for m0, m1 in ((G0.model.xception_features, G1.model.xception_features), (D0.xception_features, D1.xception_features)):
+        for bn in ("bn1", "bn2"):
+            for stat in ("running_mean", "running_var"):
+                torch.testing.assert_close(getattr(getattr(m1, bn), stat), getattr(getattr(m0, bn), stat), rtol=2e-3, atol=2e-4)
+            assert int(getattr(m1, bn).num_batches_tracked) == int(getattr(m0, bn).num_batches_tracked)
+    assert all(int(st["step"]) == 1 for st in go1.state.values()) and all(int(st["step"]) == 1 for st in do1.state.values())
+    moved = max(float((p - before[n]).abs().max()) for n, p in G1.named_parameters())
+    assert 5e-5 < moved <= 1.5e-4, moved   # one AdamW step at lr 1e-4
+    got2 = tuple(float(t) for t in gs(xf, yf))
+    assert all(np.isfinite(v) for v in got2)
+    assert all(int(st["step"]) == 2 for st in do1.state.values())
