@@ -109,39 +109,65 @@ def run_reference(args):
 
 
 def conv_roofline_step(step_fn, torch, K):
-    """One extra, instrumented step: CUDA-event pairs around every implicit-GEMM launch on the
-    launching stream -> algorithmic FLOPs / summed duration of the dominant kernel family."""
-    rec = []
+    """Dominant kernel family (tcgen05 implicit GEMM): one kernel-by-kernel step records the signature
+    of every conv launch (shapes, pixel strides, taps, epilogue options); each distinct signature is
+    then timed alone with CUDA events on the launching stream, L2 flushed before every launch, and
+    weighted by its launch count.  (Event pairs around the launches of a live step would time the
+    host: launching 6000 kernels one by one is slower than the GPU runs them.)"""
+    sigs = {}
     orig_f, orig_w = K.conv_fprop, K.conv_wgrad
 
-    def timed(fn, kind):
-        def wrap(x, w_or_g, dy, dx, *a, **kw):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            out = fn(x, w_or_g, dy, dx, *a, **kw)
-            e1.record()
-            n, h, w, cin = x.shape
-            cout = w_or_g.shape[0] if kind == "fprop" else w_or_g.shape[-1]
-            rec.append((kind, 2.0 * n * h * w * cin * cout * len(dy), e0, e1))
-            return out
-        return wrap
+    def f_wrap(x, w, dy, dx, out=None, bias=None, bn_sums=None):
+        key = ("fprop", tuple(x.shape), x.stride(2), w.shape[0], tuple(dy), tuple(dx), bias is not None, bn_sums is not None)
+        sigs[key] = sigs.get(key, 0) + 1
+        return orig_f(x, w, dy, dx, out=out, bias=bias, bn_sums=bn_sums)
 
-    K.conv_fprop, K.conv_wgrad = timed(orig_f, "fprop"), timed(orig_w, "wgrad")
+    def w_wrap(x, gy, dy, dx, dw=None):
+        key = ("wgrad", tuple(x.shape), x.stride(2), gy.shape[-1], tuple(dy), tuple(dx), False, False)
+        sigs[key] = sigs.get(key, 0) + 1
+        return orig_w(x, gy, dy, dx, dw=dw)
+
+    K.conv_fprop, K.conv_wgrad = f_wrap, w_wrap
     try:
-        # keep the GPU busy for ~0.4 s first so that the host is far ahead when the step's kernels
-        # run: each event pair then brackets the kernel alone, not the host's launch latency
-        torch.cuda._sleep(int(0.8e9))
         step_fn()
         torch.cuda.synchronize()
     finally:
         K.conv_fprop, K.conv_wgrad = orig_f, orig_w
-    flops = sum(r[1] for r in rec)
-    ms = sum(r[2].elapsed_time(r[3]) for r in rec)
-    by = {}
-    for kind, f, e0, e1 in rec:
+    dev = torch.device("cuda", torch.cuda.current_device())
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    by, reps = {}, 3
+    for (kind, shape, ldx, cout, dy, dx, has_bias, has_stats), count in sigs.items():
+        n, h, w_, cin = shape
+        x = torch.randn(n, h, w_, max(ldx, cin), device=dev).bfloat16()[..., :cin]
+        nt = len(dy)
+        if kind == "fprop":
+            wt = torch.randn(cout, nt, K.pad_channels(cin) if cin > 64 else cin, device=dev).bfloat16()[..., :cin]
+            bias = torch.zeros(cout, device=dev) if has_bias else None
+            sums = torch.empty(2 * cout, dtype=torch.float64, device=dev) if has_stats else None
+            y = K.act_empty((n, h, w_, cout), dev)
+            fn = lambda: orig_f(x, wt, list(dy), list(dx), out=y, bias=bias, bn_sums=sums)
+        else:
+            gy = K.act_empty((n, h, w_, cout), dev)
+            gy.normal_()
+            dwt = torch.zeros(cout, nt, cin, device=dev)
+            fn = lambda: orig_w(x, gy, list(dy), list(dx), dw=dwt)
+        fn()
+        ms = 0.0
+        for _ in range(reps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1) / reps
         a = by.setdefault(kind, [0.0, 0.0, 0])
-        a[0] += f; a[1] += e0.elapsed_time(e1); a[2] += 1
-    return flops, ms, len(rec), {k: {"tflops": v[0] / v[1] / 1e9, "ms": v[1], "launches": v[2]} for k, v in by.items()}
+        a[0] += count * 2.0 * n * h * w_ * cin * cout * nt
+        a[1] += count * ms
+        a[2] += count
+        del x, fn
+    flops = sum(v[0] for v in by.values())
+    ms = sum(v[1] for v in by.values())
+    return flops, ms, sum(v[2] for v in by.values()), \
+        {k: {"tflops": v[0] / v[1] / 1e9, "ms": v[1], "launches": v[2]} for k, v in by.items()}
 
 
 def main():

@@ -86,6 +86,53 @@ bilinear_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restri
   }
 }
 
+// adjoint by gathering (no atomics): one thread per low-resolution pixel and 8 channels collects
+// every output pixel whose two source rows / columns include it.  The candidate range is padded by
+// one and each candidate re-runs bil_coord, so the weights are exactly the forward's.
+__global__ void __launch_bounds__(256)
+bilinear_bwd_gather_kernel(const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx, const BilGeom g) {
+  const int G = g.C >> 3;
+  const long total = long(g.N) * g.h * g.w * G;
+  const float ry = 1.f / g.sy, rx = 1.f / g.sx;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += long(gridDim.x) * blockDim.x) {
+    const int cg = int(i % G);
+    long r = i / G;
+    const int ix = int(r % g.w); r /= g.w;
+    const int iy = int(r % g.h);
+    const int n = int(r / g.h);
+    const int oy_lo = max(0, int(float(iy - 1) * ry) - 1), oy_hi = min(g.H - 1, int(float(iy + 1) * ry) + 1);
+    const int ox_lo = max(0, int(float(ix - 1) * rx) - 1), ox_hi = min(g.W - 1, int(float(ix + 1) * rx) + 1);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int oy = oy_lo; oy <= oy_hi; ++oy) {
+      int y0, y1;
+      float ly;
+      bil_coord(oy, g.sy, g.h, &y0, &y1, &ly);
+      float wy = 0.f;
+      if (y0 == iy) wy += 1.f - ly;
+      if (y1 == iy && y1 != y0) wy += ly;
+      if (wy == 0.f) continue;
+      for (int ox = ox_lo; ox <= ox_hi; ++ox) {
+        int x0, x1;
+        float lx;
+        bil_coord(ox, g.sx, g.w, &x0, &x1, &lx);
+        float wx = 0.f;
+        if (x0 == ix) wx += 1.f - lx;
+        if (x1 == ix && x1 != x0) wx += lx;
+        if (wx == 0.f) continue;
+        float v[8];
+        sp_unpack8(__ldg(reinterpret_cast<const uint4*>(gy + bil_out_index(g, n, oy, ox) + cg * 8)), v);
+        const float wgt = wy * wx;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(wgt, v[j], acc[j]);
+      }
+    }
+    float* o = gx + ((size_t(n) * g.h + iy) * g.w + ix) * g.C + cg * 8;
+    *reinterpret_cast<float4*>(o) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(o + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
+}
+
 // adjoint: scatter the output gradient into an fp32 [N,h,w,C] buffer (zeroed by the caller).
 __global__ void __launch_bounds__(256)
 bilinear_bwd_kernel(const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx, const BilGeom g) {
@@ -300,6 +347,12 @@ extern "C" int bgr_bilinear_bwd(const void* gy, int N, int h, int w, int C, int 
   BilGeom g;
   if (int rc = make_bil(&g, N, h, w, H, W, C, C, ldy, s2d)) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (g.sy >= 0.05f && g.sx >= 0.05f) {   // up-sampling by < 20x: a few dozen candidates per thread
+    bilinear_bwd_gather_kernel<<<sp_grid(long(N) * h * w * (C / 8)), 256, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(gy), gx, g);
+    BGR_LAUNCH_OK();
+    return BGR_OK;
+  }
   BGR_CUDA_OK(cudaMemsetAsync(gx, 0, sizeof(float) * size_t(N) * h * w * C, st));
   bilinear_bwd_kernel<<<sp_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(gy), gx, g);
   BGR_LAUNCH_OK();

@@ -230,10 +230,12 @@ def test_graphed_step_matches_eager():
     got = tuple(float(t) for t in gs(xf, yf))
     for i in range(2):
         assert abs(got[i] - ref[i]) <= max(4 * spread[i], 5e-3 * abs(ref[i])), (ref, spread, got)
-    for m0, m1 in ((G0.model.xception_features, G1.model.xception_features), (D0.xception_features, D1.xception_features)):
+    # G's entry layers see only the inputs (tight); D's also see the generator's output twice (loose)
+    for m0, m1, rt, at in ((G0.model.xception_features, G1.model.xception_features, 2e-3, 2e-4),
+                           (D0.xception_features, D1.xception_features, 5e-2, 5e-3)):
         for bn in ("bn1", "bn2"):
             for stat in ("running_mean", "running_var"):
-                torch.testing.assert_close(getattr(getattr(m1, bn), stat), getattr(getattr(m0, bn), stat), rtol=2e-3, atol=2e-4)
+                torch.testing.assert_close(getattr(getattr(m1, bn), stat), getattr(getattr(m0, bn), stat), rtol=rt, atol=at)
             assert int(getattr(m1, bn).num_batches_tracked) == int(getattr(m0, bn).num_batches_tracked)
     assert all(int(st["step"]) == 1 for st in go1.state.values()) and all(int(st["step"]) == 1 for st in do1.state.values())
     moved = max(float((p - before[n]).abs().max()) for n, p in G1.named_parameters())

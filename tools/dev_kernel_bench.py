@@ -20,9 +20,20 @@ def timeit(fn, n=5):
     return min(ts) * 1e3  # us
 
 
-for (N, H, W, C) in [(8, 384, 576, 128), (8, 192, 288, 256), (8, 96, 144, 728), (8, 48, 72, 728), (8, 48, 72, 1536)]:
-    x = torch.randn(N, H, W, C, device=dev).bfloat16()
-    g = torch.randn(N, H, W, C, device=dev).bfloat16()
+SHAPES = [(8, 384, 576, 128), (8, 192, 288, 256), (8, 96, 144, 728), (8, 48, 72, 728), (8, 48, 72, 1536)]
+if len(sys.argv) > 2 and sys.argv[1] == "--only":   # a short run for ncu
+    SHAPES = [SHAPES[int(sys.argv[2])]]
+
+
+def act(N, H, W, C):   # padded pixel stride as the product allocates it
+    t = K.act_empty((N, H, W, C), dev)
+    t.normal_()
+    return t
+
+
+for (N, H, W, C) in SHAPES:
+    x = act(N, H, W, C)
+    g = act(N, H, W, C)
     w9 = torch.randn(9, C, device=dev)
     nbytes = x.numel() * 2
     rows = []
@@ -35,7 +46,7 @@ for (N, H, W, C) in [(8, 384, 576, 128), (8, 192, 288, 256), (8, 96, 144, 728), 
     sums = torch.empty(2 * C, dtype=torch.float64, device=dev)
     rows.append(("bn_stats", timeit(lambda: K.bn_stats(x, sums)), nbytes))
     a = torch.ones(C, device=dev); b = torch.zeros(C, device=dev)
-    out = torch.empty_like(x)
+    out = K.act_empty((N, H, W, C), dev)
     rows.append(("bn_apply act", timeit(lambda: K.bn_apply(x, a, b, act=True, out=out)), 2 * nbytes))
     rows.append(("bn_apply act+res", timeit(lambda: K.bn_apply(x, a, b, res=g, act=True, out=out)), 3 * nbytes))
     mean = torch.zeros(C, device=dev); inv = torch.ones(C, device=dev)
