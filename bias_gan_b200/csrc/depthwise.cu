@@ -368,55 +368,114 @@ __device__ __forceinline__ bool march_item(const DwGeom& g, int segs, int RY, Ma
   return true;
 }
 
-// six column vectors of input row iy (zeros outside the image), all loads independent
-__device__ __forceinline__ void march_load_row(const __nv_bfloat16* base, const DwGeom& g, int ld, int iy,
-                                               int ox0, uint2 (&r)[6]) {
+// six column vectors of input row iy (zeros outside the image), all loads independent; bit c of the
+// returned mask says that column c lies inside the image
+__device__ __forceinline__ unsigned march_load_row(const __nv_bfloat16* base, const DwGeom& g, int ld, int iy,
+                                                   int ox0, uint2 (&r)[6]) {
   const bool rv = iy >= 0 && iy < g.H;
   const __nv_bfloat16* row = base + size_t(rv ? iy : 0) * g.W * ld;
+  unsigned mask = 0;
 #pragma unroll
   for (int c = 0; c < 6; ++c) {
     const int ix = ox0 - 1 + c;
     r[c] = make_uint2(0, 0);
-    if (rv && ix >= 0 && ix < g.W) r[c] = __ldg(reinterpret_cast<const uint2*>(row + size_t(ix) * ld));
+    if (rv && ix >= 0 && ix < g.W) {
+      r[c] = __ldg(reinterpret_cast<const uint2*>(row + size_t(ix) * ld));
+      mask |= 1u << c;
+    }
   }
+  return mask;
 }
 
-template <bool REVERSE>
+// 4 bf16 channels -> two packed fp32 pairs (bf16 -> fp32 is a 16-bit shift)
+__device__ __forceinline__ void dw_unpack22(const uint2& u, float2 (&f)[2]) {
+  f[0] = make_float2(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u));
+  f[1] = make_float2(__uint_as_float(u.y << 16), __uint_as_float(u.y & 0xffff0000u));
+}
+__device__ __forceinline__ uint2 dw_pack22(const float2 (&f)[2]) {
+  uint2 u;
+  __nv_bfloat162 lo = __floats2bfloat162_rn(f[0].x, f[0].y), hi = __floats2bfloat162_rn(f[1].x, f[1].y);
+  u.x = *reinterpret_cast<uint32_t*>(&lo);
+  u.y = *reinterpret_cast<uint32_t*>(&hi);
+  return u;
+}
+
+// Input transform fused into the load: XF 0 = none, 1 = a*x + b (BatchNorm with batch statistics
+// folded into a, b), 2 = LeakyReLU(a*x + b).  Pixels outside the image stay exactly zero (the
+// reference pads the *activated* tensor, deeplab.py:66-72).
+struct XfCoef {
+  float2 a[2], b[2];
+  float slope;
+};
+template <int XF>
+__device__ __forceinline__ void dw_transform(float2 (&v)[2], const XfCoef& t, bool inside) {
+  if (XF == 0) return;
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    float2 z = __ffma2_rn(t.a[p], v[p], t.b[p]);
+    if (XF == 2) {
+      z.x = fmaxf(z.x, t.slope * z.x);
+      z.y = fmaxf(z.y, t.slope * z.y);
+    }
+    v[p] = inside ? z : make_float2(0.f, 0.f);
+  }
+}
+template <int XF>
+__device__ __forceinline__ void dw_load_coef(XfCoef* t, const float* xa, const float* xb, float slope, int c0) {
+  if (XF == 0) return;
+  const float4 a = *reinterpret_cast<const float4*>(xa + c0), b = *reinterpret_cast<const float4*>(xb + c0);
+  t->a[0] = make_float2(a.x, a.y); t->a[1] = make_float2(a.z, a.w);
+  t->b[0] = make_float2(b.x, b.y); t->b[1] = make_float2(b.z, b.w);
+  t->slope = slope;
+}
+
+// Two scalar FMAs.  The packed FFMA2 form was measured: same time (the march waits on loads, not on
+// FMA issue) but 20-30 more registers for the aligned operand pairs, i.e. one resident block fewer.
+__device__ __forceinline__ float2 fma2s(const float2& a, const float2& b, const float2& c) {
+  return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+}
+
+template <bool REVERSE, int XF>
 __global__ void __launch_bounds__(128)
 dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
-                    __nv_bfloat16* __restrict__ y, const DwGeom g, int segs, int RY) {
+                    __nv_bfloat16* __restrict__ y, const DwGeom g, int segs, int RY,
+                    const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
   MarchItem it;
   if (!march_item(g, segs, RY, &it)) return;
-  float wr[9][kCpt];
+  float2 wr[9][2];
 #pragma unroll
   for (int k = 0; k < 9; ++k) {
     const float4 w0 = *reinterpret_cast<const float4*>(w + (REVERSE ? 8 - k : k) * g.C + it.c0);
-    wr[k][0] = w0.x; wr[k][1] = w0.y; wr[k][2] = w0.z; wr[k][3] = w0.w;
+    wr[k][0] = make_float2(w0.x, w0.y);
+    wr[k][1] = make_float2(w0.z, w0.w);
   }
-  float a0[4][kCpt], a1[4][kCpt], a2[4][kCpt];
+  XfCoef tc;
+  dw_load_coef<XF>(&tc, xa, xb, slope, it.c0);
+  float2 a0[4][2], a1[4][2], a2[4][2];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
-    for (int e = 0; e < kCpt; ++e) { a0[j][e] = 0.f; a1[j][e] = 0.f; a2[j][e] = 0.f; }
+    for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
   const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + it.c0;
   __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + it.c0;
   // input row iy adds to output rows iy+1 (ky=0), iy (ky=1), iy-1 (ky=2); then row iy-1 is complete
-  auto phase = [&](int iy, const uint2 (&rc)[6], uint2 (&rn)[6], float (&prev)[4][kCpt],
-                   float (&cur)[4][kCpt], float (&next)[4][kCpt]) {
-    if (iy + 1 <= it.oy1) march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);  // prefetch next row
+  auto phase = [&](int iy, const uint2 (&rc)[6], unsigned mc, uint2 (&rn)[6], unsigned& mn,
+                   float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
+    if (iy + 1 <= it.oy1) mn = march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);  // prefetch next row
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
-      float xv[kCpt];
-      dw_unpack4(rc[c], xv);
+      float2 xv[2];
+      dw_unpack22(rc[c], xv);
+      dw_transform<XF>(xv, tc, (mc >> c) & 1u);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int kx = c - j;
         if (kx < 0 || kx > 2) continue;
 #pragma unroll
-        for (int e = 0; e < kCpt; ++e) {
-          next[j][e] = fmaf(xv[e], wr[0 + kx][e], next[j][e]);
-          cur[j][e] = fmaf(xv[e], wr[3 + kx][e], cur[j][e]);
-          prev[j][e] = fmaf(xv[e], wr[6 + kx][e], prev[j][e]);
+        for (int e = 0; e < 2; ++e) {
+          next[j][e] = fma2s(xv[e], wr[0 + kx][e], next[j][e]);
+          cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
+          prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
         }
       }
     }
@@ -425,40 +484,44 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
       __nv_bfloat16* orow = yout + size_t(oy) * g.W * g.ldy;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        if (it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + size_t(it.ox0 + j) * g.ldy) = dw_pack4(prev[j]);
+        if (it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + size_t(it.ox0 + j) * g.ldy) = dw_pack22(prev[j]);
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j)
 #pragma unroll
-      for (int e = 0; e < kCpt; ++e) prev[j][e] = 0.f;
+      for (int e = 0; e < 2; ++e) prev[j][e] = make_float2(0.f, 0.f);
   };
   uint2 rA[6], rB[6];
-  march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
+  unsigned mA, mB = 0;
+  mA = march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
   for (int iy = it.oy0 - 1; iy <= it.oy1; iy += 6) {
-    phase(iy, rA, rB, a0, a1, a2);
-    if (iy + 1 <= it.oy1) phase(iy + 1, rB, rA, a1, a2, a0);
-    if (iy + 2 <= it.oy1) phase(iy + 2, rA, rB, a2, a0, a1);
-    if (iy + 3 <= it.oy1) phase(iy + 3, rB, rA, a0, a1, a2);
-    if (iy + 4 <= it.oy1) phase(iy + 4, rA, rB, a1, a2, a0);
-    if (iy + 5 <= it.oy1) phase(iy + 5, rB, rA, a2, a0, a1);
+    phase(iy, rA, mA, rB, mB, a0, a1, a2);
+    if (iy + 1 <= it.oy1) phase(iy + 1, rB, mB, rA, mA, a1, a2, a0);
+    if (iy + 2 <= it.oy1) phase(iy + 2, rA, mA, rB, mB, a2, a0, a1);
+    if (iy + 3 <= it.oy1) phase(iy + 3, rB, mB, rA, mA, a0, a1, a2);
+    if (iy + 4 <= it.oy1) phase(iy + 4, rA, mA, rB, mB, a1, a2, a0);
+    if (iy + 5 <= it.oy1) phase(iy + 5, rB, mB, rA, mA, a2, a0, a1);
   }
 }
 
 // dw[ky][kx][c] += sum dy[oy][ox] * x[oy+ky-1][ox+kx-1]; marching over input rows with the three
 // neighbouring dy rows kept (packed) in registers.  Rows of dy outside the segment count as zero.
+// XF: x is LeakyReLU/affine of the stored tensor, recomputed on load (see dw_transform).
+template <int XF>
 __global__ void __launch_bounds__(128)
 dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                      float* __restrict__ dw, const DwGeom g, int segs, int RY) {
+                      float* __restrict__ dw, const DwGeom g, int segs, int RY,
+                      const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
   extern __shared__ float sh[];  // [9][C]
   for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
   MarchItem it;
   if (march_item(g, segs, RY, &it)) {
-    float acc[9][kCpt];
+    float2 acc[9][2];
 #pragma unroll
-    for (int k = 0; k < 9; ++k)
-#pragma unroll
-      for (int e = 0; e < kCpt; ++e) acc[k][e] = 0.f;
+    for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
+    XfCoef tc;
+    dw_load_coef<XF>(&tc, xa, xb, slope, it.c0);
     const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + it.c0;
     const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + it.c0;
     auto load_dy = [&](int oy, uint2 (&d)[4]) {
@@ -471,48 +534,53 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
       }
     };
     // at input row iy: prev/cur/next = dy rows iy-1 / iy / iy+1 ; rn / dnn = prefetch for row iy+1
-    auto phase = [&](int iy, const uint2 (&rc)[6], uint2 (&rn)[6], const uint2 (&prev)[4], const uint2 (&cur)[4],
-                     const uint2 (&next)[4], uint2 (&dnn)[4]) {
+    auto phase = [&](int iy, const uint2 (&rc)[6], unsigned mc, uint2 (&rn)[6], unsigned& mn,
+                     const uint2 (&prev)[4], const uint2 (&cur)[4], const uint2 (&next)[4], uint2 (&dnn)[4]) {
       if (iy + 1 <= it.oy1) {
-        march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);
+        mn = march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);
         load_dy(iy + 2, dnn);
       }
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
-        float xv[kCpt];
-        dw_unpack4(rc[c], xv);
+        float2 xv[2];
+        dw_unpack22(rc[c], xv);
+        dw_transform<XF>(xv, tc, (mc >> c) & 1u);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int kx = c - j;
           if (kx < 0 || kx > 2) continue;
-          float gp[kCpt], gc[kCpt], gn[kCpt];
-          dw_unpack4(prev[j], gp);  // oy = iy-1 -> ky = 2
-          dw_unpack4(cur[j], gc);   // oy = iy   -> ky = 1
-          dw_unpack4(next[j], gn);  // oy = iy+1 -> ky = 0
+          float2 gp[2], gc[2], gn[2];
+          dw_unpack22(prev[j], gp);  // oy = iy-1 -> ky = 2
+          dw_unpack22(cur[j], gc);   // oy = iy   -> ky = 1
+          dw_unpack22(next[j], gn);  // oy = iy+1 -> ky = 0
 #pragma unroll
-          for (int e = 0; e < kCpt; ++e) {
-            acc[0 + kx][e] = fmaf(gn[e], xv[e], acc[0 + kx][e]);
-            acc[3 + kx][e] = fmaf(gc[e], xv[e], acc[3 + kx][e]);
-            acc[6 + kx][e] = fmaf(gp[e], xv[e], acc[6 + kx][e]);
+          for (int e = 0; e < 2; ++e) {
+            acc[0 + kx][e] = fma2s(gn[e], xv[e], acc[0 + kx][e]);
+            acc[3 + kx][e] = fma2s(gc[e], xv[e], acc[3 + kx][e]);
+            acc[6 + kx][e] = fma2s(gp[e], xv[e], acc[6 + kx][e]);
           }
         }
       }
     };
     uint2 rA[6], rB[6], d0[4], d1[4], d2[4], d3[4];
-    march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
+    unsigned mA, mB = 0;
+    mA = march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
     load_dy(it.oy0 - 2, d0);
     load_dy(it.oy0 - 1, d1);
     load_dy(it.oy0, d2);
     for (int iy = it.oy0 - 1; iy <= it.oy1; iy += 4) {
-      phase(iy, rA, rB, d0, d1, d2, d3);
-      if (iy + 1 <= it.oy1) phase(iy + 1, rB, rA, d1, d2, d3, d0);
-      if (iy + 2 <= it.oy1) phase(iy + 2, rA, rB, d2, d3, d0, d1);
-      if (iy + 3 <= it.oy1) phase(iy + 3, rB, rA, d3, d0, d1, d2);
+      phase(iy, rA, mA, rB, mB, d0, d1, d2, d3);
+      if (iy + 1 <= it.oy1) phase(iy + 1, rB, mB, rA, mA, d1, d2, d3, d0);
+      if (iy + 2 <= it.oy1) phase(iy + 2, rA, mA, rB, mB, d2, d3, d0, d1);
+      if (iy + 3 <= it.oy1) phase(iy + 3, rB, mB, rA, mA, d3, d0, d1, d2);
     }
 #pragma unroll
-    for (int k = 0; k < 9; ++k)
-#pragma unroll
-      for (int e = 0; e < kCpt; ++e) atomicAdd(&sh[k * g.C + it.c0 + e], acc[k][e]);
+    for (int k = 0; k < 9; ++k) {
+      atomicAdd(&sh[k * g.C + it.c0 + 0], acc[k][0].x);
+      atomicAdd(&sh[k * g.C + it.c0 + 1], acc[k][0].y);
+      atomicAdd(&sh[k * g.C + it.c0 + 2], acc[k][1].x);
+      atomicAdd(&sh[k * g.C + it.c0 + 3], acc[k][1].y);
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
@@ -577,7 +645,7 @@ extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, co
     int segs, RY;
     unsigned blocks;
     march_plan(g, &segs, &RY, &blocks);
-    dw_march_fwd_kernel<false><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY);
+    dw_march_fwd_kernel<false, 0><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY, nullptr, nullptr, 0.f);
   } else if (!launch_fwd_strip<false>(X, w, Y, g, st))
     dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, st>>>(X, w, Y, g);
   BGR_LAUNCH_OK();
@@ -601,7 +669,7 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
       int segs, RY;
       unsigned blocks;
       march_plan(r, &segs, &RY, &blocks);
-      dw_march_fwd_kernel<true><<<blocks, 128, 0, st>>>(DY, w, DX, r, segs, RY);
+      dw_march_fwd_kernel<true, 0><<<blocks, 128, 0, st>>>(DY, w, DX, r, segs, RY, nullptr, nullptr, 0.f);
       done = true;
     } else {
       done = launch_fwd_strip<true>(DY, w, DX, r, st);
@@ -632,6 +700,60 @@ static int launch_wgrad_strip(const __nv_bfloat16* x, const __nv_bfloat16* dy, f
   return BGR_OK;
 }
 
+template <int XF>
+static int launch_march_wgrad(const __nv_bfloat16* x, const __nv_bfloat16* dy, float* dw, const DwGeom& g,
+                              const float* xa, const float* xb, float slope, cudaStream_t st) {
+  auto kern = dw_march_wgrad_kernel<XF>;
+  static bool configured = false;
+  if (!configured) {
+    BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    configured = true;
+  }
+  int segs, RY;
+  unsigned blocks;
+  march_plan(g, &segs, &RY, &blocks);
+  kern<<<blocks, 128, 9 * g.C * sizeof(float), st>>>(x, dy, dw, g, segs, RY, xa, xb, slope);
+  return BGR_OK;
+}
+
+// Stride-1, dilation-1 depthwise conv of act(a*x + b) without materialising it: the BatchNorm
+// (+LeakyReLU) that precedes the depthwise conv of every SeparableConv2d_same inside a block
+// (deeplab.py:100-118) is applied while loading.  act: 0 = affine only, 1 = LeakyReLU(slope).
+extern "C" int bgr_dw_fwd_bn(const void* x, int N, int H, int W, int C, int ldx, const float* w,
+                             const float* a, const float* b, int act, float slope, void* y, int ldy,
+                             void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, 1, 1, ldx, ldy)) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto Y = static_cast<__nv_bfloat16*>(y);
+  int segs, RY;
+  unsigned blocks;
+  march_plan(g, &segs, &RY, &blocks);
+  if (act) dw_march_fwd_kernel<false, 2><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY, a, b, slope);
+  else dw_march_fwd_kernel<false, 1><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY, a, b, slope);
+  BGR_LAUNCH_OK();
+  return BGR_OK;
+}
+
+// Weight gradient of bgr_dw_fwd_bn: x is the stored pre-BatchNorm tensor, transformed on load.
+extern "C" int bgr_dw_wgrad_bn(const void* x, int N, int H, int W, int C, int ldx, const float* a,
+                               const float* b, int act, float slope, const void* dy, int ldy, float* dw,
+                               void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, 1, 1, ldx, ldy)) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * C, st));
+  if (9 * C * sizeof(float) > 160 * 1024) return fail(BGR_ERR_ARG, "depthwise wgrad: too many channels");
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto DY = static_cast<const __nv_bfloat16*>(dy);
+  int rc = act ? launch_march_wgrad<2>(X, DY, dw, g, a, b, slope, st)
+               : launch_march_wgrad<1>(X, DY, dw, g, a, b, slope, st);
+  if (rc) return rc;
+  BGR_LAUNCH_OK();
+  return BGR_OK;
+}
+
 extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, const void* dy, int ldy,
                             int stride, int dil, float* dw, void* stream) {
   DwGeom g;
@@ -642,17 +764,7 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto DY = static_cast<const __nv_bfloat16*>(dy);
   int rc = BGR_OK;
-  if (stride == 1 && dil == 1) {
-    static bool configured = false;
-    if (!configured) {
-      BGR_CUDA_OK(cudaFuncSetAttribute(dw_march_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-      configured = true;
-    }
-    int segs, RY;
-    unsigned blocks;
-    march_plan(g, &segs, &RY, &blocks);
-    dw_march_wgrad_kernel<<<blocks, 128, 9 * C * sizeof(float), st>>>(X, DY, dw, g, segs, RY);
-  }
+  if (stride == 1 && dil == 1) rc = launch_march_wgrad<0>(X, DY, dw, g, nullptr, nullptr, 0.f, st);
   else if (stride == 1 && dil == 2) rc = launch_wgrad_strip<1, 2>(X, DY, dw, g, st);
   else if (stride == 2 && dil == 1) rc = launch_wgrad_strip<2, 1>(X, DY, dw, g, st);
   else {

@@ -126,10 +126,14 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __res
 // ---------------------------------------------------------------- backward, pass 1:
 // dyh = g * act'(out) (bf16, = gradient of the residual input too) and per-channel
 // sums s1 = sum dyh, s2 = sum dyh * xhat  with xhat = (x - mean) * invstd.
-template <bool ACT>
+// ACT: 0 = no activation, 1 = sign of the stored activation output, 2 = sign recomputed from
+// a*x + b (the activated tensor was never stored, see bgr_dw_fwd_bn); then `out` carries a and
+// `out + C` ... is unused: a, b come in through `xa`, `xb`.
+template <int ACT>
 __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ out,
-                     int ldo, const __nv_bfloat16* __restrict__ x, int ldx,
+                     int ldo, const float* __restrict__ xa, const float* __restrict__ xb,
+                     const __nv_bfloat16* __restrict__ x, int ldx,
                      const float* __restrict__ mean, const float* __restrict__ invstd,
                      __nv_bfloat16* __restrict__ dyh, int ldd, long M, int C, int rows_per_block, float slope,
                      double* __restrict__ sums /* [2][C] */) {
@@ -142,18 +146,23 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
   for (int gi = threadIdx.x % m.G; gi < m.G; gi += (m.G >= 256 ? 256 : m.G)) {
     const int r = m.G >= 256 ? 0 : threadIdx.x / m.G;
     if (r >= m.R) break;
-    float mu[8], is[8], s1[8], s2[8];
+    float mu[8], is[8], s1[8], s2[8], ca[8], cb[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { mu[j] = mean[gi * 8 + j]; is[j] = invstd[gi * 8 + j]; s1[j] = 0.f; s2[j] = 0.f; }
+    for (int j = 0; j < 8; ++j) {
+      mu[j] = mean[gi * 8 + j]; is[j] = invstd[gi * 8 + j]; s1[j] = 0.f; s2[j] = 0.f;
+      ca[j] = ACT == 2 ? xa[gi * 8 + j] : 0.f;
+      cb[j] = ACT == 2 ? xb[gi * 8 + j] : 0.f;
+    }
     for (long row = r0 + r; row < r1; row += m.R) {
       float gv[8], xv[8], ov[8];
       unpack8(*reinterpret_cast<const uint4*>(g + row * ldg + gi * 8), gv);
       unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + gi * 8), xv);
-      if (ACT) unpack8(*reinterpret_cast<const uint4*>(out + row * ldo + gi * 8), ov);
+      if (ACT == 1) unpack8(*reinterpret_cast<const uint4*>(out + row * ldo + gi * 8), ov);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float d = gv[j];
-        if (ACT) d = ov[j] > 0.f ? d : slope * d;
+        if (ACT == 1) d = ov[j] > 0.f ? d : slope * d;
+        if (ACT == 2) d = fmaf(ca[j], xv[j], cb[j]) > 0.f ? d : slope * d;
         // statistics are taken from the bf16-rounded value pass 2 will read back, so that the
         // mean subtraction cancels exactly (matters when M is tiny, e.g. the image-pool branch)
         d = __bfloat162float(__float2bfloat16_rn(d));
@@ -277,10 +286,10 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
   return BGR_OK;
 }
 
-extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
-                               const float* mean, const float* invstd, const float* gamma, int act,
-                               float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
-                               float* coef_ws, void* stream) {
+static int bn_backward_impl(const void* g, int ldg, const void* out, int ldo, const float* xa, const float* xb,
+                            const void* x, int ldx, const float* mean, const float* invstd,
+                            const float* gamma, int act, float slope, long M, int C, void* dyh, void* dx,
+                            int ldd, double* sums, float* coef_ws, void* stream) {
   BGR_CHECK_C8(C);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   BGR_CUDA_OK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
@@ -290,8 +299,9 @@ extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo,
   auto O = static_cast<const __nv_bfloat16*>(out);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto D = static_cast<__nv_bfloat16*>(dyh);
-  if (act) bn_bwd_reduce_kernel<true><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
-  else bn_bwd_reduce_kernel<false><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  if (act == 2) bn_bwd_reduce_kernel<2><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  else bn_bwd_reduce_kernel<0><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
   BGR_LAUNCH_OK();
   bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
   BGR_LAUNCH_OK();
@@ -299,4 +309,22 @@ extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo,
                                                                     static_cast<__nv_bfloat16*>(dx), ldd, M, C);
   BGR_LAUNCH_OK();
   return BGR_OK;
+}
+
+extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
+                               const float* mean, const float* invstd, const float* gamma, int act,
+                               float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
+                               float* coef_ws, void* stream) {
+  return bn_backward_impl(g, ldg, out, ldo, nullptr, nullptr, x, ldx, mean, invstd, gamma, act ? 1 : 0, slope, M, C,
+                          dyh, dx, ldd, sums, coef_ws, stream);
+}
+
+// Backward of a BatchNorm(+LeakyReLU) whose output was consumed on the fly (bgr_dw_fwd_bn): the
+// activation derivative is recomputed from a*x + b instead of being read from a stored output.
+extern "C" int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const float* b, const void* x,
+                                         int ldx, const float* mean, const float* invstd,
+                                         const float* gamma, int act, float slope, long M, int C, void* dyh,
+                                         void* dx, int ldd, double* sums, float* coef_ws, void* stream) {
+  return bn_backward_impl(g, ldg, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
+                          ldd, sums, coef_ws, stream);
 }

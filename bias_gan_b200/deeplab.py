@@ -10,11 +10,16 @@ mutates the block input, so the skip path and `low_level_feat` see the activated
 reproduced by fusing that activation into the producer of each block input.
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
 
 from . import functional as F_
+
+
+# debugging switch: False materialises every BatchNorm output (bn_apply) before its depthwise conv
+FUSE_BN_INTO_DEPTHWISE = os.environ.get("BGR_NO_BN_DW_FUSION", "0") != "1"
 
 
 def _hold_conv(cin, cout, k, groups=1, bias=False):
@@ -73,24 +78,31 @@ class Block(nn.Module):
         mods = list(self.rep)
         x = a
         i = 0
-        pending = None  # (raw conv output, bn) waiting for its fused BN(+act)
+        pending = None  # (raw conv output [+ its BatchNorm sums], bn, followed by LeakyReLU?)
         tail_bn = None
         while i < len(mods):
             m = mods[i]
             if isinstance(m, SeparableConv2d_same):
-                if pending is not None:  # BN followed directly by a conv: no activation between
-                    x = F_.bn_act(pending[0], pending[1], act=False)
-                    pending = None
                 has_bn = i + 1 < len(mods) and isinstance(mods[i + 1], nn.BatchNorm2d)
-                y = m(x, want_stats=has_bn and mods[i + 1].training)
+                want = has_bn and mods[i + 1].training
+                if pending is not None:
+                    py, pbn, pact = pending
+                    pending = None
+                    if m.stride == 1 and m.dilation == 1 and pbn.training and FUSE_BN_INTO_DEPTHWISE:
+                        # BatchNorm (+LeakyReLU) applied while the depthwise kernel loads: never stored
+                        t = F_.bn_act_depthwise(py, pbn, m.conv1.weight, act=pact)
+                        y = F_.conv2d(t, m.pointwise.weight, want_stats=want)
+                    else:
+                        y = m(F_.bn_act(py, pbn, act=pact), want_stats=want)
+                else:
+                    y = m(x, want_stats=want)
                 if has_bn:
-                    pending = (y, mods[i + 1])
+                    bn = mods[i + 1]
                     i += 2
-                    # is this BN followed by the (identity-held) relu?
-                    if i < len(mods) and isinstance(mods[i], nn.Identity):
-                        x = F_.bn_act(pending[0], pending[1], act=True)
-                        pending = None
+                    act = i < len(mods) and isinstance(mods[i], nn.Identity)  # the (identity-held) relu
+                    if act:
                         i += 1
+                    pending = (y, bn, act)
                     continue
                 x = y
             i += 1

@@ -143,6 +143,54 @@ class _BNAct(torch.autograd.Function):
         return dx, ggamma, gbeta, gres, None, None, None, None, None, None
 
 
+class _BNActDepthwise(torch.autograd.Function):
+    """t = depthwise3x3(act(BatchNorm_train(y))) (stride 1, dilation 1) without storing the activated
+    tensor: the statistics come from the producing conv's epilogue, the normalisation and LeakyReLU
+    are applied while the depthwise kernel loads y, and backward recomputes them the same way."""
+
+    @staticmethod
+    def forward(ctx, y, sums, gamma, beta, running_mean, running_var, eps, momentum, act, dw_weight):
+        M = y.numel() // y.shape[-1]
+        C = y.shape[-1]
+        if sums is None:
+            sums = K.bn_stats(y)
+        mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var)
+        w9 = L.cached(dw_weight, "dw9", lambda w: w.reshape(C, 9).t().contiguous().float())
+        ctx.save_for_backward(y, mean, invstd, a, b, gamma, w9)
+        ctx.act = act
+        return K.dw_fwd_bn(y, w9, a, b, act, SLOPE)
+
+    @staticmethod
+    def backward(ctx, g):
+        y, mean, invstd, a, b, gamma, w9 = ctx.saved_tensors
+        g = _bf16c(g)
+        C = y.shape[-1]
+        gw = None
+        if ctx.needs_input_grad[9]:
+            gw = K.dw_wgrad_bn(y, a, b, ctx.act, g, SLOPE).t().reshape(C, 1, 3, 3)
+        gy = ggamma = gbeta = None
+        if ctx.needs_input_grad[0]:
+            gx = K.dw_dgrad(g, w9, 1, 1, tuple(y.shape))
+            gy, _, bsums = K.bn_backward_recompute(gx, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
+            ggamma = bsums[C:].float() if ctx.needs_input_grad[2] else None
+            gbeta = bsums[:C].float() if ctx.needs_input_grad[3] else None
+        return gy, None, ggamma, gbeta, None, None, None, None, None, gw
+
+
+def bn_act_depthwise(y, bn, dw_weight, act=True):
+    """depthwise3x3(bn_act(y, bn, act=act), dw_weight) for a training-mode BatchNorm, fused (see
+    _BNActDepthwise).  `y` may be the (y, sums) pair of a conv called with want_stats=True."""
+    sums = None
+    if isinstance(y, tuple):
+        y, sums = y
+    if not bn.training:
+        return depthwise3x3(bn_act(y, bn, act=act), dw_weight)
+    if bn.num_batches_tracked is not None:
+        bn.num_batches_tracked += 1
+    return _BNActDepthwise.apply(y, sums, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, bn.momentum,
+                                 act, dw_weight)
+
+
 class _AffineAct(torch.autograd.Function):
     """Eval-mode BatchNorm (running statistics folded into a, b) + activation; forward only."""
 

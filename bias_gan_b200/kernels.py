@@ -224,6 +224,43 @@ def dw_fwd(x, w9, stride, dil, out=None):
     return out
 
 
+def dw_fwd_bn(x, w9, a, b, act, slope=0.2, out=None):
+    """Stride-1 dilation-1 depthwise conv of act(a*x + b) with the transform applied on load."""
+    N, H, W, C, ldx = _nhwc_view(x)
+    if out is None:
+        out = act_empty((N, H, W, C), x.device)
+    _, _, _, _, ldy = _nhwc_view(out)
+    assert w9.dtype == torch.float32 and tuple(w9.shape) == (9, C) and w9.is_contiguous()
+    assert a.dtype == b.dtype == torch.float32 and a.numel() == b.numel() == C
+    check(_lib.lib().bgr_dw_fwd_bn(ptr(x), N, H, W, C, ldx, ptr(w9), ptr(a), ptr(b), int(act), c_float(slope),
+                                   ptr(out), ldy, stream_ptr()))
+    return out
+
+
+def dw_wgrad_bn(x, a, b, act, gy, slope=0.2):
+    N, H, W, C, ldx = _nhwc_view(x)
+    _, _, _, _, ldy = _nhwc_view(gy)
+    dw = torch.empty((9, C), dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_dw_wgrad_bn(ptr(x), N, H, W, C, ldx, ptr(a), ptr(b), int(act), c_float(slope), ptr(gy), ldy,
+                                     ptr(dw), stream_ptr()))
+    return dw
+
+
+def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2):
+    """bn_backward for a BatchNorm(+act) whose output was never stored: act' from sign(a*x + b)."""
+    M, C, ldx = _rows(x)
+    Mg, Cg, ldg = _rows(g)
+    assert (Mg, Cg) == (M, C)
+    dyh = act_empty(x.shape, x.device)
+    dx = act_empty(x.shape, x.device)
+    sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+    coef = torch.empty(5 * C, dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_bn_backward_recompute(ptr(g), ldg, ptr(a), ptr(b), ptr(x), ldx, ptr(mean), ptr(invstd),
+                                               ptr(gamma), int(act), c_float(slope), c_long(M), C, ptr(dyh), ptr(dx),
+                                               _rows(dx)[2], ptr(sums), ptr(coef), stream_ptr()))
+    return dx, dyh, sums
+
+
 def dw_dgrad(gy, w9, stride, dil, in_shape):
     N, H, W, C = in_shape
     _, _, _, _, ldy = _nhwc_view(gy)

@@ -130,6 +130,13 @@ int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void
                     long M, int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
                     void* stream);
 
+/* Same, for a BatchNorm(+LeakyReLU) whose activated output was never stored because the depthwise
+ * conv that follows applied it while loading (bgr_dw_fwd_bn): act' comes from sign(a*x + b). */
+int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const float* b, const void* x, int ldx,
+                              const float* mean, const float* invstd, const float* gamma, int act,
+                              float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
+                              float* coef_ws, void* stream);
+
 /* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
  * w, dw: fp32 [9][C].  Output size ceil(H/stride) x ceil(W/stride). */
 int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* w, int stride, int dil,
@@ -138,6 +145,14 @@ int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy, const floa
                  void* dx, int ldx, void* stream);
 int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, const void* dy, int ldy, int stride,
                  int dil, float* dw, void* stream);
+/* Stride-1 dilation-1 depthwise conv of act(a[c]*x + b[c]) (act: 0 affine, 1 LeakyReLU(slope)) with
+ * the transform applied on load and zero padding applied after it: BatchNorm2d (+LeakyReLU) followed
+ * by SeparableConv2d_same.conv1 (deeplab.py:100-118,75-87) without storing the activated tensor;
+ * and its weight gradient (x = the stored pre-BatchNorm tensor). */
+int bgr_dw_fwd_bn(const void* x, int N, int H, int W, int C, int ldx, const float* w, const float* a,
+                  const float* b, int act, float slope, void* y, int ldy, void* stream);
+int bgr_dw_wgrad_bn(const void* x, int N, int H, int W, int C, int ldx, const float* a, const float* b,
+                    int act, float slope, const void* dy, int ldy, float* dw, void* stream);
 /* y[n,oy,ox,:] = x[n,2oy,2ox,:] (input of the stride-2 1x1 skip convs, deeplab.py:95) + adjoint. */
 int bgr_subsample2(const void* x, int N, int H, int W, int C, int ldx, void* y, int ldy, void* stream);
 int bgr_subsample2_bwd(const void* dy, int N, int H, int W, int C, int ldy, void* dx, int ldx, void* stream);

@@ -207,6 +207,37 @@ def test_bn_act_train(dev, C, M_shape, act, with_res):
     assert int(bn_p.num_batches_tracked) == 1
 
 
+@pytest.mark.parametrize("C,N,H,W", [(128, 2, 24, 36), (728, 2, 13, 9), (1024, 1, 6, 7)])
+@pytest.mark.parametrize("act", [True, False])
+def test_bn_act_depthwise_fused(dev, C, N, H, W, act):
+    """BatchNorm(+LeakyReLU) applied while the depthwise kernel loads (bgr_dw_fwd_bn / bgr_dw_wgrad_bn /
+    bgr_bn_backward_recompute) against PyTorch fp32 BatchNorm2d -> leaky_relu -> F.pad -> depthwise conv."""
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(9)
+    y = (torch.randn(N, C, H, W, generator=g) * 1.5 + 0.3).to(dev).bfloat16()
+    w = (torch.randn(C, 1, 3, 3, generator=g) / 3).to(dev)
+    go = torch.randn(N, C, H, W, generator=g).to(dev).bfloat16()
+    bn_ref, bn_p = torch.nn.BatchNorm2d(C).to(dev).train(), torch.nn.BatchNorm2d(C).to(dev).train()
+    with torch.no_grad():
+        bn_ref.weight.copy_(1 + 0.1 * torch.randn(C, generator=g)); bn_ref.bias.copy_(0.1 * torch.randn(C, generator=g))
+        bn_p.load_state_dict(bn_ref.state_dict())
+    yr, wr = y.float().requires_grad_(True), w.clone().requires_grad_(True)
+    o = bn_ref(yr)
+    if act:
+        o = F.leaky_relu(o, 0.2)
+    o = F.conv2d(F.pad(o, (1, 1, 1, 1)), wr, groups=C)
+    o.backward(go.float())
+    yp, wp = nhwc(y).requires_grad_(True), w.clone().requires_grad_(True)
+    op = F_.bn_act_depthwise(yp, bn_p, wp, act=act)
+    op.backward(nhwc(go))
+    assert rel(nchw(op), o) < 4e-3
+    assert rel(nchw(yp.grad), yr.grad) < 1e-2
+    assert rel(wp.grad, wr.grad) < 2e-3
+    assert rel(bn_p.weight.grad, bn_ref.weight.grad) < 5e-3
+    assert rel(bn_p.bias.grad, bn_ref.bias.grad) < 5e-3
+    torch.testing.assert_close(bn_p.running_var, bn_ref.running_var, rtol=1e-3, atol=1e-4)
+
+
 # --------------------------------------------------------------------------------- depthwise
 @pytest.mark.parametrize("C,H,W,stride,dil", [(128, 24, 36, 1, 1), (128, 25, 37, 2, 1), (728, 6, 9, 1, 1),
                                               (1536, 5, 7, 1, 2), (256, 12, 18, 2, 1)])
