@@ -343,6 +343,9 @@ def main():
     pk, pk_src = peaks()
     value = world * B / (ms_step * 1e-3)
     e2e = world * B / (ms_e2e * 1e-3)
+    for m in (G, D):   # rank 0 alone runs the instrumented step: no collectives in it
+        if hasattr(m, "grad_sync"):
+            m.grad_sync.enabled = False
     flops, ms_conv, n_conv, by_kind = conv_roofline_step(eager_step, torch, K)  # kernel by kernel, not the graph
     ach = flops / (ms_conv * 1e-3) / 1e12
     line = {"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,

@@ -39,11 +39,14 @@ class BucketedAllReduce:
         self.launched = [False] * len(self.buckets)
         self.inflight = []
         self.handles = []
+        self.enabled = True   # False: gradients stay local (single-rank diagnostics between collective steps)
         if self.world > 1:
             for p in params:
                 self.handles.append(p.register_post_accumulate_grad_hook(self._hook))
 
     def _hook(self, p):
+        if not self.enabled:
+            return
         bi = self.bucket_of[p]
         self.pending[bi] -= 1
         if self.pending[bi] == 0 and not self.launched[bi]:
@@ -62,7 +65,7 @@ class BucketedAllReduce:
     def finish(self):
         """Wait for all buckets (launching the ones backward did not complete) and write the
         averaged gradients back.  Call between backward() and optimizer.step()."""
-        if self.world == 1:
+        if self.world == 1 or not self.enabled:
             return
         for bi in range(len(self.buckets)):
             if not self.launched[bi] and self.pending[bi] < len(self.buckets[bi]):
