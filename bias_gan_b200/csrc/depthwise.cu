@@ -159,7 +159,9 @@ dw_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
     if (G < 256) break;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
+  // sh is [9][C]; dw is stored [C][9] = the parameter's own [C,1,3,3] layout
+  // (contiguous global reductions; the transposition happens on the shared-memory side)
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[(i % 9) * g.C + i / 9]);
 }
 
 // y[n,oy,ox,:] = x[n,2oy,2ox,:]  /  adjoint: dx = 0 except dx[n,2oy,2ox,:] = dy[n,oy,ox,:]
@@ -325,7 +327,9 @@ dw_wgrad_strip_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
     if (G < 256) break;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
+  // sh is [9][C]; dw is stored [C][9] = the parameter's own [C,1,3,3] layout
+  // (contiguous global reductions; the transposition happens on the shared-memory side)
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[(i % 9) * g.C + i / 9]);
 }
 
 // ---------------------------------------------------------------- column-marching variants
@@ -350,22 +354,22 @@ __device__ __forceinline__ uint2 dw_pack4(const float (&f)[4]) {
 }
 
 struct MarchItem {
-  int c0, ox0, oy0, oy1, n;
+  int ox0, oy0, oy1, n;
 };
-__device__ __forceinline__ bool march_item(const DwGeom& g, int segs, int RY, MarchItem* it) {
-  const int G = g.C / kCpt;
+// Work decomposition of the marching kernels.  A block is 4 warps that share one block of 32 channel
+// groups (128 channels, lane = group); each warp loops over items = (image, row segment, 4-column
+// strip).  Weights / reduction registers live for the whole loop, and the weight-gradient kernel
+// flushes 9 x 128 values per block instead of 9 x C.
+struct MarchSched {
+  int segs, RY, cblocks, items;
+};
+__device__ __forceinline__ void march_decode(const DwGeom& g, const MarchSched& s, int item, MarchItem* it) {
   const int strips = (g.W + 3) >> 2;
-  const unsigned total = unsigned(g.N) * segs * strips * G;
-  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= total) return false;
-  it->c0 = (i % G) * kCpt;
-  unsigned t = i / G;
-  it->ox0 = (t % strips) * 4;
-  t /= strips;
-  it->oy0 = (t % segs) * RY;
-  it->n = t / segs;
-  it->oy1 = min(it->oy0 + RY, g.H);
-  return true;
+  it->ox0 = (item % strips) * 4;
+  const int t = item / strips;
+  it->oy0 = (t % s.segs) * s.RY;
+  it->n = t / s.segs;
+  it->oy1 = min(it->oy0 + s.RY, g.H);
 }
 
 // six column vectors of input row iy (zeros outside the image), all loads independent; bit c of the
@@ -436,28 +440,32 @@ __device__ __forceinline__ float2 fma2s(const float2& a, const float2& b, const 
 }
 
 template <bool REVERSE, int XF>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 3)
 dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
-                    __nv_bfloat16* __restrict__ y, const DwGeom g, int segs, int RY,
+                    __nv_bfloat16* __restrict__ y, const DwGeom g, const MarchSched sc,
                     const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
-  MarchItem it;
-  if (!march_item(g, segs, RY, &it)) return;
+  const int c0 = ((blockIdx.x % sc.cblocks) * 32 + (threadIdx.x & 31)) * kCpt;
+  if (c0 >= g.C) return;
   float2 wr[9][2];
 #pragma unroll
   for (int k = 0; k < 9; ++k) {
-    const float4 w0 = *reinterpret_cast<const float4*>(w + (REVERSE ? 8 - k : k) * g.C + it.c0);
+    const float4 w0 = *reinterpret_cast<const float4*>(w + (REVERSE ? 8 - k : k) * g.C + c0);
     wr[k][0] = make_float2(w0.x, w0.y);
     wr[k][1] = make_float2(w0.z, w0.w);
   }
   XfCoef tc;
-  dw_load_coef<XF>(&tc, xa, xb, slope, it.c0);
+  dw_load_coef<XF>(&tc, xa, xb, slope, c0);
+  const int item_step = (gridDim.x / sc.cblocks) * 4;
+  for (int item = (blockIdx.x / sc.cblocks) * 4 + (threadIdx.x >> 5); item < sc.items; item += item_step) {
+  MarchItem it;
+  march_decode(g, sc, item, &it);
   float2 a0[4][2], a1[4][2], a2[4][2];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
     for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
-  const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + it.c0;
-  __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + it.c0;
+  const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
+  __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + c0;
   // input row iy adds to output rows iy+1 (ky=0), iy (ky=1), iy-1 (ky=2); then row iy-1 is complete
   auto phase = [&](int iy, const uint2 (&rc)[6], unsigned mc, uint2 (&rn)[6], unsigned& mn,
                    float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
@@ -502,28 +510,35 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
     if (iy + 4 <= it.oy1) phase(iy + 4, rA, mA, rB, mB, a1, a2, a0);
     if (iy + 5 <= it.oy1) phase(iy + 5, rB, mB, rA, mA, a2, a0, a1);
   }
+  }  // items
 }
 
 // dw[ky][kx][c] += sum dy[oy][ox] * x[oy+ky-1][ox+kx-1]; marching over input rows with the three
 // neighbouring dy rows kept (packed) in registers.  Rows of dy outside the segment count as zero.
 // XF: x is LeakyReLU/affine of the stored tensor, recomputed on load (see dw_transform).
 template <int XF>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 3)
 dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                      float* __restrict__ dw, const DwGeom g, int segs, int RY,
+                      float* __restrict__ dw, const DwGeom g, const MarchSched sc,
                       const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
-  extern __shared__ float sh[];  // [9][C]
-  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
+  __shared__ float sh[9 * 128];  // [9][128 channels of this block]
+  for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
-  MarchItem it;
-  if (march_item(g, segs, RY, &it)) {
+  const int cb0 = (blockIdx.x % sc.cblocks) * 128;
+  const int lc = (threadIdx.x & 31) * kCpt;      // channel offset inside the block's 128
+  const int c0 = cb0 + lc;
+  if (c0 < g.C) {
     float2 acc[9][2];
 #pragma unroll
     for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
     XfCoef tc;
-    dw_load_coef<XF>(&tc, xa, xb, slope, it.c0);
-    const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + it.c0;
-    const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + it.c0;
+    dw_load_coef<XF>(&tc, xa, xb, slope, c0);
+    const int item_step = (gridDim.x / sc.cblocks) * 4;
+    for (int item = (blockIdx.x / sc.cblocks) * 4 + (threadIdx.x >> 5); item < sc.items; item += item_step) {
+    MarchItem it;
+    march_decode(g, sc, item, &it);
+    const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
+    const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + c0;
     auto load_dy = [&](int oy, uint2 (&d)[4]) {
       const bool ok = oy >= it.oy0 && oy < it.oy1;
 #pragma unroll
@@ -574,29 +589,41 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
       if (iy + 2 <= it.oy1) phase(iy + 2, rA, mA, rB, mB, d2, d3, d0, d1);
       if (iy + 3 <= it.oy1) phase(iy + 3, rB, mB, rA, mA, d3, d0, d1, d2);
     }
+    }  // items
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
-      atomicAdd(&sh[k * g.C + it.c0 + 0], acc[k][0].x);
-      atomicAdd(&sh[k * g.C + it.c0 + 1], acc[k][0].y);
-      atomicAdd(&sh[k * g.C + it.c0 + 2], acc[k][1].x);
-      atomicAdd(&sh[k * g.C + it.c0 + 3], acc[k][1].y);
+      atomicAdd(&sh[k * 128 + lc + 0], acc[k][0].x);
+      atomicAdd(&sh[k * 128 + lc + 1], acc[k][0].y);
+      atomicAdd(&sh[k * 128 + lc + 2], acc[k][1].x);
+      atomicAdd(&sh[k * 128 + lc + 3], acc[k][1].y);
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[i]);
+  // dw is stored [C][9] (the parameter's own layout): this block owns channels [cb0, cb0 + 128)
+  const int nch = min(128, g.C - cb0);
+  for (int i = threadIdx.x; i < 9 * nch; i += blockDim.x) atomicAdd(&dw[cb0 * 9 + i], sh[(i % 9) * 128 + i / 9]);
 }
 
-// rows per segment so that the launch has >= ~200k threads (several resident 128-thread blocks per SM)
-static void march_plan(const DwGeom& g, int* segs, int* RY, unsigned* blocks) {
-  const long per_seg = long(g.N) * ((g.W + 3) / 4) * (g.C / kCpt);
-  long s = (200000 + per_seg - 1) / per_seg;
-  if (s < 1) s = 1;
-  long ry = (g.H + s - 1) / s;
-  if (ry < 6) ry = 6;
-  if (ry > g.H) ry = g.H;
-  *RY = int(ry);
-  *segs = int((g.H + ry - 1) / ry);
-  *blocks = unsigned((per_seg * *segs + 127) / 128);
+// Row segments short enough that every warp gets ~8 items (the last partial round of items then
+// costs little) but not shorter than ~6 rows
+// (each segment re-reads two halo rows); one wave of blocks: 3 resident 128-thread blocks per SM.
+static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
+  int sms = 148, dev = 0;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int G = g.C / kCpt, strips = (g.W + 3) / 4;
+  sc->cblocks = (G + 31) / 32;
+  int pb_max = sms * 3 / sc->cblocks;
+  if (pb_max < 1) pb_max = 1;
+  long segs = (32L * pb_max + long(g.N) * strips - 1) / (long(g.N) * strips);   // ~8 items per warp
+  const long max_segs = (g.H + 5) / 6;
+  if (segs > max_segs) segs = max_segs;
+  if (segs < 1) segs = 1;
+  sc->RY = int((g.H + segs - 1) / segs);
+  sc->segs = (g.H + sc->RY - 1) / sc->RY;
+  sc->items = g.N * sc->segs * strips;
+  const int ipw = (sc->items + 4 * pb_max - 1) / (4 * pb_max);   // items per warp
+  const int pb = (sc->items + 4 * ipw - 1) / (4 * ipw);
+  *blocks = unsigned(pb) * sc->cblocks;
 }
 
 static int ew_grid(long total) {
@@ -642,10 +669,10 @@ extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, co
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto Y = static_cast<__nv_bfloat16*>(y);
   if (stride == 1 && dil == 1) {
-    int segs, RY;
+    MarchSched sc;
     unsigned blocks;
-    march_plan(g, &segs, &RY, &blocks);
-    dw_march_fwd_kernel<false, 0><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY, nullptr, nullptr, 0.f);
+    march_plan(g, &sc, &blocks);
+    dw_march_fwd_kernel<false, 0><<<blocks, 128, 0, st>>>(X, w, Y, g, sc, nullptr, nullptr, 0.f);
   } else if (!launch_fwd_strip<false>(X, w, Y, g, st))
     dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, st>>>(X, w, Y, g);
   BGR_LAUNCH_OK();
@@ -666,10 +693,10 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
     r.ldx = ldy;
     r.ldy = ldx;
     if (dil == 1) {
-      int segs, RY;
+      MarchSched sc;
       unsigned blocks;
-      march_plan(r, &segs, &RY, &blocks);
-      dw_march_fwd_kernel<true, 0><<<blocks, 128, 0, st>>>(DY, w, DX, r, segs, RY, nullptr, nullptr, 0.f);
+      march_plan(r, &sc, &blocks);
+      dw_march_fwd_kernel<true, 0><<<blocks, 128, 0, st>>>(DY, w, DX, r, sc, nullptr, nullptr, 0.f);
       done = true;
     } else {
       done = launch_fwd_strip<true>(DY, w, DX, r, st);
@@ -703,16 +730,10 @@ static int launch_wgrad_strip(const __nv_bfloat16* x, const __nv_bfloat16* dy, f
 template <int XF>
 static int launch_march_wgrad(const __nv_bfloat16* x, const __nv_bfloat16* dy, float* dw, const DwGeom& g,
                               const float* xa, const float* xb, float slope, cudaStream_t st) {
-  auto kern = dw_march_wgrad_kernel<XF>;
-  static bool configured = false;
-  if (!configured) {
-    BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    configured = true;
-  }
-  int segs, RY;
+  MarchSched sc;
   unsigned blocks;
-  march_plan(g, &segs, &RY, &blocks);
-  kern<<<blocks, 128, 9 * g.C * sizeof(float), st>>>(x, dy, dw, g, segs, RY, xa, xb, slope);
+  march_plan(g, &sc, &blocks);
+  dw_march_wgrad_kernel<XF><<<blocks, 128, 0, st>>>(x, dy, dw, g, sc, xa, xb, slope);
   return BGR_OK;
 }
 
@@ -727,11 +748,11 @@ extern "C" int bgr_dw_fwd_bn(const void* x, int N, int H, int W, int C, int ldx,
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto Y = static_cast<__nv_bfloat16*>(y);
-  int segs, RY;
+  MarchSched sc;
   unsigned blocks;
-  march_plan(g, &segs, &RY, &blocks);
-  if (act) dw_march_fwd_kernel<false, 2><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY, a, b, slope);
-  else dw_march_fwd_kernel<false, 1><<<blocks, 128, 0, st>>>(X, w, Y, g, segs, RY, a, b, slope);
+  march_plan(g, &sc, &blocks);
+  if (act) dw_march_fwd_kernel<false, 2><<<blocks, 128, 0, st>>>(X, w, Y, g, sc, a, b, slope);
+  else dw_march_fwd_kernel<false, 1><<<blocks, 128, 0, st>>>(X, w, Y, g, sc, a, b, slope);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

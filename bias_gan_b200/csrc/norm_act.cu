@@ -74,8 +74,9 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, long M, int 
                                    float eps, float momentum, float* __restrict__ mean,
                                    float* __restrict__ invstd, float* __restrict__ a,
                                    float* __restrict__ b, float* __restrict__ running_mean,
-                                   float* __restrict__ running_var) {
+                                   float* __restrict__ running_var, long long* __restrict__ num_batches) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && num_batches) *num_batches += 1;   // nn.BatchNorm2d.num_batches_tracked
   if (c >= C) return;
   const double mu = sums[c] / double(M);
   double var = sums[C + c] / double(M) - mu * mu;
@@ -188,7 +189,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
 // prepared by a tiny kernel so the streaming pass has no fp64 and only vector loads.
 __global__ void bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ invstd,
                                    const float* __restrict__ gamma, const double* __restrict__ sums,
-                                   long M, int C, float* __restrict__ coef /* [5][C] */) {
+                                   long M, int C, float* __restrict__ coef /* [7][C] */) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   coef[c] = (gamma ? gamma[c] : 1.f) * invstd[c];
@@ -196,6 +197,8 @@ __global__ void bn_bwd_coef_kernel(const float* __restrict__ mean, const float* 
   coef[2 * C + c] = float(sums[C + c] / double(M));
   coef[3 * C + c] = mean[c];
   coef[4 * C + c] = invstd[c];
+  coef[5 * C + c] = float(sums[c]);       // dL/dbeta
+  coef[6 * C + c] = float(sums[C + c]);   // dL/dgamma
 }
 
 __device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
@@ -263,9 +266,10 @@ extern "C" int bgr_bn_stats(const void* x, long M, int C, int ld, double* sums, 
 
 extern "C" int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const float* beta,
                                float eps, float momentum, float* mean, float* invstd, float* a, float* b,
-                               float* running_mean, float* running_var, void* stream) {
+                               float* running_mean, float* running_var, long long* num_batches_tracked,
+                               void* stream) {
   bn_finalize_kernel<<<(C + 127) / 128, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      sums, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var);
+      sums, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var, num_batches_tracked);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

@@ -427,3 +427,66 @@ extern "C" int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, i
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
+
+// ---------------------------------------------------------------- weight layouts
+// fp32 master weights [Cout][Cin][taps] (PyTorch's [Cout,Cin,kh,kw]) -> bf16 GEMM operand
+// [rows][taps][pitch]: rows = Cout, inner = Cin (fprop) or, transposed, rows = Cin, inner = Cout
+// (dgrad).  The padding up to `pitch` is written as zeros.  One launch per parameter instead of a
+// permute + cast + pad chain.
+namespace bgr {
+// fprop layout: out[co][t][ci] = w[co][ci][t].  One block = one cout x 256 cins: the contiguous
+// [256][taps] fp32 chunk is read coalesced into shared memory and written tap-major.
+__global__ void __launch_bounds__(256)
+weight_to_gemm_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int Cin, int taps, int pitch) {
+  extern __shared__ float sh[];   // [256][taps]
+  const int co = blockIdx.x, ci0 = blockIdx.y * 256;
+  const int n = min(256, pitch - ci0);            // columns to write (zeros beyond Cin)
+  const int nv = max(0, min(256, Cin - ci0));     // columns that exist in w
+  const float* src = w + (size_t(co) * Cin + ci0) * taps;
+  for (int i = threadIdx.x; i < nv * taps; i += 256) sh[i] = src[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < n * taps; i += 256) {
+    const int t = i / n, k = i - t * n;
+    out[(size_t(co) * taps + t) * pitch + ci0 + k] = __float2bfloat16_rn(k < nv ? sh[k * taps + t] : 0.f);
+  }
+}
+// dgrad layout: out[j][co] = w2d[co][j] with j = ci*taps + t -> (ci, t) rows: a 2-D transpose in
+// 32x32 shared-memory tiles (coalesced on both sides); co in [Cout, pitch) is written as zero.
+__global__ void __launch_bounds__(256)
+weight_to_gemm_t_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int Cout, int J, int pitch) {
+  __shared__ float tile[32][33];
+  const int j0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+#pragma unroll
+  for (int r = ty; r < 32; r += 8) {
+    const int co = c0 + r, j = j0 + tx;
+    tile[r][tx] = (co < Cout && j < J) ? w[size_t(co) * J + j] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = ty; r < 32; r += 8) {
+    const int j = j0 + r, co = c0 + tx;
+    if (j < J && co < pitch) out[size_t(j) * pitch + co] = __float2bfloat16_rn(tile[tx][r]);
+  }
+}
+}  // namespace bgr
+
+extern "C" int bgr_weight_to_gemm(const float* w, int Cout, int Cin, int taps, int transpose, void* out, int pitch,
+                                  void* stream) {
+  const int inner = transpose ? Cout : Cin;
+  if (pitch < inner) return bgr::fail(BGR_ERR_ARG, "weight_to_gemm: pitch smaller than the inner dimension");
+  if (taps < 1 || taps > 16) return bgr::fail(BGR_ERR_ARG, "weight_to_gemm: taps must be in [1,16]");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  auto O = static_cast<__nv_bfloat16*>(out);
+  if (transpose) {
+    // [Cout][J = Cin*taps] -> [J][pitch]: row j = ci*taps + t is exactly out[ci][t][:]
+    const int J = Cin * taps;
+    dim3 grid((J + 31) / 32, (pitch + 31) / 32);
+    bgr::weight_to_gemm_t_kernel<<<grid, 256, 0, st>>>(w, O, Cout, J, pitch);
+  } else {
+    dim3 grid(Cout, (pitch + 255) / 256);
+    bgr::weight_to_gemm_kernel<<<grid, 256, 256 * taps * sizeof(float), st>>>(w, O, Cin, taps, pitch);
+  }
+  BGR_LAUNCH_OK();
+  return BGR_OK;
+}

@@ -108,7 +108,7 @@ class _Depthwise(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             gx = K.dw_dgrad(g, w9, stride, dil, shape)
         if ctx.needs_input_grad[1]:
-            gw = K.dw_wgrad(x, g, stride, dil).t().reshape(shape[3], 1, 3, 3)
+            gw = K.dw_wgrad(x, g, stride, dil).view(shape[3], 1, 3, 3)
         return gx, gw, None, None
 
 
@@ -120,11 +120,11 @@ class _BNAct(torch.autograd.Function):
     """out = act(BatchNorm_train(y) [+ res]) with batch statistics (nn.BatchNorm2d training mode)."""
 
     @staticmethod
-    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act, sums):
+    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act, sums, nbt):
         M = y.numel() // y.shape[-1]
         if sums is None:
             sums = K.bn_stats(y)
-        mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var)
+        mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var, nbt)
         out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
         ctx.save_for_backward(y, out if act else None, mean, invstd, gamma)
         ctx.act = act
@@ -137,10 +137,10 @@ class _BNAct(torch.autograd.Function):
         g = _bf16c(g)
         C = y.shape[-1]
         dx, dyh, sums = K.bn_backward(g, out, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
-        ggamma = sums[C:].float() if ctx.needs_input_grad[1] else None
-        gbeta = sums[:C].float() if ctx.needs_input_grad[2] else None
+        ggamma = sums[C:] if ctx.needs_input_grad[1] else None
+        gbeta = sums[:C] if ctx.needs_input_grad[2] else None
         gres = dyh if (ctx.has_res and ctx.needs_input_grad[3]) else None
-        return dx, ggamma, gbeta, gres, None, None, None, None, None, None
+        return dx, ggamma, gbeta, gres, None, None, None, None, None, None, None
 
 
 class _BNActDepthwise(torch.autograd.Function):
@@ -149,12 +149,12 @@ class _BNActDepthwise(torch.autograd.Function):
     are applied while the depthwise kernel loads y, and backward recomputes them the same way."""
 
     @staticmethod
-    def forward(ctx, y, sums, gamma, beta, running_mean, running_var, eps, momentum, act, dw_weight):
+    def forward(ctx, y, sums, gamma, beta, running_mean, running_var, eps, momentum, act, dw_weight, nbt):
         M = y.numel() // y.shape[-1]
         C = y.shape[-1]
         if sums is None:
             sums = K.bn_stats(y)
-        mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var)
+        mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var, nbt)
         w9 = L.cached(dw_weight, "dw9", lambda w: w.reshape(C, 9).t().contiguous().float())
         ctx.save_for_backward(y, mean, invstd, a, b, gamma, w9)
         ctx.act = act
@@ -167,14 +167,14 @@ class _BNActDepthwise(torch.autograd.Function):
         C = y.shape[-1]
         gw = None
         if ctx.needs_input_grad[9]:
-            gw = K.dw_wgrad_bn(y, a, b, ctx.act, g, SLOPE).t().reshape(C, 1, 3, 3)
+            gw = K.dw_wgrad_bn(y, a, b, ctx.act, g, SLOPE).view(C, 1, 3, 3)
         gy = ggamma = gbeta = None
         if ctx.needs_input_grad[0]:
             gx = K.dw_dgrad(g, w9, 1, 1, tuple(y.shape))
             gy, _, bsums = K.bn_backward_recompute(gx, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
-            ggamma = bsums[C:].float() if ctx.needs_input_grad[2] else None
-            gbeta = bsums[:C].float() if ctx.needs_input_grad[3] else None
-        return gy, None, ggamma, gbeta, None, None, None, None, None, gw
+            ggamma = bsums[C:] if ctx.needs_input_grad[2] else None
+            gbeta = bsums[:C] if ctx.needs_input_grad[3] else None
+        return gy, None, ggamma, gbeta, None, None, None, None, None, gw, None
 
 
 def bn_act_depthwise(y, bn, dw_weight, act=True):
@@ -185,10 +185,8 @@ def bn_act_depthwise(y, bn, dw_weight, act=True):
         y, sums = y
     if not bn.training:
         return depthwise3x3(bn_act(y, bn, act=act), dw_weight)
-    if bn.num_batches_tracked is not None:
-        bn.num_batches_tracked += 1
     return _BNActDepthwise.apply(y, sums, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, bn.momentum,
-                                 act, dw_weight)
+                                 act, dw_weight, _nbt(bn))
 
 
 class _AffineAct(torch.autograd.Function):
@@ -203,16 +201,25 @@ class _AffineAct(torch.autograd.Function):
         raise NotImplementedError("eval-mode BatchNorm backward is not on the training hot path")
 
 
+def _nbt(bn):
+    """num_batches_tracked as the device int64 the finalize kernel increments (None if untracked)."""
+    t = bn.num_batches_tracked
+    if t is None:
+        return None
+    if not t.is_cuda:   # a module left on the host: keep nn.BatchNorm2d's own bookkeeping
+        t += 1
+        return None
+    return t
+
+
 def bn_act(y, bn, res=None, act=True, sums=None):
     """`bn` is a torch.nn.BatchNorm2d-compatible module (weight, bias, running_*, eps, momentum).
     `y` may be the (y, sums) pair of a conv called with want_stats=True."""
     if isinstance(y, tuple):
         y, sums = y
     if bn.training:
-        if bn.num_batches_tracked is not None:
-            bn.num_batches_tracked += 1
         return _BNAct.apply(y, bn.weight, bn.bias, res, bn.running_mean, bn.running_var, bn.eps,
-                            bn.momentum, act, sums)
+                            bn.momentum, act, sums, _nbt(bn))
     a = (bn.weight * torch.rsqrt(bn.running_var + bn.eps)).float().contiguous()
     b = (bn.bias - bn.running_mean * a).float().contiguous()
     return _AffineAct.apply(y, a, b, res, act)

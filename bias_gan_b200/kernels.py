@@ -93,6 +93,17 @@ def conv_fprop(x, w, dy, dx, out=None, bias=None, bn_sums=None):
     return out
 
 
+def weight_to_gemm(w, transpose):
+    """fp32 cuda [Cout, Cin, kh, kw] -> bf16 [rows, taps, inner] view of a zero-padded [rows, taps, pitch]."""
+    assert w.is_cuda and w.dtype == torch.float32 and w.is_contiguous() and w.dim() == 4
+    Cout, Cin, kh, kw = w.shape
+    rows, inner = (Cin, Cout) if transpose else (Cout, Cin)
+    pitch = inner if inner % 64 == 0 else (inner + 63) // 64 * 64
+    out = torch.empty((rows, kh * kw, pitch), dtype=torch.bfloat16, device=w.device)
+    check(_lib.lib().bgr_weight_to_gemm(ptr(w), Cout, Cin, kh * kw, int(transpose), ptr(out), pitch, stream_ptr()))
+    return out if pitch == inner else out[..., :inner]
+
+
 def conv_wgrad(x, gy, dy, dx, dw=None):
     """dw[Cout, ntaps, Cin] (fp32) += sum_pixels gy[p, co] * x[p + tap, ci]."""
     N, H, W, Cin, ldx = _nhwc_view(x)
@@ -169,13 +180,13 @@ def bn_stats(x, sums=None):
     return sums
 
 
-def bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var):
+def bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var, num_batches_tracked=None):
     C = sums.numel() // 2
     dev = sums.device
     mean, invstd, a, b = (torch.empty(C, dtype=torch.float32, device=dev) for _ in range(4))
     check(_lib.lib().bgr_bn_finalize(ptr(sums), c_long(M), C, ptr(gamma), ptr(beta), c_float(eps), c_float(momentum),
                                      ptr(mean), ptr(invstd), ptr(a), ptr(b), ptr(running_mean),
-                                     ptr(running_var), stream_ptr()))
+                                     ptr(running_var), ptr(num_batches_tracked), stream_ptr()))
     return mean, invstd, a, b
 
 
@@ -195,7 +206,8 @@ def bn_apply(x, a, b, res=None, act=True, slope=0.2, out=None):
 
 
 def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2):
-    """Returns (dx, dyh, sums) — dyh is also the gradient of the residual input."""
+    """Returns (dx, dyh, grads) — dyh is also the gradient of the residual input; grads = fp32
+    [dL/dbeta (C) | dL/dgamma (C)]."""
     M, C, ldx = _rows(x)
     Mg, Cg, ldg = _rows(g)
     assert (Mg, Cg) == (M, C)
@@ -206,11 +218,11 @@ def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2):
     dyh = act_empty(x.shape, x.device)
     dx = act_empty(x.shape, x.device)
     sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
-    coef = torch.empty(5 * C, dtype=torch.float32, device=x.device)
+    coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_bn_backward(ptr(g), ldg, ptr(out) if act else ctypes.c_void_p(0), ldo, ptr(x), ldx,
                                      ptr(mean), ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
                                      ptr(dyh), ptr(dx), _rows(dx)[2], ptr(sums), ptr(coef), stream_ptr()))
-    return dx, dyh, sums
+    return dx, dyh, coef[5 * C:7 * C]   # fp32 [dL/dbeta | dL/dgamma]
 
 
 def dw_fwd(x, w9, stride, dil, out=None):
@@ -240,7 +252,7 @@ def dw_fwd_bn(x, w9, a, b, act, slope=0.2, out=None):
 def dw_wgrad_bn(x, a, b, act, gy, slope=0.2):
     N, H, W, C, ldx = _nhwc_view(x)
     _, _, _, _, ldy = _nhwc_view(gy)
-    dw = torch.empty((9, C), dtype=torch.float32, device=x.device)
+    dw = torch.empty((C, 9), dtype=torch.float32, device=x.device)   # the parameter's [C,1,3,3] layout
     check(_lib.lib().bgr_dw_wgrad_bn(ptr(x), N, H, W, C, ldx, ptr(a), ptr(b), int(act), c_float(slope), ptr(gy), ldy,
                                      ptr(dw), stream_ptr()))
     return dw
@@ -254,11 +266,11 @@ def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2):
     dyh = act_empty(x.shape, x.device)
     dx = act_empty(x.shape, x.device)
     sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
-    coef = torch.empty(5 * C, dtype=torch.float32, device=x.device)
+    coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_bn_backward_recompute(ptr(g), ldg, ptr(a), ptr(b), ptr(x), ldx, ptr(mean), ptr(invstd),
                                                ptr(gamma), int(act), c_float(slope), c_long(M), C, ptr(dyh), ptr(dx),
                                                _rows(dx)[2], ptr(sums), ptr(coef), stream_ptr()))
-    return dx, dyh, sums
+    return dx, dyh, coef[5 * C:7 * C]   # fp32 [dL/dbeta | dL/dgamma]
 
 
 def dw_dgrad(gy, w9, stride, dil, in_shape):
@@ -273,7 +285,7 @@ def dw_dgrad(gy, w9, stride, dil, in_shape):
 def dw_wgrad(x, gy, stride, dil):
     N, H, W, C, ldx = _nhwc_view(x)
     _, _, _, _, ldy = _nhwc_view(gy)
-    dw = torch.empty((9, C), dtype=torch.float32, device=x.device)
+    dw = torch.empty((C, 9), dtype=torch.float32, device=x.device)   # the parameter's [C,1,3,3] layout
     check(_lib.lib().bgr_dw_wgrad(ptr(x), N, H, W, C, ldx, ptr(gy), ldy, stride, dil, ptr(dw), stream_ptr()))
     return dw
 

@@ -54,12 +54,18 @@ def _padded_rows(src, rows, taps, K):
 def gemm_weight(w):
     """[Cout, Cin, kh, kw] -> bf16 [Cout, kh*kw, Cin] (tap-major, Cin contiguous, padded row pitch)."""
     Cout, Cin, kh, kw = w.shape
+    if w.is_cuda and w.dtype == torch.float32 and w.is_contiguous():
+        from . import kernels as K
+        return K.weight_to_gemm(w.detach(), False)   # one kernel instead of permute + cast + pad
     return _padded_rows(w.permute(0, 2, 3, 1).reshape(Cout, kh * kw, Cin), Cout, kh * kw, Cin)
 
 
 def gemm_weight_t(w):
     """Data-gradient weights: bf16 [Cin, kh*kw, Cout]; used with negated tap offsets."""
     Cout, Cin, kh, kw = w.shape
+    if w.is_cuda and w.dtype == torch.float32 and w.is_contiguous():
+        from . import kernels as K
+        return K.weight_to_gemm(w.detach(), True)
     return _padded_rows(w.permute(1, 2, 3, 0).reshape(Cin, kh * kw, Cout), Cin, kh * kw, Cout)
 
 

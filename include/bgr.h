@@ -103,6 +103,12 @@ int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const v
  * the nn.BatchNorm2d that follows every such conv in the reference (deeplab.py:179,183,334,...)
  * without re-reading y (same contract as bgr_bn_stats). */
 
+/* fp32 master weight [Cout][Cin][taps] (nn.Conv2d.weight) -> the bf16 operand bgr_conv_fprop reads:
+ * [Cout][taps][pitch] (transpose = 0) or, for the data gradient, [Cin][taps][pitch] with Cout
+ * innermost (transpose = 1); pitch >= inner dimension, padding written as zeros. */
+int bgr_weight_to_gemm(const float* w, int Cout, int Cin, int taps, int transpose, void* out, int pitch,
+                       void* stream);
+
 /* dw[co,t,ci] += sum_{n,h,w} dy_[n,h,w,co] * x[n, h+dy[t], w+dx[t], ci]   (fp32, accumulated:
  * zero dw first).  Same views as bgr_conv_fprop. */
 int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx, const void* dy_, int Cout,
@@ -115,16 +121,17 @@ int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx, const v
 int bgr_bn_stats(const void* x, long M, int C, int ld, double* sums, void* stream);
 /* mean, invstd = 1/sqrt(var_biased+eps), a = gamma*invstd, b = beta - mean*a; running stats
  * updated with `momentum` and the unbiased variance (nn.BatchNorm2d semantics); gamma/beta/
- * running_* may be NULL. */
+ * running_* may be NULL; num_batches_tracked (device int64, may be NULL) is incremented by one. */
 int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const float* beta, float eps,
                     float momentum, float* mean, float* invstd, float* a, float* b,
-                    float* running_mean, float* running_var, void* stream);
+                    float* running_mean, float* running_var, long long* num_batches_tracked, void* stream);
 /* out = act(a*x + b [+ res]); act != 0: LeakyReLU(slope). */
 int bgr_bn_apply(const void* x, int ldx, const float* a, const float* b, const void* res, int ldr,
                  void* out, int ldo, long M, int C, int act, float slope, void* stream);
 /* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; dyh ([M][C], pixel stride ldd) receives
  * g*act'(out), which is also dL/dres; dx (same stride) receives dL/dx; sums (fp64 [2][C]) receives
- * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat; coef_ws: fp32 [5][C] workspace. */
+ * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat; coef_ws: fp32 [7][C] workspace whose rows 5 and 6
+ * return dL/dbeta and dL/dgamma in fp32. */
 int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
                     const float* mean, const float* invstd, const float* gamma, int act, float slope,
                     long M, int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
@@ -138,7 +145,7 @@ int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const floa
                               float* coef_ws, void* stream);
 
 /* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
- * w, dw: fp32 [9][C].  Output size ceil(H/stride) x ceil(W/stride). */
+ * w: fp32 [9][C] (tap-major); dw: fp32 [C][9] (the parameter's own [C,1,3,3] layout).  Output size ceil(H/stride) x ceil(W/stride). */
 int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* w, int stride, int dil,
                void* y, int ldy, void* stream);
 int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy, const float* w, int stride, int dil,

@@ -103,6 +103,21 @@ def test_conv_fprop_dgrad_wgrad(dev, N, H, W, Cin, Cout, ks, dil, bias):
         assert rel(bp.grad, br.grad) < 1e-4
 
 
+@pytest.mark.parametrize("Cout,Cin,k", [(24, 728, 3), (728, 728, 1), (16, 256, 1), (128, 16, 3)])
+def test_weight_to_gemm_bit_exact(dev, Cout, Cin, k):
+    """bgr_weight_to_gemm == permute + bf16 round (RNE) of the fp32 master weights, zero padding."""
+    from bias_gan_b200 import kernels as K
+    w = torch.randn(Cout, Cin, k, k, generator=torch.Generator().manual_seed(3)).to(dev)
+    a = K.weight_to_gemm(w, False)
+    assert tuple(a.shape) == (Cout, k * k, Cin) and a.stride(1) % 64 == 0
+    assert torch.equal(a, w.permute(0, 2, 3, 1).reshape(Cout, k * k, Cin).bfloat16())
+    t = K.weight_to_gemm(w, True)
+    assert torch.equal(t, w.permute(1, 2, 3, 0).reshape(Cin, k * k, Cout).bfloat16())
+    if t.stride(1) != Cout:   # padding must be real zeros
+        full = torch.as_strided(t, (Cin, k * k, t.stride(1)), t.stride())
+        assert float(full[..., Cout:].abs().max()) == 0.0
+
+
 @pytest.mark.parametrize("block_n", [0, 128, 256])
 @pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil", [
     (2, 48, 72, 728, 728, 1, 1), (1, 19, 37, 304, 256, 3, 1), (3, 40, 56, 128, 1536, 1, 1), (1, 24, 40, 128, 48, 1, 1),
