@@ -372,25 +372,6 @@ __device__ __forceinline__ void march_decode(const DwGeom& g, const MarchSched& 
   it->oy1 = min(it->oy0 + s.RY, g.H);
 }
 
-// six column vectors of input row iy (zeros outside the image), all loads independent; bit c of the
-// returned mask says that column c lies inside the image
-__device__ __forceinline__ unsigned march_load_row(const __nv_bfloat16* base, const DwGeom& g, int ld, int iy,
-                                                   int ox0, uint2 (&r)[6]) {
-  const bool rv = iy >= 0 && iy < g.H;
-  const __nv_bfloat16* row = base + size_t(rv ? iy : 0) * g.W * ld;
-  unsigned mask = 0;
-#pragma unroll
-  for (int c = 0; c < 6; ++c) {
-    const int ix = ox0 - 1 + c;
-    r[c] = make_uint2(0, 0);
-    if (rv && ix >= 0 && ix < g.W) {
-      r[c] = __ldg(reinterpret_cast<const uint2*>(row + size_t(ix) * ld));
-      mask |= 1u << c;
-    }
-  }
-  return mask;
-}
-
 // 4 bf16 channels -> two packed fp32 pairs (bf16 -> fp32 is a 16-bit shift)
 __device__ __forceinline__ void dw_unpack22(const uint2& u, float2 (&f)[2]) {
   f[0] = make_float2(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u));
@@ -439,13 +420,53 @@ __device__ __forceinline__ float2 fma2s(const float2& a, const float2& b, const 
   return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
 }
 
+// ---- asynchronous row ring.  The march is bound by memory-level parallelism (measured: 168
+// registers -> 12 warps per SM x one prefetched row = 18 KB in flight per SM = 2.7 TB/s), so rows are
+// fetched kRing ahead with cp.async into a per-warp shared-memory ring: no registers are held by
+// loads in flight and every lane reads back only the 8-byte slots it copied itself (no barriers).
+constexpr int kRing = 4;
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem, bool valid) {
+  const unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(smem));
+  const int sz = valid ? 8 : 0;   // 0 source bytes = zero fill
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(sa), "l"(gmem), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// issue the six column vectors of input row iy into ring slot `slot` ([col][lane] x 8 bytes)
+__device__ __forceinline__ void march_issue_row(uint2* slot, const __nv_bfloat16* base, const DwGeom& g, int ld,
+                                                int iy, int ox0, bool in_range) {
+  const bool rv = in_range && iy >= 0 && iy < g.H;
+  const __nv_bfloat16* row = base + size_t(rv ? iy : 0) * g.W * ld;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const int ix = ox0 - 1 + c;
+    const bool ok = rv && ix >= 0 && ix < g.W;
+    cp_async8(slot + c * 32, ok ? row + size_t(ix) * ld : base, ok);
+  }
+}
+// column validity bits of a strip (bit c <-> column ox0 - 1 + c)
+__device__ __forceinline__ unsigned march_col_mask(const DwGeom& g, int ox0) {
+  unsigned m = 0;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const int ix = ox0 - 1 + c;
+    if (ix >= 0 && ix < g.W) m |= 1u << c;
+  }
+  return m;
+}
+
 template <bool REVERSE, int XF>
 __global__ void __launch_bounds__(128, 3)
 dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                     __nv_bfloat16* __restrict__ y, const DwGeom g, const MarchSched sc,
                     const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
-  const int c0 = ((blockIdx.x % sc.cblocks) * 32 + (threadIdx.x & 31)) * kCpt;
+  __shared__ uint2 ring_all[4][kRing][6 * 32];   // [warp][slot][col][lane]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = ((blockIdx.x % sc.cblocks) * 32 + lane) * kCpt;
   if (c0 >= g.C) return;
+  uint2* ring = &ring_all[warp][0][lane];
   float2 wr[9][2];
 #pragma unroll
   for (int k = 0; k < 9; ++k) {
@@ -456,61 +477,69 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
   XfCoef tc;
   dw_load_coef<XF>(&tc, xa, xb, slope, c0);
   const int item_step = (gridDim.x / sc.cblocks) * 4;
-  for (int item = (blockIdx.x / sc.cblocks) * 4 + (threadIdx.x >> 5); item < sc.items; item += item_step) {
-  MarchItem it;
-  march_decode(g, sc, item, &it);
-  float2 a0[4][2], a1[4][2], a2[4][2];
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-#pragma unroll
-    for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
-  const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
-  __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + c0;
-  // input row iy adds to output rows iy+1 (ky=0), iy (ky=1), iy-1 (ky=2); then row iy-1 is complete
-  auto phase = [&](int iy, const uint2 (&rc)[6], unsigned mc, uint2 (&rn)[6], unsigned& mn,
-                   float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
-    if (iy + 1 <= it.oy1) mn = march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);  // prefetch next row
-#pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      float2 xv[2];
-      dw_unpack22(rc[c], xv);
-      dw_transform<XF>(xv, tc, (mc >> c) & 1u);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int kx = c - j;
-        if (kx < 0 || kx > 2) continue;
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          next[j][e] = fma2s(xv[e], wr[0 + kx][e], next[j][e]);
-          cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
-          prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
-        }
-      }
-    }
-    const int oy = iy - 1;
-    if (oy >= it.oy0 && oy < it.oy1) {
-      __nv_bfloat16* orow = yout + size_t(oy) * g.W * g.ldy;
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + size_t(it.ox0 + j) * g.ldy) = dw_pack22(prev[j]);
-    }
+  for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
+    MarchItem it;
+    march_decode(g, sc, item, &it);
+    float2 a0[4][2], a1[4][2], a2[4][2];
 #pragma unroll
     for (int j = 0; j < 4; ++j)
 #pragma unroll
-      for (int e = 0; e < 2; ++e) prev[j][e] = make_float2(0.f, 0.f);
-  };
-  uint2 rA[6], rB[6];
-  unsigned mA, mB = 0;
-  mA = march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
-  for (int iy = it.oy0 - 1; iy <= it.oy1; iy += 6) {
-    phase(iy, rA, mA, rB, mB, a0, a1, a2);
-    if (iy + 1 <= it.oy1) phase(iy + 1, rB, mB, rA, mA, a1, a2, a0);
-    if (iy + 2 <= it.oy1) phase(iy + 2, rA, mA, rB, mB, a2, a0, a1);
-    if (iy + 3 <= it.oy1) phase(iy + 3, rB, mB, rA, mA, a0, a1, a2);
-    if (iy + 4 <= it.oy1) phase(iy + 4, rA, mA, rB, mB, a1, a2, a0);
-    if (iy + 5 <= it.oy1) phase(iy + 5, rB, mB, rA, mA, a2, a0, a1);
+      for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
+    const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
+    __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + c0;
+    const unsigned cmask = march_col_mask(g, it.ox0);
+    const int first = it.oy0 - 1;   // rows first .. oy1 are consumed, one per phase
+#pragma unroll
+    for (int r = 0; r < kRing; ++r) {
+      march_issue_row(ring + r * (6 * 32), xin, g, g.ldx, first + r, it.ox0, first + r <= it.oy1);
+      cp_async_commit();
+    }
+    // input row iy adds to output rows iy+1 (ky=0), iy (ky=1), iy-1 (ky=2); then row iy-1 is complete
+    auto phase = [&](int iy, float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
+      cp_async_wait<kRing - 1>();   // the oldest outstanding group is row iy
+      uint2* slot = ring + ((iy - first) & (kRing - 1)) * (6 * 32);
+      uint2 rc[6];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
+      march_issue_row(slot, xin, g, g.ldx, iy + kRing, it.ox0, iy + kRing <= it.oy1);   // refill the slot
+      cp_async_commit();
+      const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        float2 xv[2];
+        dw_unpack22(rc[c], xv);
+        dw_transform<XF>(xv, tc, (mc >> c) & 1u);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int kx = c - j;
+          if (kx < 0 || kx > 2) continue;
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            next[j][e] = fma2s(xv[e], wr[0 + kx][e], next[j][e]);
+            cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
+            prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
+          }
+        }
+      }
+      const int oy = iy - 1;
+      if (oy >= it.oy0 && oy < it.oy1) {
+        __nv_bfloat16* orow = yout + size_t(oy) * g.W * g.ldy;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + size_t(it.ox0 + j) * g.ldy) = dw_pack22(prev[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) prev[j][e] = make_float2(0.f, 0.f);
+    };
+    for (int iy = first; iy <= it.oy1; iy += 3) {
+      phase(iy, a0, a1, a2);
+      if (iy + 1 <= it.oy1) phase(iy + 1, a1, a2, a0);
+      if (iy + 2 <= it.oy1) phase(iy + 2, a2, a0, a1);
+    }
+    cp_async_wait<0>();   // drain the (empty) tail groups before the ring is reused by the next item
   }
-  }  // items
 }
 
 // dw[ky][kx][c] += sum dy[oy][ox] * x[oy+ky-1][ox+kx-1]; marching over input rows with the three
@@ -521,74 +550,87 @@ __global__ void __launch_bounds__(128, 3)
 dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                       float* __restrict__ dw, const DwGeom g, const MarchSched sc,
                       const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
-  __shared__ float sh[9 * 128];  // [9][128 channels of this block]
+  __shared__ float sh[9 * 128];                       // [9][128 channels of this block]
+  __shared__ uint2 ring_all[4][kRing][10 * 32];       // [warp][slot][6 x cols + 4 dy cols][lane]
   for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int cb0 = (blockIdx.x % sc.cblocks) * 128;
-  const int lc = (threadIdx.x & 31) * kCpt;      // channel offset inside the block's 128
+  const int lc = lane * kCpt;      // channel offset inside the block's 128
   const int c0 = cb0 + lc;
   if (c0 < g.C) {
+    uint2* ring = &ring_all[warp][0][lane];
     float2 acc[9][2];
 #pragma unroll
     for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
     XfCoef tc;
     dw_load_coef<XF>(&tc, xa, xb, slope, c0);
     const int item_step = (gridDim.x / sc.cblocks) * 4;
-    for (int item = (blockIdx.x / sc.cblocks) * 4 + (threadIdx.x >> 5); item < sc.items; item += item_step) {
-    MarchItem it;
-    march_decode(g, sc, item, &it);
-    const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
-    const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + c0;
-    auto load_dy = [&](int oy, uint2 (&d)[4]) {
-      const bool ok = oy >= it.oy0 && oy < it.oy1;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        d[j] = make_uint2(0, 0);
-        if (ok && it.ox0 + j < g.W)
-          d[j] = __ldg(reinterpret_cast<const uint2*>(gin + (size_t(oy) * g.W + it.ox0 + j) * g.ldy));
-      }
-    };
-    // at input row iy: prev/cur/next = dy rows iy-1 / iy / iy+1 ; rn / dnn = prefetch for row iy+1
-    auto phase = [&](int iy, const uint2 (&rc)[6], unsigned mc, uint2 (&rn)[6], unsigned& mn,
-                     const uint2 (&prev)[4], const uint2 (&cur)[4], const uint2 (&next)[4], uint2 (&dnn)[4]) {
-      if (iy + 1 <= it.oy1) {
-        mn = march_load_row(xin, g, g.ldx, iy + 1, it.ox0, rn);
-        load_dy(iy + 2, dnn);
-      }
-#pragma unroll
-      for (int c = 0; c < 6; ++c) {
-        float2 xv[2];
-        dw_unpack22(rc[c], xv);
-        dw_transform<XF>(xv, tc, (mc >> c) & 1u);
+    for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
+      MarchItem it;
+      march_decode(g, sc, item, &it);
+      const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
+      const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + c0;
+      const unsigned cmask = march_col_mask(g, it.ox0);
+      const int first = it.oy0 - 1;
+      // group r = input row r and the dy row r + 1 (first needed, as "next", in phase r); dy rows
+      // outside the segment count as zero
+      auto issue = [&](uint2* slot, int r) {
+        const bool in_range = r <= it.oy1;
+        march_issue_row(slot, xin, g, g.ldx, r, it.ox0, in_range);
+        const int oy = r + 1;
+        const bool ok = in_range && oy >= it.oy0 && oy < it.oy1;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const int kx = c - j;
-          if (kx < 0 || kx > 2) continue;
-          float2 gp[2], gc[2], gn[2];
-          dw_unpack22(prev[j], gp);  // oy = iy-1 -> ky = 2
-          dw_unpack22(cur[j], gc);   // oy = iy   -> ky = 1
-          dw_unpack22(next[j], gn);  // oy = iy+1 -> ky = 0
+          const bool okj = ok && it.ox0 + j < g.W;
+          cp_async8(slot + (6 + j) * 32, okj ? gin + (size_t(oy) * g.W + it.ox0 + j) * g.ldy : gin, okj);
+        }
+        cp_async_commit();
+      };
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            acc[0 + kx][e] = fma2s(gn[e], xv[e], acc[0 + kx][e]);
-            acc[3 + kx][e] = fma2s(gc[e], xv[e], acc[3 + kx][e]);
-            acc[6 + kx][e] = fma2s(gp[e], xv[e], acc[6 + kx][e]);
+      for (int r = 0; r < kRing; ++r) issue(ring + r * (10 * 32), first + r);
+      // at input row iy: prev / cur / next = dy rows iy-1 / iy / iy+1
+      auto phase = [&](int iy, const uint2 (&prev)[4], const uint2 (&cur)[4], uint2 (&next)[4]) {
+        cp_async_wait<kRing - 1>();
+        uint2* slot = ring + ((iy - first) & (kRing - 1)) * (10 * 32);
+        uint2 rc[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) next[j] = slot[(6 + j) * 32];
+        issue(slot, iy + kRing);
+        const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          float2 xv[2];
+          dw_unpack22(rc[c], xv);
+          dw_transform<XF>(xv, tc, (mc >> c) & 1u);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int kx = c - j;
+            if (kx < 0 || kx > 2) continue;
+            float2 gp[2], gc[2], gn[2];
+            dw_unpack22(prev[j], gp);  // oy = iy-1 -> ky = 2
+            dw_unpack22(cur[j], gc);   // oy = iy   -> ky = 1
+            dw_unpack22(next[j], gn);  // oy = iy+1 -> ky = 0
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              acc[0 + kx][e] = fma2s(gn[e], xv[e], acc[0 + kx][e]);
+              acc[3 + kx][e] = fma2s(gc[e], xv[e], acc[3 + kx][e]);
+              acc[6 + kx][e] = fma2s(gp[e], xv[e], acc[6 + kx][e]);
+            }
           }
         }
+      };
+      uint2 d0[4], d1[4], d2[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) d0[j] = d1[j] = d2[j] = make_uint2(0, 0);
+      for (int iy = first; iy <= it.oy1; iy += 3) {
+        phase(iy, d0, d1, d2);
+        if (iy + 1 <= it.oy1) phase(iy + 1, d1, d2, d0);
+        if (iy + 2 <= it.oy1) phase(iy + 2, d2, d0, d1);
       }
-    };
-    uint2 rA[6], rB[6], d0[4], d1[4], d2[4], d3[4];
-    unsigned mA, mB = 0;
-    mA = march_load_row(xin, g, g.ldx, it.oy0 - 1, it.ox0, rA);
-    load_dy(it.oy0 - 2, d0);
-    load_dy(it.oy0 - 1, d1);
-    load_dy(it.oy0, d2);
-    for (int iy = it.oy0 - 1; iy <= it.oy1; iy += 4) {
-      phase(iy, rA, mA, rB, mB, d0, d1, d2, d3);
-      if (iy + 1 <= it.oy1) phase(iy + 1, rB, mB, rA, mA, d1, d2, d3, d0);
-      if (iy + 2 <= it.oy1) phase(iy + 2, rA, mA, rB, mB, d2, d3, d0, d1);
-      if (iy + 3 <= it.oy1) phase(iy + 3, rB, mB, rA, mA, d3, d0, d1, d2);
-    }
+      cp_async_wait<0>();
     }  // items
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
