@@ -9,6 +9,10 @@
 
 #include "bgr_internal.h"
 
+#ifndef BGR_DW_FFMA2
+#define BGR_DW_FFMA2 0   // packed fp32 FMAs (FFMA2): measured no faster (fwd) or slower (wgrad, spills)
+#endif
+
 namespace bgr {
 
 __device__ __forceinline__ void dw_unpack8(const uint4& u, float (&f)[8]) {
@@ -417,7 +421,11 @@ __device__ __forceinline__ void dw_load_coef(XfCoef* t, const float* xa, const f
 // Two scalar FMAs.  The packed FFMA2 form was measured: same time (the march waits on loads, not on
 // FMA issue) but 20-30 more registers for the aligned operand pairs, i.e. one resident block fewer.
 __device__ __forceinline__ float2 fma2s(const float2& a, const float2& b, const float2& c) {
+#if BGR_DW_FFMA2
+  return __ffma2_rn(a, b, c);
+#else
   return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+#endif
 }
 
 // ---- asynchronous row ring.  The march is bound by memory-level parallelism (measured: 168

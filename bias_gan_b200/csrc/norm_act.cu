@@ -29,6 +29,11 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return u;
 }
 
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+  *reinterpret_cast<float4*>(f) = *reinterpret_cast<const float4*>(p);
+  *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(p + 4);
+}
+
 // Thread -> (row lane r, channel group g) mapping shared by the reduction kernels:
 // G = C/8 groups.  If G <= 256 a block covers R = 256/G rows at a time, else each thread loops
 // over groups g = tid, tid+256, ...
@@ -95,32 +100,55 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, long M, int 
 }
 
 // ---------------------------------------------------------------- apply: out = act(a*x + b [+ res])
+// Thread = one fixed group of 8 channels (coefficients stay in registers) x rows r, r+R, ...;
+// blockDim = G*R with R = 256/G rows per block step when G = C/8 <= 256, else 256 threads looping
+// over groups.  (The first version re-read a and b for every 16 bytes of data: L1-bound at 91 %.)
 template <bool ACT, bool RES>
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __restrict__ a,
                 const float* __restrict__ b, const __nv_bfloat16* __restrict__ res, int ldr,
                 __nv_bfloat16* __restrict__ out, int ldo, long M, int C, float slope) {
   const int G = C >> 3;
-  const long total = M * G;
-  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += long(gridDim.x) * blockDim.x) {
-    const int g = int(i % G);
-    const long row = i / G;
-    float f[8], r[8];
-    unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + g * 8), f);
-    if (RES) unpack8(*reinterpret_cast<const uint4*>(res + row * ldr + g * 8), r);
-    const float4 a0 = *reinterpret_cast<const float4*>(a + g * 8), a1 = *reinterpret_cast<const float4*>(a + g * 8 + 4);
-    const float4 b0 = *reinterpret_cast<const float4*>(b + g * 8), b1 = *reinterpret_cast<const float4*>(b + g * 8 + 4);
-    const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-    const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+  const int R = G >= 256 ? 1 : 256 / G;
+  const int g0 = G >= 256 ? threadIdx.x : threadIdx.x % G;
+  const int r = G >= 256 ? 0 : threadIdx.x / G;
+  const long rstep = long(gridDim.x) * R;
+  for (int g = g0; g < G; g += 256) {
+    float av[8], bv[8];
+    load8f(a + g * 8, av);
+    load8f(b + g * 8, bv);
+    auto one = [&](long row, const uint4& xu, const uint4& ru) {
+      float f[8], rr[8];
+      unpack8(xu, f);
+      if (RES) unpack8(ru, rr);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float v = fmaf(av[j], f[j], bv[j]);
-      if (RES) v += r[j];
-      if (ACT) v = v > 0.f ? v : slope * v;
-      f[j] = v;
+      for (int j = 0; j < 8; ++j) {
+        float v = fmaf(av[j], f[j], bv[j]);
+        if (RES) v += rr[j];
+        if (ACT) v = v > 0.f ? v : slope * v;
+        f[j] = v;
+      }
+      *reinterpret_cast<uint4*>(out + row * ldo + g * 8) = pack8(f);
+    };
+    long row = long(blockIdx.x) * R + r;
+    for (; row + rstep < M; row += 2 * rstep) {   // two rows in flight per thread
+      const long row2 = row + rstep;
+      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
+      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + g * 8);
+      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+      if (RES) {
+        r0 = *reinterpret_cast<const uint4*>(res + row * ldr + g * 8);
+        r1 = *reinterpret_cast<const uint4*>(res + row2 * ldr + g * 8);
+      }
+      one(row, x0, r0);
+      one(row2, x1, r1);
     }
-    *reinterpret_cast<uint4*>(out + row * ldo + g * 8) = pack8(f);
+    if (row < M) {
+      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
+      uint4 r0 = make_uint4(0, 0, 0, 0);
+      if (RES) r0 = *reinterpret_cast<const uint4*>(res + row * ldr + g * 8);
+      one(row, x0, r0);
+    }
   }
 }
 
@@ -201,49 +229,71 @@ __global__ void bn_bwd_coef_kernel(const float* __restrict__ mean, const float* 
   coef[6 * C + c] = float(sums[C + c]);   // dL/dgamma
 }
 
-__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
-  *reinterpret_cast<float4*>(f) = *reinterpret_cast<const float4*>(p);
-  *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(p + 4);
-}
-
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* __restrict__ x, int ldx,
                     const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, int ldd, long M,
                     int C) {
+  // same thread -> (channel group, rows) mapping as bn_apply_kernel: the five coefficient vectors
+  // are loaded once per thread instead of once per 16 bytes of data
   const int G = C >> 3;
-  const long total = M * G;
-  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += long(gridDim.x) * blockDim.x) {
-    const int g = int(i % G);
-    const long row = i / G;
-    float d[8], xv[8], c0[8], k1[8], k2[8], mu[8], is[8];
-    unpack8(*reinterpret_cast<const uint4*>(dyh + row * ldd + g * 8), d);
-    unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + g * 8), xv);
+  const int R = G >= 256 ? 1 : 256 / G;
+  const int g0 = G >= 256 ? threadIdx.x : threadIdx.x % G;
+  const int r = G >= 256 ? 0 : threadIdx.x / G;
+  const long rstep = long(gridDim.x) * R;
+  for (int g = g0; g < G; g += 256) {
+    float c0[8], k1[8], k2[8], mu[8], is[8];
     load8f(coef + g * 8, c0);
     load8f(coef + C + g * 8, k1);
     load8f(coef + 2 * C + g * 8, k2);
     load8f(coef + 3 * C + g * 8, mu);
     load8f(coef + 4 * C + g * 8, is);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) d[j] = c0[j] * (d[j] - k1[j] - (xv[j] - mu[j]) * is[j] * k2[j]);
-    *reinterpret_cast<uint4*>(dx + row * ldd + g * 8) = pack8(d);
+    for (int j = 0; j < 8; ++j) k2[j] *= is[j];   // (x - mu) * is * k2
+    auto one = [&](long row, const uint4& du, const uint4& xu) {
+      float d[8], xv[8];
+      unpack8(du, d);
+      unpack8(xu, xv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = c0[j] * (d[j] - k1[j] - (xv[j] - mu[j]) * k2[j]);
+      *reinterpret_cast<uint4*>(dx + row * ldd + g * 8) = pack8(d);
+    };
+    long row = long(blockIdx.x) * R + r;
+    for (; row + rstep < M; row += 2 * rstep) {
+      const long row2 = row + rstep;
+      const uint4 d0 = *reinterpret_cast<const uint4*>(dyh + row * ldd + g * 8);
+      const uint4 d1 = *reinterpret_cast<const uint4*>(dyh + row2 * ldd + g * 8);
+      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
+      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + g * 8);
+      one(row, d0, x0);
+      one(row2, d1, x1);
+    }
+    if (row < M)
+      one(row, *reinterpret_cast<const uint4*>(dyh + row * ldd + g * 8),
+          *reinterpret_cast<const uint4*>(x + row * ldx + g * 8));
   }
+}
+
+// grid / block of the (channel group, rows) streaming kernels
+static void rowgroup_launch(long M, int C, int* grid, int* block) {
+  const int G = C / 8;
+  const int R = G >= 256 ? 1 : 256 / G;
+  *block = G >= 256 ? 256 : G * R;
+  long blocks = (M + long(R) * 4 - 1) / (long(R) * 4);   // >= 4 rows per thread
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  *grid = int(blocks < 1 ? 1 : blocks);
 }
 
 static int reduce_grid(long M, int C, int* rows_per_block) {
   const int G = C / 8;
   const int R = G >= 256 ? 1 : 256 / G;
   long blocks = (M + long(R) * 8 - 1) / (long(R) * 8);  // >= 8 row iterations per thread
-  if (blocks > 148 * 2) blocks = 148 * 2;  // two CTAs per SM: keeps the per-channel global atomics few
+  // four CTAs per SM (the register limit) for narrow tensors; two for wide ones, where every extra
+  // block costs 2*C fp64 global atomics and the tensors are small anyway
+  const long cap = C <= 256 ? 148 * 4 : 148 * 2;
+  if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   *rows_per_block = int((M + blocks - 1) / blocks);
   return int((M + *rows_per_block - 1) / *rows_per_block);
-}
-
-static int elementwise_grid(long total) {
-  long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  return int(blocks < 1 ? 1 : blocks);
 }
 
 }  // namespace bgr
@@ -278,14 +328,15 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
                             void* out, int ldo, long M, int C, int act, float slope, void* stream) {
   BGR_CHECK_C8(C);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const int grid = elementwise_grid(M * (C / 8));
+  int grid, block;
+  rowgroup_launch(M, C, &grid, &block);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto R = static_cast<const __nv_bfloat16*>(res);
   auto O = static_cast<__nv_bfloat16*>(out);
-  if (act && res) bn_apply_kernel<true, true><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
-  else if (act) bn_apply_kernel<true, false><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
-  else if (res) bn_apply_kernel<false, true><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
-  else bn_apply_kernel<false, false><<<grid, 256, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  if (act && res) bn_apply_kernel<true, true><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  else if (act) bn_apply_kernel<true, false><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  else if (res) bn_apply_kernel<false, true><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  else bn_apply_kernel<false, false><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -309,8 +360,9 @@ static int bn_backward_impl(const void* g, int ldg, const void* out, int ldo, co
   BGR_LAUNCH_OK();
   bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
   BGR_LAUNCH_OK();
-  bn_bwd_apply_kernel<<<elementwise_grid(M * (C / 8)), 256, 0, st>>>(D, X, ldx, coef_ws,
-                                                                    static_cast<__nv_bfloat16*>(dx), ldd, M, C);
+  int agrid, ablock;
+  rowgroup_launch(M, C, &agrid, &ablock);
+  bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(D, X, ldx, coef_ws, static_cast<__nv_bfloat16*>(dx), ldd, M, C);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
