@@ -442,16 +442,19 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// issue the six column vectors of input row iy into ring slot `slot` ([col][lane] x 8 bytes)
-__device__ __forceinline__ void march_issue_row(uint2* slot, const __nv_bfloat16* base, const DwGeom& g, int ld,
-                                                int iy, int ox0, bool in_range) {
-  const bool rv = in_range && iy >= 0 && iy < g.H;
-  const __nv_bfloat16* row = base + size_t(rv ? iy : 0) * g.W * ld;
+// issue the six column vectors of input row iy into ring slot `slot` ([col][lane] x 8 bytes).
+// 32-bit element offsets from the item's base pointer (one image is < 2^31 elements); INTERIOR =
+// all six columns of the strip lie inside the image, so only the row needs a validity test.
+template <bool INTERIOR>
+__device__ __forceinline__ void march_issue_row(uint2* slot, const __nv_bfloat16* base, int H, int rowstride,
+                                                int colbase, int ld, int iy, unsigned cmask, bool in_range) {
+  const bool rv = in_range && iy >= 0 && iy < H;
+  const int ro = (rv ? iy : 0) * rowstride + colbase;
 #pragma unroll
   for (int c = 0; c < 6; ++c) {
-    const int ix = ox0 - 1 + c;
-    const bool ok = rv && ix >= 0 && ix < g.W;
-    cp_async8(slot + c * 32, ok ? row + size_t(ix) * ld : base, ok);
+    const bool ok = INTERIOR ? rv : (rv && ((cmask >> c) & 1u));
+    const int off = INTERIOR ? ro + c * ld : (ok ? ro + c * ld : 0);
+    cp_async8(slot + c * 32, base + off, ok);
   }
 }
 // column validity bits of a strip (bit c <-> column ox0 - 1 + c)
@@ -463,6 +466,74 @@ __device__ __forceinline__ unsigned march_col_mask(const DwGeom& g, int ox0) {
     if (ix >= 0 && ix < g.W) m |= 1u << c;
   }
   return m;
+}
+
+// one item (image, row segment, 4-column strip) of the forward / data-gradient march
+template <bool INTERIOR, int XF>
+__device__ __forceinline__ void march_fwd_item(const __nv_bfloat16* __restrict__ xin, __nv_bfloat16* __restrict__ yout,
+                                               const DwGeom& g, const MarchItem& it, const float2 (&wr)[9][2],
+                                               const XfCoef& tc, uint2* ring) {
+  float2 a0[4][2], a1[4][2], a2[4][2];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
+  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(g, it.ox0);
+  const int first = it.oy0 - 1;   // rows first .. oy1 are consumed, one per phase
+  const int rowstride = g.W * g.ldx, colbase = (it.ox0 - 1) * g.ldx;
+  const int orowstride = g.W * g.ldy, ocol = it.ox0 * g.ldy;
+#pragma unroll
+  for (int r = 0; r < kRing; ++r) {
+    march_issue_row<INTERIOR>(ring + r * (6 * 32), xin, g.H, rowstride, colbase, g.ldx, first + r, cmask,
+                              first + r <= it.oy1);
+    cp_async_commit();
+  }
+  // input row iy adds to output rows iy+1 (ky=0), iy (ky=1), iy-1 (ky=2); then row iy-1 is complete
+  auto phase = [&](int iy, float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
+    cp_async_wait<kRing - 1>();   // the oldest outstanding group is row iy
+    uint2* slot = ring + ((iy - first) & (kRing - 1)) * (6 * 32);
+    uint2 rc[6];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
+    march_issue_row<INTERIOR>(slot, xin, g.H, rowstride, colbase, g.ldx, iy + kRing, cmask,
+                              iy + kRing <= it.oy1);   // refill the slot
+    cp_async_commit();
+    const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      float2 xv[2];
+      dw_unpack22(rc[c], xv);
+      dw_transform<XF>(xv, tc, (mc >> c) & 1u);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int kx = c - j;
+        if (kx < 0 || kx > 2) continue;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          next[j][e] = fma2s(xv[e], wr[0 + kx][e], next[j][e]);
+          cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
+          prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
+        }
+      }
+    }
+    const int oy = iy - 1;
+    if (oy >= it.oy0 && oy < it.oy1) {
+      __nv_bfloat16* orow = yout + (oy * orowstride + ocol);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (INTERIOR || it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + j * g.ldy) = dw_pack22(prev[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) prev[j][e] = make_float2(0.f, 0.f);
+  };
+  for (int iy = first; iy <= it.oy1; iy += 3) {
+    phase(iy, a0, a1, a2);
+    if (iy + 1 <= it.oy1) phase(iy + 1, a1, a2, a0);
+    if (iy + 2 <= it.oy1) phase(iy + 2, a2, a0, a1);
+  }
+  cp_async_wait<0>();   // drain the (empty) tail groups before the ring is reused by the next item
 }
 
 template <bool REVERSE, int XF>
@@ -488,71 +559,89 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
   for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
     MarchItem it;
     march_decode(g, sc, item, &it);
-    float2 a0[4][2], a1[4][2], a2[4][2];
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
     const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
     __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + c0;
-    const unsigned cmask = march_col_mask(g, it.ox0);
-    const int first = it.oy0 - 1;   // rows first .. oy1 are consumed, one per phase
-#pragma unroll
-    for (int r = 0; r < kRing; ++r) {
-      march_issue_row(ring + r * (6 * 32), xin, g, g.ldx, first + r, it.ox0, first + r <= it.oy1);
-      cp_async_commit();
-    }
-    // input row iy adds to output rows iy+1 (ky=0), iy (ky=1), iy-1 (ky=2); then row iy-1 is complete
-    auto phase = [&](int iy, float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
-      cp_async_wait<kRing - 1>();   // the oldest outstanding group is row iy
-      uint2* slot = ring + ((iy - first) & (kRing - 1)) * (6 * 32);
-      uint2 rc[6];
-#pragma unroll
-      for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
-      march_issue_row(slot, xin, g, g.ldx, iy + kRing, it.ox0, iy + kRing <= it.oy1);   // refill the slot
-      cp_async_commit();
-      const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
-#pragma unroll
-      for (int c = 0; c < 6; ++c) {
-        float2 xv[2];
-        dw_unpack22(rc[c], xv);
-        dw_transform<XF>(xv, tc, (mc >> c) & 1u);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int kx = c - j;
-          if (kx < 0 || kx > 2) continue;
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            next[j][e] = fma2s(xv[e], wr[0 + kx][e], next[j][e]);
-            cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
-            prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
-          }
-        }
-      }
-      const int oy = iy - 1;
-      if (oy >= it.oy0 && oy < it.oy1) {
-        __nv_bfloat16* orow = yout + size_t(oy) * g.W * g.ldy;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + size_t(it.ox0 + j) * g.ldy) = dw_pack22(prev[j]);
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-#pragma unroll
-        for (int e = 0; e < 2; ++e) prev[j][e] = make_float2(0.f, 0.f);
-    };
-    for (int iy = first; iy <= it.oy1; iy += 3) {
-      phase(iy, a0, a1, a2);
-      if (iy + 1 <= it.oy1) phase(iy + 1, a1, a2, a0);
-      if (iy + 2 <= it.oy1) phase(iy + 2, a2, a0, a1);
-    }
-    cp_async_wait<0>();   // drain the (empty) tail groups before the ring is reused by the next item
+    if (it.ox0 >= 1 && it.ox0 + 5 <= g.W)   // warp-uniform: columns ox0-1 .. ox0+4 all inside
+      march_fwd_item<true, XF>(xin, yout, g, it, wr, tc, ring);
+    else
+      march_fwd_item<false, XF>(xin, yout, g, it, wr, tc, ring);
   }
 }
 
 // dw[ky][kx][c] += sum dy[oy][ox] * x[oy+ky-1][ox+kx-1]; marching over input rows with the three
 // neighbouring dy rows kept (packed) in registers.  Rows of dy outside the segment count as zero.
 // XF: x is LeakyReLU/affine of the stored tensor, recomputed on load (see dw_transform).
+// one item of the weight-gradient march: acc[ky*3+kx] += dy[oy][ox] * x[oy+ky-1][ox+kx-1]
+template <bool INTERIOR, int XF>
+__device__ __forceinline__ void march_wgrad_item(const __nv_bfloat16* __restrict__ xin,
+                                                 const __nv_bfloat16* __restrict__ gin, const DwGeom& g,
+                                                 const MarchItem& it, float2 (&acc)[9][2], const XfCoef& tc,
+                                                 uint2* ring) {
+  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(g, it.ox0);
+  const int first = it.oy0 - 1;
+  const int rowstride = g.W * g.ldx, colbase = (it.ox0 - 1) * g.ldx;
+  const int grow = g.W * g.ldy, gcol = it.ox0 * g.ldy;
+  // group r = input row r and the dy row r + 1 (first needed, as "next", in phase r); dy rows
+  // outside the segment count as zero
+  auto issue = [&](uint2* slot, int r) {
+    const bool in_range = r <= it.oy1;
+    march_issue_row<INTERIOR>(slot, xin, g.H, rowstride, colbase, g.ldx, r, cmask, in_range);
+    const int oy = r + 1;
+    const bool ok = in_range && oy >= it.oy0 && oy < it.oy1;
+    const int go = (ok ? oy : 0) * grow + gcol;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const bool okj = INTERIOR ? ok : (ok && it.ox0 + j < g.W);
+      cp_async8(slot + (6 + j) * 32, gin + (INTERIOR || okj ? go + j * g.ldy : 0), okj);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int r = 0; r < kRing; ++r) issue(ring + r * (10 * 32), first + r);
+  // at input row iy: prev / cur / next = dy rows iy-1 / iy / iy+1
+  auto phase = [&](int iy, const uint2 (&prev)[4], const uint2 (&cur)[4], uint2 (&next)[4]) {
+    cp_async_wait<kRing - 1>();
+    uint2* slot = ring + ((iy - first) & (kRing - 1)) * (10 * 32);
+    uint2 rc[6];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) next[j] = slot[(6 + j) * 32];
+    issue(slot, iy + kRing);
+    const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      float2 xv[2];
+      dw_unpack22(rc[c], xv);
+      dw_transform<XF>(xv, tc, (mc >> c) & 1u);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int kx = c - j;
+        if (kx < 0 || kx > 2) continue;
+        float2 gp[2], gc[2], gn[2];
+        dw_unpack22(prev[j], gp);  // oy = iy-1 -> ky = 2
+        dw_unpack22(cur[j], gc);   // oy = iy   -> ky = 1
+        dw_unpack22(next[j], gn);  // oy = iy+1 -> ky = 0
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          acc[0 + kx][e] = fma2s(gn[e], xv[e], acc[0 + kx][e]);
+          acc[3 + kx][e] = fma2s(gc[e], xv[e], acc[3 + kx][e]);
+          acc[6 + kx][e] = fma2s(gp[e], xv[e], acc[6 + kx][e]);
+        }
+      }
+    }
+  };
+  uint2 d0[4], d1[4], d2[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) d0[j] = d1[j] = d2[j] = make_uint2(0, 0);
+  for (int iy = first; iy <= it.oy1; iy += 3) {
+    phase(iy, d0, d1, d2);
+    if (iy + 1 <= it.oy1) phase(iy + 1, d1, d2, d0);
+    if (iy + 2 <= it.oy1) phase(iy + 2, d2, d0, d1);
+  }
+  cp_async_wait<0>();
+}
+
 template <int XF>
 __global__ void __launch_bounds__(128, 3)
 dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
@@ -579,67 +668,11 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
       march_decode(g, sc, item, &it);
       const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
       const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + c0;
-      const unsigned cmask = march_col_mask(g, it.ox0);
-      const int first = it.oy0 - 1;
-      // group r = input row r and the dy row r + 1 (first needed, as "next", in phase r); dy rows
-      // outside the segment count as zero
-      auto issue = [&](uint2* slot, int r) {
-        const bool in_range = r <= it.oy1;
-        march_issue_row(slot, xin, g, g.ldx, r, it.ox0, in_range);
-        const int oy = r + 1;
-        const bool ok = in_range && oy >= it.oy0 && oy < it.oy1;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const bool okj = ok && it.ox0 + j < g.W;
-          cp_async8(slot + (6 + j) * 32, okj ? gin + (size_t(oy) * g.W + it.ox0 + j) * g.ldy : gin, okj);
-        }
-        cp_async_commit();
-      };
-#pragma unroll
-      for (int r = 0; r < kRing; ++r) issue(ring + r * (10 * 32), first + r);
-      // at input row iy: prev / cur / next = dy rows iy-1 / iy / iy+1
-      auto phase = [&](int iy, const uint2 (&prev)[4], const uint2 (&cur)[4], uint2 (&next)[4]) {
-        cp_async_wait<kRing - 1>();
-        uint2* slot = ring + ((iy - first) & (kRing - 1)) * (10 * 32);
-        uint2 rc[6];
-#pragma unroll
-        for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) next[j] = slot[(6 + j) * 32];
-        issue(slot, iy + kRing);
-        const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
-#pragma unroll
-        for (int c = 0; c < 6; ++c) {
-          float2 xv[2];
-          dw_unpack22(rc[c], xv);
-          dw_transform<XF>(xv, tc, (mc >> c) & 1u);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int kx = c - j;
-            if (kx < 0 || kx > 2) continue;
-            float2 gp[2], gc[2], gn[2];
-            dw_unpack22(prev[j], gp);  // oy = iy-1 -> ky = 2
-            dw_unpack22(cur[j], gc);   // oy = iy   -> ky = 1
-            dw_unpack22(next[j], gn);  // oy = iy+1 -> ky = 0
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              acc[0 + kx][e] = fma2s(gn[e], xv[e], acc[0 + kx][e]);
-              acc[3 + kx][e] = fma2s(gc[e], xv[e], acc[3 + kx][e]);
-              acc[6 + kx][e] = fma2s(gp[e], xv[e], acc[6 + kx][e]);
-            }
-          }
-        }
-      };
-      uint2 d0[4], d1[4], d2[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) d0[j] = d1[j] = d2[j] = make_uint2(0, 0);
-      for (int iy = first; iy <= it.oy1; iy += 3) {
-        phase(iy, d0, d1, d2);
-        if (iy + 1 <= it.oy1) phase(iy + 1, d1, d2, d0);
-        if (iy + 2 <= it.oy1) phase(iy + 2, d2, d0, d1);
-      }
-      cp_async_wait<0>();
-    }  // items
+      if (it.ox0 >= 1 && it.ox0 + 5 <= g.W)
+        march_wgrad_item<true, XF>(xin, gin, g, it, acc, tc, ring);
+      else
+        march_wgrad_item<false, XF>(xin, gin, g, it, acc, tc, ring);
+    }
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
       atomicAdd(&sh[k * 128 + lc + 0], acc[k][0].x);
