@@ -359,21 +359,32 @@ __device__ __forceinline__ uint2 dw_pack4(const float (&f)[4]) {
 
 struct MarchItem {
   int ox0, oy0, oy1, n;
+  int H, W;      // extent of the (sub-)grid this item marches over
+  int off;       // pixel offset of the sub-grid origin inside the image (dilation parity)
 };
 // Work decomposition of the marching kernels.  A block is 4 warps that share one block of 32 channel
-// groups (128 channels, lane = group); each warp loops over items = (image, row segment, 4-column
-// strip).  Weights / reduction registers live for the whole loop, and the weight-gradient kernel
-// flushes 9 x 128 values per block instead of 9 x C.
+// groups (128 channels, lane = group); each warp loops over items = (image, dilation parity, row
+// segment, 4-column strip).  A dilation-d conv is d*d independent dilation-1 convs on the parity
+// sub-grids (rows py, py+d, ...; columns px, px+d, ...), so the same march serves every dilation
+// with the row / column strides multiplied by d.  Weights / reduction registers live for the whole
+// loop, and the weight-gradient kernel flushes 9 x 128 values per block instead of 9 x C.
 struct MarchSched {
-  int segs, RY, cblocks, items;
+  int segs, RY, cblocks, items, dil;
 };
 __device__ __forceinline__ void march_decode(const DwGeom& g, const MarchSched& s, int item, MarchItem* it) {
-  const int strips = (g.W + 3) >> 2;
+  const int Ws = (g.W + s.dil - 1) / s.dil;
+  const int strips = (Ws + 3) >> 2;
   it->ox0 = (item % strips) * 4;
-  const int t = item / strips;
+  int t = item / strips;
   it->oy0 = (t % s.segs) * s.RY;
-  it->n = t / s.segs;
-  it->oy1 = min(it->oy0 + s.RY, g.H);
+  t /= s.segs;
+  const int par = t % (s.dil * s.dil);
+  it->n = t / (s.dil * s.dil);
+  const int py = par / s.dil, px = par - py * s.dil;
+  it->H = (g.H - py + s.dil - 1) / s.dil;
+  it->W = (g.W - px + s.dil - 1) / s.dil;
+  it->off = py * g.W + px;
+  it->oy1 = min(it->oy0 + s.RY, it->H);
 }
 
 // 4 bf16 channels -> two packed fp32 pairs (bf16 -> fp32 is a 16-bit shift)
@@ -458,12 +469,12 @@ __device__ __forceinline__ void march_issue_row(uint2* slot, const __nv_bfloat16
   }
 }
 // column validity bits of a strip (bit c <-> column ox0 - 1 + c)
-__device__ __forceinline__ unsigned march_col_mask(const DwGeom& g, int ox0) {
+__device__ __forceinline__ unsigned march_col_mask(int W, int ox0) {
   unsigned m = 0;
 #pragma unroll
   for (int c = 0; c < 6; ++c) {
     const int ix = ox0 - 1 + c;
-    if (ix >= 0 && ix < g.W) m |= 1u << c;
+    if (ix >= 0 && ix < W) m |= 1u << c;
   }
   return m;
 }
@@ -471,20 +482,20 @@ __device__ __forceinline__ unsigned march_col_mask(const DwGeom& g, int ox0) {
 // one item (image, row segment, 4-column strip) of the forward / data-gradient march
 template <bool INTERIOR, int XF>
 __device__ __forceinline__ void march_fwd_item(const __nv_bfloat16* __restrict__ xin, __nv_bfloat16* __restrict__ yout,
-                                               const DwGeom& g, const MarchItem& it, const float2 (&wr)[9][2],
-                                               const XfCoef& tc, uint2* ring) {
+                                               const DwGeom& g, int dil, const MarchItem& it,
+                                               const float2 (&wr)[9][2], const XfCoef& tc, uint2* ring) {
   float2 a0[4][2], a1[4][2], a2[4][2];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
     for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
-  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(g, it.ox0);
+  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(it.W, it.ox0);
   const int first = it.oy0 - 1;   // rows first .. oy1 are consumed, one per phase
-  const int rowstride = g.W * g.ldx, colbase = (it.ox0 - 1) * g.ldx;
-  const int orowstride = g.W * g.ldy, ocol = it.ox0 * g.ldy;
+  const int cstep = g.ldx * dil, rowstride = g.W * cstep, colbase = (it.ox0 - 1) * cstep;
+  const int ostep = g.ldy * dil, orowstride = g.W * ostep, ocol = it.ox0 * ostep;
 #pragma unroll
   for (int r = 0; r < kRing; ++r) {
-    march_issue_row<INTERIOR>(ring + r * (6 * 32), xin, g.H, rowstride, colbase, g.ldx, first + r, cmask,
+    march_issue_row<INTERIOR>(ring + r * (6 * 32), xin, it.H, rowstride, colbase, cstep, first + r, cmask,
                               first + r <= it.oy1);
     cp_async_commit();
   }
@@ -495,10 +506,10 @@ __device__ __forceinline__ void march_fwd_item(const __nv_bfloat16* __restrict__
     uint2 rc[6];
 #pragma unroll
     for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
-    march_issue_row<INTERIOR>(slot, xin, g.H, rowstride, colbase, g.ldx, iy + kRing, cmask,
+    march_issue_row<INTERIOR>(slot, xin, it.H, rowstride, colbase, cstep, iy + kRing, cmask,
                               iy + kRing <= it.oy1);   // refill the slot
     cp_async_commit();
-    const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
+    const unsigned mc = (iy >= 0 && iy < it.H) ? cmask : 0u;
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
       float2 xv[2];
@@ -521,7 +532,7 @@ __device__ __forceinline__ void march_fwd_item(const __nv_bfloat16* __restrict__
       __nv_bfloat16* orow = yout + (oy * orowstride + ocol);
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        if (INTERIOR || it.ox0 + j < g.W) *reinterpret_cast<uint2*>(orow + j * g.ldy) = dw_pack22(prev[j]);
+        if (INTERIOR || it.ox0 + j < it.W) *reinterpret_cast<uint2*>(orow + j * ostep) = dw_pack22(prev[j]);
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j)
@@ -559,12 +570,12 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
   for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
     MarchItem it;
     march_decode(g, sc, item, &it);
-    const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
-    __nv_bfloat16* yout = y + size_t(it.n) * g.H * g.W * g.ldy + c0;
-    if (it.ox0 >= 1 && it.ox0 + 5 <= g.W)   // warp-uniform: columns ox0-1 .. ox0+4 all inside
-      march_fwd_item<true, XF>(xin, yout, g, it, wr, tc, ring);
+    const __nv_bfloat16* xin = x + (size_t(it.n) * g.H * g.W + it.off) * g.ldx + c0;
+    __nv_bfloat16* yout = y + (size_t(it.n) * g.H * g.W + it.off) * g.ldy + c0;
+    if (it.ox0 >= 1 && it.ox0 + 5 <= it.W)   // warp-uniform: columns ox0-1 .. ox0+4 all inside
+      march_fwd_item<true, XF>(xin, yout, g, sc.dil, it, wr, tc, ring);
     else
-      march_fwd_item<false, XF>(xin, yout, g, it, wr, tc, ring);
+      march_fwd_item<false, XF>(xin, yout, g, sc.dil, it, wr, tc, ring);
   }
 }
 
@@ -575,24 +586,24 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
 template <bool INTERIOR, int XF>
 __device__ __forceinline__ void march_wgrad_item(const __nv_bfloat16* __restrict__ xin,
                                                  const __nv_bfloat16* __restrict__ gin, const DwGeom& g,
-                                                 const MarchItem& it, float2 (&acc)[9][2], const XfCoef& tc,
-                                                 uint2* ring) {
-  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(g, it.ox0);
+                                                 int dil, const MarchItem& it, float2 (&acc)[9][2],
+                                                 const XfCoef& tc, uint2* ring) {
+  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(it.W, it.ox0);
   const int first = it.oy0 - 1;
-  const int rowstride = g.W * g.ldx, colbase = (it.ox0 - 1) * g.ldx;
-  const int grow = g.W * g.ldy, gcol = it.ox0 * g.ldy;
+  const int cstep = g.ldx * dil, rowstride = g.W * cstep, colbase = (it.ox0 - 1) * cstep;
+  const int gstep = g.ldy * dil, grow = g.W * gstep, gcol = it.ox0 * gstep;
   // group r = input row r and the dy row r + 1 (first needed, as "next", in phase r); dy rows
   // outside the segment count as zero
   auto issue = [&](uint2* slot, int r) {
     const bool in_range = r <= it.oy1;
-    march_issue_row<INTERIOR>(slot, xin, g.H, rowstride, colbase, g.ldx, r, cmask, in_range);
+    march_issue_row<INTERIOR>(slot, xin, it.H, rowstride, colbase, cstep, r, cmask, in_range);
     const int oy = r + 1;
     const bool ok = in_range && oy >= it.oy0 && oy < it.oy1;
     const int go = (ok ? oy : 0) * grow + gcol;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const bool okj = INTERIOR ? ok : (ok && it.ox0 + j < g.W);
-      cp_async8(slot + (6 + j) * 32, gin + (INTERIOR || okj ? go + j * g.ldy : 0), okj);
+      const bool okj = INTERIOR ? ok : (ok && it.ox0 + j < it.W);
+      cp_async8(slot + (6 + j) * 32, gin + (INTERIOR || okj ? go + j * gstep : 0), okj);
     }
     cp_async_commit();
   };
@@ -608,7 +619,7 @@ __device__ __forceinline__ void march_wgrad_item(const __nv_bfloat16* __restrict
 #pragma unroll
     for (int j = 0; j < 4; ++j) next[j] = slot[(6 + j) * 32];
     issue(slot, iy + kRing);
-    const unsigned mc = (iy >= 0 && iy < g.H) ? cmask : 0u;
+    const unsigned mc = (iy >= 0 && iy < it.H) ? cmask : 0u;
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
       float2 xv[2];
@@ -666,12 +677,12 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
     for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
       MarchItem it;
       march_decode(g, sc, item, &it);
-      const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
-      const __nv_bfloat16* gin = dy + size_t(it.n) * g.H * g.W * g.ldy + c0;
-      if (it.ox0 >= 1 && it.ox0 + 5 <= g.W)
-        march_wgrad_item<true, XF>(xin, gin, g, it, acc, tc, ring);
+      const __nv_bfloat16* xin = x + (size_t(it.n) * g.H * g.W + it.off) * g.ldx + c0;
+      const __nv_bfloat16* gin = dy + (size_t(it.n) * g.H * g.W + it.off) * g.ldy + c0;
+      if (it.ox0 >= 1 && it.ox0 + 5 <= it.W)
+        march_wgrad_item<true, XF>(xin, gin, g, sc.dil, it, acc, tc, ring);
       else
-        march_wgrad_item<false, XF>(xin, gin, g, it, acc, tc, ring);
+        march_wgrad_item<false, XF>(xin, gin, g, sc.dil, it, acc, tc, ring);
     }
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
@@ -693,17 +704,20 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
 static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
   int sms = 148, dev = 0;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int G = g.C / kCpt, strips = (g.W + 3) / 4;
+  const int dil = g.dil < 1 ? 1 : g.dil;
+  const int Hs = (g.H + dil - 1) / dil, Ws = (g.W + dil - 1) / dil, NP = g.N * dil * dil;
+  const int G = g.C / kCpt, strips = (Ws + 3) / 4;
+  sc->dil = dil;
   sc->cblocks = (G + 31) / 32;
   int pb_max = sms * 3 / sc->cblocks;
   if (pb_max < 1) pb_max = 1;
-  long segs = (32L * pb_max + long(g.N) * strips - 1) / (long(g.N) * strips);   // ~8 items per warp
-  const long max_segs = (g.H + 5) / 6;
+  long segs = (32L * pb_max + long(NP) * strips - 1) / (long(NP) * strips);   // ~8 items per warp
+  const long max_segs = (Hs + 5) / 6;
   if (segs > max_segs) segs = max_segs;
   if (segs < 1) segs = 1;
-  sc->RY = int((g.H + segs - 1) / segs);
-  sc->segs = (g.H + sc->RY - 1) / sc->RY;
-  sc->items = g.N * sc->segs * strips;
+  sc->RY = int((Hs + segs - 1) / segs);
+  sc->segs = (Hs + sc->RY - 1) / sc->RY;
+  sc->items = NP * sc->segs * strips;
   const int ipw = (sc->items + 4 * pb_max - 1) / (4 * pb_max);   // items per warp
   const int pb = (sc->items + 4 * ipw - 1) / (4 * ipw);
   *blocks = unsigned(pb) * sc->cblocks;
@@ -751,7 +765,7 @@ extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, co
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto Y = static_cast<__nv_bfloat16*>(y);
-  if (stride == 1 && dil == 1) {
+  if (stride == 1) {   // any dilation: parity sub-grids
     MarchSched sc;
     unsigned blocks;
     march_plan(g, &sc, &blocks);
@@ -775,15 +789,11 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
     DwGeom r = g;
     r.ldx = ldy;
     r.ldy = ldx;
-    if (dil == 1) {
-      MarchSched sc;
-      unsigned blocks;
-      march_plan(r, &sc, &blocks);
-      dw_march_fwd_kernel<true, 0><<<blocks, 128, 0, st>>>(DY, w, DX, r, sc, nullptr, nullptr, 0.f);
-      done = true;
-    } else {
-      done = launch_fwd_strip<true>(DY, w, DX, r, st);
-    }
+    MarchSched sc;
+    unsigned blocks;
+    march_plan(r, &sc, &blocks);
+    dw_march_fwd_kernel<true, 0><<<blocks, 128, 0, st>>>(DY, w, DX, r, sc, nullptr, nullptr, 0.f);
+    done = true;
   }
   if (!done) dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
   BGR_LAUNCH_OK();
@@ -868,8 +878,7 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto DY = static_cast<const __nv_bfloat16*>(dy);
   int rc = BGR_OK;
-  if (stride == 1 && dil == 1) rc = launch_march_wgrad<0>(X, DY, dw, g, nullptr, nullptr, 0.f, st);
-  else if (stride == 1 && dil == 2) rc = launch_wgrad_strip<1, 2>(X, DY, dw, g, st);
+  if (stride == 1) rc = launch_march_wgrad<0>(X, DY, dw, g, nullptr, nullptr, 0.f, st);   // any dilation
   else if (stride == 2 && dil == 1) rc = launch_wgrad_strip<2, 1>(X, DY, dw, g, st);
   else {
     const long P = long(N) * g.Ho * g.Wo;

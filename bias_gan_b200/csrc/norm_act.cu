@@ -182,11 +182,11 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
       ca[j] = ACT == 2 ? xa[gi * 8 + j] : 0.f;
       cb[j] = ACT == 2 ? xb[gi * 8 + j] : 0.f;
     }
-    for (long row = r0 + r; row < r1; row += m.R) {
+    auto one = [&](long row, const uint4& gu, const uint4& xu, const uint4& ou) {
       float gv[8], xv[8], ov[8];
-      unpack8(*reinterpret_cast<const uint4*>(g + row * ldg + gi * 8), gv);
-      unpack8(*reinterpret_cast<const uint4*>(x + row * ldx + gi * 8), xv);
-      if (ACT == 1) unpack8(*reinterpret_cast<const uint4*>(out + row * ldo + gi * 8), ov);
+      unpack8(gu, gv);
+      unpack8(xu, xv);
+      if (ACT == 1) unpack8(ou, ov);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float d = gv[j];
@@ -200,7 +200,24 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
         s2[j] += d * (xv[j] - mu[j]) * is[j];
       }
       *reinterpret_cast<uint4*>(dyh + row * ldd + gi * 8) = pack8(gv);
+    };
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    long row = r0 + r;
+    for (; row + m.R < r1; row += 2 * m.R) {   // two rows (6 loads) in flight per thread
+      const long row2 = row + m.R;
+      const uint4 g0 = *reinterpret_cast<const uint4*>(g + row * ldg + gi * 8);
+      const uint4 g1 = *reinterpret_cast<const uint4*>(g + row2 * ldg + gi * 8);
+      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + gi * 8);
+      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + gi * 8);
+      const uint4 o0 = ACT == 1 ? *reinterpret_cast<const uint4*>(out + row * ldo + gi * 8) : z4;
+      const uint4 o1 = ACT == 1 ? *reinterpret_cast<const uint4*>(out + row2 * ldo + gi * 8) : z4;
+      one(row, g0, x0, o0);
+      one(row2, g1, x1, o1);
     }
+    if (row < r1)
+      one(row, *reinterpret_cast<const uint4*>(g + row * ldg + gi * 8),
+          *reinterpret_cast<const uint4*>(x + row * ldx + gi * 8),
+          ACT == 1 ? *reinterpret_cast<const uint4*>(out + row * ldo + gi * 8) : z4);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       atomicAdd(&sh[gi * 8 + j], s1[j]);

@@ -255,7 +255,8 @@ def test_bn_act_depthwise_fused(dev, C, N, H, W, act):
 
 # --------------------------------------------------------------------------------- depthwise
 @pytest.mark.parametrize("C,H,W,stride,dil", [(128, 24, 36, 1, 1), (128, 25, 37, 2, 1), (728, 6, 9, 1, 1),
-                                              (1536, 5, 7, 1, 2), (256, 12, 18, 2, 1)])
+                                              (1536, 5, 7, 1, 2), (256, 12, 18, 2, 1), (128, 13, 11, 1, 2),
+                                              (64, 9, 10, 1, 4), (136, 48, 72, 1, 2), (8, 3, 2, 1, 1)])
 def test_depthwise(dev, C, H, W, stride, dil):
     from bias_gan_b200 import functional as F_
     g = torch.Generator(device="cpu").manual_seed(5)
