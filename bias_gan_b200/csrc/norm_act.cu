@@ -160,7 +160,8 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __res
 // `out + C` ... is unused: a, b come in through `xa`, `xb`.
 template <int ACT>
 __global__ void __launch_bounds__(256)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ out,
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ g2,
+                     int ldg2, const __nv_bfloat16* __restrict__ out,
                      int ldo, const float* __restrict__ xa, const float* __restrict__ xb,
                      const __nv_bfloat16* __restrict__ x, int ldx,
                      const float* __restrict__ mean, const float* __restrict__ invstd,
@@ -185,6 +186,12 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
     auto one = [&](long row, const uint4& gu, const uint4& xu, const uint4& ou) {
       float gv[8], xv[8], ov[8];
       unpack8(gu, gv);
+      if (g2 != nullptr) {   // second gradient of the same tensor (residual path), summed in fp32
+        float hv[8];
+        unpack8(*reinterpret_cast<const uint4*>(g2 + row * ldg2 + gi * 8), hv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gv[j] += hv[j];
+      }
       unpack8(xu, xv);
       if (ACT == 1) unpack8(ou, ov);
 #pragma unroll
@@ -358,7 +365,8 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
   return BGR_OK;
 }
 
-static int bn_backward_impl(const void* g, int ldg, const void* out, int ldo, const float* xa, const float* xb,
+static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
+                            const float* xa, const float* xb,
                             const void* x, int ldx, const float* mean, const float* invstd,
                             const float* gamma, int act, float slope, long M, int C, void* dyh, void* dx,
                             int ldd, double* sums, float* coef_ws, void* stream) {
@@ -368,12 +376,13 @@ static int bn_backward_impl(const void* g, int ldg, const void* out, int ldo, co
   int rpb;
   const int grid = reduce_grid(M, C, &rpb);
   auto G = static_cast<const __nv_bfloat16*>(g);
+  auto G2 = static_cast<const __nv_bfloat16*>(g2);
   auto O = static_cast<const __nv_bfloat16*>(out);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto D = static_cast<__nv_bfloat16*>(dyh);
-  if (act == 2) bn_bwd_reduce_kernel<2><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
-  else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
-  else bn_bwd_reduce_kernel<0><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  if (act == 2) bn_bwd_reduce_kernel<2><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  else bn_bwd_reduce_kernel<0><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
   BGR_LAUNCH_OK();
   bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
   BGR_LAUNCH_OK();
@@ -384,11 +393,11 @@ static int bn_backward_impl(const void* g, int ldg, const void* out, int ldo, co
   return BGR_OK;
 }
 
-extern "C" int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
-                               const float* mean, const float* invstd, const float* gamma, int act,
-                               float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
-                               float* coef_ws, void* stream) {
-  return bn_backward_impl(g, ldg, out, ldo, nullptr, nullptr, x, ldx, mean, invstd, gamma, act ? 1 : 0, slope, M, C,
+extern "C" int bgr_bn_backward(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
+                               const void* x, int ldx, const float* mean, const float* invstd,
+                               const float* gamma, int act, float slope, long M, int C, void* dyh, void* dx,
+                               int ldd, double* sums, float* coef_ws, void* stream) {
+  return bn_backward_impl(g, ldg, g2, ldg2, out, ldo, nullptr, nullptr, x, ldx, mean, invstd, gamma, act ? 1 : 0, slope, M, C,
                           dyh, dx, ldd, sums, coef_ws, stream);
 }
 
@@ -398,6 +407,6 @@ extern "C" int bgr_bn_backward_recompute(const void* g, int ldg, const float* a,
                                          int ldx, const float* mean, const float* invstd,
                                          const float* gamma, int act, float slope, long M, int C, void* dyh,
                                          void* dx, int ldd, double* sums, float* coef_ws, void* stream) {
-  return bn_backward_impl(g, ldg, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
+  return bn_backward_impl(g, ldg, nullptr, 0, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
                           ldd, sums, coef_ws, stream);
 }

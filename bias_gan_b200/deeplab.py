@@ -74,7 +74,12 @@ class Block(nn.Module):
             rep.append(SeparableConv2d_same(planes, planes, 3, stride=1))
         self.rep = nn.Sequential(*rep)
 
-    def forward(self, a, act_out):
+    def forward(self, a, act_out, dual_out=False):
+        """`a` may be a pair of handles (a_main, a_side) of the same tensor (bn_act(dual=True)): the
+        separable convs read a_main, the skip / residual path a_side, so that their gradients reach
+        the producing BatchNorm's backward separately and are summed there.  dual_out=True returns
+        such a pair for the next block."""
+        a, a_side = a if isinstance(a, tuple) else (a, a)
         mods = list(self.rep)
         x = a
         i = 0
@@ -109,13 +114,13 @@ class Block(nn.Module):
         if pending is not None:
             tail_bn = pending  # last rep element is a BN: fuse with the residual add
         if self.skip is not None:
-            s_in = F_.subsample2(a) if self.stride == 2 else a
+            s_in = F_.subsample2(a_side) if self.stride == 2 else a_side
             s = F_.conv2d(s_in, self.skip.weight, want_stats=self.skipbn.training)
             if tail_bn is not None:
                 x = F_.bn_act(tail_bn[0], tail_bn[1], act=False)
-            return F_.bn_act(s, self.skipbn, res=x, act=act_out)
+            return F_.bn_act(s, self.skipbn, res=x, act=act_out, dual=dual_out)
         if tail_bn is not None:
-            return F_.bn_act(tail_bn[0], tail_bn[1], res=a, act=act_out)
+            return F_.bn_act(tail_bn[0], tail_bn[1], res=a_side, act=act_out, dual=dual_out)
         raise NotImplementedError("identity-skip block ending in a convolution does not occur in Xception")
 
 
@@ -165,13 +170,13 @@ class Xception(nn.Module):
         [N,H/16,W/16,2048], low_level [N,H/4,W/4,128]) — both activated, as the reference's
         in-place LeakyReLUs leave them."""
         x = F_.bn_act(F_.conv_s2d(field, self.conv1.weight, self.bn1.training), self.bn1, act=True)
-        x = F_.bn_act(F_.conv2d(x, self.conv2.weight, want_stats=self.bn2.training), self.bn2, act=True)
-        x = self.block1(x, act_out=True)
-        low = x
-        x = self.block2(x, act_out=True)
-        x = self.block3(x, act_out=True)
+        x = F_.bn_act(F_.conv2d(x, self.conv2.weight, want_stats=self.bn2.training), self.bn2, act=True, dual=True)
+        x = self.block1(x, act_out=True, dual_out=True)
+        low = x[0]
+        x = self.block2(x, act_out=True, dual_out=True)
+        x = self.block3(x, act_out=True, dual_out=True)
         for i in range(4, 20):
-            x = getattr(self, "block%d" % i)(x, act_out=True)
+            x = getattr(self, "block%d" % i)(x, act_out=True, dual_out=True)
         x = self.block20(x, act_out=False)
         x = F_.bn_act(self.conv3(x, self.bn3.training), self.bn3, act=True)
         x = F_.bn_act(self.conv4(x, self.bn4.training), self.bn4, act=True)

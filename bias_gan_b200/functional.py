@@ -120,7 +120,7 @@ class _BNAct(torch.autograd.Function):
     """out = act(BatchNorm_train(y) [+ res]) with batch statistics (nn.BatchNorm2d training mode)."""
 
     @staticmethod
-    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act, sums, nbt):
+    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act, sums, nbt, dual):
         M = y.numel() // y.shape[-1]
         if sums is None:
             sums = K.bn_stats(y)
@@ -129,18 +129,23 @@ class _BNAct(torch.autograd.Function):
         ctx.save_for_backward(y, out if act else None, mean, invstd, gamma)
         ctx.act = act
         ctx.has_res = res is not None
+        if dual:   # a second handle of the same tensor: its gradient arrives separately (see bn_act)
+            return out, out[...]
         return out
 
     @staticmethod
-    def backward(ctx, g):
+    def backward(ctx, g, g2=None):
         y, out, mean, invstd, gamma = ctx.saved_tensors
+        if g is None:
+            g, g2 = g2, None
         g = _bf16c(g)
+        g2 = _bf16c(g2) if g2 is not None else None
         C = y.shape[-1]
-        dx, dyh, sums = K.bn_backward(g, out, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
+        dx, dyh, sums = K.bn_backward(g, out, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE, g2=g2)
         ggamma = sums[C:] if ctx.needs_input_grad[1] else None
         gbeta = sums[:C] if ctx.needs_input_grad[2] else None
         gres = dyh if (ctx.has_res and ctx.needs_input_grad[3]) else None
-        return dx, ggamma, gbeta, gres, None, None, None, None, None, None, None
+        return dx, ggamma, gbeta, gres, None, None, None, None, None, None, None, None
 
 
 class _BNActDepthwise(torch.autograd.Function):
@@ -212,17 +217,22 @@ def _nbt(bn):
     return t
 
 
-def bn_act(y, bn, res=None, act=True, sums=None):
+def bn_act(y, bn, res=None, act=True, sums=None, dual=False):
     """`bn` is a torch.nn.BatchNorm2d-compatible module (weight, bias, running_*, eps, momentum).
-    `y` may be the (y, sums) pair of a conv called with want_stats=True."""
+    `y` may be the (y, sums) pair of a conv called with want_stats=True.
+    dual=True returns two handles (out, out') of the same tensor for a result that feeds two paths
+    (a block input: separable convs + skip/residual): autograd then delivers the two gradients
+    separately and the BatchNorm backward kernel adds them while loading, instead of a separate
+    full-tensor add kernel."""
     if isinstance(y, tuple):
         y, sums = y
     if bn.training:
         return _BNAct.apply(y, bn.weight, bn.bias, res, bn.running_mean, bn.running_var, bn.eps,
-                            bn.momentum, act, sums, _nbt(bn))
+                            bn.momentum, act, sums, _nbt(bn), dual)
     a = (bn.weight * torch.rsqrt(bn.running_var + bn.eps)).float().contiguous()
     b = (bn.bias - bn.running_mean * a).float().contiguous()
-    return _AffineAct.apply(y, a, b, res, act)
+    out = _AffineAct.apply(y, a, b, res, act)
+    return (out, out) if dual else out
 
 
 class _Subsample2(torch.autograd.Function):

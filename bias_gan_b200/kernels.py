@@ -205,12 +205,16 @@ def bn_apply(x, a, b, res=None, act=True, slope=0.2, out=None):
     return out
 
 
-def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2):
+def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2, g2=None):
     """Returns (dx, dyh, grads) — dyh is also the gradient of the residual input; grads = fp32
     [dL/dbeta (C) | dL/dgamma (C)]."""
     M, C, ldx = _rows(x)
     Mg, Cg, ldg = _rows(g)
     assert (Mg, Cg) == (M, C)
+    ldg2 = 0
+    if g2 is not None:
+        M2, C2, ldg2 = _rows(g2)
+        assert (M2, C2) == (M, C)
     ldo = 0
     if act:
         Mo, Co, ldo = _rows(out)
@@ -219,7 +223,7 @@ def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2):
     dx = act_empty(x.shape, x.device)
     sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
     coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
-    check(_lib.lib().bgr_bn_backward(ptr(g), ldg, ptr(out) if act else ctypes.c_void_p(0), ldo, ptr(x), ldx,
+    check(_lib.lib().bgr_bn_backward(ptr(g), ldg, ptr(g2), ldg2, ptr(out) if act else ctypes.c_void_p(0), ldo, ptr(x), ldx,
                                      ptr(mean), ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
                                      ptr(dyh), ptr(dx), _rows(dx)[2], ptr(sums), ptr(coef), stream_ptr()))
     return dx, dyh, coef[5 * C:7 * C]   # fp32 [dL/dbeta | dL/dgamma]

@@ -128,11 +128,14 @@ int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const
 /* out = act(a*x + b [+ res]); act != 0: LeakyReLU(slope). */
 int bgr_bn_apply(const void* x, int ldx, const float* a, const float* b, const void* res, int ldr,
                  void* out, int ldo, long M, int C, int act, float slope, void* stream);
-/* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; dyh ([M][C], pixel stride ldd) receives
+/* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; g2 (optional, NULL): a second gradient
+ * of the same output, added on load (the block input feeds both the separable convs and the skip /
+ * residual path, deeplab.py:137-141); dyh ([M][C], pixel stride ldd) receives
  * g*act'(out), which is also dL/dres; dx (same stride) receives dL/dx; sums (fp64 [2][C]) receives
  * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat; coef_ws: fp32 [7][C] workspace whose rows 5 and 6
  * return dL/dbeta and dL/dgamma in fp32. */
-int bgr_bn_backward(const void* g, int ldg, const void* out, int ldo, const void* x, int ldx,
+int bgr_bn_backward(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
+                    const void* x, int ldx,
                     const float* mean, const float* invstd, const float* gamma, int act, float slope,
                     long M, int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
                     void* stream);

@@ -29,11 +29,11 @@ for n in names:
     getattr(xr, n).register_forward_hook(lambda m, i, o, n=n: ref_out.__setitem__(n, o.detach().clone()))
 for n in names:
     if n.startswith("block"):
-        getattr(xp, n).register_forward_hook(lambda m, i, o, n=n: prod_out.__setitem__(n, o.detach().permute(0, 3, 1, 2).float()))
+        getattr(xp, n).register_forward_hook(lambda m, i, o, n=n: prod_out.__setitem__(n, (o[0] if isinstance(o, tuple) else o).detach().permute(0, 3, 1, 2).float()))
 for tag, mods in (("aspp1", (Gr.model.aspp1, Gp.model.aspp1)), ("aspp2", (Gr.model.aspp2, Gp.model.aspp2)),
                   ("aspp4", (Gr.model.aspp4, Gp.model.aspp4))):
     mods[0].register_forward_hook(lambda m, i, o, n=tag: ref_out.__setitem__(n, o.detach().clone()))
-    mods[1].register_forward_hook(lambda m, i, o, n=tag: prod_out.__setitem__(n, o.detach().permute(0, 3, 1, 2).float()))
+    mods[1].register_forward_hook(lambda m, i, o, n=tag: prod_out.__setitem__(n, (o[0] if isinstance(o, tuple) else o).detach().permute(0, 3, 1, 2).float()))
 
 out_r = Gr(x)
 with torch.autocast("cuda", dtype=torch.bfloat16):
