@@ -28,6 +28,7 @@ struct ConvParams {
   int ntaps, kblocks;       // taps and 64-channel blocks per tap
   int Cout, Cin, ld_out;    // valid channels, output row stride (elements)
   int m_tiles, n_tiles;     // fprop only: pixel tiles, Cout tiles
+  int dbg;                  // development switch (0 in production)
   int chunks_per_split;     // wgrad only
   int total_chunks;         // wgrad only
   int dy[kMaxTaps], dx[kMaxTaps];
@@ -41,23 +42,9 @@ struct ConvParams {
 //   warps 2-5 epilogue: tcgen05.ld -> (+bias) -> bf16 -> 128B-swizzled smem -> TMA store in
 //             64-channel chunks (two staging buffers), overlapped with the next tile's MMAs.
 //             Optional fused BatchNorm statistics: per-channel sum / sum-of-squares of the
-//             bf16-rounded outputs by a lane-transposing butterfly, smem atomics, then one fp64
-//             global atomic per channel and tile.
+//             bf16-rounded outputs, read back from the staged tile (column sums), kept in registers
+//             for the CTA's life, then one fp64 global atomic per channel and CTA.
 // ------------------------------------------------------------------------------------------
-// Sum v[0..31] over the 32 lanes of a warp: lane l ends with column l's total in v[0].
-__device__ __forceinline__ void warp_transpose_reduce32(float (&v)[32], int lane) {
-#pragma unroll
-  for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
-    const bool upper = (lane & off) != 0;
-#pragma unroll
-    for (int i = 0; i < n / 2; ++i) {
-      const float send = upper ? v[i] : v[i + n / 2];
-      const float keep = upper ? v[i + n / 2] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-    }
-  }
-}
-
 template <int BLOCK_N, int STAGES, bool STATS>
 __global__ void __launch_bounds__(192, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -165,10 +152,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int q = warp & 3;                  // TMEM lane quadrant this warp may access
     const int row = q * 32 + lane;           // tile row = pixel (row % BW, row / BW) of the rectangle
     const int epi_tid = threadIdx.x - 64;    // 0..127
-    const int ly = row / p.BW, lx = row - ly * p.BW;
     uint8_t* my_row = nullptr;
     uint32_t lt = 0, chunk_ctr = 0;
-    // BatchNorm partial sums of this CTA's Cout tile: lane l keeps channels c*64 + h*32 + l
+    // BatchNorm partial sums of this CTA's Cout tile over this warp's rows: st_*[c*2 + e] <-> channel c*64 + 2*lane + e
     float st_sum[BLOCK_N / 32], st_sq[BLOCK_N / 32];
 #pragma unroll
     for (int i = 0; i < BLOCK_N / 32; ++i) st_sum[i] = st_sq[i] = 0.f;
@@ -177,7 +163,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const int ty = (mt / p.tiles_x) % p.tiles_y;
       const int n = mt / (p.tiles_x * p.tiles_y);
       const int x0 = tx * p.BW, y0 = ty * p.BH;
-      const bool row_ok = (y0 + ly < p.H) && (x0 + lx < p.W);
+      const bool tile_full = (y0 + p.BH <= p.H) && (x0 + p.BW <= p.W);
       const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
       mbar_wait(&tfull[acc], aph);
       tc_fence_after();
@@ -207,12 +193,6 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           o.z = pack_bf16(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5]));
           o.w = pack_bf16(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7]));
           *reinterpret_cast<uint4*>(my_row + ((j ^ (row & 7)) << 4)) = o;
-          if (STATS) {  // keep the rounded values for the statistics
-            v[j * 8 + 0] = o.x << 16; v[j * 8 + 1] = o.x & 0xffff0000u;
-            v[j * 8 + 2] = o.y << 16; v[j * 8 + 3] = o.y & 0xffff0000u;
-            v[j * 8 + 4] = o.z << 16; v[j * 8 + 5] = o.z & 0xffff0000u;
-            v[j * 8 + 6] = o.w << 16; v[j * 8 + 7] = o.w & 0xffff0000u;
-          }
         }
         fence_proxy_async();
         named_bar_sync(1, 128);
@@ -220,21 +200,36 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           tma_store_5d(&tmO, buf, ch0, 0, x0, y0, n);
           bulk_commit_group();
         }
-        if (STATS) {
+        if (STATS && p.dbg != 1) {
+          // Column sums straight from the staged bf16 tile (already the rounded values): warp q sums
+          // its 32 rows, lane l the channel pair (2l, 2l+1) = one 4-byte word per row; within a row the
+          // 32 lanes read 32 distinct banks.  (A register butterfly over the fp32 accumulators cost 3x
+          // the instructions: FSEL 26 %, SHFL 10 % of the kernel.)
+          const uint8_t* col = buf + ((lane & 3) << 2);
+          const int chunk16 = lane >> 2;
+          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+          if (tile_full) {   // straight-line body: the 32 loads pipeline
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            float a[32], b[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float f = row_ok ? __uint_as_float(v[h * 32 + j]) : 0.f;
-              a[j] = f;
-              b[j] = f * f;
+            for (int rr = 0; rr < 32; ++rr) {
+              const int r = q * 32 + rr;
+              const uint32_t wv = *reinterpret_cast<const uint32_t*>(col + r * 128 + ((chunk16 ^ (r & 7)) << 4));
+              const float f0 = __uint_as_float(wv << 16), f1 = __uint_as_float(wv & 0xffff0000u);
+              s0 += f0; s1 += f1;
+              q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
             }
-            warp_transpose_reduce32(a, lane);
-            warp_transpose_reduce32(b, lane);
-            st_sum[c * 2 + h] += a[0];
-            st_sq[c * 2 + h] += b[0];
+          } else {           // ragged tile: rows outside the image do not count
+            for (int rr = 0; rr < 32; ++rr) {
+              const int r = q * 32 + rr;
+              const int yy = r / p.BW, xx = r - yy * p.BW;
+              if (y0 + yy >= p.H || x0 + xx >= p.W) continue;
+              const uint32_t wv = *reinterpret_cast<const uint32_t*>(col + r * 128 + ((chunk16 ^ (r & 7)) << 4));
+              const float f0 = __uint_as_float(wv << 16), f1 = __uint_as_float(wv & 0xffff0000u);
+              s0 += f0; s1 += f1;
+              q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+            }
           }
+          st_sum[c * 2 + 0] += s0; st_sum[c * 2 + 1] += s1;
+          st_sq[c * 2 + 0] += q0;  st_sq[c * 2 + 1] += q1;
         }
         ++chunk_ctr;
       }
@@ -244,9 +239,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     if (STATS) {  // combine the four warps in shared memory, then one fp64 atomic per channel and CTA
 #pragma unroll
-      for (int i = 0; i < BLOCK_N / 32; ++i) {
-        atomicAdd(&s_stats[i * 32 + lane], st_sum[i]);
-        atomicAdd(&s_stats[BLOCK_N + i * 32 + lane], st_sq[i]);
+      for (int i = 0; i < BLOCK_N / 32; ++i) {   // st_*[c*2 + e] <-> channel c*64 + 2*lane + e
+        const int ch = (i >> 1) * 64 + 2 * lane + (i & 1);
+        atomicAdd(&s_stats[ch], st_sum[i]);
+        atomicAdd(&s_stats[BLOCK_N + ch], st_sq[i]);
       }
       named_bar_sync(2, 128);
       for (int i = epi_tid; i < BLOCK_N; i += 128) {
@@ -490,7 +486,9 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* 
 using namespace bgr;
 
 static int g_force_block_n = 0;
+static int g_conv_dbg = 0;
 extern "C" void bgr_debug_conv_block_n(int bn) { g_force_block_n = bn; }
+extern "C" void bgr_debug_conv_mode(int m) { g_conv_dbg = m; }
 
 // Cout tile width: 256 halves the activation re-reads and the shared-memory operand traffic per
 // FLOP, 128 quantises better onto the SMs; compare the number of SM rounds each needs.
@@ -522,6 +520,7 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
   p.kblocks = (Cin + kBlockK - 1) / kBlockK;
   p.Cout = Cout; p.Cin = Cin; p.ld_out = ldy;
   for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
+  p.dbg = g_conv_dbg;
   const int bn = pick_block_n(p.m_tiles, Cout);
   p.n_tiles = (Cout + bn - 1) / bn;
   CUtensorMap tmA, tmB, tmO;

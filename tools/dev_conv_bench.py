@@ -52,6 +52,11 @@ for (N, H, W, Cin, Cout, ks, dil) in SHAPES:
         _lib.lib().bgr_debug_conv_block_n(bn)
         t1 = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y))
         t2 = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y, bn_sums=sums))
+        if os.environ.get("BGR_DBG"):
+            _lib.lib().bgr_debug_conv_mode(int(os.environ["BGR_DBG"]))
+            t2b = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y, bn_sums=sums))
+            _lib.lib().bgr_debug_conv_mode(0)
+            line += "(dbg %.1f us) " % t2b
         t3 = timeit(lambda: K.conv_fprop(gy, wt, dy, dx, out=gx))
         line += "[bn%3d] fprop %7.1f us %6.0f TF/s | +stats %7.1f us | dgrad %7.1f us %6.0f TF/s  " % (
             bn, t1, fl / t1 / 1e6, t2, t3, fl / t3 / 1e6)
