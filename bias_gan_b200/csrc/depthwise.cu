@@ -582,6 +582,307 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
 // dw[ky][kx][c] += sum dy[oy][ox] * x[oy+ky-1][ox+kx-1]; marching over input rows with the three
 // neighbouring dy rows kept (packed) in registers.  Rows of dy outside the segment count as zero.
 // XF: x is LeakyReLU/affine of the stored tensor, recomputed on load (see dw_transform).
+// ---------------------------------------------------------------- stride-2 marches (dilation 1)
+// y[oy][ox] = sum w[ky][kx] x[2oy+ky-1][2ox+kx-1].  Lane = 4 channels, warp = 128 channels x a strip of
+// 4 output columns (9 input columns 2ox0-1 .. 2ox0+7) marching down the input rows 2oy0-1 .. 2oy1-1:
+// an even row 2o is the middle tap row of output row o, an odd row 2o+1 is the bottom tap row of o
+// and the top tap row of o+1.  Items = (image, output-row segment, output strip); same cp.async ring.
+__device__ __forceinline__ void march_decode_s2(const DwGeom& g, const MarchSched& s, int item, MarchItem* it) {
+  const int strips = (g.Wo + 3) >> 2;
+  it->ox0 = (item % strips) * 4;
+  const int t = item / strips;
+  it->oy0 = (t % s.segs) * s.RY;
+  it->n = t / s.segs;
+  it->H = g.H; it->W = g.W; it->off = 0;
+  it->oy1 = min(it->oy0 + s.RY, g.Ho);
+}
+// nine column vectors of input row iy into ring slot `slot` ([col][lane] x 8 bytes)
+template <bool INTERIOR>
+__device__ __forceinline__ void march_issue_row9(uint2* slot, const __nv_bfloat16* base, int H, int W, int rowstride,
+                                                 int ix0, int ld, int iy, bool in_range) {
+  const bool rv = in_range && iy >= 0 && iy < H;
+  const int ro = (rv ? iy : 0) * rowstride + ix0 * ld;
+#pragma unroll
+  for (int c = 0; c < 9; ++c) {
+    const bool ok = INTERIOR ? rv : (rv && ix0 + c >= 0 && ix0 + c < W);
+    cp_async8(slot + c * 32, base + (INTERIOR || ok ? ro + c * ld : 0), ok);
+  }
+}
+
+template <bool INTERIOR>
+__device__ __forceinline__ void march_fwd_s2_item(const __nv_bfloat16* __restrict__ xin, __nv_bfloat16* __restrict__ yout,
+                                                  const DwGeom& g, const MarchItem& it, const float2 (&wr)[9][2],
+                                                  uint2* ring) {
+  const int first = 2 * it.oy0 - 1, last = 2 * it.oy1 - 1;   // input rows consumed, one per phase
+  const int rowstride = g.W * g.ldx, ix0 = 2 * it.ox0 - 1;
+  const int orowstride = g.Wo * g.ldy, ocol = it.ox0 * g.ldy;
+  float2 cur[4][2];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) cur[j][0] = cur[j][1] = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int r = 0; r < kRing; ++r) {
+    march_issue_row9<INTERIOR>(ring + r * (9 * 32), xin, g.H, g.W, rowstride, ix0, g.ldx, first + r, first + r <= last);
+    cp_async_commit();
+  }
+  auto fetch = [&](int iy, uint2 (&rc)[9]) {
+    cp_async_wait<kRing - 1>();
+    uint2* slot = ring + ((iy - first) & (kRing - 1)) * (9 * 32);
+#pragma unroll
+    for (int c = 0; c < 9; ++c) rc[c] = slot[c * 32];
+    march_issue_row9<INTERIOR>(slot, xin, g.H, g.W, rowstride, ix0, g.ldx, iy + kRing, iy + kRing <= last);
+    cp_async_commit();
+  };
+  // odd row 2o+1: finishes output row o (bottom taps), starts output row o+1 (top taps)
+  auto phase_odd = [&](int iy, bool store) {
+    uint2 rc[9];
+    fetch(iy, rc);
+    float2 nxt[4][2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) nxt[j][0] = nxt[j][1] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int c = 0; c < 9; ++c) {
+      float2 xv[2];
+      dw_unpack22(rc[c], xv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int kx = c - 2 * j;
+        if (kx < 0 || kx > 2) continue;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          cur[j][e] = fma2s(xv[e], wr[6 + kx][e], cur[j][e]);
+          nxt[j][e] = fma2s(xv[e], wr[0 + kx][e], nxt[j][e]);
+        }
+      }
+    }
+    if (store) {
+      __nv_bfloat16* orow = yout + (((iy - 1) >> 1) * orowstride + ocol);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (INTERIOR || it.ox0 + j < g.Wo) *reinterpret_cast<uint2*>(orow + j * g.ldy) = dw_pack22(cur[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { cur[j][0] = nxt[j][0]; cur[j][1] = nxt[j][1]; }
+  };
+  auto phase_even = [&](int iy) {
+    uint2 rc[9];
+    fetch(iy, rc);
+#pragma unroll
+    for (int c = 0; c < 9; ++c) {
+      float2 xv[2];
+      dw_unpack22(rc[c], xv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int kx = c - 2 * j;
+        if (kx < 0 || kx > 2) continue;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
+      }
+    }
+  };
+  phase_odd(first, false);
+  for (int o = it.oy0; o < it.oy1; ++o) {
+    phase_even(2 * o);
+    phase_odd(2 * o + 1, true);
+  }
+  cp_async_wait<0>();
+}
+
+__global__ void __launch_bounds__(128, 3)
+dw_march_fwd_s2_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                       __nv_bfloat16* __restrict__ y, const DwGeom g, const MarchSched sc) {
+  __shared__ uint2 ring_all[4][kRing][9 * 32];   // [warp][slot][col][lane]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = ((blockIdx.x % sc.cblocks) * 32 + lane) * kCpt;
+  if (c0 >= g.C) return;
+  uint2* ring = &ring_all[warp][0][lane];
+  float2 wr[9][2];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const float4 w0 = *reinterpret_cast<const float4*>(w + k * g.C + c0);
+    wr[k][0] = make_float2(w0.x, w0.y);
+    wr[k][1] = make_float2(w0.z, w0.w);
+  }
+  const int item_step = (gridDim.x / sc.cblocks) * 4;
+  for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
+    MarchItem it;
+    march_decode_s2(g, sc, item, &it);
+    const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
+    __nv_bfloat16* yout = y + size_t(it.n) * g.Ho * g.Wo * g.ldy + c0;
+    // warp-uniform: input columns 2ox0-1 .. 2ox0+7 and output columns ox0 .. ox0+3 all inside
+    if (it.ox0 >= 1 && 2 * it.ox0 + 7 < g.W && it.ox0 + 3 < g.Wo)
+      march_fwd_s2_item<true>(xin, yout, g, it, wr, ring);
+    else
+      march_fwd_s2_item<false>(xin, yout, g, it, wr, ring);
+  }
+}
+
+// Stride-2 data gradient.  x[r][s] feeds y[oy][ox] with ky = r - 2oy + 1, kx = s - 2ox + 1, so the 2x2
+// block dx[2i+p][2j+q] depends on gy[i..i+1][j..j+1] only:
+//   (0,0) w11 g00                         (0,1) w12 g00 + w10 g01
+//   (1,0) w21 g00 + w01 g10               (1,1) w22 g00 + w20 g01 + w02 g10 + w00 g11
+// Thread = 8 channels x one low-resolution position: 4 loads (3 of them shared with neighbours through
+// L1/L2), 4 stores, 9 FMAs per channel; straight-line body so that the loads of a thread pipeline.
+__global__ void __launch_bounds__(256)
+dw_dgrad_s2_kernel(const __nv_bfloat16* __restrict__ gy, const float* __restrict__ w,
+                   __nv_bfloat16* __restrict__ dx, const DwGeom g) {
+  const int G = g.C >> 3;
+  const int Hb = (g.H + 1) >> 1, Wb = (g.W + 1) >> 1;   // 2x2 blocks of dx (= Ho x Wo)
+  const long total = long(g.N) * Hb * Wb * G;
+  for (long t = long(blockIdx.x) * blockDim.x + threadIdx.x; t < total; t += long(gridDim.x) * blockDim.x) {
+    const int cg = int(t % G);
+    long r = t / G;
+    const int j = int(r % Wb); r /= Wb;
+    const int i = int(r % Hb);
+    const int n = int(r / Hb);
+    const bool vi = i + 1 < g.Ho, vj = j + 1 < g.Wo;
+    const __nv_bfloat16* gb = gy + ((size_t(n) * g.Ho + i) * g.Wo + j) * g.ldy + cg * 8;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    const uint4 u00 = *reinterpret_cast<const uint4*>(gb);
+    const uint4 u01 = vj ? *reinterpret_cast<const uint4*>(gb + g.ldy) : z;
+    const uint4 u10 = vi ? *reinterpret_cast<const uint4*>(gb + size_t(g.Wo) * g.ldy) : z;
+    const uint4 u11 = (vi && vj) ? *reinterpret_cast<const uint4*>(gb + size_t(g.Wo + 1) * g.ldy) : z;
+    float g00[8], g01[8], g10[8], g11[8], wk[9][8];
+    dw_unpack8(u00, g00); dw_unpack8(u01, g01); dw_unpack8(u10, g10); dw_unpack8(u11, g11);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(w + k * g.C + cg * 8);
+      const float4 b = *reinterpret_cast<const float4*>(w + k * g.C + cg * 8 + 4);
+      wk[k][0] = a.x; wk[k][1] = a.y; wk[k][2] = a.z; wk[k][3] = a.w;
+      wk[k][4] = b.x; wk[k][5] = b.y; wk[k][6] = b.z; wk[k][7] = b.w;
+    }
+    float o00[8], o01[8], o10[8], o11[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      o00[e] = wk[4][e] * g00[e];
+      o01[e] = fmaf(wk[5][e], g00[e], wk[3][e] * g01[e]);
+      o10[e] = fmaf(wk[7][e], g00[e], wk[1][e] * g10[e]);
+      o11[e] = fmaf(wk[8][e], g00[e], fmaf(wk[6][e], g01[e], fmaf(wk[2][e], g10[e], wk[0][e] * g11[e])));
+    }
+    const int y0 = 2 * i, x0 = 2 * j;
+    const bool vy = y0 + 1 < g.H, vx = x0 + 1 < g.W;
+    __nv_bfloat16* ob = dx + ((size_t(n) * g.H + y0) * g.W + x0) * g.ldx + cg * 8;
+    *reinterpret_cast<uint4*>(ob) = dw_pack8(o00);
+    if (vx) *reinterpret_cast<uint4*>(ob + g.ldx) = dw_pack8(o01);
+    if (vy) *reinterpret_cast<uint4*>(ob + size_t(g.W) * g.ldx) = dw_pack8(o10);
+    if (vx && vy) *reinterpret_cast<uint4*>(ob + size_t(g.W + 1) * g.ldx) = dw_pack8(o11);
+  }
+}
+
+// Stride-2 weight gradient: acc[ky][kx] += gy[o][j] * x[2o+ky-1][2j+kx-1], marching down the input
+// rows like march_fwd_s2_item; the gy row o+1 travels in the ring group of input row 2o+1 (where it is
+// first needed, as the row whose top taps that input row feeds).
+template <bool INTERIOR>
+__device__ __forceinline__ void march_wgrad_s2_item(const __nv_bfloat16* __restrict__ xin,
+                                                    const __nv_bfloat16* __restrict__ gin, const DwGeom& g,
+                                                    const MarchItem& it, float2 (&acc)[9][2], uint2* ring) {
+  const int first = 2 * it.oy0 - 1, last = 2 * it.oy1 - 1;
+  const int rowstride = g.W * g.ldx, ix0 = 2 * it.ox0 - 1;
+  const int grow = g.Wo * g.ldy, gcol = it.ox0 * g.ldy;
+  constexpr int kSlot = 13 * 32;   // 9 x columns + 4 gy columns
+  auto issue = [&](uint2* slot, int r) {
+    const bool in_range = r <= last;
+    march_issue_row9<INTERIOR>(slot, xin, g.H, g.W, rowstride, ix0, g.ldx, r, in_range);
+    const int o = (r + 1) >> 1;                       // odd r = 2o'-1 carries gy row o' = (r+1)/2
+    const bool ok = in_range && (r & 1) && o >= it.oy0 && o < it.oy1;
+    const int go = (ok ? o : 0) * grow + gcol;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const bool okj = INTERIOR ? ok : (ok && it.ox0 + j < g.Wo);
+      cp_async8(slot + (9 + j) * 32, gin + (INTERIOR || okj ? go + j * g.ldy : 0), okj);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int r = 0; r < kRing; ++r) issue(ring + r * kSlot, first + r);
+  uint2 gc[4], gn[4];   // gy rows o (current) and o+1 (next), packed
+#pragma unroll
+  for (int j = 0; j < 4; ++j) gc[j] = gn[j] = make_uint2(0, 0);
+  auto fetch = [&](int iy, uint2 (&rc)[9], bool take_g) {
+    cp_async_wait<kRing - 1>();
+    uint2* slot = ring + ((iy - first) & (kRing - 1)) * kSlot;
+#pragma unroll
+    for (int c = 0; c < 9; ++c) rc[c] = slot[c * 32];
+    if (take_g) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) gn[j] = slot[(9 + j) * 32];
+    }
+    issue(slot, iy + kRing);
+  };
+  auto accumulate = [&](const uint2 (&rc)[9], const uint2 (&grow_)[4], int ky) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 gv[2];
+      dw_unpack22(grow_[j], gv);
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        float2 xv[2];
+        dw_unpack22(rc[2 * j + kx], xv);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) acc[ky * 3 + kx][e] = fma2s(gv[e], xv[e], acc[ky * 3 + kx][e]);
+      }
+    }
+  };
+  // odd row 2o+1: bottom taps (ky=2) of gy row o = gc, top taps (ky=0) of gy row o+1 = gn (just fetched)
+  {
+    uint2 rc[9];
+    fetch(first, rc, true);          // row 2oy0-1: only the top taps of gy row oy0
+    accumulate(rc, gn, 0);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) gc[j] = gn[j];
+  }
+  for (int o = it.oy0; o < it.oy1; ++o) {
+    uint2 rc[9];
+    fetch(2 * o, rc, false);
+    accumulate(rc, gc, 1);
+    fetch(2 * o + 1, rc, true);
+    accumulate(rc, gc, 2);
+    accumulate(rc, gn, 0);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) gc[j] = gn[j];
+  }
+  cp_async_wait<0>();
+}
+
+__global__ void __launch_bounds__(128, 2)
+dw_march_wgrad_s2_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                         float* __restrict__ dw, const DwGeom g, const MarchSched sc) {
+  __shared__ float sh[9 * 128];
+  extern __shared__ uint2 ring_dyn[];               // [4 warps][kRing][13 * 32]
+  for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cb0 = (blockIdx.x % sc.cblocks) * 128;
+  const int lc = lane * kCpt;
+  const int c0 = cb0 + lc;
+  if (c0 < g.C) {
+    uint2* ring = ring_dyn + warp * (kRing * 13 * 32) + lane;
+    float2 acc[9][2];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
+    const int item_step = (gridDim.x / sc.cblocks) * 4;
+    for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
+      MarchItem it;
+      march_decode_s2(g, sc, item, &it);
+      const __nv_bfloat16* xin = x + size_t(it.n) * g.H * g.W * g.ldx + c0;
+      const __nv_bfloat16* gin = dy + size_t(it.n) * g.Ho * g.Wo * g.ldy + c0;
+      if (it.ox0 >= 1 && 2 * it.ox0 + 7 < g.W && it.ox0 + 3 < g.Wo)
+        march_wgrad_s2_item<true>(xin, gin, g, it, acc, ring);
+      else
+        march_wgrad_s2_item<false>(xin, gin, g, it, acc, ring);
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      atomicAdd(&sh[k * 128 + lc + 0], acc[k][0].x);
+      atomicAdd(&sh[k * 128 + lc + 1], acc[k][0].y);
+      atomicAdd(&sh[k * 128 + lc + 2], acc[k][1].x);
+      atomicAdd(&sh[k * 128 + lc + 3], acc[k][1].y);
+    }
+  }
+  __syncthreads();
+  const int nch = min(128, g.C - cb0);
+  for (int i = threadIdx.x; i < 9 * nch; i += blockDim.x) atomicAdd(&dw[cb0 * 9 + i], sh[(i % 9) * 128 + i / 9]);
+}
+
 // one item of the weight-gradient march: acc[ky*3+kx] += dy[oy][ox] * x[oy+ky-1][ox+kx-1]
 template <bool INTERIOR, int XF>
 __device__ __forceinline__ void march_wgrad_item(const __nv_bfloat16* __restrict__ xin,
@@ -723,6 +1024,13 @@ static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
   *blocks = unsigned(pb) * sc->cblocks;
 }
 
+// plan of the stride-2 marches: items over the *output* grid
+static void march_plan_s2(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
+  DwGeom o = g;
+  o.H = g.Ho; o.W = g.Wo; o.dil = 1;
+  march_plan(o, sc, blocks);
+}
+
 static int ew_grid(long total) {
   long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
@@ -770,6 +1078,11 @@ extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, co
     unsigned blocks;
     march_plan(g, &sc, &blocks);
     dw_march_fwd_kernel<false, 0><<<blocks, 128, 0, st>>>(X, w, Y, g, sc, nullptr, nullptr, 0.f);
+  } else if (stride == 2 && dil == 1) {
+    MarchSched sc;
+    unsigned blocks;
+    march_plan_s2(g, &sc, &blocks);
+    dw_march_fwd_s2_kernel<<<blocks, 128, 0, st>>>(X, w, Y, g, sc);
   } else if (!launch_fwd_strip<false>(X, w, Y, g, st))
     dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, st>>>(X, w, Y, g);
   BGR_LAUNCH_OK();
@@ -793,6 +1106,10 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
     unsigned blocks;
     march_plan(r, &sc, &blocks);
     dw_march_fwd_kernel<true, 0><<<blocks, 128, 0, st>>>(DY, w, DX, r, sc, nullptr, nullptr, 0.f);
+    done = true;
+  }
+  if (!done && stride == 2 && dil == 1) {
+    dw_dgrad_s2_kernel<<<ew_grid(long(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
     done = true;
   }
   if (!done) dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
@@ -879,7 +1196,18 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
   auto DY = static_cast<const __nv_bfloat16*>(dy);
   int rc = BGR_OK;
   if (stride == 1) rc = launch_march_wgrad<0>(X, DY, dw, g, nullptr, nullptr, 0.f, st);   // any dilation
-  else if (stride == 2 && dil == 1) rc = launch_wgrad_strip<2, 1>(X, DY, dw, g, st);
+  else if (stride == 2 && dil == 1) {
+    constexpr int ring_bytes = 4 * kRing * 13 * 32 * 8;   // 53 KB: above the 48 KB static limit
+    static bool configured = false;
+    if (!configured) {
+      BGR_CUDA_OK(cudaFuncSetAttribute(dw_march_wgrad_s2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ring_bytes));
+      configured = true;
+    }
+    MarchSched sc;
+    unsigned blocks;
+    march_plan_s2(g, &sc, &blocks);
+    dw_march_wgrad_s2_kernel<<<blocks, 128, ring_bytes, st>>>(X, DY, dw, g, sc);
+  }
   else {
     const long P = long(N) * g.Ho * g.Wo;
     const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
