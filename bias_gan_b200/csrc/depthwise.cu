@@ -5,6 +5,7 @@
 //   wgrad : dw[k][c] = sum_pixels dy * x_shifted   (per-channel reduction)
 // plus the stride-2 pixel subsample used in front of the 1x1 stride-2 skip convs (deeplab.py:95)
 // and its adjoint.  CUDA-core, HBM/L2-bound: 8 channels (128 bit) per thread.
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 #include "bgr_internal.h"
@@ -999,9 +1000,14 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
   for (int i = threadIdx.x; i < 9 * nch; i += blockDim.x) atomicAdd(&dw[cb0 * 9 + i], sh[(i % 9) * 128 + i / 9]);
 }
 
-// Row segments short enough that every warp gets ~8 items (the last partial round of items then
-// costs little) but not shorter than ~6 rows
-// (each segment re-reads two halo rows); one wave of blocks: 3 resident 128-thread blocks per SM.
+// Row segmentation by a cost model.  The marches are issue-bound (ncu at the 48x72x728 mid-flow shape:
+// 68 % issue-active, long-scoreboard stalls ~0), so a launch costs about
+//   rounds x (RY + 2 halo rows + ~3 rows of ring fill / drain),   rounds = ceil(items / resident warps),
+// and the segment count that minimises it wins: long segments when they still fill every warp once
+// (mid flow: 2 segments of 24 rows, one item per warp, instead of 8 x 6 rows with 33 % halo work),
+// many short rounds only when the image is large.  One wave of blocks: 3 resident blocks per SM.
+// (Swept on B200 over forced segment lengths and fill fractions: the model is within ~6 % of the best
+// forced plan at every trunk shape; the HBM-bound 384x576 shape is insensitive between 20 and 128 rows.)
 static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
   int sms = 148, dev = 0;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -1012,14 +1018,21 @@ static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
   sc->cblocks = (G + 31) / 32;
   int pb_max = sms * 3 / sc->cblocks;
   if (pb_max < 1) pb_max = 1;
-  long segs = (32L * pb_max + long(NP) * strips - 1) / (long(NP) * strips);   // ~8 items per warp
-  const long max_segs = (Hs + 5) / 6;
-  if (segs > max_segs) segs = max_segs;
-  if (segs < 1) segs = 1;
-  sc->RY = int((Hs + segs - 1) / segs);
+  const long warps = 4L * pb_max, per_seg = long(NP) * strips;
+  long best_cost = -1;
+  int best_ry = Hs;
+  for (int segs = 1; segs <= Hs; ++segs) {
+    const int ry = (Hs + segs - 1) / segs;
+    if (segs > 1 && ry == (Hs + segs - 2) / (segs - 1)) continue;   // same RY as the previous candidate
+    const long items = per_seg * ((Hs + ry - 1) / ry);
+    const long cost = ((items + warps - 1) / warps) * (ry + 5);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_ry = ry; }
+    if (ry <= 2) break;
+  }
+  sc->RY = best_ry;
   sc->segs = (Hs + sc->RY - 1) / sc->RY;
   sc->items = NP * sc->segs * strips;
-  const int ipw = (sc->items + 4 * pb_max - 1) / (4 * pb_max);   // items per warp
+  const int ipw = int((sc->items + warps - 1) / warps);   // items per warp
   const int pb = (sc->items + 4 * ipw - 1) / (4 * ipw);
   *blocks = unsigned(pb) * sc->cblocks;
 }

@@ -11,6 +11,8 @@ flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
 def timeit(fn, n=5):
     fn(); torch.cuda.synchronize()
+    if os.environ.get("BGR_ONCE"):   # under ncu: one launch of each kernel is enough
+        return 1.0
     ts = []
     for _ in range(n):
         flush.zero_()
