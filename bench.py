@@ -159,15 +159,30 @@ def conv_roofline_step(step_fn, torch, K):
             e0.record(); fn(); e1.record()
             torch.cuda.synchronize()
             ms += e0.elapsed_time(e1) / reps
-        a = by.setdefault(kind, [0.0, 0.0, 0])
+        a = by.setdefault(kind, [0.0, 0.0, 0, 0.0])
         a[0] += count * 2.0 * n * h * w_ * cin * cout * nt
         a[1] += count * ms
         a[2] += count
+        # algorithmic bytes: every operand and the result once (bf16 activations/weights, fp32 dW)
+        px = n * h * w_
+        a[3] += count * (2.0 * px * (cin + cout) + cout * nt * cin * (2.0 if kind == "fprop" else 4.0))
         del x, fn
     flops = sum(v[0] for v in by.values())
     ms = sum(v[1] for v in by.values())
     return flops, ms, sum(v[2] for v in by.values()), \
-        {k: {"tflops": v[0] / v[1] / 1e9, "ms": v[1], "launches": v[2]} for k, v in by.items()}
+        {k: {"tflops": v[0] / v[1] / 1e9, "ms": v[1], "launches": v[2], "algorithmic_bytes": v[3]} for k, v in by.items()}
+
+
+def conv_traffic(n_launches):
+    """DRAM bytes per conv launch from the committed ncu capture of this same step (profiles/):
+    measured once per round under ncu, never inside a timed run."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_conv_traffic.json")))
+    except (OSError, ValueError):
+        return None, None
+    if t.get("launches_per_step") != n_launches:   # the capture is of another schedule: do not quote it
+        return None, "profiles/r01_conv_traffic.json is stale (%s launches per step there)" % t.get("launches_per_step")
+    return t["dram_bytes_per_launch"], "profiles/r01_conv_traffic.json"
 
 
 def main():
@@ -348,6 +363,8 @@ def main():
             m.grad_sync.enabled = False
     flops, ms_conv, n_conv, by_kind = conv_roofline_step(eager_step, torch, K)  # kernel by kernel, not the graph
     ach = flops / (ms_conv * 1e-3) / 1e12
+    traffic, traffic_src = conv_traffic(n_conv)
+    alg_bytes = sum(v["algorithmic_bytes"] for v in by_kind.values()) / max(n_conv, 1)
     line = {"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -363,7 +380,9 @@ def main():
                     "pipeline": "pinned-host -> device copy of step i+1 on a copy stream while step i computes"},
             "roofline": {"bound": "tensor", "kernel": "conv_fprop_kernel/conv_wgrad_kernel (tcgen05 implicit GEMM)",
                          "achieved": ach, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                         "frac": ach / pk["bf16_tflops_sustained"], "traffic": None, "peak_source": pk_src + " (sustained)",
+                         "frac": ach / pk["bf16_tflops_sustained"], "traffic": traffic, "traffic_unit": "DRAM bytes per launch (mean over the step's conv launches)",
+                         "traffic_source": traffic_src, "algorithmic_bytes_per_launch": alg_bytes,
+                         "peak_source": pk_src + " (sustained)",
                          "launches_per_step": n_conv, "conv_ms_per_step": ms_conv, "by_kind": by_kind},
             "step_roofline": {"useful_gflop_per_sample": W_MIN / 1e9, "achieved_tflops": value / world * W_MIN / 1e12,
                               "frac_of_sustained_bf16": value / world * W_MIN / 1e12 / pk["bf16_tflops_sustained"]},

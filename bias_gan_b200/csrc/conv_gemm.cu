@@ -126,27 +126,34 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
-      uint32_t it = 0, lt = 0;
-      for (int mt = mt_first; mt < p.m_tiles; mt += mt_step, ++lt) {
-        const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
-        mbar_wait(&tempty[acc], aph ^ 1);
+    // The whole warp walks the loop (uniform control flow); one elected lane issues.  Per k-block
+    // the issuing thread has ~512 tensor-pipe cycles of work to hide behind, so the loop carries
+    // running (stage, phase) counters and descriptor low words instead of divisions and rebuilds.
+    constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
+    const uint64_t da0 = umma_desc_sw128(smem_u32(sA), 16, 1024), db0 = umma_desc_sw128(smem_u32(sB), 16, 1024);
+    const uint32_t a_hi = uint32_t(da0 >> 32), b_hi = uint32_t(db0 >> 32);
+    const uint32_t a_lo0 = uint32_t(da0), b_lo0 = uint32_t(db0);
+    uint32_t s = 0, ph = 0, lt = 0;
+    for (int mt = mt_first; mt < p.m_tiles; mt += mt_step, ++lt) {
+      const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
+      mbar_wait(&tempty[acc], aph ^ 1);
+      tc_fence_after();
+      const uint32_t d = tmem + acc * BLOCK_N;
+      for (int i = 0; i < iters; ++i) {
+        mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t d = tmem + acc * BLOCK_N;
-        for (int i = 0; i < iters; ++i, ++it) {
-          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-          mbar_wait(&full[s], ph);
-          tc_fence_after();
-          const uint64_t da = umma_desc_sw128(smem_u32(sA + s * A_BYTES), 16, 1024);
-          const uint64_t db = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
+        if (elect_one_sync()) {
+          const uint32_t al = a_lo0 + s * (A_BYTES >> 4), bl = b_lo0 + s * (B_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k)
-            umma_bf16(d, da + uint64_t(k * 2), db + uint64_t(k * 2), idesc, (i | k) != 0);
+            umma_bf16_w(d, al + k * 2, a_hi, bl + k * 2, b_hi, idesc, k ? 1u : uint32_t(i != 0));
           umma_commit(&empty[s]);
         }
-        umma_commit(&tfull[acc]);
+        __syncwarp();
+        if (++s == STAGES) { s = 0; ph ^= 1; }
       }
+      if (elect_one_sync()) umma_commit(&tfull[acc]);
+      __syncwarp();
     }
   } else {
     const int q = warp & 3;                  // TMEM lane quadrant this warp may access
@@ -171,6 +178,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int c = 0; c < BLOCK_N / 64; ++c) {
         const int ch0 = n0 + c * 64;
         if (ch0 >= p.Cout) break;
+        if (p.dbg == 2) break;   // timing experiments only (bgr_debug_conv_mode): no epilogue at all
         uint8_t* buf = sO + (chunk_ctr & 1) * O_BYTES;
         if (epi_tid == 0) bulk_wait_group_read<1>();   // the store issued two chunks ago has left smem
         named_bar_sync(1, 128);
@@ -179,6 +187,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         tmem_ld32(taddr, v);
         tmem_ld32(taddr + 32, v + 32);
         tmem_ld_wait();
+        if (p.dbg == 3) { ++chunk_ctr; continue; }   // TMEM reads only
         if (bias != nullptr) {
 #pragma unroll
           for (int j = 0; j < 64; ++j)
@@ -196,7 +205,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
         fence_proxy_async();
         named_bar_sync(1, 128);
-        if (epi_tid == 0) {
+        if (epi_tid == 0 && p.dbg != 4) {   // dbg 4: everything but the TMA store
           tma_store_5d(&tmO, buf, ch0, 0, x0, y0, n);
           bulk_commit_group();
         }
@@ -330,22 +339,26 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
         }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N, 1, 1);
-        for (int it = 0; it < iters; ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          mbar_wait(&full[s], ph);
-          tc_fence_after();
-          const uint64_t da = umma_desc_sw128(smem_u32(sA + s * A_BYTES), BOX_BYTES, 1024);
-          const uint64_t db = umma_desc_sw128(smem_u32(sB + s * B_BYTES), BOX_BYTES, 1024);
+      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N, 1, 1);
+      const uint64_t da0 = umma_desc_sw128(smem_u32(sA), BOX_BYTES, 1024), db0 = umma_desc_sw128(smem_u32(sB), BOX_BYTES, 1024);
+      const uint32_t a_hi = uint32_t(da0 >> 32), b_hi = uint32_t(db0 >> 32);
+      const uint32_t a_lo0 = uint32_t(da0), b_lo0 = uint32_t(db0);
+      uint32_t s = 0, ph = 0;
+      for (int it = 0; it < iters; ++it) {   // warp-uniform; one elected lane issues (see fprop)
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        if (elect_one_sync()) {
+          const uint32_t al = a_lo0 + s * (A_BYTES >> 4), bl = b_lo0 + s * (B_BYTES >> 4);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k)  // 16 pixel rows = 2048 B per MMA
-            umma_bf16(tmem, da + uint64_t(k * 128), db + uint64_t(k * 128), idesc, (it | k) != 0);
+            umma_bf16_w(tmem, al + k * 128, a_hi, bl + k * 128, b_hi, idesc, k ? 1u : uint32_t(it != 0));
           umma_commit(&empty[s]);
         }
-        umma_commit(tmem_full);
+        __syncwarp();
+        if (++s == STAGES) { s = 0; ph ^= 1; }
       }
+      if (elect_one_sync()) umma_commit(tmem_full);
+      __syncwarp();
     } else {
       const int q = warp & 3;
       mbar_wait(tmem_full, 0);

@@ -4,12 +4,43 @@ Each Function's forward/backward is one or a few C-ABI launches (kernels.py); Py
 only orders them.  Parameter tensors keep the reference's shapes ([Cout,Cin,kh,kw] etc.) so that
 state dicts interchange; GEMM-layout bf16 copies are derived per call (tiny tensors).
 """
+import contextlib
+import os
+
 import torch
 
 from . import kernels as K
 from . import layouts as L
 
 SLOPE = 0.2  # nn.LeakyReLU(0.2) everywhere in the reference (deeplab.py:100,180,334,365)
+
+# The weight gradient of a layer does not feed the rest of the backward pass, so it is launched on a
+# second stream, forked from and joined back into the calling stream inside the same autograd node.
+# Under graph capture the fork/join become plain edges: the weight-gradient kernel fills the SMs that
+# the data-gradient kernel leaves idle in its last (partial) round of tiles and during its ramps.
+SIDE_STREAM = os.environ.get("BGR_NO_SIDE_STREAM") is None
+_side_streams = {}
+
+
+@contextlib.contextmanager
+def _side_stream(ref):
+    """Work inside runs on the device's side stream, after everything queued so far; the caller
+    joins with _join(ref) before returning the results."""
+    if not (SIDE_STREAM and ref.is_cuda):
+        yield
+        return
+    dev = ref.device.index
+    side = _side_streams.get(dev)
+    if side is None:
+        side = _side_streams[dev] = torch.cuda.Stream(device=ref.device)
+    side.wait_stream(torch.cuda.current_stream(ref.device))
+    with torch.cuda.stream(side):
+        yield
+
+
+def _join(ref):
+    if SIDE_STREAM and ref.is_cuda and ref.device.index in _side_streams:
+        torch.cuda.current_stream(ref.device).wait_stream(_side_streams[ref.device.index])
 
 
 def _bf16c(t):
@@ -42,12 +73,14 @@ class _Conv(torch.autograd.Function):
         dy, dx = ctx.taps
         g = _bf16c(g)
         gx = gw = gb = None
+        if ctx.needs_input_grad[1]:
+            with _side_stream(g):
+                gw = L.from_gemm_grad(K.conv_wgrad(x, g, dy, dx), weight.shape)
         if ctx.needs_input_grad[0]:
             gx = K.conv_fprop(g, L.cached(weight, "gemm_t", L.gemm_weight_t), [-v for v in dy], [-v for v in dx])
-        if ctx.needs_input_grad[1]:
-            gw = L.from_gemm_grad(K.conv_wgrad(x, g, dy, dx), weight.shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = K.bn_stats(g)[: g.shape[-1]].float()
+        _join(g)
         return gx, gw, gb, None, None
 
 
@@ -78,11 +111,13 @@ class _ConvS2D(torch.autograd.Function):
         field, weight = ctx.saved_tensors
         g = _bf16c(g)
         gf = gw = None
+        if ctx.needs_input_grad[1]:
+            with _side_stream(g):
+                gw = L.s2d_weight_grad(K.conv_wgrad(field, g, L.S2D_DY, L.S2D_DX), weight.shape)
         if ctx.needs_input_grad[0]:
             w2t = L.cached(weight, "s2d_t", lambda w: L.s2d_weight(w).permute(2, 1, 0).to(torch.bfloat16).contiguous())
             gf = K.conv_fprop(g, w2t, [-v for v in L.S2D_DY], [-v for v in L.S2D_DX])
-        if ctx.needs_input_grad[1]:
-            gw = L.s2d_weight_grad(K.conv_wgrad(field, g, L.S2D_DY, L.S2D_DX), weight.shape)
+        _join(g)
         return gf, gw, None
 
 
@@ -105,10 +140,12 @@ class _Depthwise(torch.autograd.Function):
         stride, dil, shape = ctx.cfg
         g = _bf16c(g)
         gx = gw = None
+        if ctx.needs_input_grad[1]:
+            with _side_stream(g):
+                gw = K.dw_wgrad(x, g, stride, dil).view(shape[3], 1, 3, 3)
         if ctx.needs_input_grad[0]:
             gx = K.dw_dgrad(g, w9, stride, dil, shape)
-        if ctx.needs_input_grad[1]:
-            gw = K.dw_wgrad(x, g, stride, dil).view(shape[3], 1, 3, 3)
+        _join(g)
         return gx, gw, None, None
 
 
@@ -172,13 +209,15 @@ class _BNActDepthwise(torch.autograd.Function):
         C = y.shape[-1]
         gw = None
         if ctx.needs_input_grad[9]:
-            gw = K.dw_wgrad_bn(y, a, b, ctx.act, g, SLOPE).view(C, 1, 3, 3)
+            with _side_stream(g):
+                gw = K.dw_wgrad_bn(y, a, b, ctx.act, g, SLOPE).view(C, 1, 3, 3)
         gy = ggamma = gbeta = None
         if ctx.needs_input_grad[0]:
             gx = K.dw_dgrad(g, w9, 1, 1, tuple(y.shape))
             gy, _, bsums = K.bn_backward_recompute(gx, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
             ggamma = bsums[C:] if ctx.needs_input_grad[2] else None
             gbeta = bsums[:C] if ctx.needs_input_grad[3] else None
+        _join(g)
         return gy, None, ggamma, gbeta, None, None, None, None, None, gw, None
 
 
