@@ -430,8 +430,10 @@ __device__ __forceinline__ void dw_load_coef(XfCoef* t, const float* xa, const f
   t->slope = slope;
 }
 
-// Two scalar FMAs.  The packed FFMA2 form was measured: same time (the march waits on loads, not on
-// FMA issue) but 20-30 more registers for the aligned operand pairs, i.e. one resident block fewer.
+// Two scalar FMAs.  The packed FFMA2 form was measured twice (before and after the cp.async ring):
+// same time to the microsecond at every trunk shape, as is a ring of 8 rows instead of 4 -- at the
+// mid-flow shape the march is bound by neither issue slots nor load latency but by its fixed ramp
+// (weights, item decode, first ring fill from cold HBM) on 25 us of work.
 __device__ __forceinline__ float2 fma2s(const float2& a, const float2& b, const float2& c) {
 #if BGR_DW_FFMA2
   return __ffma2_rn(a, b, c);
@@ -577,6 +579,178 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
       march_fwd_item<true, XF>(xin, yout, g, sc.dil, it, wr, tc, ring);
     else
       march_fwd_item<false, XF>(xin, yout, g, sc.dil, it, wr, tc, ring);
+  }
+}
+
+// ---------------------------------------------------------------- data gradient + BatchNorm backward pass 1
+// Backward of  t = depthwise3x3(act(a*q + b))  (stride 1, dilation 1; q = the pointwise conv's raw
+// output, a/b = its BatchNorm folded with batch statistics).  The march computes the data gradient
+// row by row; instead of writing it and letting a second kernel re-read it together with q, the
+// finished row is masked by act'(a*q + b) on the spot, rounded to bf16, stored as dyh and summed
+// into the two BatchNorm reductions  s1 = sum dyh,  s2 = sum dyh * (q - mean) * invstd  per channel.
+// The q row travels in the same cp.async ring group as the gradient row that completes it.
+struct BnRedCoef {
+  float2 a[2], b[2], mu[2], is[2];
+  float slope;
+  int act;
+};
+
+template <bool INTERIOR>
+__device__ __forceinline__ void march_dgrad_bnred_item(const __nv_bfloat16* __restrict__ gin,
+                                                       const __nv_bfloat16* __restrict__ qin, int ldq,
+                                                       __nv_bfloat16* __restrict__ dout, const DwGeom& g,
+                                                       const MarchItem& it, const float2 (&wr)[9][2],
+                                                       const BnRedCoef& tc, float2 (&s1)[2], float2 (&s2)[2],
+                                                       uint2* ring) {
+  constexpr int kSlot = 10 * 32;   // 6 gradient columns of row iy + 4 q columns of row iy - 1
+  float2 a0[4][2], a1[4][2], a2[4][2];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
+  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(it.W, it.ox0);
+  const int first = it.oy0 - 1;
+  const int rowstride = g.W * g.ldx, colbase = (it.ox0 - 1) * g.ldx;
+  const int orowstride = g.W * g.ldy, ocol = it.ox0 * g.ldy;
+  const int qrowstride = g.W * ldq, qcol = it.ox0 * ldq;
+  auto issue = [&](uint2* slot, int iy) {
+    march_issue_row<INTERIOR>(slot, gin, it.H, rowstride, colbase, g.ldx, iy, cmask, iy <= it.oy1);
+    const int oy = iy - 1;
+    const bool ok = oy >= it.oy0 && oy < it.oy1;
+    const int qo = (ok ? oy : 0) * qrowstride + qcol;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const bool okj = INTERIOR ? ok : (ok && it.ox0 + j < it.W);
+      cp_async8(slot + (6 + j) * 32, qin + (INTERIOR || okj ? qo + j * ldq : 0), okj);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int r = 0; r < kRing; ++r) issue(ring + r * kSlot, first + r);
+  auto phase = [&](int iy, float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
+    cp_async_wait<kRing - 1>();
+    uint2* slot = ring + ((iy - first) & (kRing - 1)) * kSlot;
+    uint2 rc[6], qc[4];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) qc[j] = slot[(6 + j) * 32];
+    issue(slot, iy + kRing);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      float2 xv[2];
+      dw_unpack22(rc[c], xv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int kx = c - j;
+        if (kx < 0 || kx > 2) continue;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          next[j][e] = fma2s(xv[e], wr[0 + kx][e], next[j][e]);
+          cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
+          prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
+        }
+      }
+    }
+    const int oy = iy - 1;
+    if (oy >= it.oy0 && oy < it.oy1) {
+      __nv_bfloat16* orow = dout + (oy * orowstride + ocol);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (!INTERIOR && it.ox0 + j >= it.W) continue;
+        float2 qv[2];
+        dw_unpack22(qc[j], qv);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          if (tc.act) {
+            const float zx = fmaf(tc.a[e].x, qv[e].x, tc.b[e].x), zy = fmaf(tc.a[e].y, qv[e].y, tc.b[e].y);
+            prev[j][e].x = zx > 0.f ? prev[j][e].x : tc.slope * prev[j][e].x;
+            prev[j][e].y = zy > 0.f ? prev[j][e].y : tc.slope * prev[j][e].y;
+          }
+        }
+        const uint2 packed = dw_pack22(prev[j]);
+        *reinterpret_cast<uint2*>(orow + j * g.ldy) = packed;
+        float2 dr[2];   // the rounded values pass 2 reads back: the mean subtraction then cancels exactly
+        dw_unpack22(packed, dr);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          s1[e].x += dr[e].x;
+          s1[e].y += dr[e].y;
+          s2[e].x = fmaf(dr[e].x, (qv[e].x - tc.mu[e].x) * tc.is[e].x, s2[e].x);
+          s2[e].y = fmaf(dr[e].y, (qv[e].y - tc.mu[e].y) * tc.is[e].y, s2[e].y);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) prev[j][e] = make_float2(0.f, 0.f);
+  };
+  for (int iy = first; iy <= it.oy1; iy += 3) {
+    phase(iy, a0, a1, a2);
+    if (iy + 1 <= it.oy1) phase(iy + 1, a1, a2, a0);
+    if (iy + 2 <= it.oy1) phase(iy + 2, a2, a0, a1);
+  }
+  cp_async_wait<0>();
+}
+
+__global__ void __launch_bounds__(128, 2)
+dw_march_dgrad_bnred_kernel(const __nv_bfloat16* __restrict__ gy, const float* __restrict__ w,
+                            const __nv_bfloat16* __restrict__ q, int ldq, __nv_bfloat16* __restrict__ dyh,
+                            const DwGeom g, const MarchSched sc, const float* __restrict__ xa,
+                            const float* __restrict__ xb, const float* __restrict__ mean,
+                            const float* __restrict__ invstd, float slope, int act, double* __restrict__ sums) {
+  __shared__ uint2 ring_all[4][kRing][10 * 32];   // [warp][slot][col][lane]
+  __shared__ float sh[2 * 128];
+  for (int i = threadIdx.x; i < 2 * 128; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cb0 = (blockIdx.x % sc.cblocks) * 128;
+  const int lc = lane * kCpt, c0 = cb0 + lc;
+  if (c0 < g.C) {
+    uint2* ring = &ring_all[warp][0][lane];
+    float2 wr[9][2];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {   // mirrored taps: the data gradient is the same stencil reversed
+      const float4 w0 = *reinterpret_cast<const float4*>(w + (8 - k) * g.C + c0);
+      wr[k][0] = make_float2(w0.x, w0.y);
+      wr[k][1] = make_float2(w0.z, w0.w);
+    }
+    BnRedCoef tc;
+    {
+      const float4 a = *reinterpret_cast<const float4*>(xa + c0), b = *reinterpret_cast<const float4*>(xb + c0);
+      const float4 m = *reinterpret_cast<const float4*>(mean + c0), r = *reinterpret_cast<const float4*>(invstd + c0);
+      tc.a[0] = make_float2(a.x, a.y); tc.a[1] = make_float2(a.z, a.w);
+      tc.b[0] = make_float2(b.x, b.y); tc.b[1] = make_float2(b.z, b.w);
+      tc.mu[0] = make_float2(m.x, m.y); tc.mu[1] = make_float2(m.z, m.w);
+      tc.is[0] = make_float2(r.x, r.y); tc.is[1] = make_float2(r.z, r.w);
+      tc.slope = slope; tc.act = act;
+    }
+    float2 s1[2], s2[2];
+    s1[0] = s1[1] = s2[0] = s2[1] = make_float2(0.f, 0.f);
+    const int item_step = (gridDim.x / sc.cblocks) * 4;
+    for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
+      MarchItem it;
+      march_decode(g, sc, item, &it);
+      const size_t img = size_t(it.n) * g.H * g.W;
+      const __nv_bfloat16* gin = gy + img * g.ldx + c0;
+      const __nv_bfloat16* qin = q + img * ldq + c0;
+      __nv_bfloat16* dout = dyh + img * g.ldy + c0;
+      if (it.ox0 >= 1 && it.ox0 + 5 <= it.W)
+        march_dgrad_bnred_item<true>(gin, qin, ldq, dout, g, it, wr, tc, s1, s2, ring);
+      else
+        march_dgrad_bnred_item<false>(gin, qin, ldq, dout, g, it, wr, tc, s1, s2, ring);
+    }
+    atomicAdd(&sh[lc + 0], s1[0].x); atomicAdd(&sh[lc + 1], s1[0].y);
+    atomicAdd(&sh[lc + 2], s1[1].x); atomicAdd(&sh[lc + 3], s1[1].y);
+    atomicAdd(&sh[128 + lc + 0], s2[0].x); atomicAdd(&sh[128 + lc + 1], s2[0].y);
+    atomicAdd(&sh[128 + lc + 2], s2[1].x); atomicAdd(&sh[128 + lc + 3], s2[1].y);
+  }
+  __syncthreads();
+  const int nch = min(128, g.C - cb0);
+  for (int i = threadIdx.x; i < 2 * nch; i += blockDim.x) {
+    const int half = i / nch, c = i - half * nch;
+    atomicAdd(&sums[half * g.C + cb0 + c], double(sh[half * 128 + c]));
   }
 }
 
@@ -1008,7 +1182,7 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
 // many short rounds only when the image is large.  One wave of blocks: 3 resident blocks per SM.
 // (Swept on B200 over forced segment lengths and fill fractions: the model is within ~6 % of the best
 // forced plan at every trunk shape; the HBM-bound 384x576 shape is insensitive between 20 and 128 rows.)
-static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
+static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks, int blocks_per_sm = 3) {
   int sms = 148, dev = 0;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int dil = g.dil < 1 ? 1 : g.dil;
@@ -1016,7 +1190,7 @@ static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
   const int G = g.C / kCpt, strips = (Ws + 3) / 4;
   sc->dil = dil;
   sc->cblocks = (G + 31) / 32;
-  int pb_max = sms * 3 / sc->cblocks;
+  int pb_max = sms * blocks_per_sm / sc->cblocks;
   if (pb_max < 1) pb_max = 1;
   const long warps = 4L * pb_max, per_seg = long(NP) * strips;
   long best_cost = -1;
@@ -1038,10 +1212,10 @@ static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
 }
 
 // plan of the stride-2 marches: items over the *output* grid
-static void march_plan_s2(const DwGeom& g, MarchSched* sc, unsigned* blocks) {
+static void march_plan_s2(const DwGeom& g, MarchSched* sc, unsigned* blocks, int blocks_per_sm = 3) {
   DwGeom o = g;
   o.H = g.Ho; o.W = g.Wo; o.dil = 1;
-  march_plan(o, sc, blocks);
+  march_plan(o, sc, blocks, blocks_per_sm);
 }
 
 static int ew_grid(long total) {
@@ -1126,6 +1300,28 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
     done = true;
   }
   if (!done) dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
+  BGR_LAUNCH_OK();
+  return BGR_OK;
+}
+
+// dyh = act'(a*q + b) * dgrad(dy) and the BatchNorm backward sums of it (see dw_march_dgrad_bnred_kernel);
+// sums = fp64 [sum dyh (C) | sum dyh * xhat (C)], zeroed here.
+extern "C" int bgr_dw_dgrad_bn_reduce(const void* dy, int N, int H, int W, int C, int ldy, const float* w,
+                                      const void* q, int ldq, const float* xa, const float* xb, const float* mean,
+                                      const float* invstd, int act, float slope, void* dyh, int ldd, double* sums,
+                                      void* stream) {
+  DwGeom g;
+  if (int rc = make_geom(&g, N, H, W, C, 1, 1, ldy, ldd)) return rc;   // the march reads dy (ldx) and writes dyh (ldy)
+  if (C % 4) return fail(BGR_ERR_ARG, "depthwise: channel count must be a multiple of 4");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  BGR_CUDA_OK(cudaMemsetAsync(sums, 0, 2 * size_t(C) * sizeof(double), st));
+  MarchSched sc;
+  unsigned blocks;
+  march_plan(g, &sc, &blocks, 2);   // 202 registers: two resident blocks per SM
+  dw_march_dgrad_bnred_kernel<<<blocks, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dy), w,
+                                                      static_cast<const __nv_bfloat16*>(q), ldq,
+                                                      static_cast<__nv_bfloat16*>(dyh), g, sc, xa, xb, mean, invstd,
+                                                      slope, act, sums);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -1218,7 +1414,7 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
     }
     MarchSched sc;
     unsigned blocks;
-    march_plan_s2(g, &sc, &blocks);
+    march_plan_s2(g, &sc, &blocks, 2);   // 192 registers: two resident blocks per SM
     dw_march_wgrad_s2_kernel<<<blocks, 128, ring_bytes, st>>>(X, DY, dw, g, sc);
   }
   else {

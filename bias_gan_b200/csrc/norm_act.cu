@@ -410,3 +410,21 @@ extern "C" int bgr_bn_backward_recompute(const void* g, int ldg, const float* a,
   return bn_backward_impl(g, ldg, nullptr, 0, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
                           ldd, sums, coef_ws, stream);
 }
+
+// Pass 2 alone, for a pass 1 that ran inside another kernel (bgr_dw_dgrad_bn_reduce): dyh and its
+// fp64 sums are given; writes dx and the coefficient rows (rows 5, 6 = dL/dbeta, dL/dgamma).
+extern "C" int bgr_bn_backward_apply(const void* dyh, const void* x, int ldx, const float* mean, const float* invstd,
+                                     const float* gamma, const double* sums, long M, int C, void* dx, int ldd,
+                                     float* coef_ws, void* stream) {
+  BGR_CHECK_C8(C);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
+  BGR_LAUNCH_OK();
+  int agrid, ablock;
+  rowgroup_launch(M, C, &agrid, &ablock);
+  bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(static_cast<const __nv_bfloat16*>(dyh),
+                                                static_cast<const __nv_bfloat16*>(x), ldx, coef_ws,
+                                                static_cast<__nv_bfloat16*>(dx), ldd, M, C);
+  BGR_LAUNCH_OK();
+  return BGR_OK;
+}

@@ -19,6 +19,11 @@ SLOPE = 0.2  # nn.LeakyReLU(0.2) everywhere in the reference (deeplab.py:100,180
 # Under graph capture the fork/join become plain edges: the weight-gradient kernel fills the SMs that
 # the data-gradient kernel leaves idle in its last (partial) round of tiles and during its ramps.
 SIDE_STREAM = os.environ.get("BGR_NO_SIDE_STREAM") is None
+# Pass 1 of the BatchNorm backward inside the depthwise data-gradient march (bgr_dw_dgrad_bn_reduce).
+# Off by default: measured on B200 the step is 128.7 ms with it and 128.2 ms without -- the march is
+# instruction-bound, and the masking + two reductions cost it as much as the separate streaming
+# reduce kernel (34 us at the mid-flow shape) that they replace.
+FUSE_DGRAD_BN_REDUCE = os.environ.get("BGR_DGRAD_BN_FUSION") is not None
 _side_streams = {}
 
 
@@ -213,8 +218,12 @@ class _BNActDepthwise(torch.autograd.Function):
                 gw = K.dw_wgrad_bn(y, a, b, ctx.act, g, SLOPE).view(C, 1, 3, 3)
         gy = ggamma = gbeta = None
         if ctx.needs_input_grad[0]:
-            gx = K.dw_dgrad(g, w9, 1, 1, tuple(y.shape))
-            gy, _, bsums = K.bn_backward_recompute(gx, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
+            if FUSE_DGRAD_BN_REDUCE:
+                dyh, sums = K.dw_dgrad_bn_reduce(g, w9, y, a, b, mean, invstd, ctx.act, SLOPE)
+                gy, bsums = K.bn_backward_apply(dyh, y, mean, invstd, gamma, sums)
+            else:
+                gx = K.dw_dgrad(g, w9, 1, 1, tuple(y.shape))
+                gy, _, bsums = K.bn_backward_recompute(gx, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
             ggamma = bsums[C:] if ctx.needs_input_grad[2] else None
             gbeta = bsums[:C] if ctx.needs_input_grad[3] else None
         _join(g)

@@ -277,6 +277,31 @@ def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2):
     return dx, dyh, coef[5 * C:7 * C]   # fp32 [dL/dbeta | dL/dgamma]
 
 
+def dw_dgrad_bn_reduce(gy, w9, q, a, b, mean, invstd, act, slope=0.2):
+    """(dyh, sums): the stride-1 depthwise data gradient masked by act'(a*q + b), and the fp64
+    BatchNorm-backward sums of it, from one march (see bgr.h)."""
+    N, H, W, C, ldq = _nhwc_view(q)
+    Ng, Hg, Wg, Cg, ldy = _nhwc_view(gy)
+    assert (Ng, Hg, Wg, Cg) == (N, H, W, C)
+    dyh = act_empty(q.shape, q.device)
+    sums = torch.empty(2 * C, dtype=torch.float64, device=q.device)
+    check(_lib.lib().bgr_dw_dgrad_bn_reduce(ptr(gy), N, H, W, C, ldy, ptr(w9), ptr(q), ldq, ptr(a), ptr(b), ptr(mean),
+                                            ptr(invstd), int(act), c_float(slope), ptr(dyh), _nhwc_view(dyh)[4],
+                                            ptr(sums), stream_ptr()))
+    return dyh, sums
+
+
+def bn_backward_apply(dyh, x, mean, invstd, gamma, sums):
+    """Pass 2 of the BatchNorm backward: (dx, fp32 [dL/dbeta | dL/dgamma])."""
+    M, C, ldx = _rows(x)
+    dx = act_empty(x.shape, x.device)
+    assert _rows(dyh)[2] == _rows(dx)[2]
+    coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_bn_backward_apply(ptr(dyh), ptr(x), ldx, ptr(mean), ptr(invstd), ptr(gamma), ptr(sums),
+                                           c_long(M), C, ptr(dx), _rows(dx)[2], ptr(coef), stream_ptr()))
+    return dx, coef[5 * C:7 * C]
+
+
 def dw_dgrad(gy, w9, stride, dil, in_shape):
     N, H, W, C = in_shape
     _, _, _, _, ldy = _nhwc_view(gy)

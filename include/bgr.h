@@ -147,6 +147,22 @@ int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const floa
                               float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
                               float* coef_ws, void* stream);
 
+/* Data gradient of a stride-1 depthwise 3x3 conv fused with pass 1 of the backward of the
+ * BatchNorm(+LeakyReLU) that produced its input on the fly (bgr_dw_fwd_bn): writes
+ * dyh = act'(a*q + b) * dgrad(dy) (bf16, pixel stride ldd) and sums = fp64 [sum dyh | sum dyh*xhat].
+ * Replaces, for those layers, bgr_dw_dgrad followed by pass 1 of bgr_bn_backward_recompute
+ * (reference: autograd of deeplab.py:66-79 SeparableConv2d_same + nn.BatchNorm2d). */
+int bgr_dw_dgrad_bn_reduce(const void* dy, int N, int H, int W, int C, int ldy, const float* w9,
+                           const void* q, int ldq, const float* a, const float* b, const float* mean,
+                           const float* invstd, int act, float slope, void* dyh, int ldd, double* sums,
+                           void* stream);
+
+/* Pass 2 of the BatchNorm backward from given dyh and sums: dx = gamma*invstd*(dyh - s1/M - xhat*s2/M);
+ * coef_ws = fp32 [7][C] workspace, rows 5 and 6 return dL/dbeta and dL/dgamma. */
+int bgr_bn_backward_apply(const void* dyh, const void* x, int ldx, const float* mean, const float* invstd,
+                          const float* gamma, const double* sums, long M, int C, void* dx, int ldd,
+                          float* coef_ws, void* stream);
+
 /* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
  * w: fp32 [9][C] (tap-major); dw: fp32 [C][9] (the parameter's own [C,1,3,3] layout).  Output size ceil(H/stride) x ceil(W/stride). */
 int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* w, int stride, int dil,

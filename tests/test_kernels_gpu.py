@@ -222,12 +222,16 @@ def test_bn_act_train(dev, C, M_shape, act, with_res):
     assert int(bn_p.num_batches_tracked) == 1
 
 
-@pytest.mark.parametrize("C,N,H,W", [(128, 2, 24, 36), (728, 2, 13, 9), (1024, 1, 6, 7)])
+@pytest.mark.parametrize("C,N,H,W", [(128, 2, 24, 36), (728, 2, 13, 9), (1024, 1, 6, 7), (256, 3, 70, 45)])
 @pytest.mark.parametrize("act", [True, False])
-def test_bn_act_depthwise_fused(dev, C, N, H, W, act):
-    """BatchNorm(+LeakyReLU) applied while the depthwise kernel loads (bgr_dw_fwd_bn / bgr_dw_wgrad_bn /
-    bgr_bn_backward_recompute) against PyTorch fp32 BatchNorm2d -> leaky_relu -> F.pad -> depthwise conv."""
+@pytest.mark.parametrize("fuse_reduce", [True, False])
+def test_bn_act_depthwise_fused(dev, C, N, H, W, act, fuse_reduce, monkeypatch):
+    """BatchNorm(+LeakyReLU) applied while the depthwise kernel loads (bgr_dw_fwd_bn / bgr_dw_wgrad_bn) and
+    its backward -- pass 1 inside the data-gradient march (bgr_dw_dgrad_bn_reduce + bgr_bn_backward_apply)
+    or as separate kernels (bgr_dw_dgrad + bgr_bn_backward_recompute) -- against PyTorch fp32
+    BatchNorm2d -> leaky_relu -> F.pad -> depthwise conv."""
     from bias_gan_b200 import functional as F_
+    monkeypatch.setattr(F_, "FUSE_DGRAD_BN_REDUCE", fuse_reduce)
     g = torch.Generator(device="cpu").manual_seed(9)
     y = (torch.randn(N, C, H, W, generator=g) * 1.5 + 0.3).to(dev).bfloat16()
     w = (torch.randn(C, 1, 3, 3, generator=g) / 3).to(dev)
