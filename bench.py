@@ -108,6 +108,56 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def run_torch_gpu(args, autocast):
+    """Same-GPU comparator ("the bar to beat", not the CPU baseline and not the product):
+    the oracle port of the reference modules through stock PyTorch/cuDNN on cuda:0, the reference's own
+    step schedule (train_gan.py:250-298), fp32 or bf16 autocast, device-timed like the product arm."""
+    import torch
+    from oracle import ref_model as R
+    dev = torch.device("cuda", 0)
+    torch.backends.cudnn.benchmark = True
+    g = torch.Generator().manual_seed(1)
+    line = {"impl": "torch-bf16-autocast" if autocast else "torch-fp32", "metric": METRIC, "unit": "samples/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "data": "synthetic",
+            "dtype": "bf16 autocast" if autocast else "f32 (TF32 off)"}
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    for b in (args.batch, args.batch // 2, args.batch // 4):
+        G = D = go = do = None
+        try:
+            torch.manual_seed(333)
+            G, D = R.GeneratorRef(C, C).to(dev).train(), R.DiscriminatorRef(C, (H, W)).to(dev).train()
+            opt = lambda m: torch.optim.AdamW(m.parameters(), lr=1e-4, eps=1e-8, weight_decay=1e-5, fused=True)
+            go, do = opt(G), opt(D)
+            crit = R.GANLossRef("ModifiedMinMax", b, dev)
+            x, y = torch.randn(b, C, H, W, generator=g).to(dev), torch.randn(b, C, H, W, generator=g).to(dev)
+
+            def step():
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                    R.gan_step_ref(G, D, go, do, crit, x, y)
+            for _ in range(max(args.warmup, 2)):
+                step()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(args.steps):
+                step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / args.steps
+            line.update({"value": b / (ms * 1e-3), "ms_per_step": ms, "peak_mem_gib": torch.cuda.max_memory_allocated() / 2 ** 30,
+                         "config": {"workload": "reference modules (oracle port) via PyTorch/cuDNN on 1xB200, reference step "
+                                                "schedule, 16x768x1152 fields, local batch %d" % b}})
+            break
+        except torch.cuda.OutOfMemoryError:
+            import gc
+            G = D = go = do = step = None
+            gc.collect()
+            torch.cuda.empty_cache()
+            line["note"] = "batch %d does not fit in HBM with stock PyTorch" % b
+    print(json.dumps(line), flush=True)
+
+
 def conv_roofline_step(step_fn, torch, K):
     """Dominant kernel family (tcgen05 implicit GEMM): one kernel-by-kernel step records the signature
     of every conv launch (shapes, pixel strides, taps, epilogue options); each distinct signature is
@@ -200,6 +250,8 @@ def main():
                     help="warm up, then run --steps steps between cudaProfilerStart/Stop and exit (for ncu "
                          "--profile-from-start off); prints no bench value")
     args = ap.parse_args()
+    if args.impl in ("torch-bf16", "torch-fp32"):
+        return run_torch_gpu(args, args.impl == "torch-bf16")
     if args.impl == "reference":
         return run_reference(args)
 
