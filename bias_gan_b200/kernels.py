@@ -146,6 +146,26 @@ def stage_normalize(src, layout, channels, shift, scale, crop=None, flip=(False,
     return out
 
 
+def channel_stats(src, layout="NCHW"):
+    """Per-sample, per-channel (mean, mean-square, min, max) in fp64 on the device: returns a [B,4,Cf]
+    fp64 tensor.  src: [B,Cf,H,W] ('NCHW') or [B,H,W,Cf] ('NHWC') device tensor as the reader returns
+    it (see bgr_channel_stats in bgr.h)."""
+    assert src.is_cuda and src.is_contiguous() and src.dim() == 4
+    if layout == "NCHW":
+        B, Cf, H, W = src.shape
+        lay, rows = 0, B * Cf
+    else:
+        B, H, W, Cf = src.shape
+        lay, rows = 1, B
+    # enough chunks for four resident blocks per SM, but at least 16K elements each
+    splits = max(1, min((148 * 4 + rows - 1) // rows, (H * W * (1 if lay == 0 else Cf)) // 16384, 4096))
+    part = torch.empty(B * Cf * splits * 4, dtype=torch.float64, device=src.device)
+    out = torch.empty((B, 4, Cf), dtype=torch.float64, device=src.device)
+    check(_lib.lib().bgr_channel_stats(ptr(src), _SRC_DTYPES[src.dtype], lay, B, Cf, H, W, splits, ptr(part), ptr(out),
+                                       stream_ptr()))
+    return out
+
+
 # ---------------------------------------------------------------------------------------------
 # BatchNorm / activation / depthwise / decoder helpers.  Tensors are bf16 [..., C] whose leading
 # dims are dense with a uniform pixel stride (channel slices of wider buffers are fine).

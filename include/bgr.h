@@ -83,6 +83,17 @@ int bgr_stage_normalize(const void* src, int src_dtype, int src_layout, int B, i
                         int x0, int h, int w, int flip_h, int flip_v, void* dst, int s2d,
                         void* stream);
 
+/* ---- per-channel dataset statistics (src/utils/summarize_data_gpsro.py:31-50 create_token) ---- */
+
+/* out[b][k][c] (fp64, k = 0 mean, 1 mean-square, 2 min, 3 max) over the H*W pixels of channel c of
+ * sample b: one reference "token" per sample (the reference's np.load(...).astype(float64) followed
+ * by np.average / np.amin / np.amax over the spatial axes).  src: device payload of B samples, dtype
+ * BGR_*, layout BGR_NCHW [B,Cf,H,W] or BGR_NHWC [B,H,W,Cf].  partials: device fp64 workspace of
+ * B*Cf*splits*4 values; splits (>= 1) = chunks each plane is cut into for parallelism; the partials
+ * are combined in a fixed order, so the result is independent of scheduling.  B*Cf <= 65535. */
+int bgr_channel_stats(const void* src, int src_dtype, int src_layout, int B, int Cf, int H, int W,
+                      int splits, double* partials, double* out, void* stream);
+
 /* ---- implicit-GEMM convolution (tcgen05 / TMEM / TMA) ------------------------------------ */
 
 /* y[n,h,w,co] = bias[co] + sum_{t,ci} x[n, h+dy[t], w+dx[t], ci] * w[co,t,ci]   (zero outside)

@@ -56,3 +56,11 @@ for (N, H, W, C) in SHAPES:
     print("shape N%d %dx%d C%d  (%.1f MB per tensor)" % (N, H, W, C, nbytes / 1e6))
     for name, us, by in rows:
         print("   %-26s %9.1f us   %7.0f GB/s" % (name, us, by / us / 1e3))
+
+# dataset statistics (bgr_channel_stats): one read of the fp32 payload, 8 fields of 16 x 768 x 1152
+if len(sys.argv) <= 2:
+    xs = torch.randn(8, 16, 768, 1152, device=dev)
+    print("shape 8 fields 16x768x1152 fp32  (%.1f MB)" % (xs.numel() * 4 / 1e6))
+    for lay, t in (("NCHW", xs), ("NHWC", xs.permute(0, 2, 3, 1).contiguous())):
+        us = timeit(lambda: K.channel_stats(t, lay))
+        print("   %-26s %9.1f us   %7.0f GB/s" % ("channel_stats " + lay, us, xs.numel() * 4 / us / 1e3))
