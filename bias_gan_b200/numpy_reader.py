@@ -31,7 +31,7 @@ class numpy_reader(object):
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h is not None and h.value:
+        if h is not None and h.value and _lib is not None and ctypes is not None:   # modules may be gone at interpreter exit
             _lib.lib().bgr_reader_destroy(h)
             self._h = ctypes.c_void_p(0)
 

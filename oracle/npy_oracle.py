@@ -162,3 +162,14 @@ def merge_token(t1, t2):
     n = n1 + n2
     return (n, (n1 / n) * m1 + (n2 / n) * m2, (n1 / n) * s1 + (n2 / n) * s2,
             np.minimum(lo1, lo2), np.maximum(hi1, hi2))
+
+
+def gpsro_file_shard(names, shuffle=True, seed=12345, shard_idx=0, shard_num=1):
+    """gpsro_dataset.py:19-33 (init_files): `data_in_*.npy` names with the prefix stripped, sorted,
+    shuffled by np.random.RandomState(seed) (the dataset's only RNG, first use), contiguous shard
+    [idx*size, (idx+1)*size) with size = n // shard_num (remainder dropped)."""
+    allfiles = sorted(x.replace("data_in_", "") for x in names if x.endswith(".npy") and x.startswith("data_in_"))
+    if shuffle:
+        np.random.RandomState(seed).shuffle(allfiles)
+    size = len(allfiles) // shard_num
+    return allfiles[size * shard_idx: size * shard_idx + size]
