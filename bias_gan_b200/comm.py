@@ -136,3 +136,37 @@ class comm(object):
 
     def DistributedOptimizer(self, optimizer, named_parameters=None, compression_name=None, op_name=None):
         return optimizer
+
+    # ---- checkpoint interchange (comm/distributed.py:108-157; writer: train_gan.py:401-431) -------
+    @staticmethod
+    def _strip(sd):
+        """The reference's key hack: apex/torch DDP prefix every key with `module.`."""
+        return {k.replace("module.", ""): v for k, v in sd.items()}
+
+    def init_training_state(self, model, optimizer, checkpoint_name, device_id):
+        if (checkpoint_name is not None) and os.path.isfile(checkpoint_name):
+            checkpoint = torch.load(checkpoint_name, map_location=device_id)
+            optimizer.load_state_dict(checkpoint["optimizer"])
+            model.load_state_dict(self._strip(checkpoint["model"]))
+            return checkpoint["step"], checkpoint["epoch"]
+        return 0, 0
+
+    def init_gan_training_state(self, gmodel, dmodel, gopt, dopt, checkpoint_name, device_id):
+        """Restart from a `.cpt` written by the reference trainer (or by save_gan_checkpoint): the
+        parameter names are the compatibility contract, so the files interchange both ways."""
+        if (checkpoint_name is not None) and os.path.isfile(checkpoint_name):
+            checkpoint = torch.load(checkpoint_name, map_location=device_id)
+            gopt.load_state_dict(checkpoint["g_opt"])
+            dopt.load_state_dict(checkpoint["d_opt"])
+            gmodel.load_state_dict(self._strip(checkpoint["generator"]))
+            dmodel.load_state_dict(self._strip(checkpoint["discriminator"]))
+            return checkpoint["step"], checkpoint["epoch"]
+        return 0, 0
+
+    def save_gan_checkpoint(self, path, step, epoch, generator, discriminator, g_opt, d_opt):
+        """The dictionary train_gan.py:402-411 saves (`amp` is empty: opt level O0 has no loss-scaler state)."""
+        if self.rank() == 0:
+            torch.save({"step": step, "epoch": epoch, "generator": generator.state_dict(),
+                        "discriminator": discriminator.state_dict(), "g_opt": g_opt.state_dict(),
+                        "d_opt": d_opt.state_dict(), "amp": {}}, path)
+
