@@ -53,7 +53,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   constexpr uint32_t A_BYTES = kBlockM * kBlockK * 2;
   constexpr uint32_t B_BYTES = BLOCK_N * kBlockK * 2;
   constexpr uint32_t O_BYTES = kBlockM * 64 * 2;       // one 64-channel output chunk
-  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N;
+  constexpr uint32_t TMEM_COLS = BLOCK_N > 128 ? 512 : 2 * BLOCK_N;   // allocations are powers of two
   constexpr uint32_t NEEDED = STAGES * (A_BYTES + B_BYTES) + 2 * O_BYTES + 2 * BLOCK_N * 4 +
                               (2 * STAGES + 4) * 8 + 16;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -504,18 +504,26 @@ extern "C" void bgr_debug_conv_block_n(int bn) { g_force_block_n = bn; }
 extern "C" void bgr_debug_conv_mode(int m) { g_conv_dbg = m; }
 
 // Cout tile width: 256 halves the activation re-reads and the shared-memory operand traffic per
-// FLOP, 128 quantises better onto the SMs; compare the number of SM rounds each needs.
+// FLOP, 128 quantises better onto the SMs, 192 sits between: 728 (= 768 padded) output channels at
+// the 48x72 mid-flow shape are 3 x 256 -> 49 CTA groups -> 216 pixel tiles in 5 rounds (4.41 needed),
+// but 4 x 192 -> 37 groups (all 148 SMs) -> 6 rounds of 0.75-size tiles = 4.5.  Compare the
+// schedules' costs: rounds x tile width / relative efficiency of that width.  Measured: the 192-wide
+// tile runs at 0.84-0.87 of the 256-wide one per FLOP (1203 vs 1386 TFLOP/s at 1536->1536), which
+// cancels its better quantisation at the mid-flow shape to the microsecond (38.9 us both), so with
+// the measured weight it is never picked today; it stays selectable (bgr_debug_conv_block_n, tests).
 static int pick_block_n(int m_tiles, int Cout) {
   if (Cout <= 64) return 64;
   if (Cout <= 128) return 128;
-  if (g_force_block_n == 128 || g_force_block_n == 256) return g_force_block_n;
+  if (g_force_block_n == 128 || g_force_block_n == 192 || g_force_block_n == 256) return g_force_block_n;
   const int sms = sm_count();
-  auto rounds = [&](int n_tiles) {
+  auto rounds = [&](int bn) {
+    const int n_tiles = (Cout + bn - 1) / bn;
     const int groups = sms / n_tiles > 0 ? sms / n_tiles : 1;
     return long((m_tiles + groups - 1) / groups);
   };
-  const long r128 = rounds((Cout + 127) / 128), r256 = rounds((Cout + 255) / 256);
-  return (r256 * 18 <= r128 * 10) ? 256 : 128;
+  const long c128 = rounds(128) * 128 * 100 / 90, c192 = rounds(192) * 192 * 100 / 86, c256 = rounds(256) * 256;
+  if (c192 < c256 && c192 < c128) return 192;
+  return c256 <= c128 ? 256 : 128;
 }
 
 extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w,
@@ -551,10 +559,12 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
     BGR_CUDA_OK(cudaMemsetAsync(bn_sums, 0, sizeof(double) * 2 * Cout, st));
     if (bn == 64) return launch_fprop<64, 6, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
     if (bn == 128) return launch_fprop<128, 6, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
+    if (bn == 192) return launch_fprop<192, 4, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
     return launch_fprop<256, 4, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
   }
   if (bn == 64) return launch_fprop<64, 6, false>(tmA, tmB, tmO, bias, nullptr, p, st);
   if (bn == 128) return launch_fprop<128, 6, false>(tmA, tmB, tmO, bias, nullptr, p, st);
+  if (bn == 192) return launch_fprop<192, 4, false>(tmA, tmB, tmO, bias, nullptr, p, st);
   return launch_fprop<256, 4, false>(tmA, tmB, tmO, bias, nullptr, p, st);
 }
 

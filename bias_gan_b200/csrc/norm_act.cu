@@ -206,7 +206,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
         s1[j] += d;
         s2[j] += d * (xv[j] - mu[j]) * is[j];
       }
-      *reinterpret_cast<uint4*>(dyh + row * ldd + gi * 8) = pack8(gv);
+      if (dyh != nullptr) *reinterpret_cast<uint4*>(dyh + row * ldd + gi * 8) = pack8(gv);
     };
     const uint4 z4 = make_uint4(0, 0, 0, 0);
     long row = r0 + r;
@@ -293,6 +293,63 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* 
     }
     if (row < M)
       one(row, *reinterpret_cast<const uint4*>(dyh + row * ldd + g * 8),
+          *reinterpret_cast<const uint4*>(x + row * ldx + g * 8));
+  }
+}
+
+// Pass 2 without a stored dyh (the BatchNorm whose activation was applied on load, bgr_dw_fwd_bn):
+// dyh = bf16(g * act'(a*x + b)) is recomputed from g and x -- x is read anyway -- exactly as pass 1
+// computed it for the sums, so pass 1 need not write it and this pass need not read it back.
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, const __nv_bfloat16* __restrict__ x,
+                              int ldx, const float* __restrict__ xa, const float* __restrict__ xb,
+                              const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, int ldd, long M,
+                              int C, float slope, int act) {
+  const int G = C >> 3;
+  const int R = G >= 256 ? 1 : 256 / G;
+  const int g0 = G >= 256 ? threadIdx.x : threadIdx.x % G;
+  const int r = G >= 256 ? 0 : threadIdx.x / G;
+  const long rstep = long(gridDim.x) * R;
+  for (int g = g0; g < G; g += 256) {
+    float c0[8], k1[8], k2[8], mu[8], is[8], ca[8], cb[8];
+    load8f(coef + g * 8, c0);
+    load8f(coef + C + g * 8, k1);
+    load8f(coef + 2 * C + g * 8, k2);
+    load8f(coef + 3 * C + g * 8, mu);
+    load8f(coef + 4 * C + g * 8, is);
+    if (act) {
+      load8f(xa + g * 8, ca);
+      load8f(xb + g * 8, cb);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) k2[j] *= is[j];
+    auto one = [&](long row, const uint4& gu, const uint4& xu) {
+      float d[8], xv[8];
+      unpack8(gu, d);
+      unpack8(xu, xv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = d[j];
+        if (act) {
+          v = fmaf(ca[j], xv[j], cb[j]) > 0.f ? v : slope * v;
+          v = __bfloat162float(__float2bfloat16_rn(v));   // the value pass 1 summed
+        }
+        d[j] = c0[j] * (v - k1[j] - (xv[j] - mu[j]) * k2[j]);
+      }
+      *reinterpret_cast<uint4*>(dx + row * ldd + g * 8) = pack8(d);
+    };
+    long row = long(blockIdx.x) * R + r;
+    for (; row + rstep < M; row += 2 * rstep) {
+      const long row2 = row + rstep;
+      const uint4 d0 = *reinterpret_cast<const uint4*>(gin + row * ldg + g * 8);
+      const uint4 d1 = *reinterpret_cast<const uint4*>(gin + row2 * ldg + g * 8);
+      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
+      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + g * 8);
+      one(row, d0, x0);
+      one(row2, d1, x1);
+    }
+    if (row < M)
+      one(row, *reinterpret_cast<const uint4*>(gin + row * ldg + g * 8),
           *reinterpret_cast<const uint4*>(x + row * ldx + g * 8));
   }
 }
@@ -388,7 +445,13 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
   BGR_LAUNCH_OK();
   int agrid, ablock;
   rowgroup_launch(M, C, &agrid, &ablock);
-  bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(D, X, ldx, coef_ws, static_cast<__nv_bfloat16*>(dx), ldd, M, C);
+  if (D == nullptr) {
+    if (g2 != nullptr || act == 1) return fail(BGR_ERR_ARG, "bn_backward: dyh may be NULL only on the recompute path");
+    bn_bwd_apply_recompute_kernel<<<agrid, ablock, 0, st>>>(G, ldg, X, ldx, xa, xb, coef_ws, static_cast<__nv_bfloat16*>(dx),
+                                                            ldd, M, C, slope, act == 2);
+  } else {
+    bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(D, X, ldx, coef_ws, static_cast<__nv_bfloat16*>(dx), ldd, M, C);
+  }
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

@@ -282,12 +282,12 @@ def dw_wgrad_bn(x, a, b, act, gy, slope=0.2):
     return dw
 
 
-def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2):
+def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2, want_dyh=False):
     """bn_backward for a BatchNorm(+act) whose output was never stored: act' from sign(a*x + b)."""
     M, C, ldx = _rows(x)
     Mg, Cg, ldg = _rows(g)
     assert (Mg, Cg) == (M, C)
-    dyh = act_empty(x.shape, x.device)
+    dyh = act_empty(x.shape, x.device) if want_dyh else None   # NULL: pass 2 recomputes it from g and x
     dx = act_empty(x.shape, x.device)
     sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
     coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)

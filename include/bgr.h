@@ -152,7 +152,9 @@ int bgr_bn_backward(const void* g, int ldg, const void* g2, int ldg2, const void
                     void* stream);
 
 /* Same, for a BatchNorm(+LeakyReLU) whose activated output was never stored because the depthwise
- * conv that follows applied it while loading (bgr_dw_fwd_bn): act' comes from sign(a*x + b). */
+ * conv that follows applied it while loading (bgr_dw_fwd_bn): act' comes from sign(a*x + b).
+ * dyh may be NULL: pass 2 then recomputes it from g and x (which it reads anyway) instead of pass 1
+ * writing and pass 2 re-reading it -- one tensor pass less in each. */
 int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const float* b, const void* x, int ldx,
                               const float* mean, const float* invstd, const float* gamma, int act,
                               float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,

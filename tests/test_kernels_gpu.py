@@ -118,7 +118,7 @@ def test_weight_to_gemm_bit_exact(dev, Cout, Cin, k):
         assert float(full[..., Cout:].abs().max()) == 0.0
 
 
-@pytest.mark.parametrize("block_n", [0, 128, 256])
+@pytest.mark.parametrize("block_n", [0, 128, 192, 256])
 @pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil", [
     (2, 48, 72, 728, 728, 1, 1), (1, 19, 37, 304, 256, 3, 1), (3, 40, 56, 128, 1536, 1, 1), (1, 24, 40, 128, 48, 1, 1),
     (2, 12, 18, 264, 320, 3, 2)])
