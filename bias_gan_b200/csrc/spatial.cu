@@ -319,9 +319,53 @@ field_convert_kernel(__nv_bfloat16* __restrict__ field, float* __restrict__ nchw
   }
 }
 
+// Generator input with noise planes (deeplab_gan.py:88-90: cat((input_raw, input_noise), dim=1)) in the
+// field layout: out[n, by, bx, q, 0:C] = field[n, by, bx, q, :], out[.., C:C+nd] = bf16(noise[n, k, 2by+py, 2bx+px]),
+// out[.., C+nd:Cp] = 0 (the entry conv's weight rows for those channels are zero as well).
+__global__ void __launch_bounds__(256)
+field_append_noise_kernel(const uint4* __restrict__ field, const float* __restrict__ noise, uint4* __restrict__ out,
+                          int N, int C, int nd, int Cp, int H, int W) {
+  const int gin = C >> 3, gout = Cp >> 3;
+  const long total = long(N) * (H >> 1) * (W >> 1) * 4 * gout;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
+    const int g = int(i % gout);
+    const long pq = i / gout;  // (n, by, bx, q)
+    uint4 v;
+    if (g < gin) {
+      v = field[pq * gin + g];
+    } else {
+      const int q = int(pq & 3);
+      long r = pq >> 2;
+      const int bx = int(r % (W >> 1)); r /= (W >> 1);
+      const int by = int(r % (H >> 1));
+      const int n = int(r / (H >> 1));
+      const int y = 2 * by + (q >> 1), x = 2 * bx + (q & 1);
+      __align__(16) __nv_bfloat16 e[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = g * 8 + j - C;
+        e[j] = __float2bfloat16_rn(k < nd ? noise[(size_t(size_t(n) * nd + k) * H + y) * W + x] : 0.f);
+      }
+      v = *reinterpret_cast<uint4*>(e);
+    }
+    out[i] = v;
+  }
+}
+
 }  // namespace bgr
 
 using namespace bgr;
+
+extern "C" int bgr_field_append_noise(const void* field, const float* noise, void* out, int N, int C, int nd, int Cp,
+                                      int H, int W, void* stream) {
+  if (C % 8 || Cp % 8 || Cp < C + nd || nd < 1 || (H & 1) || (W & 1))
+    return fail(BGR_ERR_ARG, "field_append_noise: need C, Cp multiples of 8, Cp >= C + nd, nd >= 1, even H and W");
+  field_append_noise_kernel<<<sp_grid(long(N) * (H / 2) * (W / 2) * 4 * (Cp / 8)), 256, 0,
+                              reinterpret_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint4*>(field), noise, static_cast<uint4*>(out), N, C, nd, Cp, H, W);
+  BGR_LAUNCH_OK();
+  return BGR_OK;
+}
 
 static int make_bil(BilGeom* g, int N, int h, int w, int H, int W, int C, int ldx, int ldy, int s2d) {
   if (C % 8 || C < 8) return fail(BGR_ERR_ARG, "bilinear: channel count must be a multiple of 8");

@@ -56,25 +56,73 @@ class Discriminator(nn.Module):
                 m.eval()
 
 
+class _NoiseSlot:
+    def __init__(self, shape, device):
+        self.host = torch.empty(shape, pin_memory=torch.device(device).type == "cuda")
+        self.dev = torch.empty(shape, device=device)
+        self.copied = None
+
+    def draw(self, dist):
+        if self.copied is not None:
+            self.copied.synchronize()      # the previous copy out of the pinned buffer has finished
+        self.host.copy_(dist.rsample(self.host.shape))
+        self.dev.copy_(self.host, non_blocking=True)   # stream-ordered after the previous step's reads
+        if self.dev.is_cuda:
+            self.copied = torch.cuda.Event()
+            self.copied.record()
+
+
 class Generator(nn.Module):
     def __init__(self, n_input, n_output, upsampler_type, noise_type, noise_dimensions, os=16, pretrained=False,
                  normalizer=nn.BatchNorm2d):
         super().__init__()
         self.noise_dimensions = noise_dimensions
         self.n_output = n_output
+        self._noise_slots, self._noise_cursor = None, 0
         if noise_type == "Uniform":
             self.dist = torch.distributions.uniform.Uniform(0.0, 1.0)
         elif noise_type == "Normal":
             self.dist = torch.distributions.normal.Normal(0.0, 1.0)
         else:
             raise NotImplementedError("Error, noise type {} not supported.".format(noise_type))
-        if noise_dimensions > 0:
-            raise NotImplementedError("noise_dimensions > 0 needs C+nd channel fields (not built yet)")
         self.model = DeepLabv3_plus(n_input=n_input + noise_dimensions, n_output=n_output, os=os,
                                     upsampler_type=upsampler_type, pretrained=pretrained, normalizer=normalizer)
 
     def forward_field(self, field):
+        """deeplab_gan.py:85-94.  The noise planes are drawn like the reference's — `dist.rsample`
+        on the CPU generator, [B, nd, H, W] fp32 — so a seeded run sees the same noise; they join the
+        field in one kernel, padded with zero channels to a multiple of 16 so that the 4*(C+nd)
+        channels of a block pixel fill whole 128-byte lines for the entry conv's TMA boxes."""
+        nd = self.noise_dimensions
+        if nd > 0:
+            B, H2, W2, C4 = field.shape
+            shape = (B, nd, 2 * H2, 2 * W2)
+            if self._noise_slots is None:
+                noise = self.dist.rsample(shape)
+                if field.is_cuda:
+                    noise = noise.pin_memory().to(field.device, non_blocking=True)
+            else:   # static buffers (CUDA graphs): the k-th forward of a step reads slot k
+                if self._noise_cursor == len(self._noise_slots):
+                    self._noise_slots.append(_NoiseSlot(shape, field.device))
+                    self._noise_slots[-1].draw(self.dist)
+                noise = self._noise_slots[self._noise_cursor].dev
+                self._noise_cursor += 1
+            field = F_.append_noise(field, noise, (C4 // 4 + nd + 15) // 16 * 16)
         return self.model(field)
 
+    def static_noise(self, enable=True):
+        """Keep the noise planes in persistent device buffers, one per forward of a step, so that a
+        captured CUDA graph (step.GraphedGanStep) contains no host RNG and no host->device copy."""
+        self._noise_slots = [] if enable else None
+        self._noise_cursor = 0
+
+    def rewind_noise(self):
+        self._noise_cursor = 0
+
+    def redraw_noise(self, first=0, last=None):
+        """Draw fresh noise into slots [first, last) on the CPU generator, in slot order."""
+        for slot in (self._noise_slots or [])[first:last]:
+            slot.draw(self.dist)
+
     def forward(self, input_raw):
-        return F_.from_field(self.model(F_.to_field(input_raw)), self.n_output)
+        return F_.from_field(self.forward_field(F_.to_field(input_raw)), self.n_output)

@@ -94,6 +94,10 @@ def conv2d(x, weight, bias=None, dilation=1, want_stats=False):
     return _Conv.apply(x, weight, bias, dilation, want_stats)
 
 
+def _pad_cin(w, Cp):
+    return w if w.shape[1] == Cp else torch.nn.functional.pad(w, (0, 0, 0, 0, 0, Cp - w.shape[1]))
+
+
 class _ConvS2D(torch.autograd.Function):
     """3x3 stride-2 pad-1 entry conv (deeplab.py:178) on a field stored as 2x2 space-to-depth
     blocks: a 2x2-tap stride-1 implicit GEMM with K = 4 taps x 4*C channels."""
@@ -101,7 +105,11 @@ class _ConvS2D(torch.autograd.Function):
     @staticmethod
     def forward(ctx, field, weight, want_stats):
         ctx.save_for_backward(field, weight)
-        w2 = L.cached(weight, "s2d", lambda w: L.s2d_weight(w).to(torch.bfloat16).contiguous())
+        # a field wider than the weight's Cin carries zero channels (noise concat padded to a 128-byte
+        # line, deeplab_gan.Generator): the weight gets zero rows there and their gradient is dropped
+        ctx.Cp = Cp = field.shape[-1] // 4
+        assert Cp >= weight.shape[1]
+        w2 = L.cached(weight, "s2d", lambda w: L.s2d_weight(_pad_cin(w, Cp)).to(torch.bfloat16).contiguous())
         sums = None
         if want_stats:
             sums = torch.empty(2 * weight.shape[0], dtype=torch.float64, device=field.device)
@@ -118,9 +126,12 @@ class _ConvS2D(torch.autograd.Function):
         gf = gw = None
         if ctx.needs_input_grad[1]:
             with _side_stream(g):
-                gw = L.s2d_weight_grad(K.conv_wgrad(field, g, L.S2D_DY, L.S2D_DX), weight.shape)
+                Cout, Cin = weight.shape[:2]
+                gw = L.s2d_weight_grad(K.conv_wgrad(field, g, L.S2D_DY, L.S2D_DX), (Cout, ctx.Cp, 3, 3))[:, :Cin].contiguous()
         if ctx.needs_input_grad[0]:
-            w2t = L.cached(weight, "s2d_t", lambda w: L.s2d_weight(w).permute(2, 1, 0).to(torch.bfloat16).contiguous())
+            Cp = ctx.Cp
+            w2t = L.cached(weight, "s2d_t",
+                           lambda w: L.s2d_weight(_pad_cin(w, Cp)).permute(2, 1, 0).to(torch.bfloat16).contiguous())
             gf = K.conv_fprop(g, w2t, [-v for v in L.S2D_DY], [-v for v in L.S2D_DX])
         _join(g)
         return gf, gw, None
@@ -402,6 +413,25 @@ class _FromField(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         return K.nchw_to_field(g.float().contiguous()), None
+
+
+class _AppendNoise(torch.autograd.Function):
+    """cat((input_raw, input_noise), dim=1) of deeplab_gan.py:90 on fields; Cp = padded channel count."""
+
+    @staticmethod
+    def forward(ctx, field, noise, Cp):
+        ctx.C = field.shape[-1] // 4
+        return K.field_append_noise(field, noise, Cp)
+
+    @staticmethod
+    def backward(ctx, g):
+        N, H2, W2, _ = g.shape
+        gf = g.view(N, H2, W2, 4, -1)[..., :ctx.C].reshape(N, H2, W2, 4 * ctx.C) if ctx.needs_input_grad[0] else None
+        return gf, None, None   # the noise is a sample, not a parameter: no gradient is asked for
+
+
+def append_noise(field, noise, Cp):
+    return _AppendNoise.apply(field, noise, Cp)
 
 
 def to_field(x_nchw):

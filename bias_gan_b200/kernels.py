@@ -429,3 +429,16 @@ def nchw_to_field(x):
     out = torch.empty((N, H // 2, W // 2, 4 * C), dtype=torch.bfloat16, device=x.device)
     check(_lib.lib().bgr_nchw_to_field(ptr(x), ptr(out), N, C, H, W, stream_ptr()))
     return out
+
+
+def field_append_noise(field, noise, Cp):
+    """deeplab_gan.py:88-90 in the field layout: [N,H/2,W/2,4C] bf16 + fp32 NCHW noise [N,nd,H,W] ->
+    [N,H/2,W/2,4*Cp] (channels per sub-pixel: input, noise, zero padding)."""
+    N, H2, W2, C4 = field.shape
+    C = C4 // 4
+    Nn, nd, H, W = noise.shape
+    assert field.dtype == torch.bfloat16 and field.is_contiguous() and noise.dtype == torch.float32 \
+        and noise.is_contiguous() and noise.is_cuda and (Nn, H, W) == (N, 2 * H2, 2 * W2)
+    out = torch.empty((N, H2, W2, 4 * Cp), dtype=torch.bfloat16, device=field.device)
+    check(_lib.lib().bgr_field_append_noise(ptr(field), ptr(noise), ptr(out), N, C, nd, Cp, H, W, stream_ptr()))
+    return out

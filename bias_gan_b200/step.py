@@ -74,9 +74,11 @@ class GraphedGanStep:
         self.crit_gan, self.crit_reg, self.step_kw = crit_gan, crit_reg, step_kw
         self.inputs = torch.zeros(field_shape, dtype=torch.bfloat16, device=device)
         self.real = torch.zeros(field_shape, dtype=torch.bfloat16, device=device)
+        self.noisy = getattr(G, "noise_dimensions", 0) > 0
         cpu_rng = torch.get_rng_state()
         crit_gan.draw_labels()
-        torch.set_rng_state(cpu_rng)      # the capture-time draws must not advance the label stream
+        if self.noisy:
+            G.static_noise(True)          # slots are created (and filled once) by the warm-up forwards
         # state that the warm-up steps touch: parameters, buffers, optimizer moments
         tensors = [t for m in (G, D) for t in list(m.parameters()) + list(m.buffers())]
         side = torch.cuda.Stream(device=device)
@@ -94,6 +96,7 @@ class GraphedGanStep:
                     opt_snap = [(t, opt_before.get(id(t), None)) for t in opt_tensors()]
                     opt_snap = [(t, torch.zeros_like(t) if s0 is None else s0) for t, s0 in opt_snap]
             L.invalidate_cache()
+        torch.set_rng_state(cpu_rng)      # the capture-time draws must not advance the label / noise stream
         torch.cuda.current_stream(device).wait_stream(side)
         torch.cuda.synchronize(device)
         from . import _lib
@@ -113,6 +116,8 @@ class GraphedGanStep:
         torch.cuda.synchronize(device)
 
     def _run(self):
+        if self.noisy:
+            self.G.rewind_noise()
         return gan_step(self.G, self.D, self.g_opt, self.d_opt, self.crit_gan, self.crit_reg, self.inputs, self.real,
                         **self.step_kw)
 
@@ -123,6 +128,11 @@ class GraphedGanStep:
             self.inputs.copy_(inputs)
         if real is not None:
             self.real.copy_(real)
+        # host RNG in the reference's order: [G noise] -> label_fake, label_real, swap -> [G noise]
+        if self.noisy:
+            self.G.redraw_noise(0, 1)
         self.crit_gan.draw_labels()
+        if self.noisy:
+            self.G.redraw_noise(1, None)
         self.graph.replay()
         return self.d_loss, self.g_loss

@@ -220,6 +220,11 @@ int bgr_l1_loss_grad(const void* a, const void* b, long n, float gscale, void* g
 /* field layout (bf16 [N,H/2,W/2,(py,px,c)]) <-> fp32 NCHW, the tensors the training script sees. */
 int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream);
 int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W, void* stream);
+/* Generator.forward's noise concat (deeplab_gan.py:88-90) in the field layout: out [N,H/2,W/2,4*Cp] =
+ * per 2x2 sub-pixel the C channels of `field` [N,H/2,W/2,4*C], then the nd planes of `noise` (fp32
+ * NCHW [N,nd,H,W], rounded to bf16), then zeros up to Cp (C, Cp multiples of 8, Cp >= C+nd). */
+int bgr_field_append_noise(const void* field, const float* noise, void* out, int N, int C, int nd, int Cp,
+                           int H, int W, void* stream);
 
 #ifdef __cplusplus
 }

@@ -159,11 +159,25 @@ class DeepLabRef(nn.Module):
 
 
 class GeneratorRef(nn.Module):
-    def __init__(self, n_input, n_output, os=16):
+    """deeplab_gan.py:65-94.  With noise_dimensions > 0 the noise planes are drawn on the CPU
+    generator (`dist.rsample((B, nd, H, W))`), moved to the input's device and concatenated after
+    the input channels (deeplab_gan.py:88-90)."""
+
+    def __init__(self, n_input, n_output, os=16, noise_type="Normal", noise_dimensions=0):
         super().__init__()
-        self.model = DeepLabRef(n_input, n_output, os)
+        self.noise_dimensions = noise_dimensions
+        if noise_type == "Uniform":
+            self.dist = torch.distributions.uniform.Uniform(0.0, 1.0)
+        elif noise_type == "Normal":
+            self.dist = torch.distributions.normal.Normal(0.0, 1.0)
+        else:
+            raise NotImplementedError("Error, noise type {} not supported.".format(noise_type))
+        self.model = DeepLabRef(n_input + noise_dimensions, n_output, os)
 
     def forward(self, x):
+        if self.noise_dimensions > 0:
+            z = self.dist.rsample((x.shape[0], self.noise_dimensions, x.shape[2], x.shape[3])).to(x.device)
+            x = torch.cat((x, z), dim=1)
         return self.model(x)
 
 

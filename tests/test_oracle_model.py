@@ -79,3 +79,26 @@ def test_state_dict_keys_match_product():
         assert list(a.keys()) == list(b.keys())
         for k in a:
             assert a[k].shape == b[k].shape, k
+
+
+NOISE_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "noise_golden.pt")
+
+
+@pytest.mark.parametrize("kind,nd", [("Normal", 1), ("Uniform", 2)])
+def test_noise_generator_matches_reference_golden(kind, nd):
+    """GeneratorRef with noise planes (deeplab_gan.py:85-94) against the reference's own module
+    (tests/golden/make_noise_golden.py): same CPU-generator draw, same concat position."""
+    gold = torch.load(NOISE_GOLD, weights_only=False)
+    m = gold["meta"]
+    x, y = seeded_fields(5, m["B"], m["C"], m["H"], m["W"])
+    G = seed_state(R.GeneratorRef(m["C"], m["C"], noise_type=kind, noise_dimensions=nd), 11).train()
+    torch.manual_seed(m["noise_seed"])
+    fake = G(x)
+    F.l1_loss(fake, y).backward()
+    g = gold["%s%d" % (kind, nd)]
+    torch.testing.assert_close(fake.detach().bfloat16().float(), g["fake"].float(), rtol=2e-2, atol=2e-2)
+    params = dict(G.named_parameters())
+    for k, (norm, head) in g["grads"].items():
+        gr = params[k].grad
+        assert abs(float(gr.double().norm()) - norm) <= 2e-3 * norm + 1e-7, k
+        torch.testing.assert_close(gr.flatten()[:8], head, rtol=5e-3, atol=1e-6 + 1e-3 * norm / gr.numel() ** 0.5)
