@@ -6,7 +6,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libbgr.so")
+# BGR_LIB = another build of the same C ABI (A/B measurements of one kernel on the same box)
+LIB_PATH = os.environ.get("BGR_LIB") or os.path.join(_HERE, "lib", "libbgr.so")
 
 BGR_OK = 0
 BGR_ERR_RUNTIME = -1

@@ -534,3 +534,69 @@ extern "C" int bgr_weight_to_gemm(const float* w, int Cout, int Cin, int taps, i
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
+
+// ---------------------------------------------------------------- all derived weight copies of a model, one launch
+// After an optimizer step every GEMM-layout copy is stale: ~430 weight_to_gemm launches plus ~250 depthwise
+// transposes per G+D step, each a 3-5 us node on the critical path of the step's CUDA graph.  This kernel
+// rebuilds all of them from a descriptor table: block -> descriptor by binary search over the prefix sums
+// of the per-descriptor block counts, then the same tile code as the single-tensor kernels above.
+namespace bgr {
+__global__ void __launch_bounds__(256)
+weights_prepare_kernel(const BgrWeightDesc* __restrict__ descs, const int* __restrict__ first_block, int ndesc) {
+  __shared__ float sh[256 * 9];   // mode 0: [256][taps <= 9]; mode 1: a 32x33 tile
+  int lo = 0, hi = ndesc - 1;
+  while (lo < hi) {               // last d with first_block[d] <= blockIdx.x
+    const int mid = (lo + hi + 1) >> 1;
+    if (first_block[mid] <= int(blockIdx.x)) lo = mid; else hi = mid - 1;
+  }
+  const BgrWeightDesc d = descs[lo];
+  const int b = int(blockIdx.x) - first_block[lo];
+  const float* __restrict__ w = d.src;
+  if (d.mode == 0) {              // out[co][t][ci] = w[co][ci][t]
+    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(d.dst);
+    const int co = b / d.gx, ci0 = (b % d.gx) * 256, taps = d.taps;
+    const int n = min(256, d.pitch - ci0);
+    const int nv = max(0, min(256, d.Cin - ci0));
+    const float* src = w + (size_t(co) * d.Cin + ci0) * taps;
+    for (int i = threadIdx.x; i < nv * taps; i += 256) sh[i] = src[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < n * taps; i += 256) {
+      const int t = i / n, k = i - t * n;
+      out[(size_t(co) * taps + t) * d.pitch + ci0 + k] = __float2bfloat16_rn(k < nv ? sh[k * taps + t] : 0.f);
+    }
+  } else if (d.mode == 1) {       // out[j = ci*taps + t][co] = w[co][j]
+    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(d.dst);
+    float (*tile)[33] = reinterpret_cast<float (*)[33]>(sh);
+    const int J = d.Cin * d.taps;
+    const int j0 = (b % d.gx) * 32, c0 = (b / d.gx) * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int r = ty; r < 32; r += 8) {
+      const int co = c0 + r, j = j0 + tx;
+      tile[r][tx] = (co < d.Cout && j < J) ? w[size_t(co) * J + j] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = ty; r < 32; r += 8) {
+      const int j = j0 + r, co = c0 + tx;
+      if (j < J && co < d.pitch) out[size_t(j) * d.pitch + co] = __float2bfloat16_rn(tile[tx][r]);
+    }
+  } else {                        // depthwise: fp32 out[t][c] = w[c][t], t < 9
+    float* out = static_cast<float*>(d.dst);
+    const int i = b * 256 + threadIdx.x;
+    if (i < 9 * d.Cout) {
+      const int t = i / d.Cout, c = i - t * d.Cout;
+      out[i] = w[c * 9 + t];
+    }
+  }
+}
+}  // namespace bgr
+
+extern "C" int bgr_weights_prepare(const BgrWeightDesc* descs, const int* first_block, int ndesc, int total_blocks,
+                                   void* stream) {
+  if (ndesc < 1 || total_blocks < 1) return bgr::fail(BGR_ERR_ARG, "weights_prepare: empty descriptor table");
+  bgr::weights_prepare_kernel<<<total_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(descs, first_block, ndesc);
+  BGR_LAUNCH_OK();
+  return BGR_OK;
+}
+

@@ -126,3 +126,36 @@ class Generator(nn.Module):
 
     def forward(self, input_raw):
         return F_.from_field(self.forward_field(F_.to_field(input_raw)), self.n_output)
+
+
+def gradient_penalty(critic, images_fake, images_real, eta=None):
+    """WGAN-GP term of the critic loss (deeplab_gan.py:98-114, train_gan.py:257-258): eta ~ U(0,1) per
+    sample drawn on the CPU generator, one more train-mode critic forward on the interpolate, the
+    gradient of the logits with respect to it (no create_graph: like the reference's, the result
+    carries no parameter gradient), mean over pixels of (||grad||_2 over channels - 1)^2.
+
+    Takes what the caller has: fp32 NCHW tensors (the reference's call) or bf16 fields
+    [N, H/2, W/2, 4C] (the step loop); `eta` = a [N,1,1,1] device tensor drawn earlier
+    (GANLoss.draw_labels, for CUDA graphs)."""
+    if eta is None:
+        eta = torch.distributions.uniform.Uniform(0.0, 1.0).rsample((images_fake.shape[0], 1, 1, 1))
+        eta = eta.to(images_fake.device)
+    field = images_fake.dtype == torch.bfloat16
+    interpol = eta * images_fake.detach().float() + (1.0 - eta) * images_real.detach().float()
+    interpol = (interpol.bfloat16() if field else interpol).requires_grad_(True)
+    params = [p for p in critic.parameters() if p.requires_grad]
+    for p in params:   # only the data-gradient kernels run: no weight gradient is asked for
+        p.requires_grad_(False)
+    try:
+        with torch.enable_grad():
+            logits, _ = critic.forward_field(interpol) if field else critic(interpol)
+            gradients = torch.autograd.grad(outputs=logits, inputs=interpol, grad_outputs=torch.ones_like(logits))[0]
+    finally:
+        for p in params:
+            p.requires_grad_(True)
+    if field:   # channels of one pixel = the C entries of one (py, px) sub-block
+        N, H2, W2, C4 = gradients.shape
+        norms = gradients.view(N, H2, W2, 4, C4 // 4).float().norm(2, dim=-1)
+    else:
+        norms = gradients.norm(2, dim=1)
+    return ((norms - 1.0) ** 2).mean()

@@ -25,6 +25,7 @@ SIDE_STREAM = os.environ.get("BGR_NO_SIDE_STREAM") is None
 # reduce kernel (34 us at the mid-flow shape) that they replace.
 FUSE_DGRAD_BN_REDUCE = os.environ.get("BGR_DGRAD_BN_FUSION") is not None
 _side_streams = {}
+_forked = set()
 
 
 @contextlib.contextmanager
@@ -39,12 +40,17 @@ def _side_stream(ref):
     if side is None:
         side = _side_streams[dev] = torch.cuda.Stream(device=ref.device)
     side.wait_stream(torch.cuda.current_stream(ref.device))
+    _forked.add(dev)
     with torch.cuda.stream(side):
         yield
 
 
 def _join(ref):
-    if SIDE_STREAM and ref.is_cuda and ref.device.index in _side_streams:
+    # only a node that forked joins: waiting on a side stream that holds no work of the current CUDA-graph
+    # capture would wait on a non-captured event and invalidate the capture (data-gradient-only backward
+    # passes, e.g. deeplab_gan.gradient_penalty)
+    if ref.is_cuda and ref.device.index in _forked:
+        _forked.discard(ref.device.index)
         torch.cuda.current_stream(ref.device).wait_stream(_side_streams[ref.device.index])
 
 
@@ -61,6 +67,7 @@ class _Conv(torch.autograd.Function):
         ks = weight.shape[-1]
         dy, dx = K.taps_for(ks, dil)
         ctx.save_for_backward(x, weight)
+        ctx.set_materialize_grads(False)   # no zero-filled fp64 "gradient" for the BatchNorm sums output
         ctx.taps = (dy, dx)
         ctx.has_bias = bias is not None
         sums = None
@@ -74,6 +81,8 @@ class _Conv(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g, *unused):
+        if g is None:
+            return None, None, None, None, None
         x, weight = ctx.saved_tensors
         dy, dx = ctx.taps
         g = _bf16c(g)
@@ -105,6 +114,7 @@ class _ConvS2D(torch.autograd.Function):
     @staticmethod
     def forward(ctx, field, weight, want_stats):
         ctx.save_for_backward(field, weight)
+        ctx.set_materialize_grads(False)
         # a field wider than the weight's Cin carries zero channels (noise concat padded to a 128-byte
         # line, deeplab_gan.Generator): the weight gets zero rows there and their gradient is dropped
         ctx.Cp = Cp = field.shape[-1] // 4
@@ -121,6 +131,8 @@ class _ConvS2D(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g, *unused):
+        if g is None:
+            return None, None, None
         field, weight = ctx.saved_tensors
         g = _bf16c(g)
         gf = gw = None

@@ -442,3 +442,11 @@ def field_append_noise(field, noise, Cp):
     out = torch.empty((N, H2, W2, 4 * Cp), dtype=torch.bfloat16, device=field.device)
     check(_lib.lib().bgr_field_append_noise(ptr(field), ptr(noise), ptr(out), N, C, nd, Cp, H, W, stream_ptr()))
     return out
+
+
+def weights_prepare(descs, first_block, ndesc, total_blocks):
+    """One launch for every derived weight copy of a model (layouts.WeightPack owns the tables)."""
+    assert descs.is_cuda and descs.dtype == torch.uint8 and descs.numel() == 40 * ndesc
+    assert first_block.is_cuda and first_block.dtype == torch.int32 and first_block.numel() == ndesc + 1
+    check(_lib.lib().bgr_weights_prepare(ptr(descs), ptr(first_block), ndesc, total_blocks, stream_ptr()))
+

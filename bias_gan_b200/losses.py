@@ -23,7 +23,8 @@ class GANLoss:
             self.dist_fake = torch.distributions.uniform.Uniform(0.0, 0.2)
             self.dist_swap = torch.distributions.uniform.Uniform(0.0, 1.0)
         elif mode == "Wasserstein":
-            pass
+            self.dist_eta = torch.distributions.uniform.Uniform(0.0, 1.0)   # gradient_penalty's draw
+            self._eta = None
         else:
             raise NotImplementedError("Error, {} loss not implemented".format(mode))
         self._static = None   # (label_for_fake, label_for_real) device buffers once draw_labels() is used
@@ -33,7 +34,14 @@ class GANLoss:
         draws in the same order as d_loss (losses.py:146-153) — into persistent device buffers.
         After the first call d_loss() reads those buffers instead of drawing, which keeps host RNG
         and host->device copies out of a captured CUDA graph (step.GraphedGanStep)."""
-        if self.mode != "ModifiedMinMax":
+        if self.mode == "Wasserstein":   # the critic phase's only host draw: gradient_penalty's eta
+            eta = self.dist_eta.rsample((self.batch_size, 1, 1, 1))
+            if self._eta is None:
+                pin = torch.cuda.is_available() and torch.device(self.device).type == "cuda"
+                self._eta_host = torch.empty(eta.shape, pin_memory=pin)
+                self._eta = torch.empty(eta.shape, device=self.device)
+            self._eta_host.copy_(eta)
+            self._eta.copy_(self._eta_host, non_blocking=True)
             return
         label_fake = self.dist_fake.rsample(self.label_fake.shape)
         label_real = self.dist_real.rsample(self.label_real.shape)
@@ -58,6 +66,10 @@ class GANLoss:
         if self.dist_swap.sample() < 0.05:
             label_fake, label_real = label_real, label_fake
         return 0.5 * (self.criterion(logits_fake, label_fake) + self.criterion(logits_real, label_real))
+
+    def static_eta(self):
+        """The pre-drawn interpolation weights (None unless draw_labels() is in use)."""
+        return getattr(self, "_eta", None)
 
     def g_loss(self, logits_fake):
         if self.mode == "Wasserstein":

@@ -9,15 +9,23 @@ are identical to the reference-faithful schedule (`lean=False`).
 """
 import torch
 
+import os
+
 from . import layouts as L
 
+# one bgr_weights_prepare launch per network and phase instead of per-layer weight copies (A/B switch)
+PACK_WEIGHTS = os.environ.get("BGR_PACK_WEIGHTS", "1") != "0"
 
-def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_reg=1.0, lean=True,
+
+def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_reg=1.0, w_gp=10.0, lean=True,
              train_discriminator=True, train_generator=True, warmup=False):
     """inputs / real: bf16 field tensors [N, H/2, W/2, 4C].  Returns (d_loss, g_loss) as 0-d device
     tensors (no host sync; comm.metric_average decides when to read them)."""
     d_loss = g_loss = None
+    prep = L.prepare_weights if (PACK_WEIGHTS and inputs.is_cuda) else (lambda m: None)
     if train_discriminator:
+        prep(G)
+        prep(D)
         if lean:
             with torch.no_grad():
                 fake = G.forward_field(inputs)
@@ -26,6 +34,9 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
         logits_real, _ = D.forward_field(real)
         logits_fake, _ = D.forward_field(fake)
         d_loss = crit_gan.d_loss(logits_real, logits_fake)
+        if crit_gan.mode == "Wasserstein":   # train_gan.py:257-258
+            from .deeplab_gan import gradient_penalty
+            d_loss = d_loss + w_gp * gradient_penalty(D, fake, real, eta=crit_gan.static_eta())
         d_opt.zero_grad(set_to_none=True)
         d_loss.backward()
         if hasattr(D, "grad_sync"):
@@ -34,6 +45,8 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
         L.invalidate_cache(D)
         del fake, logits_real, logits_fake
     if train_generator:
+        prep(G)
+        prep(D)      # D changed in the critic phase: rebuilt once here instead of layer by layer
         fake = G.forward_field(inputs)
         if lean:
             for p in D.parameters():

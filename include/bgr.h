@@ -226,6 +226,23 @@ int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W
 int bgr_field_append_noise(const void* field, const float* noise, void* out, int N, int C, int nd, int Cp,
                            int H, int W, void* stream);
 
+/* Every derived weight copy of a model in one launch (what layouts.py / kernels.weight_to_gemm build one
+ * parameter at a time after each optimizer step).  descs / first_block are DEVICE arrays: descriptor d owns
+ * blocks [first_block[d], first_block[d+1]) of the 256-thread grid of total_blocks blocks.
+ *   mode 0: bf16 dst[Cout][taps][pitch] = src[Cout][Cin][taps] (fprop operand), gx = ceil(pitch/256),
+ *           blocks = Cout*gx, taps <= 9;
+ *   mode 1: bf16 dst[Cin][taps][pitch] = src transposed (data-gradient operand), gx = ceil(Cin*taps/32),
+ *           blocks = gx*ceil(pitch/32);
+ *   mode 2: fp32 dst[9][Cout] = src[Cout][9] (depthwise taps), blocks = ceil(9*Cout/256).
+ * Padding columns up to pitch are written as zeros. */
+typedef struct BgrWeightDesc {
+  const float* src;
+  void* dst;
+  int Cout, Cin, taps, pitch, mode, gx;
+} BgrWeightDesc;
+int bgr_weights_prepare(const BgrWeightDesc* descs, const int* first_block, int ndesc, int total_blocks,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

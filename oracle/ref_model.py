@@ -225,13 +225,28 @@ class GANLossRef:
         return self.criterion(logits_fake, self.ones)
 
 
-def gan_step_ref(G, D, g_opt, d_opt, crit, inputs, real, w_gan=1.0, w_reg=1.0):
+def gradient_penalty_ref(critic, images_fake, images_real):
+    """deeplab_gan.py:98-114.  eta ~ U(0,1) per sample on the CPU generator; the interpolate is a fresh
+    leaf (`Variable(..., requires_grad=True)`), the critic runs in its current (train) mode — so its
+    BatchNorm running statistics advance once more — and the input gradient is taken WITHOUT
+    create_graph: the penalty is a number added to the reported d_loss, it contributes no parameter
+    gradient (the reference has the create_graph arguments commented out)."""
+    eta = torch.distributions.uniform.Uniform(0.0, 1.0).rsample((images_fake.shape[0], 1, 1, 1)).to(images_fake.device)
+    interpol = (eta * images_fake + (1.0 - eta) * images_real).detach().requires_grad_(True)
+    logits, _ = critic(interpol)
+    gradients = torch.autograd.grad(outputs=logits, inputs=interpol, grad_outputs=torch.ones_like(logits))[0]
+    return ((gradients.norm(2, dim=1) - 1.0) ** 2).mean()
+
+
+def gan_step_ref(G, D, g_opt, d_opt, crit, inputs, real, w_gan=1.0, w_reg=1.0, w_gp=10.0):
     """One step with both phases active (train_gan.py:250-298, generator_warmup_steps = 0, update
     frequencies 1, amp O0).  Returns (d_loss, g_loss, outputs_fake of the G phase)."""
     fake = G(inputs)  # not detached in the reference (SURVEY F8)
     lr_, _ = D(real)
     lf_, _ = D(fake)
     d_loss = crit.d_loss(lr_, lf_)
+    if crit.mode == "Wasserstein":  # train_gan.py:257-258
+        d_loss = d_loss + w_gp * gradient_penalty_ref(D, fake, real)
     d_opt.zero_grad()
     d_loss.backward()
     d_opt.step()

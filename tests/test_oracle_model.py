@@ -102,3 +102,30 @@ def test_noise_generator_matches_reference_golden(kind, nd):
         gr = params[k].grad
         assert abs(float(gr.double().norm()) - norm) <= 2e-3 * norm + 1e-7, k
         torch.testing.assert_close(gr.flatten()[:8], head, rtol=5e-3, atol=1e-6 + 1e-3 * norm / gr.numel() ** 0.5)
+
+
+def test_gradient_penalty_matches_reference_golden():
+    """gradient_penalty_ref / Wasserstein GANLossRef against the reference's own functions
+    (tests/golden/make_gp_golden.py): value, RNG consumption, the extra BatchNorm update, and that
+    the penalty carries no parameter gradient (create_graph is commented out in the reference)."""
+    gold = torch.load(os.path.join(os.path.dirname(NOISE_GOLD), "gp_golden.pt"), weights_only=False)
+    m = gold["meta"]
+    D = seed_state(R.DiscriminatorRef(m["C"], (m["H"], m["W"])), 12).train()
+    fake, real = seeded_fields(5, m["B"], m["C"], m["H"], m["W"])
+    torch.manual_seed(m["seed"])
+    crit = R.GANLossRef("Wasserstein", m["B"], torch.device("cpu"))
+    lr_, _ = D(real)
+    lf_, _ = D(fake)
+    d_loss = crit.d_loss(lr_, lf_)
+    gp = R.gradient_penalty_ref(D, fake, real)
+    assert gp.requires_grad == gold["gp_requires_grad"] is False
+    assert torch.equal(torch.get_rng_state(), gold["rng_after"])
+    assert int(D.xception_features.bn1.num_batches_tracked) == gold["nbt"] == 3
+    torch.testing.assert_close(d_loss.detach(), gold["d_loss"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(crit.g_loss(lf_).detach(), gold["g_loss"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(gp, gold["gp"], rtol=2e-3, atol=1e-6)
+    (d_loss + 10.0 * gp).backward()
+    g = D.xception_features.conv1.weight.grad
+    norm, head = gold["grad"]
+    assert abs(float(g.double().norm()) - norm) <= 2e-3 * norm
+    torch.testing.assert_close(g.flatten()[:8], head, rtol=5e-3, atol=1e-3 * norm / g.numel() ** 0.5)

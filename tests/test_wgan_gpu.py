@@ -1,0 +1,90 @@
+"""Wasserstein critic path (deeplab_gan.py:98-114, losses.py:129-172, train_gan.py:257-258)
+on the sm_100a kernels against the fp32 oracle (pinned by tests/golden/gp_golden.pt)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+B, C, H, W = 4, 16, 256, 384
+
+
+def _setup():
+    from bias_gan_b200 import deeplab_gan as P
+    from oracle import ref_model as R
+    from oracle.seeded import seed_state, seeded_fields
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = torch.device("cuda", 0)
+    fake, real = seeded_fields(5, B, C, H, W)
+    mk = lambda cls, *a: seed_state(cls(*a), 12).to(dev).train()
+    return P, R, dev, fake.to(dev), real.to(dev), mk
+
+
+def test_gradient_penalty_matches_oracle():
+    P, R, dev, fake, real, mk = _setup()
+    from bias_gan_b200 import kernels as K
+    Dp, Dp2 = mk(P.Discriminator, C, 16, False, torch.nn.BatchNorm2d, (H, W)), mk(P.Discriminator, C, 16, False, torch.nn.BatchNorm2d, (H, W))
+    Dr, Da = mk(R.DiscriminatorRef, C, (H, W)), mk(R.DiscriminatorRef, C, (H, W))
+    torch.manual_seed(31)
+    gp_r = R.gradient_penalty_ref(Dr, fake, real)
+    rng = torch.get_rng_state()
+    torch.manual_seed(31)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        gp_a = R.gradient_penalty_ref(Da, fake, real)
+    torch.manual_seed(31)
+    gp_p = P.gradient_penalty(Dp, fake, real)                       # the reference's call: fp32 NCHW
+    assert torch.equal(torch.get_rng_state(), rng)
+    torch.manual_seed(31)
+    gp_f = P.gradient_penalty(Dp2, K.nchw_to_field(fake), K.nchw_to_field(real))   # the step loop's call: fields
+    assert not gp_p.requires_grad and not gp_f.requires_grad
+    assert all(p.requires_grad for p in Dp.parameters()) and all(p.grad is None for p in Dp.parameters())
+    floor = abs(float(gp_a) - float(gp_r))
+    for got in (gp_p, gp_f):
+        assert abs(float(got) - float(gp_r)) <= 1.5 * floor + 5e-2 * abs(float(gp_r)), (float(got), float(gp_r), float(gp_a))
+    # the penalty's forward is a train-mode forward: BatchNorm statistics advance like the reference's
+    assert int(Dp.xception_features.bn1.num_batches_tracked) == int(Dr.xception_features.bn1.num_batches_tracked) == 1
+    torch.testing.assert_close(Dp.xception_features.bn1.running_mean, Dr.xception_features.bn1.running_mean, rtol=2e-2, atol=2e-3)
+
+
+def test_wasserstein_step_eager_and_graphed():
+    P, R, dev, fake, real, mk = _setup()
+    from bias_gan_b200 import kernels as K
+    from bias_gan_b200.losses import GANLoss, L1LossField
+    from bias_gan_b200.step import GraphedGanStep, gan_step
+    from oracle.seeded import seed_state
+    import torch.nn.functional as F
+    b, h, w = 2, 64, 96
+    x, y = fake[:b, :, :h, :w].contiguous(), real[:b, :, :h, :w].contiguous()
+    xf, yf = K.nchw_to_field(x), K.nchw_to_field(y)
+    opt = lambda m, **kw: torch.optim.AdamW(m.parameters(), lr=1e-4, eps=1e-8, weight_decay=1e-5, **kw)
+
+    def build(mod, fused):
+        if mod is P:
+            G = seed_state(P.Generator(C, C, "Interpolate", "Normal", 0), 21).to(dev).train()
+            D = seed_state(P.Discriminator(C, input_size=(h, w)), 22).to(dev).train()
+        else:
+            G = seed_state(R.GeneratorRef(C, C), 21).to(dev).train()
+            D = seed_state(R.DiscriminatorRef(C, (h, w)), 22).to(dev).train()
+        kw = dict(fused=True, capturable=True) if fused else {}
+        return G, D, opt(G, **kw), opt(D, **kw)
+
+    Gr, Dr, gor, dor = build(R, False)
+    torch.manual_seed(17)
+    dl_r, gl_r, _ = R.gan_step_ref(Gr, Dr, gor, dor, R.GANLossRef("Wasserstein", b, dev), x, y)
+    rng = torch.get_rng_state()
+    G0, D0, go0, do0 = build(P, False)
+    torch.manual_seed(17)
+    dl0, gl0 = gan_step(G0, D0, go0, do0, GANLoss("Wasserstein", b, dev), L1LossField(), xf, yf)
+    assert torch.equal(torch.get_rng_state(), rng)
+    # D phase = three train-mode critic forwards (real, fake, interpolate), G phase one more
+    assert int(D0.xception_features.bn1.num_batches_tracked) == int(Dr.xception_features.bn1.num_batches_tracked) == 4
+    G1, D1, go1, do1 = build(P, True)
+    torch.manual_seed(17)
+    gs = GraphedGanStep(G1, D1, go1, do1, GANLoss("Wasserstein", b, dev), L1LossField(), tuple(xf.shape), dev)
+    torch.manual_seed(17)
+    dl1, gl1 = gs(xf, yf)
+    assert torch.equal(torch.get_rng_state(), rng)
+    for got in ((dl0, gl0), (dl1, gl1)):   # tiny-configuration noise: see test_graphed_step_matches_eager
+        assert abs(float(got[0]) - float(dl_r)) <= 0.35 * abs(float(dl_r)) + 0.1, (float(got[0]), float(dl_r))
+        assert abs(float(got[1]) - float(gl_r)) <= 0.35 * abs(float(gl_r)) + 0.1, (float(got[1]), float(gl_r))
+    dl2, gl2 = gs(xf, yf)
+    assert all(torch.isfinite(t) for t in (dl2, gl2))
