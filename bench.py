@@ -105,7 +105,7 @@ def run_reference(args):
             "config": {"workload": "1xB200 config: G+D train step, 16x768x1152 fields, batch 8/GPU (reference CPU path on a bounded sample)"},
             "cpu_baseline": {"value": v, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_torch_gpu(args, autocast):
@@ -155,7 +155,7 @@ def run_torch_gpu(args, autocast):
             gc.collect()
             torch.cuda.empty_cache()
             line["note"] = "batch %d does not fit in HBM with stock PyTorch" % b
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def conv_roofline_step(step_fn, torch, K):
@@ -235,7 +235,28 @@ def conv_traffic(n_launches):
     return t["dram_bytes_per_launch"], "profiles/r01_conv_traffic.json"
 
 
+_OUT = None
+
+
+def _claim_stdout():
+    """The driver reads ONE JSON line from stdout; NCCL (its version banner) and other native libraries
+    write to fd 1 directly.  Keep a private handle on the real stdout for the result line and point fd 1 at
+    stderr for everything else."""
+    global _OUT
+    if _OUT is None:
+        sys.stdout.flush()
+        _OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    _claim_stdout()
+    _OUT.write(json.dumps(line) + "\n")
+    _OUT.flush()
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -394,7 +415,7 @@ def main():
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
         if rank == 0:
-            print(json.dumps({"profile_only": True, "steps": args.steps}), flush=True)
+            emit({"profile_only": True, "steps": args.steps})
         return
     sampler = ClockSampler(lrank)
     if rank == 0:
@@ -444,7 +465,7 @@ def main():
         v, dt, sample = cpu_oracle_sample(1, 0, threads)
         line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample,
                                 "seconds": dt}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 if __name__ == "__main__":
