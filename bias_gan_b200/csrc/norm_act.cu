@@ -301,7 +301,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* 
 // dyh = bf16(g * act'(a*x + b)) is recomputed from g and x -- x is read anyway -- exactly as pass 1
 // computed it for the sums, so pass 1 need not write it and this pass need not read it back.
 __global__ void __launch_bounds__(256)
-bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, const __nv_bfloat16* __restrict__ x,
+bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, const __nv_bfloat16* __restrict__ gin2,
+                              int ldg2, const __nv_bfloat16* __restrict__ x,
                               int ldx, const float* __restrict__ xa, const float* __restrict__ xb,
                               const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, int ldd, long M,
                               int C, float slope, int act) {
@@ -326,14 +327,20 @@ bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, co
     auto one = [&](long row, const uint4& gu, const uint4& xu) {
       float d[8], xv[8];
       unpack8(gu, d);
+      if (gin2 != nullptr) {   // the second gradient of a dual-handle output, summed in fp32 as pass 1 did
+        float hv[8];
+        unpack8(*reinterpret_cast<const uint4*>(gin2 + row * ldg2 + g * 8), hv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] += hv[j];
+      }
       unpack8(xu, xv);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float v = d[j];
         if (act) {
           v = fmaf(ca[j], xv[j], cb[j]) > 0.f ? v : slope * v;
-          v = __bfloat162float(__float2bfloat16_rn(v));   // the value pass 1 summed
         }
+        if (act || gin2 != nullptr) v = __bfloat162float(__float2bfloat16_rn(v));   // the value pass 1 summed
         d[j] = c0[j] * (v - k1[j] - (xv[j] - mu[j]) * k2[j]);
       }
       *reinterpret_cast<uint4*>(dx + row * ldd + g * 8) = pack8(d);
@@ -446,8 +453,8 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
   int agrid, ablock;
   rowgroup_launch(M, C, &agrid, &ablock);
   if (D == nullptr) {
-    if (g2 != nullptr || act == 1) return fail(BGR_ERR_ARG, "bn_backward: dyh may be NULL only on the recompute path");
-    bn_bwd_apply_recompute_kernel<<<agrid, ablock, 0, st>>>(G, ldg, X, ldx, xa, xb, coef_ws, static_cast<__nv_bfloat16*>(dx),
+    if (act == 1) return fail(BGR_ERR_ARG, "bn_backward: dyh may be NULL only on the recompute path");
+    bn_bwd_apply_recompute_kernel<<<agrid, ablock, 0, st>>>(G, ldg, G2, ldg2, X, ldx, xa, xb, coef_ws, static_cast<__nv_bfloat16*>(dx),
                                                             ldd, M, C, slope, act == 2);
   } else {
     bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(D, X, ldx, coef_ws, static_cast<__nv_bfloat16*>(dx), ldd, M, C);
@@ -471,6 +478,16 @@ extern "C" int bgr_bn_backward_recompute(const void* g, int ldg, const float* a,
                                          const float* gamma, int act, float slope, long M, int C, void* dyh,
                                          void* dx, int ldd, double* sums, float* coef_ws, void* stream) {
   return bn_backward_impl(g, ldg, nullptr, 0, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
+                          ldd, sums, coef_ws, stream);
+}
+
+// The same with a second gradient of the output (a dual-handle block input): both passes add g2 on load.
+extern "C" int bgr_bn_backward_recompute_dual(const void* g, int ldg, const void* g2, int ldg2, const float* a,
+                                              const float* b, const void* x, int ldx, const float* mean,
+                                              const float* invstd, const float* gamma, int act, float slope, long M,
+                                              int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
+                                              void* stream) {
+  return bn_backward_impl(g, ldg, g2, ldg2, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
                           ldd, sums, coef_ws, stream);
 }
 

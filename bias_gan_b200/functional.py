@@ -24,6 +24,8 @@ SIDE_STREAM = os.environ.get("BGR_NO_SIDE_STREAM") is None
 # instruction-bound, and the masking + two reductions cost it as much as the separate streaming
 # reduce kernel (34 us at the mid-flow shape) that they replace.
 FUSE_DGRAD_BN_REDUCE = os.environ.get("BGR_DGRAD_BN_FUSION") is not None
+# BatchNorm backward of residual-free layers from (g, y) alone (A/B switch, see _BNAct)
+RECOMPUTE_BN_BWD = os.environ.get("BGR_RECOMPUTE_BN_BWD", "1") != "0"
 _side_streams = {}
 _forked = set()
 
@@ -191,22 +193,29 @@ class _BNAct(torch.autograd.Function):
             sums = K.bn_stats(y)
         mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var, nbt)
         out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
-        ctx.save_for_backward(y, out if act else None, mean, invstd, gamma)
-        ctx.act = act
         ctx.has_res = res is not None
+        # without a residual input act' = sign(a*y + b) is recomputed in backward (RECOMPUTE_BN_BWD): the stored
+        # output is not read and no dyh tensor makes the round trip between the two passes
+        ctx.recompute = RECOMPUTE_BN_BWD and not ctx.has_res
+        ctx.save_for_backward(y, out if (act and not ctx.recompute) else None, mean, invstd, gamma,
+                              a if ctx.recompute else None, b if ctx.recompute else None)
+        ctx.act = act
         if dual:   # a second handle of the same tensor: its gradient arrives separately (see bn_act)
             return out, out[...]
         return out
 
     @staticmethod
     def backward(ctx, g, g2=None):
-        y, out, mean, invstd, gamma = ctx.saved_tensors
+        y, out, mean, invstd, gamma, a, b = ctx.saved_tensors
         if g is None:
             g, g2 = g2, None
         g = _bf16c(g)
         g2 = _bf16c(g2) if g2 is not None else None
         C = y.shape[-1]
-        dx, dyh, sums = K.bn_backward(g, out, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE, g2=g2)
+        if ctx.recompute:
+            dx, dyh, sums = K.bn_backward_recompute(g, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE, g2=g2)
+        else:
+            dx, dyh, sums = K.bn_backward(g, out, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE, g2=g2)
         ggamma = sums[C:] if ctx.needs_input_grad[1] else None
         gbeta = sums[:C] if ctx.needs_input_grad[2] else None
         gres = dyh if (ctx.has_res and ctx.needs_input_grad[3]) else None

@@ -282,11 +282,23 @@ def dw_wgrad_bn(x, a, b, act, gy, slope=0.2):
     return dw
 
 
-def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2, want_dyh=False):
-    """bn_backward for a BatchNorm(+act) whose output was never stored: act' from sign(a*x + b)."""
+def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2, want_dyh=False, g2=None):
+    """bn_backward for a BatchNorm(+act) whose output was never stored: act' from sign(a*x + b).
+    g2: a second gradient of the same output (dual handle), added on load by both passes."""
     M, C, ldx = _rows(x)
     Mg, Cg, ldg = _rows(g)
     assert (Mg, Cg) == (M, C)
+    if g2 is not None:
+        M2, C2, ldg2 = _rows(g2)
+        assert (M2, C2) == (M, C)
+        dyh = act_empty(x.shape, x.device) if want_dyh else None
+        dx = act_empty(x.shape, x.device)
+        sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+        coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
+        check(_lib.lib().bgr_bn_backward_recompute_dual(ptr(g), ldg, ptr(g2), ldg2, ptr(a), ptr(b), ptr(x), ldx, ptr(mean),
+                                                        ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
+                                                        ptr(dyh), ptr(dx), _rows(dx)[2], ptr(sums), ptr(coef), stream_ptr()))
+        return dx, dyh, coef[5 * C:7 * C]
     dyh = act_empty(x.shape, x.device) if want_dyh else None   # NULL: pass 2 recomputes it from g and x
     dx = act_empty(x.shape, x.device)
     sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)

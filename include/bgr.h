@@ -160,6 +160,15 @@ int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const floa
                               float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
                               float* coef_ws, void* stream);
 
+/* bgr_bn_backward_recompute with a second gradient g2 of the same output (NULL = none), added on load by
+ * both passes.  Serves every BatchNorm(+LeakyReLU) without a residual input: the stored output is not
+ * read (act' from sign(a*x + b)) and, with dyh = NULL, no dyh tensor is written or re-read. */
+int bgr_bn_backward_recompute_dual(const void* g, int ldg, const void* g2, int ldg2, const float* a,
+                                   const float* b, const void* x, int ldx, const float* mean,
+                                   const float* invstd, const float* gamma, int act, float slope, long M,
+                                   int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
+                                   void* stream);
+
 /* Data gradient of a stride-1 depthwise 3x3 conv fused with pass 1 of the backward of the
  * BatchNorm(+LeakyReLU) that produced its input on the fly (bgr_dw_fwd_bn): writes
  * dyh = act'(a*q + b) * dgrad(dy) (bf16, pixel stride ldd) and sums = fp64 [sum dyh | sum dyh*xhat].

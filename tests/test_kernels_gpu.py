@@ -222,6 +222,39 @@ def test_bn_act_train(dev, C, M_shape, act, with_res):
     assert int(bn_p.num_batches_tracked) == 1
 
 
+@pytest.mark.parametrize("C,M_shape", [(128, (2, 24, 36)), (728, (2, 6, 9)), (2048, (2, 3, 5))])
+@pytest.mark.parametrize("act", [True, False])
+@pytest.mark.parametrize("dual", [True, False])
+def test_bn_backward_recompute_equals_stored_path(dev, C, M_shape, act, dual, monkeypatch):
+    """Residual-free BatchNorm backward from (g [, g2], y) alone -- act' from sign(a*y + b), no dyh round
+    trip -- against the path that reads the stored output and writes dyh: same sums, same dx."""
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(9)
+    N, H, W = M_shape
+    y = nhwc((torch.randn(N, C, H, W, generator=g) * 2 + 0.5).to(dev).bfloat16())
+    go = nhwc(torch.randn(N, C, H, W, generator=g).to(dev).bfloat16())
+    go2 = nhwc(torch.randn(N, C, H, W, generator=g).to(dev).bfloat16())
+    res = {}
+    for flag in (True, False):
+        monkeypatch.setattr(F_, "RECOMPUTE_BN_BWD", flag)
+        bn = torch.nn.BatchNorm2d(C).to(dev).train()
+        with torch.no_grad():
+            gg = torch.Generator(device="cpu").manual_seed(10)
+            bn.weight.copy_(1 + 0.1 * torch.randn(C, generator=gg)); bn.bias.copy_(0.1 * torch.randn(C, generator=gg))
+        yp = y.clone().requires_grad_(True)
+        if dual:
+            o1, o2 = F_.bn_act(yp, bn, act=act, dual=True)
+            torch.autograd.backward([o1, o2], [go, go2])
+        else:
+            F_.bn_act(yp, bn, act=act).backward(go)
+        res[flag] = (yp.grad.clone(), bn.weight.grad.clone(), bn.bias.grad.clone())
+    a, b = res[True], res[False]
+    same = (a[0].view(torch.int16) == b[0].view(torch.int16)).float().mean()
+    assert float(same) >= 0.995, float(same)     # fp32 atomic order in the sums may move a last bf16 bit
+    assert rel(a[0].float(), b[0].float()) < 2e-3
+    assert rel(a[1], b[1]) < 1e-4 and rel(a[2], b[2]) < 1e-4
+
+
 @pytest.mark.parametrize("C,N,H,W", [(128, 2, 24, 36), (728, 2, 13, 9), (1024, 1, 6, 7), (256, 3, 70, 45)])
 @pytest.mark.parametrize("act", [True, False])
 @pytest.mark.parametrize("fuse_reduce", [True, False])
