@@ -196,7 +196,9 @@ class _BNAct(torch.autograd.Function):
         ctx.has_res = res is not None
         # without a residual input act' = sign(a*y + b) is recomputed in backward (RECOMPUTE_BN_BWD): the stored
         # output is not read and no dyh tensor makes the round trip between the two passes
-        ctx.recompute = RECOMPUTE_BN_BWD and not ctx.has_res
+        # (not for dual handles: with a second gradient to add the stored path measures faster, 521 vs 718 us
+        # on a 453 MB tensor -- the recompute kernels are half issue-bound, profiles/r01_bn_backward_ncu.txt)
+        ctx.recompute = RECOMPUTE_BN_BWD and not ctx.has_res and not dual
         ctx.save_for_backward(y, out if (act and not ctx.recompute) else None, mean, invstd, gamma,
                               a if ctx.recompute else None, b if ctx.recompute else None)
         ctx.act = act

@@ -55,6 +55,8 @@ for (N, H, W, C) in SHAPES:
     rows.append(("bn_backward (2 kernels)", timeit(lambda: K.bn_backward(g, out, x, mean, inv, a, act=True)), 7 * nbytes))
     rows.append(("bn_backward recompute", timeit(lambda: K.bn_backward_recompute(g, a, b, x, mean, inv, a, act=True)), 5 * nbytes))
     rows.append(("bn_backward recompute+g2", timeit(lambda: K.bn_backward_recompute(g, a, b, x, mean, inv, a, act=True, g2=out)), 7 * nbytes))
+    rows.append(("bn_backward stored+g2", timeit(lambda: K.bn_backward(g, out, x, mean, inv, a, act=True, g2=out)), 8 * nbytes))
+    rows.append(("bn_backward recompute+g2+dyh", timeit(lambda: K.bn_backward_recompute(g, a, b, x, mean, inv, a, act=True, g2=out, want_dyh=True)), 7 * nbytes))
     print("shape N%d %dx%d C%d  (%.1f MB per tensor)" % (N, H, W, C, nbytes / 1e6))
     for name, us, by in rows:
         print("   %-26s %9.1f us   %7.0f GB/s" % (name, us, by / us / 1e3))
