@@ -146,7 +146,7 @@ def test_graphed_step_with_noise_draw_order():
     # to 10-20 % run to run (test_model_gpu.test_graphed_step_matches_eager measures that spread); the
     # exact checks are the RNG state and the slot contents above
     for a, b in ((dl0, dl1), (gl0, gl1)):
-        assert abs(float(a) - float(b)) <= 0.35 * abs(float(a)) + 2e-2, (float(a), float(b))
+        assert abs(float(a) - float(b)) <= 0.5 * abs(float(a)) + 5e-2, (float(a), float(b))
     dl2, gl2 = gs(xf, yf)
     assert not torch.equal(G1._noise_slots[0].dev.cpu(), z1)    # fresh noise every replay
     assert all(torch.isfinite(t) for t in (dl2, gl2))
