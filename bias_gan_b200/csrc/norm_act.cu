@@ -176,10 +176,10 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
   for (int gi = threadIdx.x % m.G; gi < m.G; gi += (m.G >= 256 ? 256 : m.G)) {
     const int r = m.G >= 256 ? 0 : threadIdx.x / m.G;
     if (r >= m.R) break;
-    float mu[8], is[8], s1[8], s2[8], ca[8], cb[8];
+    float mu[8], s1[8], s2[8], ca[8], cb[8];   // s2 accumulates dyh*(x - mean); invstd is applied once at the end
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      mu[j] = mean[gi * 8 + j]; is[j] = invstd[gi * 8 + j]; s1[j] = 0.f; s2[j] = 0.f;
+      mu[j] = mean[gi * 8 + j]; s1[j] = 0.f; s2[j] = 0.f;
       ca[j] = ACT == 2 ? xa[gi * 8 + j] : 0.f;
       cb[j] = ACT == 2 ? xb[gi * 8 + j] : 0.f;
     }
@@ -204,7 +204,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
         d = __bfloat162float(__float2bfloat16_rn(d));
         gv[j] = d;
         s1[j] += d;
-        s2[j] += d * (xv[j] - mu[j]) * is[j];
+        s2[j] = fmaf(d, xv[j] - mu[j], s2[j]);
       }
       if (dyh != nullptr) *reinterpret_cast<uint4*>(dyh + row * ldd + gi * 8) = pack8(gv);
     };
@@ -228,7 +228,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       atomicAdd(&sh[gi * 8 + j], s1[j]);
-      atomicAdd(&sh[C + gi * 8 + j], s2[j]);
+      atomicAdd(&sh[C + gi * 8 + j], s2[j] * invstd[gi * 8 + j]);
     }
     if (m.G < 256) break;
   }
