@@ -167,10 +167,10 @@ def conv_roofline_step(step_fn, torch, K):
     sigs = {}
     orig_f, orig_w = K.conv_fprop, K.conv_wgrad
 
-    def f_wrap(x, w, dy, dx, out=None, bias=None, bn_sums=None):
-        key = ("fprop", tuple(x.shape), x.stride(2), w.shape[0], tuple(dy), tuple(dx), bias is not None, bn_sums is not None)
+    def f_wrap(x, w, dy, dx, out=None, bias=None, want_stats=False):
+        key = ("fprop", tuple(x.shape), x.stride(2), w.shape[0], tuple(dy), tuple(dx), bias is not None, bool(want_stats))
         sigs[key] = sigs.get(key, 0) + 1
-        return orig_f(x, w, dy, dx, out=out, bias=bias, bn_sums=bn_sums)
+        return orig_f(x, w, dy, dx, out=out, bias=bias, want_stats=want_stats)
 
     def w_wrap(x, gy, dy, dx, dw=None):
         key = ("wgrad", tuple(x.shape), x.stride(2), gy.shape[-1], tuple(dy), tuple(dx), False, False)
@@ -193,9 +193,8 @@ def conv_roofline_step(step_fn, torch, K):
         if kind == "fprop":
             wt = torch.randn(cout, nt, K.pad_channels(cin) if cin > 64 else cin, device=dev).bfloat16()[..., :cin]
             bias = torch.zeros(cout, device=dev) if has_bias else None
-            sums = torch.empty(2 * cout, dtype=torch.float64, device=dev) if has_stats else None
             y = K.act_empty((n, h, w_, cout), dev)
-            fn = lambda: orig_f(x, wt, list(dy), list(dx), out=y, bias=bias, bn_sums=sums)
+            fn = lambda: orig_f(x, wt, list(dy), list(dx), out=y, bias=bias, want_stats=has_stats)
         else:
             gy = K.act_empty((n, h, w_, cout), dev)
             gy.normal_()

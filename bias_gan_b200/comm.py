@@ -15,7 +15,18 @@ import torch.distributed as dist
 
 class BucketedAllReduce:
     """Gradient buckets of ~bucket_mb MB in reverse parameter order (≈ the order backward produces
-    them, apex DDP's default `message_size` bucketing, comm/distributed.py:197)."""
+    them, apex DDP's default `message_size` bucketing, comm/distributed.py:197).
+
+    Protocol per optimizer update: `start()` -> loss.backward() (hooks launch a bucket's all-reduce as soon
+    as its last gradient has been accumulated, on NCCL's stream, while backward continues) -> `finish()`
+    -> optimizer.step().  `start()` drops whatever an earlier backward left behind, so a backward pass
+    that touches this model's parameters without belonging to its update (the reference schedule
+    back-propagates d_loss into G and g_loss into D) can never leak stale buckets into the
+    next update; gan_step also disables the sync of the model that is not being stepped.
+
+    One bucket = one flat fp32 tensor: gradients are gathered with one multi-tensor copy, averaged by
+    the collective itself (ReduceOp.AVG on NCCL; sum and a pre-scale elsewhere) and scattered back with
+    one multi-tensor copy -- no per-parameter kernels."""
 
     def __init__(self, module, bucket_mb=32, group=None):
         self.group = group
@@ -35,14 +46,22 @@ class BucketedAllReduce:
         for bi, b in enumerate(self.buckets):
             for p in b:
                 self.bucket_of[p] = bi
+        self.flat = [None] * len(self.buckets)   # persistent flat storage, allocated on first use
+        self.handles = []
+        self.enabled = True   # False: gradients stay local (the other network's phase; single-rank diagnostics)
+        self.avg_op = None
+        self.start()
+        if self.world > 1:
+            backend = dist.get_backend(group)
+            self.avg_op = dist.ReduceOp.AVG if backend == "nccl" else None
+            for p in params:
+                self.handles.append(p.register_post_accumulate_grad_hook(self._hook))
+
+    def start(self):
+        """Forget the bookkeeping of any earlier backward pass (call before the backward of an update)."""
         self.pending = [len(b) for b in self.buckets]
         self.launched = [False] * len(self.buckets)
         self.inflight = []
-        self.handles = []
-        self.enabled = True   # False: gradients stay local (single-rank diagnostics between collective steps)
-        if self.world > 1:
-            for p in params:
-                self.handles.append(p.register_post_accumulate_grad_hook(self._hook))
 
     def _hook(self, p):
         if not self.enabled:
@@ -57,10 +76,23 @@ class BucketedAllReduce:
         self.launched[bi] = True
         if not ps:
             return
-        flat = torch.cat([p.grad.reshape(-1) for p in ps])
-        flat.mul_(1.0 / self.world)
-        work = dist.all_reduce(flat, group=self.group, async_op=True)
-        self.inflight.append((ps, flat, work))
+        n = sum(p.numel() for p in ps)
+        flat = self.flat[bi]
+        if flat is None or flat.numel() < n or flat.device != ps[0].grad.device:
+            flat = self.flat[bi] = torch.empty(sum(p.numel() for p in self.buckets[bi]), dtype=torch.float32,
+                                               device=ps[0].grad.device)
+        views, off = [], 0
+        for p in ps:
+            views.append(flat[off:off + p.numel()].view_as(p.grad))
+            off += p.numel()
+        torch._foreach_copy_(views, [p.grad for p in ps])
+        buf = flat[:n]
+        if self.avg_op is not None:
+            work = dist.all_reduce(buf, op=self.avg_op, group=self.group, async_op=True)
+        else:
+            buf.mul_(1.0 / self.world)
+            work = dist.all_reduce(buf, group=self.group, async_op=True)
+        self.inflight.append((ps, views, work))
 
     def finish(self):
         """Wait for all buckets (launching the ones backward did not complete) and write the
@@ -70,16 +102,10 @@ class BucketedAllReduce:
         for bi in range(len(self.buckets)):
             if not self.launched[bi] and self.pending[bi] < len(self.buckets[bi]):
                 self._launch(bi)
-        for ps, flat, work in self.inflight:
+        for ps, views, work in self.inflight:
             work.wait()
-            off = 0
-            for p in ps:
-                n = p.numel()
-                p.grad.copy_(flat[off:off + n].view_as(p.grad))
-                off += n
-        self.inflight = []
-        self.pending = [len(b) for b in self.buckets]
-        self.launched = [False] * len(self.buckets)
+            torch._foreach_copy_([p.grad for p in ps], views)
+        self.start()
 
 
 class comm(object):

@@ -1,5 +1,7 @@
 // Error plumbing and the TMA tensor-map encoder shared by all translation units of libbgr.so.
+#include <map>
 #include <mutex>
+#include <utility>
 
 #include "bgr_internal.h"
 
@@ -57,6 +59,33 @@ int encode_tmap_bf16(CUtensorMap* map, const void* base, int rank, const uint64_
              (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], box[1], rank > 2 ? box[2] : 0);
     return fail(BGR_ERR_CUDA, buf);
   }
+  return BGR_OK;
+}
+
+// One process normally drives one GPU, but nothing here assumes it: per-device caches are keyed by ordinal.
+int sm_count() {
+  static int cache[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cache[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev] = n;
+  }
+  return cache[dev];
+}
+
+int ensure_dyn_smem_impl(const void* kern, int bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, int> done;   // (kernel, device) -> bytes configured
+  int dev = 0;
+  BGR_CUDA_OK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_pair(kern, dev);
+  auto it = done.find(key);
+  if (it != done.end() && it->second >= bytes) return BGR_OK;
+  BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  done[key] = bytes;
   return BGR_OK;
 }
 

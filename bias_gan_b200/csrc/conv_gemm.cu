@@ -8,12 +8,16 @@
 //                    B = weights [Cout][taps][Cin] (K-major).
 //   wgrad         :  dW[co, t, ci] = sum_p dY[p, co] * X[p + off(t), ci]
 //                    both operands MN-major (channels contiguous, pixels = GEMM-K), split over
-//                    pixel chunks, fp32 atomics into dW.
+//                    pixel chunks; every split writes its own fp32 slab and the slabs are added in
+//                    split order (no atomics: the result does not depend on scheduling).
 //
 // Replaces the cuDNN/cuBLAS call sites behind nn.Conv2d in the reference
 // (src/deepCam/architecture/gpsro/deeplab.py:58,81,95,178,182,331,363,366,622,626,630).
 #include "bgr_internal.h"
 #include "tc_common.cuh"
+
+static int g_force_block_n = 0;   // development switches (bgr_debug_conv_*)
+static int g_conv_dbg = 0;
 
 namespace bgr {
 
@@ -31,6 +35,7 @@ struct ConvParams {
   int dbg;                  // development switch (0 in production)
   int chunks_per_split;     // wgrad only
   int total_chunks;         // wgrad only
+  long slab_elems;          // wgrad only: Cout*ntaps*Cin (distance between the slabs of two splits)
   int dy[kMaxTaps], dx[kMaxTaps];
 };
 
@@ -43,19 +48,20 @@ struct ConvParams {
 //             64-channel chunks (two staging buffers), overlapped with the next tile's MMAs.
 //             Optional fused BatchNorm statistics: per-channel sum / sum-of-squares of the
 //             bf16-rounded outputs, read back from the staged tile (column sums), kept in registers
-//             for the CTA's life, then one fp64 global atomic per channel and CTA.
+//             for the CTA's life; at the end the four warps are added in warp order and the CTA writes
+//             one partial row (its tiles are a fixed function of blockIdx, so the row is reproducible).
 // ------------------------------------------------------------------------------------------
 template <int BLOCK_N, int STAGES, bool STATS>
 __global__ void __launch_bounds__(192, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmO, const float* __restrict__ bias,
-                  double* __restrict__ stats, const __grid_constant__ ConvParams p) {
+                  float* __restrict__ stats /* [CTA groups][2][Cout] */, const __grid_constant__ ConvParams p) {
   constexpr uint32_t A_BYTES = kBlockM * kBlockK * 2;
   constexpr uint32_t B_BYTES = BLOCK_N * kBlockK * 2;
   constexpr uint32_t O_BYTES = kBlockM * 64 * 2;       // one 64-channel output chunk
   constexpr uint32_t TMEM_COLS = BLOCK_N > 128 ? 512 : 2 * BLOCK_N;   // allocations are powers of two
-  constexpr uint32_t NEEDED = STAGES * (A_BYTES + B_BYTES) + 2 * O_BYTES + 2 * BLOCK_N * 4 +
-                              (2 * STAGES + 4) * 8 + 16;
+  constexpr uint32_t NEEDED = STAGES * (A_BYTES + B_BYTES) + 2 * O_BYTES + (2 * STAGES + 4) * 8 + 16;
+  static_assert(4 * 2 * BLOCK_N * 4 <= 2 * O_BYTES, "the statistics combine reuses the output staging buffers");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
@@ -66,8 +72,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* sA = smem;
   uint8_t* sB = sA + STAGES * A_BYTES;
   uint8_t* sO = sB + STAGES * B_BYTES;
-  float* s_stats = reinterpret_cast<float*>(sO + 2 * O_BYTES);
-  uint64_t* full = reinterpret_cast<uint64_t*>(s_stats + 2 * BLOCK_N);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sO + 2 * O_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + 2;
@@ -95,9 +100,6 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(&tempty[b], 4);
     }
     fence_barrier_init();
-  }
-  if (STATS) {
-    for (int i = threadIdx.x; i < 2 * BLOCK_N; i += blockDim.x) s_stats[i] = 0.f;
   }
   if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
@@ -246,22 +248,26 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
     }
-    if (STATS) {  // combine the four warps in shared memory, then one fp64 atomic per channel and CTA
+    if (epi_tid == 0) bulk_wait_group_read<0>();
+    if (STATS) {
+      // The four warps' sums are added in warp order through the (now idle) output staging buffers and the
+      // CTA writes partial row mt_first of the [groups][2][Cout] workspace: no atomics, a fixed summation order.
+      named_bar_sync(2, 128);
+      float* comb = reinterpret_cast<float*>(sO);   // [4 warps][2][BLOCK_N]
 #pragma unroll
       for (int i = 0; i < BLOCK_N / 32; ++i) {   // st_*[c*2 + e] <-> channel c*64 + 2*lane + e
         const int ch = (i >> 1) * 64 + 2 * lane + (i & 1);
-        atomicAdd(&s_stats[ch], st_sum[i]);
-        atomicAdd(&s_stats[BLOCK_N + ch], st_sq[i]);
+        comb[q * 2 * BLOCK_N + ch] = st_sum[i];
+        comb[q * 2 * BLOCK_N + BLOCK_N + ch] = st_sq[i];
       }
       named_bar_sync(2, 128);
-      for (int i = epi_tid; i < BLOCK_N; i += 128) {
-        if (n0 + i < p.Cout) {
-          atomicAdd(stats + n0 + i, double(s_stats[i]));
-          atomicAdd(stats + p.Cout + n0 + i, double(s_stats[BLOCK_N + i]));
-        }
+      float* prow = stats + size_t(mt_first) * 2 * p.Cout;
+      for (int i = epi_tid; i < 2 * BLOCK_N; i += 128) {
+        const int half = i / BLOCK_N, ch = i - half * BLOCK_N;
+        if (n0 + ch < p.Cout)
+          prow[half * p.Cout + n0 + ch] = ((comb[i] + comb[2 * BLOCK_N + i]) + comb[4 * BLOCK_N + i]) + comb[6 * BLOCK_N + i];
       }
     }
-    if (epi_tid == 0) bulk_wait_group_read<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -270,7 +276,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
 // ------------------------------------------------------------------------------------------
 // wgrad: grid = (Cout tiles * Cin tiles * taps, splits).  Each CTA reduces its share of 64-pixel
-// chunks into one 128 x BLOCK_N fp32 tile in TMEM and adds it to dW with fp32 atomics.
+// chunks into one 128 x BLOCK_N fp32 tile in TMEM and stores it into the slab of its split
+// (slab 0 = dW itself when there is one split); sum_rows adds the slabs in split order.
 // ------------------------------------------------------------------------------------------
 template <int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(192, 1)
@@ -364,7 +371,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
       mbar_wait(tmem_full, 0);
       tc_fence_after();
       const int co = m0 + q * 32 + lane;
-      float* drow = dw + (size_t(co) * p.ntaps + t) * p.Cin + n0;
+      float* drow = dw + size_t(blockIdx.y) * p.slab_elems + (size_t(co) * p.ntaps + t) * p.Cin + n0;
 #pragma unroll 1
       for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
         uint32_t v[16];
@@ -374,8 +381,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
 #pragma unroll
           for (int j = 0; j < 16; j += 4)   // Cin % 8 == 0: a group of 4 is entirely in or out
             if (n0 + c0 + j < p.Cin)
-              red_add_v4(drow + c0 + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
-                         __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+              *reinterpret_cast<float4*>(drow + c0 + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                                      __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
         }
       }
     }
@@ -424,72 +431,64 @@ static int check_conv_args(const void* x, const void* w, const void* y, int Cin,
   return BGR_OK;
 }
 
-static int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
-  }
-  return n;
-}
-
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB per CTA on sm_100
 
 template <int BLOCK_N, int STAGES, bool STATS>
 static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
-                        const float* bias, double* stats, const ConvParams& p, cudaStream_t st) {
+                        const float* bias, float* stats, const ConvParams& p, int groups, cudaStream_t st) {
   constexpr size_t needed = size_t(STAGES) * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) +
-                            2 * (kBlockM * 64 * 2) + 2 * BLOCK_N * 4 + (2 * STAGES + 4) * 8 + 16;
+                            2 * (kBlockM * 64 * 2) + (2 * STAGES + 4) * 8 + 16;
   // the kernel aligns its window to 1024 B itself and traps if the slack does not suffice
   constexpr size_t smem = needed + 1024 > kMaxDynSmem ? kMaxDynSmem : needed + 1024;
   static_assert(needed <= kMaxDynSmem, "fprop stage ring does not fit");
   auto kern = conv_fprop_kernel<BLOCK_N, STAGES, STATS>;
-  static bool configured = false;
-  if (!configured) {
-    BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    configured = true;
-  }
-  int groups = sm_count() / p.n_tiles;   // CTAs per Cout tile
-  if (groups < 1) groups = 1;            // more Cout tiles than SMs: the surplus CTAs queue
-  if (groups > p.m_tiles) groups = p.m_tiles;
+  if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
   dim3 grid(groups * p.n_tiles);
   kern<<<grid, 192, smem, st>>>(tmA, tmB, tmO, bias, stats, p);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
-template <int BLOCK_N, int STAGES>
-static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* dw,
-                        ConvParams& p, cudaStream_t st) {
-  constexpr size_t smem = size_t(STAGES) * ((kBlockM + BLOCK_N) * kBlockK * 2) +
-                          (2 * STAGES + 1) * 8 + 16 + 1024;
-  auto kern = conv_wgrad_kernel<BLOCK_N, STAGES>;
-  static bool configured = false;
-  if (!configured) {
-    BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    configured = true;
-  }
-  const int tiles = ((p.Cout + kBlockM - 1) / kBlockM) * ((p.Cin + BLOCK_N - 1) / BLOCK_N) * p.ntaps;
-  // Split the pixel reduction over `splits` CTAs per tile.  Every split costs a prologue and a
-  // Cout x Cin pass of fp32 reductions through L2 (about 32 chunks' worth of MMA time), and the
-  // grid runs in rounds of one CTA per SM: take the split count with the cheapest schedule.
+// Cin tile of the weight-gradient GEMM: 256 halves the shared-memory operand traffic per FLOP; weigh it
+// against the padding
+static int wgrad_block_n(int Cin) {
+  if (Cin <= 64) return 64;
+  const int pad128 = (Cin + 127) / 128 * 128, pad256 = (Cin + 255) / 256 * 256;
+  const bool wide = g_force_block_n ? g_force_block_n == 256 : (Cin > 128 && pad256 * 13 <= pad128 * 20);
+  return wide ? 256 : 128;
+}
+
+// Split the pixel reduction over `splits` CTAs per tile.  Every split costs a prologue and a
+// Cout x Cin pass of fp32 stores + one re-read through L2 (about 32 chunks' worth of MMA time), and the
+// grid runs in rounds of one CTA per SM: take the split count with the cheapest schedule.
+static int wgrad_splits(int Cout, int Cin, int ntaps, int total_chunks, int* chunks_per_split) {
+  const int bn = wgrad_block_n(Cin);
+  const int tiles = ((Cout + kBlockM - 1) / kBlockM) * ((Cin + bn - 1) / bn) * ntaps;
   const int sms = sm_count();
   int splits = 1;
   long best = -1;
-  for (int sp = 1; sp <= 64 && sp <= p.total_chunks; ++sp) {
+  for (int sp = 1; sp <= 64 && sp <= total_chunks; ++sp) {
     const long rounds = (long(tiles) * sp + sms - 1) / sms;
-    const long cost = rounds * ((p.total_chunks + sp - 1) / sp + 32);
+    const long cost = rounds * ((total_chunks + sp - 1) / sp + 32);
     if (best < 0 || cost < best) {
       best = cost;
       splits = sp;
     }
   }
-  p.chunks_per_split = (p.total_chunks + splits - 1) / splits;
-  splits = (p.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
+  *chunks_per_split = (total_chunks + splits - 1) / splits;
+  return (total_chunks + *chunks_per_split - 1) / *chunks_per_split;
+}
+
+template <int BLOCK_N, int STAGES>
+static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* dst, int splits,
+                        const ConvParams& p, cudaStream_t st) {
+  constexpr size_t smem = size_t(STAGES) * ((kBlockM + BLOCK_N) * kBlockK * 2) +
+                          (2 * STAGES + 1) * 8 + 16 + 1024;
+  auto kern = conv_wgrad_kernel<BLOCK_N, STAGES>;
+  if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
+  const int tiles = ((p.Cout + kBlockM - 1) / kBlockM) * ((p.Cin + BLOCK_N - 1) / BLOCK_N) * p.ntaps;
   dim3 grid(tiles, splits);
-  kern<<<grid, 192, smem, st>>>(tmDY, tmX, dw, p);
+  kern<<<grid, 192, smem, st>>>(tmDY, tmX, dst, p);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -498,8 +497,6 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* 
 
 using namespace bgr;
 
-static int g_force_block_n = 0;
-static int g_conv_dbg = 0;
 extern "C" void bgr_debug_conv_block_n(int bn) { g_force_block_n = bn; }
 extern "C" void bgr_debug_conv_mode(int m) { g_conv_dbg = m; }
 
@@ -528,7 +525,7 @@ static int pick_block_n(int m_tiles, int Cout) {
 
 extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w,
                               int ldw, int Cout, int ntaps, const int* dy, const int* dx, void* y,
-                              int ldy, const float* bias, double* bn_sums, void* stream) {
+                              int ldy, const float* bias, float* bn_part, int* bn_rows, void* stream) {
   if (int rc = check_conv_args(x, w, y, Cin, ldx, Cout, ldy, ntaps)) return rc;
   if (ldw < Cin || (ldw % 8)) return fail(BGR_ERR_ARG, "conv: ldw must be >= Cin and a multiple of 8");
   ConvParams p{};
@@ -554,41 +551,66 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
     if (int rc = encode_tmap_bf16(&tmB, w, 3, dims, strides, box)) return rc;
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (bn_sums != nullptr) {
+  int groups = sm_count() / p.n_tiles;   // CTAs per Cout tile
+  if (groups < 1) groups = 1;            // more Cout tiles than SMs: the surplus CTAs queue
+  if (groups > p.m_tiles) groups = p.m_tiles;
+  if (bn_part != nullptr) {
     if (bias != nullptr) return fail(BGR_ERR_ARG, "conv: fused BatchNorm statistics exclude a bias");
-    BGR_CUDA_OK(cudaMemsetAsync(bn_sums, 0, sizeof(double) * 2 * Cout, st));
-    if (bn == 64) return launch_fprop<64, 6, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
-    if (bn == 128) return launch_fprop<128, 6, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
-    if (bn == 192) return launch_fprop<192, 4, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
-    return launch_fprop<256, 4, true>(tmA, tmB, tmO, bias, bn_sums, p, st);
+    if (bn_rows == nullptr) return fail(BGR_ERR_ARG, "conv: bn_rows must be given with bn_part");
+    if (groups > BGR_BN_MAX_ROWS) groups = BGR_BN_MAX_ROWS;
+    *bn_rows = groups;
+    if (bn == 64) return launch_fprop<64, 6, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
+    if (bn == 128) return launch_fprop<128, 6, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
+    if (bn == 192) return launch_fprop<192, 4, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
+    return launch_fprop<256, 4, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
   }
-  if (bn == 64) return launch_fprop<64, 6, false>(tmA, tmB, tmO, bias, nullptr, p, st);
-  if (bn == 128) return launch_fprop<128, 6, false>(tmA, tmB, tmO, bias, nullptr, p, st);
-  if (bn == 192) return launch_fprop<192, 4, false>(tmA, tmB, tmO, bias, nullptr, p, st);
-  return launch_fprop<256, 4, false>(tmA, tmB, tmO, bias, nullptr, p, st);
+  if (bn == 64) return launch_fprop<64, 6, false>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
+  if (bn == 128) return launch_fprop<128, 6, false>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
+  if (bn == 192) return launch_fprop<192, 4, false>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
+  return launch_fprop<256, 4, false>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
+}
+
+static void wgrad_geometry(ConvParams* p, int N, int H, int W, int Cin, int Cout, int ntaps) {
+  p->N = N; p->H = H; p->W = W;
+  pick_rect(H, W, kBlockK, &p->BW, &p->BH);
+  p->tiles_x = (W + p->BW - 1) / p->BW;
+  p->tiles_y = (H + p->BH - 1) / p->BH;
+  p->total_chunks = N * p->tiles_x * p->tiles_y;
+  p->ntaps = ntaps;
+  p->Cout = Cout; p->Cin = Cin;
+  p->slab_elems = long(Cout) * ntaps * Cin;
+}
+
+extern "C" size_t bgr_conv_wgrad_workspace(int N, int H, int W, int Cin, int Cout, int ntaps) {
+  if (ntaps < 1 || ntaps > kMaxTaps) return 0;
+  ConvParams p{};
+  wgrad_geometry(&p, N, H, W, Cin, Cout, ntaps);
+  int cps;
+  const int splits = wgrad_splits(Cout, Cin, ntaps, p.total_chunks, &cps);
+  return splits > 1 ? size_t(splits) * size_t(p.slab_elems) * sizeof(float) : 0;
 }
 
 extern "C" int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx,
                               const void* dy_, int Cout, int ldy, int ntaps, const int* dy,
-                              const int* dx, float* dw, void* stream) {
+                              const int* dx, float* dw, float* ws, size_t ws_bytes, void* stream) {
   if (int rc = check_conv_args(x, dw, dy_, Cin, ldx, Cout, ldy, ntaps)) return rc;
   ConvParams p{};
-  p.N = N; p.H = H; p.W = W;
-  pick_rect(H, W, kBlockK, &p.BW, &p.BH);
-  p.tiles_x = (W + p.BW - 1) / p.BW;
-  p.tiles_y = (H + p.BH - 1) / p.BH;
-  p.total_chunks = N * p.tiles_x * p.tiles_y;
-  p.ntaps = ntaps;
-  p.Cout = Cout; p.Cin = Cin;
+  wgrad_geometry(&p, N, H, W, Cin, Cout, ntaps);
   for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
+  int splits = wgrad_splits(Cout, Cin, ntaps, p.total_chunks, &p.chunks_per_split);
+  if (splits > 1 && (ws == nullptr || ws_bytes < size_t(splits) * size_t(p.slab_elems) * sizeof(float)))
+    return fail(BGR_ERR_ARG, "conv_wgrad: workspace smaller than bgr_conv_wgrad_workspace() asks for");
+  if ((uintptr_t(ws) & 15) != 0) return fail(BGR_ERR_ARG, "conv_wgrad: workspace must be 16-byte aligned");
   CUtensorMap tmDY, tmX;
   if (int rc = make_act_map(&tmDY, dy_, N, H, W, Cout, ldy, p.BW, p.BH)) return rc;
   if (int rc = make_act_map(&tmX, x, N, H, W, Cin, ldx, p.BW, p.BH)) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (Cin <= 64) return launch_wgrad<64, 6>(tmDY, tmX, dw, p, st);
-  // Cin tile 256 halves the shared-memory operand traffic per FLOP; weigh it against the padding
-  const int pad128 = (Cin + 127) / 128 * 128, pad256 = (Cin + 255) / 256 * 256;
-  const bool wide = g_force_block_n ? g_force_block_n == 256 : (Cin > 128 && pad256 * 13 <= pad128 * 20);
-  if (wide) return launch_wgrad<256, 4>(tmDY, tmX, dw, p, st);
-  return launch_wgrad<128, 6>(tmDY, tmX, dw, p, st);
+  float* dst = splits > 1 ? ws : dw;
+  const int bn = wgrad_block_n(Cin);
+  int rc;
+  if (bn == 64) rc = launch_wgrad<64, 6>(tmDY, tmX, dst, splits, p, st);
+  else if (bn == 256) rc = launch_wgrad<256, 4>(tmDY, tmX, dst, splits, p, st);
+  else rc = launch_wgrad<128, 6>(tmDY, tmX, dst, splits, p, st);
+  if (rc != BGR_OK || splits == 1) return rc;
+  return launch_sum_rows(ws, splits, p.slab_elems, dw, st);
 }

@@ -116,11 +116,13 @@ dw_dgrad_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ 
   }
 }
 
-// dw[k][c] += sum over output pixels.  Thread = (pixel lane, 8-channel group); each block walks a
-// contiguous range of output pixels; 72 fp32 partials per thread -> smem atomics -> global atomics.
+// dw[c][k] = sum over output pixels.  Thread = (pixel lane, 8-channel group); each block walks a
+// contiguous range of output pixels; 72 fp32 partials per thread are added into shared memory one
+// pixel lane at a time (a fixed order) and the block writes one partial row ws[blockIdx.x][C*9];
+// the rows are added in block order by sum_rows (reduce.cu).
 __global__ void __launch_bounds__(256)
 dw_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                float* __restrict__ dw, const DwGeom g, long pix_per_block) {
+                float* __restrict__ ws, const DwGeom g, long pix_per_block) {
   extern __shared__ float sh[];  // [9][C]
   for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
@@ -128,45 +130,60 @@ dw_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   const int R = G >= 256 ? 1 : 256 / G;
   const long P = long(g.N) * g.Ho * g.Wo;
   const long p0 = long(blockIdx.x) * pix_per_block, p1 = min(p0 + pix_per_block, P);
+  const int r = G >= 256 ? 0 : threadIdx.x / G;
   for (int cg = threadIdx.x % G; cg < G; cg += (G >= 256 ? 256 : G)) {
-    const int r = G >= 256 ? 0 : threadIdx.x / G;
-    if (r >= R) break;
     float acc[9][8];
 #pragma unroll
     for (int k = 0; k < 9; ++k)
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
-    for (long p = p0 + r; p < p1; p += R) {
-      const int ox = int(p % g.Wo);
-      const int oy = int((p / g.Wo) % g.Ho);
-      const int n = int(p / (long(g.Wo) * g.Ho));
-      float gv[8];
-      dw_unpack8(*reinterpret_cast<const uint4*>(dy + size_t(p) * g.ldy + cg * 8), gv);
+    if (r < R) {
+      for (long p = p0 + r; p < p1; p += R) {
+        const int ox = int(p % g.Wo);
+        const int oy = int((p / g.Wo) % g.Ho);
+        const int n = int(p / (long(g.Wo) * g.Ho));
+        float gv[8];
+        dw_unpack8(*reinterpret_cast<const uint4*>(dy + size_t(p) * g.ldy + cg * 8), gv);
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const int iy = oy * g.stride + (ky - 1) * g.dil;
-        if (iy < 0 || iy >= g.H) continue;
+        for (int ky = 0; ky < 3; ++ky) {
+          const int iy = oy * g.stride + (ky - 1) * g.dil;
+          if (iy < 0 || iy >= g.H) continue;
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const int ix = ox * g.stride + (kx - 1) * g.dil;
-          if (ix < 0 || ix >= g.W) continue;
-          float xv[8];
-          dw_unpack8(*reinterpret_cast<const uint4*>(x + (size_t(size_t(n) * g.H + iy) * g.W + ix) * g.ldx + cg * 8), xv);
+          for (int kx = 0; kx < 3; ++kx) {
+            const int ix = ox * g.stride + (kx - 1) * g.dil;
+            if (ix < 0 || ix >= g.W) continue;
+            float xv[8];
+            dw_unpack8(*reinterpret_cast<const uint4*>(x + (size_t(size_t(n) * g.H + iy) * g.W + ix) * g.ldx + cg * 8), xv);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[ky * 3 + kx][j] = fmaf(gv[j], xv[j], acc[ky * 3 + kx][j]);
+            for (int j = 0; j < 8; ++j) acc[ky * 3 + kx][j] = fmaf(gv[j], xv[j], acc[ky * 3 + kx][j]);
+          }
         }
       }
     }
+    if (R == 1) {   // one thread per channel group: no sharing
+      if (r == 0) {
 #pragma unroll
-    for (int k = 0; k < 9; ++k)
+        for (int k = 0; k < 9; ++k)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) atomicAdd(&sh[k * g.C + cg * 8 + j], acc[k][j]);
+          for (int j = 0; j < 8; ++j) sh[k * g.C + cg * 8 + j] += acc[k][j];
+      }
+    } else {        // pixel lanes add in lane order: schedule-independent (one pass per thread: G < 256)
+      for (int turn = 0; turn < R; ++turn) {
+        if (turn == r) {
+#pragma unroll
+          for (int k = 0; k < 9; ++k)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sh[k * g.C + cg * 8 + j] += acc[k][j];
+        }
+        __syncthreads();
+      }
+    }
     if (G < 256) break;
   }
   __syncthreads();
-  // sh is [9][C]; dw is stored [C][9] = the parameter's own [C,1,3,3] layout
-  // (contiguous global reductions; the transposition happens on the shared-memory side)
-  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[(i % 9) * g.C + i / 9]);
+  // sh is [9][C]; the partial row is stored [C][9] = the parameter's own [C,1,3,3] layout
+  float* row = ws + size_t(blockIdx.x) * 9 * g.C;
+  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) row[i] = sh[(i % 9) * g.C + i / 9];
 }
 
 // y[n,oy,ox,:] = x[n,2oy,2ox,:]  /  adjoint: dx = 0 except dx[n,2oy,2ox,:] = dy[n,oy,ox,:]
@@ -264,77 +281,6 @@ dw_fwd_strip_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
       if (ox0 + j < g.Wo)
         *reinterpret_cast<uint4*>(y + (size_t(size_t(n) * g.Ho + oy) * g.Wo + ox0 + j) * g.ldy + cg * 8) = dw_pack8(acc[j]);
   }
-}
-
-// dw[k][c] += sum over output pixels, strip-mined like the forward kernel.  Each block walks a
-// contiguous range of (row, strip) items for all channel groups.
-template <int S, int D, int T>
-__global__ void __launch_bounds__(256)
-dw_wgrad_strip_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                      float* __restrict__ dw, const DwGeom g, long items_per_block) {
-  constexpr int SPAN = (T - 1) * S + 2 * D + 1;
-  extern __shared__ float sh[];  // [9][C]
-  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
-  __syncthreads();
-  const int G = g.C >> 3;
-  const int R = G >= 256 ? 1 : 256 / G;
-  const int strips = (g.Wo + T - 1) / T;
-  const long items = long(g.N) * g.Ho * strips;
-  const long i0 = long(blockIdx.x) * items_per_block, i1 = min(i0 + items_per_block, items);
-  for (int cg = threadIdx.x % G; cg < G; cg += (G >= 256 ? 256 : G)) {
-    const int r = G >= 256 ? 0 : threadIdx.x / G;
-    if (r >= R) break;
-    float acc[9][8];
-#pragma unroll
-    for (int k = 0; k < 9; ++k)
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[k][e] = 0.f;
-    for (long it = i0 + r; it < i1; it += R) {
-      const int sx = int(it % strips);
-      const int oy = int((it / strips) % g.Ho);
-      const int n = int(it / (long(strips) * g.Ho));
-      const int ox0 = sx * T;
-      float gv[T][8];
-#pragma unroll
-      for (int j = 0; j < T; ++j) {
-        if (ox0 + j < g.Wo)
-          dw_unpack8(*reinterpret_cast<const uint4*>(dy + (size_t(size_t(n) * g.Ho + oy) * g.Wo + ox0 + j) * g.ldy + cg * 8), gv[j]);
-        else
-#pragma unroll
-          for (int e = 0; e < 8; ++e) gv[j][e] = 0.f;
-      }
-#pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const int iy = oy * S + (ky - 1) * D;
-        if (iy < 0 || iy >= g.H) continue;
-        const __nv_bfloat16* row = x + (size_t(size_t(n) * g.H + iy) * g.W) * g.ldx + cg * 8;
-#pragma unroll
-        for (int c = 0; c < SPAN; ++c) {
-          const int ix = ox0 * S - D + c;
-          if (ix < 0 || ix >= g.W) continue;
-          float xv[8];
-          dw_unpack8(*reinterpret_cast<const uint4*>(row + size_t(ix) * g.ldx), xv);
-#pragma unroll
-          for (int j = 0; j < T; ++j)
-#pragma unroll
-            for (int kx = 0; kx < 3; ++kx)
-              if (j * S + kx * D == c) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) acc[ky * 3 + kx][e] = fmaf(gv[j][e], xv[e], acc[ky * 3 + kx][e]);
-              }
-        }
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < 9; ++k)
-#pragma unroll
-      for (int e = 0; e < 8; ++e) atomicAdd(&sh[k * g.C + cg * 8 + e], acc[k][e]);
-    if (G < 256) break;
-  }
-  __syncthreads();
-  // sh is [9][C]; dw is stored [C][9] = the parameter's own [C,1,3,3] layout
-  // (contiguous global reductions; the transposition happens on the shared-memory side)
-  for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) atomicAdd(&dw[i], sh[(i % 9) * g.C + i / 9]);
 }
 
 // ---------------------------------------------------------------- column-marching variants
@@ -579,178 +525,6 @@ dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
       march_fwd_item<true, XF>(xin, yout, g, sc.dil, it, wr, tc, ring);
     else
       march_fwd_item<false, XF>(xin, yout, g, sc.dil, it, wr, tc, ring);
-  }
-}
-
-// ---------------------------------------------------------------- data gradient + BatchNorm backward pass 1
-// Backward of  t = depthwise3x3(act(a*q + b))  (stride 1, dilation 1; q = the pointwise conv's raw
-// output, a/b = its BatchNorm folded with batch statistics).  The march computes the data gradient
-// row by row; instead of writing it and letting a second kernel re-read it together with q, the
-// finished row is masked by act'(a*q + b) on the spot, rounded to bf16, stored as dyh and summed
-// into the two BatchNorm reductions  s1 = sum dyh,  s2 = sum dyh * (q - mean) * invstd  per channel.
-// The q row travels in the same cp.async ring group as the gradient row that completes it.
-struct BnRedCoef {
-  float2 a[2], b[2], mu[2], is[2];
-  float slope;
-  int act;
-};
-
-template <bool INTERIOR>
-__device__ __forceinline__ void march_dgrad_bnred_item(const __nv_bfloat16* __restrict__ gin,
-                                                       const __nv_bfloat16* __restrict__ qin, int ldq,
-                                                       __nv_bfloat16* __restrict__ dout, const DwGeom& g,
-                                                       const MarchItem& it, const float2 (&wr)[9][2],
-                                                       const BnRedCoef& tc, float2 (&s1)[2], float2 (&s2)[2],
-                                                       uint2* ring) {
-  constexpr int kSlot = 10 * 32;   // 6 gradient columns of row iy + 4 q columns of row iy - 1
-  float2 a0[4][2], a1[4][2], a2[4][2];
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-#pragma unroll
-    for (int e = 0; e < 2; ++e) a0[j][e] = a1[j][e] = a2[j][e] = make_float2(0.f, 0.f);
-  const unsigned cmask = INTERIOR ? 0x3fu : march_col_mask(it.W, it.ox0);
-  const int first = it.oy0 - 1;
-  const int rowstride = g.W * g.ldx, colbase = (it.ox0 - 1) * g.ldx;
-  const int orowstride = g.W * g.ldy, ocol = it.ox0 * g.ldy;
-  const int qrowstride = g.W * ldq, qcol = it.ox0 * ldq;
-  auto issue = [&](uint2* slot, int iy) {
-    march_issue_row<INTERIOR>(slot, gin, it.H, rowstride, colbase, g.ldx, iy, cmask, iy <= it.oy1);
-    const int oy = iy - 1;
-    const bool ok = oy >= it.oy0 && oy < it.oy1;
-    const int qo = (ok ? oy : 0) * qrowstride + qcol;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const bool okj = INTERIOR ? ok : (ok && it.ox0 + j < it.W);
-      cp_async8(slot + (6 + j) * 32, qin + (INTERIOR || okj ? qo + j * ldq : 0), okj);
-    }
-    cp_async_commit();
-  };
-#pragma unroll
-  for (int r = 0; r < kRing; ++r) issue(ring + r * kSlot, first + r);
-  auto phase = [&](int iy, float2 (&prev)[4][2], float2 (&cur)[4][2], float2 (&next)[4][2]) {
-    cp_async_wait<kRing - 1>();
-    uint2* slot = ring + ((iy - first) & (kRing - 1)) * kSlot;
-    uint2 rc[6], qc[4];
-#pragma unroll
-    for (int c = 0; c < 6; ++c) rc[c] = slot[c * 32];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) qc[j] = slot[(6 + j) * 32];
-    issue(slot, iy + kRing);
-#pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      float2 xv[2];
-      dw_unpack22(rc[c], xv);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int kx = c - j;
-        if (kx < 0 || kx > 2) continue;
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          next[j][e] = fma2s(xv[e], wr[0 + kx][e], next[j][e]);
-          cur[j][e] = fma2s(xv[e], wr[3 + kx][e], cur[j][e]);
-          prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
-        }
-      }
-    }
-    const int oy = iy - 1;
-    if (oy >= it.oy0 && oy < it.oy1) {
-      __nv_bfloat16* orow = dout + (oy * orowstride + ocol);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (!INTERIOR && it.ox0 + j >= it.W) continue;
-        float2 qv[2];
-        dw_unpack22(qc[j], qv);
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          if (tc.act) {
-            const float zx = fmaf(tc.a[e].x, qv[e].x, tc.b[e].x), zy = fmaf(tc.a[e].y, qv[e].y, tc.b[e].y);
-            prev[j][e].x = zx > 0.f ? prev[j][e].x : tc.slope * prev[j][e].x;
-            prev[j][e].y = zy > 0.f ? prev[j][e].y : tc.slope * prev[j][e].y;
-          }
-        }
-        const uint2 packed = dw_pack22(prev[j]);
-        *reinterpret_cast<uint2*>(orow + j * g.ldy) = packed;
-        float2 dr[2];   // the rounded values pass 2 reads back: the mean subtraction then cancels exactly
-        dw_unpack22(packed, dr);
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          s1[e].x += dr[e].x;
-          s1[e].y += dr[e].y;
-          s2[e].x = fmaf(dr[e].x, (qv[e].x - tc.mu[e].x) * tc.is[e].x, s2[e].x);
-          s2[e].y = fmaf(dr[e].y, (qv[e].y - tc.mu[e].y) * tc.is[e].y, s2[e].y);
-        }
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) prev[j][e] = make_float2(0.f, 0.f);
-  };
-  for (int iy = first; iy <= it.oy1; iy += 3) {
-    phase(iy, a0, a1, a2);
-    if (iy + 1 <= it.oy1) phase(iy + 1, a1, a2, a0);
-    if (iy + 2 <= it.oy1) phase(iy + 2, a2, a0, a1);
-  }
-  cp_async_wait<0>();
-}
-
-__global__ void __launch_bounds__(128, 2)
-dw_march_dgrad_bnred_kernel(const __nv_bfloat16* __restrict__ gy, const float* __restrict__ w,
-                            const __nv_bfloat16* __restrict__ q, int ldq, __nv_bfloat16* __restrict__ dyh,
-                            const DwGeom g, const MarchSched sc, const float* __restrict__ xa,
-                            const float* __restrict__ xb, const float* __restrict__ mean,
-                            const float* __restrict__ invstd, float slope, int act, double* __restrict__ sums) {
-  __shared__ uint2 ring_all[4][kRing][10 * 32];   // [warp][slot][col][lane]
-  __shared__ float sh[2 * 128];
-  for (int i = threadIdx.x; i < 2 * 128; i += blockDim.x) sh[i] = 0.f;
-  __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int cb0 = (blockIdx.x % sc.cblocks) * 128;
-  const int lc = lane * kCpt, c0 = cb0 + lc;
-  if (c0 < g.C) {
-    uint2* ring = &ring_all[warp][0][lane];
-    float2 wr[9][2];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {   // mirrored taps: the data gradient is the same stencil reversed
-      const float4 w0 = *reinterpret_cast<const float4*>(w + (8 - k) * g.C + c0);
-      wr[k][0] = make_float2(w0.x, w0.y);
-      wr[k][1] = make_float2(w0.z, w0.w);
-    }
-    BnRedCoef tc;
-    {
-      const float4 a = *reinterpret_cast<const float4*>(xa + c0), b = *reinterpret_cast<const float4*>(xb + c0);
-      const float4 m = *reinterpret_cast<const float4*>(mean + c0), r = *reinterpret_cast<const float4*>(invstd + c0);
-      tc.a[0] = make_float2(a.x, a.y); tc.a[1] = make_float2(a.z, a.w);
-      tc.b[0] = make_float2(b.x, b.y); tc.b[1] = make_float2(b.z, b.w);
-      tc.mu[0] = make_float2(m.x, m.y); tc.mu[1] = make_float2(m.z, m.w);
-      tc.is[0] = make_float2(r.x, r.y); tc.is[1] = make_float2(r.z, r.w);
-      tc.slope = slope; tc.act = act;
-    }
-    float2 s1[2], s2[2];
-    s1[0] = s1[1] = s2[0] = s2[1] = make_float2(0.f, 0.f);
-    const int item_step = (gridDim.x / sc.cblocks) * 4;
-    for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
-      MarchItem it;
-      march_decode(g, sc, item, &it);
-      const size_t img = size_t(it.n) * g.H * g.W;
-      const __nv_bfloat16* gin = gy + img * g.ldx + c0;
-      const __nv_bfloat16* qin = q + img * ldq + c0;
-      __nv_bfloat16* dout = dyh + img * g.ldy + c0;
-      if (it.ox0 >= 1 && it.ox0 + 5 <= it.W)
-        march_dgrad_bnred_item<true>(gin, qin, ldq, dout, g, it, wr, tc, s1, s2, ring);
-      else
-        march_dgrad_bnred_item<false>(gin, qin, ldq, dout, g, it, wr, tc, s1, s2, ring);
-    }
-    atomicAdd(&sh[lc + 0], s1[0].x); atomicAdd(&sh[lc + 1], s1[0].y);
-    atomicAdd(&sh[lc + 2], s1[1].x); atomicAdd(&sh[lc + 3], s1[1].y);
-    atomicAdd(&sh[128 + lc + 0], s2[0].x); atomicAdd(&sh[128 + lc + 1], s2[0].y);
-    atomicAdd(&sh[128 + lc + 2], s2[1].x); atomicAdd(&sh[128 + lc + 3], s2[1].y);
-  }
-  __syncthreads();
-  const int nch = min(128, g.C - cb0);
-  for (int i = threadIdx.x; i < 2 * nch; i += blockDim.x) {
-    const int half = i / nch, c = i - half * nch;
-    atomicAdd(&sums[half * g.C + cb0 + c], double(sh[half * 128 + c]));
   }
 }
 
@@ -1020,7 +794,7 @@ __device__ __forceinline__ void march_wgrad_s2_item(const __nv_bfloat16* __restr
 
 __global__ void __launch_bounds__(128, 2)
 dw_march_wgrad_s2_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                         float* __restrict__ dw, const DwGeom g, const MarchSched sc) {
+                         float* __restrict__ ws, const DwGeom g, const MarchSched sc) {
   __shared__ float sh[9 * 128];
   extern __shared__ uint2 ring_dyn[];               // [4 warps][kRing][13 * 32]
   for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sh[i] = 0.f;
@@ -1029,11 +803,11 @@ dw_march_wgrad_s2_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
   const int cb0 = (blockIdx.x % sc.cblocks) * 128;
   const int lc = lane * kCpt;
   const int c0 = cb0 + lc;
+  float2 acc[9][2];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
   if (c0 < g.C) {
     uint2* ring = ring_dyn + warp * (kRing * 13 * 32) + lane;
-    float2 acc[9][2];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
     const int item_step = (gridDim.x / sc.cblocks) * 4;
     for (int item = (blockIdx.x / sc.cblocks) * 4 + warp; item < sc.items; item += item_step) {
       MarchItem it;
@@ -1045,17 +819,24 @@ dw_march_wgrad_s2_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat1
       else
         march_wgrad_s2_item<false>(xin, gin, g, it, acc, ring);
     }
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      atomicAdd(&sh[k * 128 + lc + 0], acc[k][0].x);
-      atomicAdd(&sh[k * 128 + lc + 1], acc[k][0].y);
-      atomicAdd(&sh[k * 128 + lc + 2], acc[k][1].x);
-      atomicAdd(&sh[k * 128 + lc + 3], acc[k][1].y);
-    }
   }
-  __syncthreads();
+  for (int turn = 0; turn < 4; ++turn) {   // the four warps add in warp order: schedule-independent
+    if (turn == warp && c0 < g.C) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        sh[k * 128 + lc + 0] += acc[k][0].x;
+        sh[k * 128 + lc + 1] += acc[k][0].y;
+        sh[k * 128 + lc + 2] += acc[k][1].x;
+        sh[k * 128 + lc + 3] += acc[k][1].y;
+      }
+    }
+    __syncthreads();
+  }
+  // partial row ws[blockIdx.x / cblocks][C][9] (the parameter's own layout): this block owns channels
+  // [cb0, cb0 + 128); sum_rows (reduce.cu) adds the rows in block order
   const int nch = min(128, g.C - cb0);
-  for (int i = threadIdx.x; i < 9 * nch; i += blockDim.x) atomicAdd(&dw[cb0 * 9 + i], sh[(i % 9) * 128 + i / 9]);
+  float* row = ws + size_t(blockIdx.x / sc.cblocks) * 9 * g.C + size_t(cb0) * 9;
+  for (int i = threadIdx.x; i < 9 * nch; i += blockDim.x) row[i] = sh[(i % 9) * 128 + i / 9];
 }
 
 // one item of the weight-gradient march: acc[ky*3+kx] += dy[oy][ox] * x[oy+ky-1][ox+kx-1]
@@ -1132,7 +913,7 @@ __device__ __forceinline__ void march_wgrad_item(const __nv_bfloat16* __restrict
 template <int XF>
 __global__ void __launch_bounds__(128, 3)
 dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
-                      float* __restrict__ dw, const DwGeom g, const MarchSched sc,
+                      float* __restrict__ ws, const DwGeom g, const MarchSched sc,
                       const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
   __shared__ float sh[9 * 128];                       // [9][128 channels of this block]
   __shared__ uint2 ring_all[4][kRing][10 * 32];       // [warp][slot][6 x cols + 4 dy cols][lane]
@@ -1142,11 +923,11 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
   const int cb0 = (blockIdx.x % sc.cblocks) * 128;
   const int lc = lane * kCpt;      // channel offset inside the block's 128
   const int c0 = cb0 + lc;
+  float2 acc[9][2];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
   if (c0 < g.C) {
     uint2* ring = &ring_all[warp][0][lane];
-    float2 acc[9][2];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) acc[k][0] = acc[k][1] = make_float2(0.f, 0.f);
     XfCoef tc;
     dw_load_coef<XF>(&tc, xa, xb, slope, c0);
     const int item_step = (gridDim.x / sc.cblocks) * 4;
@@ -1160,18 +941,24 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
       else
         march_wgrad_item<false, XF>(xin, gin, g, sc.dil, it, acc, tc, ring);
     }
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      atomicAdd(&sh[k * 128 + lc + 0], acc[k][0].x);
-      atomicAdd(&sh[k * 128 + lc + 1], acc[k][0].y);
-      atomicAdd(&sh[k * 128 + lc + 2], acc[k][1].x);
-      atomicAdd(&sh[k * 128 + lc + 3], acc[k][1].y);
-    }
   }
-  __syncthreads();
-  // dw is stored [C][9] (the parameter's own layout): this block owns channels [cb0, cb0 + 128)
+  for (int turn = 0; turn < 4; ++turn) {   // the four warps add in warp order: schedule-independent
+    if (turn == warp && c0 < g.C) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        sh[k * 128 + lc + 0] += acc[k][0].x;
+        sh[k * 128 + lc + 1] += acc[k][0].y;
+        sh[k * 128 + lc + 2] += acc[k][1].x;
+        sh[k * 128 + lc + 3] += acc[k][1].y;
+      }
+    }
+    __syncthreads();
+  }
+  // partial row ws[blockIdx.x / cblocks][C][9] (the parameter's own layout): this block owns channels
+  // [cb0, cb0 + 128); sum_rows (reduce.cu) adds the rows in block order
   const int nch = min(128, g.C - cb0);
-  for (int i = threadIdx.x; i < 9 * nch; i += blockDim.x) atomicAdd(&dw[cb0 * 9 + i], sh[(i % 9) * 128 + i / 9]);
+  float* row = ws + size_t(blockIdx.x / sc.cblocks) * 9 * g.C + size_t(cb0) * 9;
+  for (int i = threadIdx.x; i < 9 * nch; i += blockDim.x) row[i] = sh[(i % 9) * 128 + i / 9];
 }
 
 // Row segmentation by a cost model.  The marches are issue-bound (ncu at the 48x72x728 mid-flow shape:
@@ -1183,8 +970,7 @@ dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* 
 // (Swept on B200 over forced segment lengths and fill fractions: the model is within ~6 % of the best
 // forced plan at every trunk shape; the HBM-bound 384x576 shape is insensitive between 20 and 128 rows.)
 static void march_plan(const DwGeom& g, MarchSched* sc, unsigned* blocks, int blocks_per_sm = 3) {
-  int sms = 148, dev = 0;
-  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = sm_count();
   const int dil = g.dil < 1 ? 1 : g.dil;
   const int Hs = (g.H + dil - 1) / dil, Ws = (g.W + dil - 1) / dil, NP = g.N * dil * dil;
   const int G = g.C / kCpt, strips = (Ws + 3) / 4;
@@ -1304,56 +1090,27 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
   return BGR_OK;
 }
 
-// dyh = act'(a*q + b) * dgrad(dy) and the BatchNorm backward sums of it (see dw_march_dgrad_bnred_kernel);
-// sums = fp64 [sum dyh (C) | sum dyh * xhat (C)], zeroed here.
-extern "C" int bgr_dw_dgrad_bn_reduce(const void* dy, int N, int H, int W, int C, int ldy, const float* w,
-                                      const void* q, int ldq, const float* xa, const float* xb, const float* mean,
-                                      const float* invstd, int act, float slope, void* dyh, int ldd, double* sums,
-                                      void* stream) {
-  DwGeom g;
-  if (int rc = make_geom(&g, N, H, W, C, 1, 1, ldy, ldd)) return rc;   // the march reads dy (ldx) and writes dyh (ldy)
-  if (C % 4) return fail(BGR_ERR_ARG, "depthwise: channel count must be a multiple of 4");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BGR_CUDA_OK(cudaMemsetAsync(sums, 0, 2 * size_t(C) * sizeof(double), st));
-  MarchSched sc;
-  unsigned blocks;
-  march_plan(g, &sc, &blocks, 2);   // 202 registers: two resident blocks per SM
-  dw_march_dgrad_bnred_kernel<<<blocks, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dy), w,
-                                                      static_cast<const __nv_bfloat16*>(q), ldq,
-                                                      static_cast<__nv_bfloat16*>(dyh), g, sc, xa, xb, mean, invstd,
-                                                      slope, act, sums);
-  BGR_LAUNCH_OK();
-  return BGR_OK;
+// partial rows of a weight-gradient launch -> dw[C][9], added in row order
+static int dw_wgrad_finish(const float* ws, int rows, int C, float* dw, cudaStream_t st) {
+  return launch_sum_rows(ws, rows, 9L * C, dw, st);
 }
-
-template <int S, int D>
-static int launch_wgrad_strip(const __nv_bfloat16* x, const __nv_bfloat16* dy, float* dw, const DwGeom& g,
-                              cudaStream_t st) {
-  auto kern = dw_wgrad_strip_kernel<S, D, kStripT>;
-  static bool configured = false;
-  if (!configured) {
-    BGR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    configured = true;
-  }
-  const long items = long(g.N) * g.Ho * ((g.Wo + kStripT - 1) / kStripT);
-  const int G = g.C / 8, R = G >= 256 ? 1 : 256 / G;
-  long blocks = (items + long(R) * 2 - 1) / (long(R) * 2);
-  if (blocks > 148 * 4) blocks = 148 * 4;
-  if (blocks < 1) blocks = 1;
-  const long ipb = (items + blocks - 1) / blocks;
-  blocks = (items + ipb - 1) / ipb;
-  kern<<<int(blocks), 256, 9 * g.C * sizeof(float), st>>>(x, dy, dw, g, ipb);
+static int dw_wgrad_ws_check(long rows, int C) {
+  if (rows * 9L * C > long(BGR_DW_WGRAD_WS_FLOATS))
+    return fail(BGR_ERR_ARG, "depthwise wgrad: workspace of BGR_DW_WGRAD_WS_FLOATS floats is too small for this launch");
   return BGR_OK;
 }
 
 template <int XF>
-static int launch_march_wgrad(const __nv_bfloat16* x, const __nv_bfloat16* dy, float* dw, const DwGeom& g,
+static int launch_march_wgrad(const __nv_bfloat16* x, const __nv_bfloat16* dy, float* dw, float* ws, const DwGeom& g,
                               const float* xa, const float* xb, float slope, cudaStream_t st) {
   MarchSched sc;
   unsigned blocks;
   march_plan(g, &sc, &blocks);
-  dw_march_wgrad_kernel<XF><<<blocks, 128, 0, st>>>(x, dy, dw, g, sc, xa, xb, slope);
-  return BGR_OK;
+  const int rows = int(blocks) / sc.cblocks;
+  if (int rc = dw_wgrad_ws_check(rows, g.C)) return rc;
+  dw_march_wgrad_kernel<XF><<<blocks, 128, 0, st>>>(x, dy, ws, g, sc, xa, xb, slope);
+  BGR_LAUNCH_OK();
+  return dw_wgrad_finish(ws, rows, g.C, dw, st);
 }
 
 // Stride-1, dilation-1 depthwise conv of act(a*x + b) without materialising it: the BatchNorm
@@ -1379,62 +1136,52 @@ extern "C" int bgr_dw_fwd_bn(const void* x, int N, int H, int W, int C, int ldx,
 // Weight gradient of bgr_dw_fwd_bn: x is the stored pre-BatchNorm tensor, transformed on load.
 extern "C" int bgr_dw_wgrad_bn(const void* x, int N, int H, int W, int C, int ldx, const float* a,
                                const float* b, int act, float slope, const void* dy, int ldy, float* dw,
-                               void* stream) {
+                               float* ws, void* stream) {
   DwGeom g;
   if (int rc = make_geom(&g, N, H, W, C, 1, 1, ldx, ldy)) return rc;
+  if (ws == nullptr) return fail(BGR_ERR_ARG, "depthwise wgrad: workspace missing");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BGR_CUDA_OK(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * C, st));
-  if (9 * C * sizeof(float) > 160 * 1024) return fail(BGR_ERR_ARG, "depthwise wgrad: too many channels");
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto DY = static_cast<const __nv_bfloat16*>(dy);
-  int rc = act ? launch_march_wgrad<2>(X, DY, dw, g, a, b, slope, st)
-               : launch_march_wgrad<1>(X, DY, dw, g, a, b, slope, st);
-  if (rc) return rc;
-  BGR_LAUNCH_OK();
-  return BGR_OK;
+  return act ? launch_march_wgrad<2>(X, DY, dw, ws, g, a, b, slope, st)
+             : launch_march_wgrad<1>(X, DY, dw, ws, g, a, b, slope, st);
 }
 
 extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, const void* dy, int ldy,
-                            int stride, int dil, float* dw, void* stream) {
+                            int stride, int dil, float* dw, float* ws, void* stream) {
   DwGeom g;
   if (int rc = make_geom(&g, N, H, W, C, stride, dil, ldx, ldy)) return rc;
+  if (ws == nullptr) return fail(BGR_ERR_ARG, "depthwise wgrad: workspace missing");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BGR_CUDA_OK(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * C, st));
-  if (9 * C * sizeof(float) > 160 * 1024) return fail(BGR_ERR_ARG, "depthwise wgrad: too many channels");
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto DY = static_cast<const __nv_bfloat16*>(dy);
-  int rc = BGR_OK;
-  if (stride == 1) rc = launch_march_wgrad<0>(X, DY, dw, g, nullptr, nullptr, 0.f, st);   // any dilation
-  else if (stride == 2 && dil == 1) {
+  if (stride == 1) return launch_march_wgrad<0>(X, DY, dw, ws, g, nullptr, nullptr, 0.f, st);   // any dilation
+  if (stride == 2 && dil == 1) {
     constexpr int ring_bytes = 4 * kRing * 13 * 32 * 8;   // 53 KB: above the 48 KB static limit
-    static bool configured = false;
-    if (!configured) {
-      BGR_CUDA_OK(cudaFuncSetAttribute(dw_march_wgrad_s2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ring_bytes));
-      configured = true;
-    }
+    if (int rc = ensure_dyn_smem(dw_march_wgrad_s2_kernel, ring_bytes)) return rc;
     MarchSched sc;
     unsigned blocks;
     march_plan_s2(g, &sc, &blocks, 2);   // 192 registers: two resident blocks per SM
-    dw_march_wgrad_s2_kernel<<<blocks, 128, ring_bytes, st>>>(X, DY, dw, g, sc);
+    const int rows = int(blocks) / sc.cblocks;
+    if (int rc = dw_wgrad_ws_check(rows, C)) return rc;
+    dw_march_wgrad_s2_kernel<<<blocks, 128, ring_bytes, st>>>(X, DY, ws, g, sc);
+    BGR_LAUNCH_OK();
+    return dw_wgrad_finish(ws, rows, C, dw, st);
   }
-  else {
-    const long P = long(N) * g.Ho * g.Wo;
-    const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
-    long blocks = (P + long(R) * 4 - 1) / (long(R) * 4);
-    if (blocks > 148 * 4) blocks = 148 * 4;
-    if (blocks < 1) blocks = 1;
-    const long ppb = (P + blocks - 1) / blocks;
-    blocks = (P + ppb - 1) / ppb;
-    static bool configured = false;
-    if (!configured) {
-      BGR_CUDA_OK(cudaFuncSetAttribute(dw_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-      configured = true;
-    }
-    dw_wgrad_kernel<<<int(blocks), 256, 9 * C * sizeof(float), st>>>(X, DY, dw, g, ppb);
-  }
-  if (rc != BGR_OK) return rc;
+  if (9 * C * sizeof(float) > 160 * 1024) return fail(BGR_ERR_ARG, "depthwise wgrad: too many channels");
+  const long P = long(N) * g.Ho * g.Wo;
+  const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
+  long blocks = (P + long(R) * 4 - 1) / (long(R) * 4);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks > long(BGR_DW_WGRAD_WS_FLOATS) / (9L * C)) blocks = long(BGR_DW_WGRAD_WS_FLOATS) / (9L * C);
+  if (blocks < 1) blocks = 1;
+  const long ppb = (P + blocks - 1) / blocks;
+  blocks = (P + ppb - 1) / ppb;
+  if (int rc = dw_wgrad_ws_check(blocks, C)) return rc;
+  if (int rc = ensure_dyn_smem(dw_wgrad_kernel, 160 * 1024)) return rc;
+  dw_wgrad_kernel<<<int(blocks), 256, 9 * C * sizeof(float), st>>>(X, DY, ws, g, ppb);
   BGR_LAUNCH_OK();
-  return BGR_OK;
+  return dw_wgrad_finish(ws, int(blocks), C, dw, st);
 }
 
 extern "C" int bgr_subsample2(const void* x, int N, int H, int W, int C, int ldx, void* y, int ldy,

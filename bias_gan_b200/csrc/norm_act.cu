@@ -3,9 +3,10 @@
 // Replaces nn.BatchNorm2d / nn.LeakyReLU / `x += skip` call sites of the reference
 // (src/deepCam/architecture/gpsro/deeplab.py:100,141,179-183,334-338,365-368,623-631).
 //
-// All kernels are HBM-bound: 128-bit accesses (8 bf16 per thread), per-channel reductions via
-// per-thread fp32 partials -> shared-memory fp32 atomics -> one fp64 global atomic per
-// channel per block (warp-shuffle-free because each thread owns fixed channels).
+// All kernels are HBM-bound: 128-bit accesses (8 bf16 per thread).  Per-channel reductions are
+// schedule-independent: per-thread fp32 partials -> one shared-memory slot per (row lane, channel),
+// added in lane order -> one partial row per block in a workspace [rows][2C] -> the finalize /
+// coefficient kernels add the rows in index order in fp64.  No floating-point atomics anywhere.
 #include <cuda_bf16.h>
 
 #include "bgr_internal.h"
@@ -43,12 +44,29 @@ struct RowGroupMap {
 };
 
 // ---------------------------------------------------------------- statistics: sum, sum of squares
+// Deposit this thread's 2 x 8 values for (row lane r, channel group g) and write the block's partial
+// row: part[blockIdx.x][i] = sum over row lanes (in lane order) of sh[r][i].
+__device__ __forceinline__ void block_partial_put(float* sh, int C, int r, int g, const float (&s)[8], const float (&q)[8]) {
+  float* dst = sh + size_t(r) * 2 * C;
+  *reinterpret_cast<float4*>(dst + g * 8) = make_float4(s[0], s[1], s[2], s[3]);
+  *reinterpret_cast<float4*>(dst + g * 8 + 4) = make_float4(s[4], s[5], s[6], s[7]);
+  *reinterpret_cast<float4*>(dst + C + g * 8) = make_float4(q[0], q[1], q[2], q[3]);
+  *reinterpret_cast<float4*>(dst + C + g * 8 + 4) = make_float4(q[4], q[5], q[6], q[7]);
+}
+__device__ __forceinline__ void block_partial_flush(const float* sh, int C, int R, float* __restrict__ part) {
+  __syncthreads();
+  float* row = part + size_t(blockIdx.x) * 2 * C;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
+    float t = sh[i];
+    for (int r = 1; r < R; ++r) t += sh[size_t(r) * 2 * C + i];
+    row[i] = t;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long M, int C, int ld, int rows_per_block,
-                double* __restrict__ sums /* [2][C] */) {
-  extern __shared__ float sh[];  // [2][C]
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
-  __syncthreads();
+                float* __restrict__ part /* [gridDim.x][2][C] */) {
+  extern __shared__ float sh[];  // [R][2][C]
   const RowGroupMap m(C);
   const long r0 = long(blockIdx.x) * rows_per_block;
   const long r1 = min(r0 + rows_per_block, M);
@@ -62,29 +80,52 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long M, int C, int ld, int 
 #pragma unroll
       for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] += f[j] * f[j]; }
     }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&sh[g * 8 + j], s[j]);
-      atomicAdd(&sh[C + g * 8 + j], q[j]);
-    }
+    block_partial_put(sh, C, r, g, s, q);
     if (m.G < 256) break;
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&sums[i], double(sh[i]));
+  block_partial_flush(sh, C, m.R, part);
 }
 
-// mean / invstd / fused affine (a, b) / running statistics (momentum, unbiased variance)
-__global__ void bn_finalize_kernel(const double* __restrict__ sums, long M, int C,
-                                   const float* __restrict__ gamma, const float* __restrict__ beta,
-                                   float eps, float momentum, float* __restrict__ mean,
-                                   float* __restrict__ invstd, float* __restrict__ a,
-                                   float* __restrict__ b, float* __restrict__ running_mean,
-                                   float* __restrict__ running_var, long long* __restrict__ num_batches) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c == 0 && num_batches) *num_batches += 1;   // nn.BatchNorm2d.num_batches_tracked
-  if (c >= C) return;
-  const double mu = sums[c] / double(M);
-  double var = sums[C + c] / double(M) - mu * mu;
+// Ordered fp64 sum of the partial rows of 32 channels: 8 row lanes (warps) x 32 channels; lane w adds
+// rows w, w+8, ...; the eight lane sums are added in lane order.  Returns true in the threads (warp 0)
+// that hold the result for a valid channel c.
+__device__ __forceinline__ bool ordered_row_sums(const float* __restrict__ part, int rows, int C, int* c_out,
+                                                 double* s_out, double* q_out) {
+  __shared__ double shd[8][2][32];
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  double s = 0.0, q = 0.0;
+  if (c < C) {
+    for (int r = rl; r < rows; r += 8) {
+      s += double(part[size_t(r) * 2 * C + c]);
+      q += double(part[size_t(r) * 2 * C + C + c]);
+    }
+  }
+  shd[rl][0][cl] = s;
+  shd[rl][1][cl] = q;
+  __syncthreads();
+  if (rl != 0 || c >= C) return false;
+#pragma unroll
+  for (int w = 1; w < 8; ++w) { s += shd[w][0][cl]; q += shd[w][1][cl]; }
+  *c_out = c; *s_out = s; *q_out = q;
+  return true;
+}
+
+// mean / invstd / fused affine (a, b) / running statistics (momentum, unbiased variance) from the
+// partial rows of the statistics pass (bn_stats_kernel or the conv epilogue).  grid = ceil(C/32) x 256.
+__global__ void __launch_bounds__(256)
+bn_finalize_kernel(const float* __restrict__ part, int rows, long M, int C,
+                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                   float eps, float momentum, float* __restrict__ mean,
+                   float* __restrict__ invstd, float* __restrict__ a,
+                   float* __restrict__ b, float* __restrict__ running_mean,
+                   float* __restrict__ running_var, long long* __restrict__ num_batches) {
+  if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches) *num_batches += 1;   // nn.BatchNorm2d.num_batches_tracked
+  int c;
+  double sum, sq;
+  if (!ordered_row_sums(part, rows, C, &c, &sum, &sq)) return;
+  const double mu = sum / double(M);
+  double var = sq / double(M) - mu * mu;
   if (var < 0) var = 0;
   const float is = float(1.0 / sqrt(var + double(eps)));
   mean[c] = float(mu);
@@ -166,10 +207,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
                      const __nv_bfloat16* __restrict__ x, int ldx,
                      const float* __restrict__ mean, const float* __restrict__ invstd,
                      __nv_bfloat16* __restrict__ dyh, int ldd, long M, int C, int rows_per_block, float slope,
-                     double* __restrict__ sums /* [2][C] */) {
-  extern __shared__ float sh[];
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
-  __syncthreads();
+                     float* __restrict__ part /* [gridDim.x][2][C] */) {
+  extern __shared__ float sh[];   // [R][2][C]
   const RowGroupMap m(C);
   const long r0 = long(blockIdx.x) * rows_per_block;
   const long r1 = min(r0 + rows_per_block, M);
@@ -226,31 +265,30 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
           *reinterpret_cast<const uint4*>(x + row * ldx + gi * 8),
           ACT == 1 ? *reinterpret_cast<const uint4*>(out + row * ldo + gi * 8) : z4);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&sh[gi * 8 + j], s1[j]);
-      atomicAdd(&sh[C + gi * 8 + j], s2[j] * invstd[gi * 8 + j]);
-    }
+    for (int j = 0; j < 8; ++j) s2[j] *= invstd[gi * 8 + j];
+    block_partial_put(sh, C, r, gi, s1, s2);
     if (m.G < 256) break;
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(&sums[i], double(sh[i]));
+  block_partial_flush(sh, C, m.R, part);
 }
 
 // backward, pass 2: dx = gamma*invstd * (dyh - s1/M - xhat * s2/M), xhat = (x - mean)*invstd.
 // Per-channel fp32 coefficients (c0 = gamma*invstd, k1 = s1/M, k2 = s2/M, mean, invstd) are
 // prepared by a tiny kernel so the streaming pass has no fp64 and only vector loads.
-__global__ void bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ invstd,
-                                   const float* __restrict__ gamma, const double* __restrict__ sums,
-                                   long M, int C, float* __restrict__ coef /* [7][C] */) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+__global__ void __launch_bounds__(256)
+bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ invstd,
+                   const float* __restrict__ gamma, const float* __restrict__ part, int rows,
+                   long M, int C, float* __restrict__ coef /* [7][C] */) {
+  int c;
+  double s1, s2;
+  if (!ordered_row_sums(part, rows, C, &c, &s1, &s2)) return;
   coef[c] = (gamma ? gamma[c] : 1.f) * invstd[c];
-  coef[C + c] = float(sums[c] / double(M));
-  coef[2 * C + c] = float(sums[C + c] / double(M));
+  coef[C + c] = float(s1 / double(M));
+  coef[2 * C + c] = float(s2 / double(M));
   coef[3 * C + c] = mean[c];
   coef[4 * C + c] = invstd[c];
-  coef[5 * C + c] = float(sums[c]);       // dL/dbeta
-  coef[6 * C + c] = float(sums[C + c]);   // dL/dgamma
+  coef[5 * C + c] = float(s1);   // dL/dbeta
+  coef[6 * C + c] = float(s2);   // dL/dgamma
 }
 
 __global__ void __launch_bounds__(256, 4)   // 64 registers (4 bytes of spill): 552 -> 513 us per 453 MB BatchNorm backward
@@ -381,6 +419,13 @@ static void rowgroup_launch(long M, int C, int* grid, int* block) {
   *grid = int(blocks < 1 ? 1 : blocks);
 }
 
+// dynamic shared memory of the reduction kernels: one slot per (row lane, 2C) = at most 16 KB
+static size_t reduce_smem(int C) {
+  const int G = C / 8;
+  const int R = G >= 256 ? 1 : 256 / G;
+  return size_t(R) * 2 * C * sizeof(float);
+}
+
 static int reduce_grid(long M, int C, int* rows_per_block) {
   const int G = C / 8;
   const int R = G >= 256 ? 1 : 256 / G;
@@ -401,23 +446,25 @@ using namespace bgr;
 #define BGR_CHECK_C8(C) \
   if ((C) % 8 || (C) < 8) return fail(BGR_ERR_ARG, "channel count must be a multiple of 8")
 
-extern "C" int bgr_bn_stats(const void* x, long M, int C, int ld, double* sums, void* stream) {
+extern "C" int bgr_bn_stats(const void* x, long M, int C, int ld, float* part, int* rows, void* stream) {
   BGR_CHECK_C8(C);
+  if (reduce_smem(C) > 48 * 1024) return fail(BGR_ERR_ARG, "bn_stats: too many channels");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BGR_CUDA_OK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
   int rpb;
   const int grid = reduce_grid(M, C, &rpb);
-  bn_stats_kernel<<<grid, 256, 2 * C * sizeof(float), st>>>(static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, sums);
+  bn_stats_kernel<<<grid, 256, reduce_smem(C), st>>>(static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, part);
   BGR_LAUNCH_OK();
+  *rows = grid;
   return BGR_OK;
 }
 
-extern "C" int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const float* beta,
+extern "C" int bgr_bn_finalize(const float* part, int rows, long M, int C, const float* gamma, const float* beta,
                                float eps, float momentum, float* mean, float* invstd, float* a, float* b,
                                float* running_mean, float* running_var, long long* num_batches_tracked,
                                void* stream) {
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      sums, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var, num_batches_tracked);
+  if (rows < 1 || rows > BGR_BN_MAX_ROWS) return fail(BGR_ERR_ARG, "bn_finalize: rows out of range");
+  bn_finalize_kernel<<<(C + 31) / 32, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      part, rows, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var, num_batches_tracked);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -443,22 +490,23 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
                             const float* xa, const float* xb,
                             const void* x, int ldx, const float* mean, const float* invstd,
                             const float* gamma, int act, float slope, long M, int C, void* dyh, void* dx,
-                            int ldd, double* sums, float* coef_ws, void* stream) {
+                            int ldd, float* part, float* coef_ws, void* stream) {
   BGR_CHECK_C8(C);
+  if (reduce_smem(C) > 48 * 1024) return fail(BGR_ERR_ARG, "bn_backward: too many channels");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BGR_CUDA_OK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
   int rpb;
   const int grid = reduce_grid(M, C, &rpb);
+  const size_t rsm = reduce_smem(C);
   auto G = static_cast<const __nv_bfloat16*>(g);
   auto G2 = static_cast<const __nv_bfloat16*>(g2);
   auto O = static_cast<const __nv_bfloat16*>(out);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto D = static_cast<__nv_bfloat16*>(dyh);
-  if (act == 2) bn_bwd_reduce_kernel<2><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
-  else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
-  else bn_bwd_reduce_kernel<0><<<grid, 256, 2 * C * sizeof(float), st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, sums);
+  if (act == 2) bn_bwd_reduce_kernel<2><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  else bn_bwd_reduce_kernel<0><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
   BGR_LAUNCH_OK();
-  bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
+  bn_bwd_coef_kernel<<<(C + 31) / 32, 256, 0, st>>>(mean, invstd, gamma, part, grid, M, C, coef_ws);
   BGR_LAUNCH_OK();
   int agrid, ablock;
   rowgroup_launch(M, C, &agrid, &ablock);
@@ -476,9 +524,9 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
 extern "C" int bgr_bn_backward(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
                                const void* x, int ldx, const float* mean, const float* invstd,
                                const float* gamma, int act, float slope, long M, int C, void* dyh, void* dx,
-                               int ldd, double* sums, float* coef_ws, void* stream) {
+                               int ldd, float* part, float* coef_ws, void* stream) {
   return bn_backward_impl(g, ldg, g2, ldg2, out, ldo, nullptr, nullptr, x, ldx, mean, invstd, gamma, act ? 1 : 0, slope, M, C,
-                          dyh, dx, ldd, sums, coef_ws, stream);
+                          dyh, dx, ldd, part, coef_ws, stream);
 }
 
 // Backward of a BatchNorm(+LeakyReLU) whose output was consumed on the fly (bgr_dw_fwd_bn): the
@@ -486,35 +534,17 @@ extern "C" int bgr_bn_backward(const void* g, int ldg, const void* g2, int ldg2,
 extern "C" int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const float* b, const void* x,
                                          int ldx, const float* mean, const float* invstd,
                                          const float* gamma, int act, float slope, long M, int C, void* dyh,
-                                         void* dx, int ldd, double* sums, float* coef_ws, void* stream) {
+                                         void* dx, int ldd, float* part, float* coef_ws, void* stream) {
   return bn_backward_impl(g, ldg, nullptr, 0, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
-                          ldd, sums, coef_ws, stream);
+                          ldd, part, coef_ws, stream);
 }
 
 // The same with a second gradient of the output (a dual-handle block input): both passes add g2 on load.
 extern "C" int bgr_bn_backward_recompute_dual(const void* g, int ldg, const void* g2, int ldg2, const float* a,
                                               const float* b, const void* x, int ldx, const float* mean,
                                               const float* invstd, const float* gamma, int act, float slope, long M,
-                                              int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
+                                              int C, void* dyh, void* dx, int ldd, float* part, float* coef_ws,
                                               void* stream) {
   return bn_backward_impl(g, ldg, g2, ldg2, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
-                          ldd, sums, coef_ws, stream);
-}
-
-// Pass 2 alone, for a pass 1 that ran inside another kernel (bgr_dw_dgrad_bn_reduce): dyh and its
-// fp64 sums are given; writes dx and the coefficient rows (rows 5, 6 = dL/dbeta, dL/dgamma).
-extern "C" int bgr_bn_backward_apply(const void* dyh, const void* x, int ldx, const float* mean, const float* invstd,
-                                     const float* gamma, const double* sums, long M, int C, void* dx, int ldd,
-                                     float* coef_ws, void* stream) {
-  BGR_CHECK_C8(C);
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  bn_bwd_coef_kernel<<<(C + 127) / 128, 128, 0, st>>>(mean, invstd, gamma, sums, M, C, coef_ws);
-  BGR_LAUNCH_OK();
-  int agrid, ablock;
-  rowgroup_launch(M, C, &agrid, &ablock);
-  bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(static_cast<const __nv_bfloat16*>(dyh),
-                                                static_cast<const __nv_bfloat16*>(x), ldx, coef_ws,
-                                                static_cast<__nv_bfloat16*>(dx), ldd, M, C);
-  BGR_LAUNCH_OK();
-  return BGR_OK;
+                          ldd, part, coef_ws, stream);
 }

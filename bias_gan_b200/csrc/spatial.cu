@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256)
 bilinear_bwd_gather_kernel(const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx, const BilGeom g) {
   const int G = g.C >> 3;
   const long total = long(g.N) * g.h * g.w * G;
-  const float ry = 1.f / g.sy, rx = 1.f / g.sx;
+  const float ry = g.sy > 0.f ? 1.f / g.sy : 0.f, rx = g.sx > 0.f ? 1.f / g.sx : 0.f;   // 0: a single source row / column
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += long(gridDim.x) * blockDim.x) {
     const int cg = int(i % G);
@@ -101,8 +101,10 @@ bilinear_bwd_gather_kernel(const __nv_bfloat16* __restrict__ gy, float* __restri
     const int ix = int(r % g.w); r /= g.w;
     const int iy = int(r % g.h);
     const int n = int(r / g.h);
-    const int oy_lo = max(0, int(float(iy - 1) * ry) - 1), oy_hi = min(g.H - 1, int(float(iy + 1) * ry) + 1);
-    const int ox_lo = max(0, int(float(ix - 1) * rx) - 1), ox_hi = min(g.W - 1, int(float(ix + 1) * rx) + 1);
+    const int oy_lo = g.sy > 0.f ? max(0, int(float(iy - 1) * ry) - 1) : 0;
+    const int oy_hi = g.sy > 0.f ? int(fminf(float(g.H - 1), float(iy + 1) * ry + 1.f)) : g.H - 1;
+    const int ox_lo = g.sx > 0.f ? max(0, int(float(ix - 1) * rx) - 1) : 0;
+    const int ox_hi = g.sx > 0.f ? int(fminf(float(g.W - 1), float(ix + 1) * rx + 1.f)) : g.W - 1;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int oy = oy_lo; oy <= oy_hi; ++oy) {
       int y0, y1;
@@ -133,45 +135,13 @@ bilinear_bwd_gather_kernel(const __nv_bfloat16* __restrict__ gy, float* __restri
   }
 }
 
-// adjoint: scatter the output gradient into an fp32 [N,h,w,C] buffer (zeroed by the caller).
-__global__ void __launch_bounds__(256)
-bilinear_bwd_kernel(const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx, const BilGeom g) {
-  const int G = g.C >> 3;
-  const long total = long(g.N) * g.H * g.W * G;
-  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += long(gridDim.x) * blockDim.x) {
-    const int cg = int(i % G);
-    long r = i / G;
-    const int ox = int(r % g.W); r /= g.W;
-    const int oy = int(r % g.H);
-    const int n = int(r / g.H);
-    int y0, y1, x0, x1;
-    float ly, lx;
-    bil_coord(oy, g.sy, g.h, &y0, &y1, &ly);
-    bil_coord(ox, g.sx, g.w, &x0, &x1, &lx);
-    float v[8];
-    sp_unpack8(*reinterpret_cast<const uint4*>(gy + bil_out_index(g, n, oy, ox) + cg * 8), v);
-    float* base = gx + size_t(n) * g.h * g.w * g.C + cg * 8;
-    const float hy = 1.f - ly, hx = 1.f - lx;
-    float* p00 = base + (size_t(y0) * g.w + x0) * g.C;
-    float* p01 = base + (size_t(y0) * g.w + x1) * g.C;
-    float* p10 = base + (size_t(y1) * g.w + x0) * g.C;
-    float* p11 = base + (size_t(y1) * g.w + x1) * g.C;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(p00 + j, hy * hx * v[j]);
-      if (lx != 0.f) atomicAdd(p01 + j, hy * lx * v[j]);
-      if (ly != 0.f) atomicAdd(p10 + j, ly * hx * v[j]);
-      if (lx != 0.f && ly != 0.f) atomicAdd(p11 + j, ly * lx * v[j]);
-    }
-  }
-}
-
 // ---------------------------------------------------------------- global average pool
-// x [N][P][C] (ld) -> out fp32 sums [N][C] (zeroed by caller); caller scales by 1/P.
+// x [N][P][C] (ld) -> partial sums ws[blockIdx.x][N][C]: the pixel lanes of a block are added in lane
+// order through shared memory, the blocks' rows in block order by sum_rows; caller scales by 1/P.
 __global__ void __launch_bounds__(256)
 gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int ld, long P, int C, long pix_per_block,
-               float* __restrict__ out) {
+               float* __restrict__ ws) {
+  extern __shared__ float sh[];   // [R][C]
   const int n = blockIdx.y;
   const int G = C >> 3;
   const int R = G >= 256 ? 1 : 256 / G;
@@ -187,8 +157,15 @@ gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int ld, long P, int C, long 
       for (int j = 0; j < 8; ++j) s[j] += f[j];
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) atomicAdd(out + size_t(n) * C + cg * 8 + j, s[j]);
+    for (int j = 0; j < 8; ++j) sh[size_t(r) * C + cg * 8 + j] = s[j];
     if (G < 256) break;
+  }
+  __syncthreads();
+  float* row = ws + (size_t(blockIdx.x) * gridDim.y + n) * C;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    float t = sh[i];
+    for (int r = 1; r < R; ++r) t += sh[size_t(r) * C + i];
+    row[i] = t;
   }
 }
 
@@ -212,10 +189,11 @@ gap_bwd_kernel(const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ 
 }
 
 // ---------------------------------------------------------------- linear head (K -> 1)
-// logits[n] += sum_i x[n,i] * w[i]     x bf16 [N][K], w bf16 [K]; logits pre-set to the bias.
+// ws[blockIdx.x][n] = this block's share of sum_i x[n,i] * w[i]     x bf16 [N][K], w bf16 [K];
+// sum_rows_block adds the blocks' rows in a fixed order onto the logits (pre-set to the bias).
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w, long K,
-                float* __restrict__ logits) {
+                float* __restrict__ ws) {
   const int n = blockIdx.y;
   const long K8 = K >> 3;
   float acc = 0.f;
@@ -234,7 +212,7 @@ head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   if (threadIdx.x == 0) {
     float t = 0.f;
     for (int i = 0; i < 8; ++i) t += red[i];
-    atomicAdd(logits + n, t);
+    ws[size_t(blockIdx.x) * gridDim.y + n] = t;
   }
 }
 
@@ -270,10 +248,10 @@ head_bwd_kernel(const float* __restrict__ g, const __nv_bfloat16* __restrict__ x
 }
 
 // ---------------------------------------------------------------- fused L1 loss + gradient
-// sum += sum |a - b| (fp64 atomic);  grad = sign(a - b) * gscale (bf16)
+// ws[blockIdx.x] = this block's share of sum |a - b|;  grad = sign(a - b) * gscale (bf16)
 __global__ void __launch_bounds__(256)
 l1_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, long n8,
-                    float gscale, __nv_bfloat16* __restrict__ grad, double* __restrict__ sum) {
+                    float gscale, __nv_bfloat16* __restrict__ grad, float* __restrict__ ws) {
   float acc = 0.f;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += long(gridDim.x) * blockDim.x) {
     float x[8], y[8], o[8];
@@ -295,7 +273,7 @@ l1_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __
   if (threadIdx.x == 0) {
     float t = 0.f;
     for (int i = 0; i < 8; ++i) t += red[i];
-    atomicAdd(sum, double(t));
+    ws[blockIdx.x] = t;
   }
 }
 
@@ -391,31 +369,28 @@ extern "C" int bgr_bilinear_bwd(const void* gy, int N, int h, int w, int C, int 
   BilGeom g;
   if (int rc = make_bil(&g, N, h, w, H, W, C, C, ldy, s2d)) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (g.sy >= 0.05f && g.sx >= 0.05f) {   // up-sampling by < 20x: a few dozen candidates per thread
-    bilinear_bwd_gather_kernel<<<sp_grid(long(N) * h * w * (C / 8)), 256, 0, st>>>(
-        static_cast<const __nv_bfloat16*>(gy), gx, g);
-    BGR_LAUNCH_OK();
-    return BGR_OK;
-  }
-  BGR_CUDA_OK(cudaMemsetAsync(gx, 0, sizeof(float) * size_t(N) * h * w * C, st));
-  bilinear_bwd_kernel<<<sp_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(gy), gx, g);
+  // always the gather form (no atomics, schedule-independent).  Broadcasts of a 1x1 map (the image-pool
+  // branch, deeplab.py:623-624) are summed by the caller with bgr_gap_fwd instead: one thread per source
+  // pixel would walk the whole image.
+  bilinear_bwd_gather_kernel<<<sp_grid(long(N) * h * w * (C / 8)), 256, 0, st>>>(
+      static_cast<const __nv_bfloat16*>(gy), gx, g);
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
-extern "C" int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* out_sums, void* stream) {
+extern "C" int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* out_sums, float* ws, void* stream) {
   if (C % 8) return fail(BGR_ERR_ARG, "gap: channel count must be a multiple of 8");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BGR_CUDA_OK(cudaMemsetAsync(out_sums, 0, sizeof(float) * size_t(N) * C, st));
   const int G = C / 8, R = G >= 256 ? 1 : 256 / G;
   long blocks = (P + long(R) * 4 - 1) / (long(R) * 4);
-  if (blocks > 64) blocks = 64;
+  if (blocks > BGR_GAP_MAX_ROWS) blocks = BGR_GAP_MAX_ROWS;
   if (blocks < 1) blocks = 1;
   const long ppb = (P + blocks - 1) / blocks;
   blocks = (P + ppb - 1) / ppb;
-  gap_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld, P, C, ppb, out_sums);
+  gap_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, size_t(R) * C * sizeof(float), st>>>(
+      static_cast<const __nv_bfloat16*>(x), ld, P, C, ppb, ws);
   BGR_LAUNCH_OK();
-  return BGR_OK;
+  return launch_sum_rows(ws, int(blocks), long(N) * C, out_sums, st);
 }
 
 extern "C" int bgr_gap_bwd(const void* g, int N, long P, int C, void* dx, void* stream) {
@@ -426,14 +401,15 @@ extern "C" int bgr_gap_bwd(const void* g, int N, long P, int C, void* dx, void* 
   return BGR_OK;
 }
 
-extern "C" int bgr_head_fwd(const void* x, const void* w, int N, long K, float* logits, void* stream) {
+extern "C" int bgr_head_fwd(const void* x, const void* w, int N, long K, float* logits, float* ws, void* stream) {
   if (K % 8) return fail(BGR_ERR_ARG, "head: K must be a multiple of 8");
   long blocks = (K / 8 + 255) / 256;
-  if (blocks > 148 * 2) blocks = 148 * 2;
-  head_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, logits);
+  if (blocks > BGR_HEAD_MAX_ROWS) blocks = BGR_HEAD_MAX_ROWS;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  head_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, st>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, ws);
   BGR_LAUNCH_OK();
-  return BGR_OK;
+  return launch_sum_rows_block(ws, int(blocks), N, logits, nullptr, st);
 }
 
 extern "C" int bgr_head_bwd(const float* g, const void* x, const void* w, int N, long K, void* dx, float* dw,
@@ -447,15 +423,15 @@ extern "C" int bgr_head_bwd(const float* g, const void* x, const void* w, int N,
 }
 
 extern "C" int bgr_l1_loss_grad(const void* a, const void* b, long n, float gscale, void* grad, double* sum,
-                                void* stream) {
+                                float* ws, void* stream) {
   if (n % 8) return fail(BGR_ERR_ARG, "l1: element count must be a multiple of 8");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  BGR_CUDA_OK(cudaMemsetAsync(sum, 0, sizeof(double), st));
-  l1_loss_grad_kernel<<<sp_grid(n / 8), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(a),
-                                                      static_cast<const __nv_bfloat16*>(b), n / 8, gscale,
-                                                      static_cast<__nv_bfloat16*>(grad), sum);
+  const int blocks = sp_grid(n / 8);   // <= BGR_LOSS_MAX_ROWS
+  l1_loss_grad_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(a),
+                                              static_cast<const __nv_bfloat16*>(b), n / 8, gscale,
+                                              static_cast<__nv_bfloat16*>(grad), ws);
   BGR_LAUNCH_OK();
-  return BGR_OK;
+  return launch_sum_rows_block(ws, blocks, 1, nullptr, sum, st);
 }
 
 extern "C" int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream) {

@@ -19,11 +19,6 @@ SLOPE = 0.2  # nn.LeakyReLU(0.2) everywhere in the reference (deeplab.py:100,180
 # Under graph capture the fork/join become plain edges: the weight-gradient kernel fills the SMs that
 # the data-gradient kernel leaves idle in its last (partial) round of tiles and during its ramps.
 SIDE_STREAM = os.environ.get("BGR_NO_SIDE_STREAM") is None
-# Pass 1 of the BatchNorm backward inside the depthwise data-gradient march (bgr_dw_dgrad_bn_reduce).
-# Off by default: measured on B200 the step is 128.7 ms with it and 128.2 ms without -- the march is
-# instruction-bound, and the masking + two reductions cost it as much as the separate streaming
-# reduce kernel (34 us at the mid-flow shape) that they replace.
-FUSE_DGRAD_BN_REDUCE = os.environ.get("BGR_DGRAD_BN_FUSION") is not None
 # BatchNorm backward of residual-free layers from (g, y) alone (A/B switch, see _BNAct)
 RECOMPUTE_BN_BWD = os.environ.get("BGR_RECOMPUTE_BN_BWD", "1") != "0"
 _side_streams = {}
@@ -69,16 +64,13 @@ class _Conv(torch.autograd.Function):
         ks = weight.shape[-1]
         dy, dx = K.taps_for(ks, dil)
         ctx.save_for_backward(x, weight)
-        ctx.set_materialize_grads(False)   # no zero-filled fp64 "gradient" for the BatchNorm sums output
+        ctx.set_materialize_grads(False)   # no zero-filled "gradient" for the BatchNorm partial-sums output
         ctx.taps = (dy, dx)
         ctx.has_bias = bias is not None
-        sums = None
-        if want_stats:  # BatchNorm statistics of y from the conv epilogue (no second pass over y)
-            sums = torch.empty(2 * weight.shape[0], dtype=torch.float64, device=x.device)
-        y = K.conv_fprop(x, L.cached(weight, "gemm", L.gemm_weight), dy, dx, bias=bias, bn_sums=sums)
+        # want_stats: BatchNorm statistics of y from the conv epilogue (no second pass over y)
+        y = K.conv_fprop(x, L.cached(weight, "gemm", L.gemm_weight), dy, dx, bias=bias, want_stats=want_stats)
         if want_stats:
-            ctx.mark_non_differentiable(sums)
-            return y, sums
+            ctx.mark_non_differentiable(y[1])
         return y
 
     @staticmethod
@@ -95,13 +87,13 @@ class _Conv(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             gx = K.conv_fprop(g, L.cached(weight, "gemm_t", L.gemm_weight_t), [-v for v in dy], [-v for v in dx])
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = K.bn_stats(g)[: g.shape[-1]].float()
+            gb = K.channel_sums(g)
         _join(g)
         return gx, gw, gb, None, None
 
 
 def conv2d(x, weight, bias=None, dilation=1, want_stats=False):
-    """want_stats=True returns (y, sums) with the fp64 [2*Cout] BatchNorm sums of y."""
+    """want_stats=True returns (y, part) with the fp32 [rows, 2*Cout] partial rows of the BatchNorm sums of y."""
     return _Conv.apply(x, weight, bias, dilation, want_stats)
 
 
@@ -122,13 +114,9 @@ class _ConvS2D(torch.autograd.Function):
         ctx.Cp = Cp = field.shape[-1] // 4
         assert Cp >= weight.shape[1]
         w2 = L.cached(weight, "s2d", lambda w: L.s2d_weight(_pad_cin(w, Cp)).to(torch.bfloat16).contiguous())
-        sums = None
+        y = K.conv_fprop(field, w2, L.S2D_DY, L.S2D_DX, want_stats=want_stats)
         if want_stats:
-            sums = torch.empty(2 * weight.shape[0], dtype=torch.float64, device=field.device)
-        y = K.conv_fprop(field, w2, L.S2D_DY, L.S2D_DX, bn_sums=sums)
-        if want_stats:
-            ctx.mark_non_differentiable(sums)
-            return y, sums
+            ctx.mark_non_differentiable(y[1])
         return y
 
     @staticmethod
@@ -252,12 +240,8 @@ class _BNActDepthwise(torch.autograd.Function):
                 gw = K.dw_wgrad_bn(y, a, b, ctx.act, g, SLOPE).view(C, 1, 3, 3)
         gy = ggamma = gbeta = None
         if ctx.needs_input_grad[0]:
-            if FUSE_DGRAD_BN_REDUCE:
-                dyh, sums = K.dw_dgrad_bn_reduce(g, w9, y, a, b, mean, invstd, ctx.act, SLOPE)
-                gy, bsums = K.bn_backward_apply(dyh, y, mean, invstd, gamma, sums)
-            else:
-                gx = K.dw_dgrad(g, w9, 1, 1, tuple(y.shape))
-                gy, _, bsums = K.bn_backward_recompute(gx, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
+            gx = K.dw_dgrad(g, w9, 1, 1, tuple(y.shape))
+            gy, _, bsums = K.bn_backward_recompute(gx, a, b, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE)
             ggamma = bsums[C:] if ctx.needs_input_grad[2] else None
             gbeta = bsums[:C] if ctx.needs_input_grad[3] else None
         _join(g)
@@ -341,7 +325,10 @@ class _Bilinear(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         shape, H, W, s2d = ctx.cfg
-        return K.bilinear_bwd(_bf16c(g), shape, H, W, s2d=s2d).to(torch.bfloat16), None, None, None
+        g = _bf16c(g)
+        if shape[1] == 1 and shape[2] == 1 and not s2d:   # broadcast of a 1x1 map: the adjoint is the pixel sum
+            return K.gap_fwd(g).to(torch.bfloat16).view(shape), None, None, None
+        return K.bilinear_bwd(g, shape, H, W, s2d=s2d).to(torch.bfloat16), None, None, None
 
 
 def bilinear(x, H, W, s2d=False):

@@ -72,9 +72,24 @@ def _nhwc_view(t):
     return N, H, W, C, ld
 
 
-def conv_fprop(x, w, dy, dx, out=None, bias=None, bn_sums=None):
+BN_MAX_ROWS = 448            # include/bgr.h: capacities of the partial-row workspaces
+DW_WGRAD_WS_FLOATS = 1 << 20
+GAP_MAX_ROWS, HEAD_MAX_ROWS, LOSS_MAX_ROWS = 64, 296, 2368
+_sm_counts = {}
+
+
+def _conv_stat_rows(device):
+    """Upper bound of the partial rows a conv epilogue writes: one per group of thread blocks <= SM count."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _sm_counts:
+        _sm_counts[idx] = min(BN_MAX_ROWS, torch.cuda.get_device_properties(idx).multi_processor_count)
+    return _sm_counts[idx]
+
+
+def conv_fprop(x, w, dy, dx, out=None, bias=None, want_stats=False):
     """y = conv(x, w).  x: [N,H,W,Cin] bf16 NHWC; w: [Cout, ntaps, Cin] bf16; out: [N,H,W,Cout].
-    bn_sums: optional fp64 [2*Cout] filled with the per-channel sum / sum of squares of y."""
+    want_stats=True returns (y, part): part = fp32 [rows, 2*Cout] partial rows of the per-channel sum /
+    sum of squares of y, written by the conv epilogue, for bn_finalize to add in row order."""
     N, H, W, Cin, ldx = _nhwc_view(x)
     Cout, ntaps, wc = w.shape
     ldw = w.stride(1) if ntaps > 1 else w.stride(0)
@@ -86,10 +101,15 @@ def conv_fprop(x, w, dy, dx, out=None, bias=None, bn_sums=None):
     assert (No, Ho, Wo, Co) == (N, H, W, Cout)
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == Cout
-    if bn_sums is not None:
-        assert bn_sums.dtype == torch.float64 and bn_sums.numel() == 2 * Cout and bn_sums.is_contiguous()
+    part, rows = None, ctypes.c_int(0)
+    if want_stats:
+        part = torch.empty((_conv_stat_rows(x.device), 2 * Cout), dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_conv_fprop(ptr(x), N, H, W, Cin, ldx, ptr(w), ldw, Cout, ntaps, int_array(dy),
-                                    int_array(dx), ptr(out), ldy, ptr(bias), ptr(bn_sums), stream_ptr()))
+                                    int_array(dx), ptr(out), ldy, ptr(bias), ptr(part), ctypes.byref(rows),
+                                    stream_ptr()))
+    if want_stats:
+        assert 1 <= rows.value <= part.shape[0]
+        return out, part[:rows.value]
     return out
 
 
@@ -105,16 +125,21 @@ def weight_to_gemm(w, transpose):
 
 
 def conv_wgrad(x, gy, dy, dx, dw=None):
-    """dw[Cout, ntaps, Cin] (fp32) += sum_pixels gy[p, co] * x[p + tap, ci]."""
+    """dw[Cout, ntaps, Cin] (fp32) = sum_pixels gy[p, co] * x[p + tap, ci]  (overwritten; the pixel splits
+    write slabs of a workspace that are added in split order)."""
     N, H, W, Cin, ldx = _nhwc_view(x)
     Ng, Hg, Wg, Cout, ldy = _nhwc_view(gy)
     assert (Ng, Hg, Wg) == (N, H, W)
     ntaps = len(dy)
     if dw is None:
-        dw = torch.zeros((Cout, ntaps, Cin), dtype=torch.float32, device=x.device)
+        dw = torch.empty((Cout, ntaps, Cin), dtype=torch.float32, device=x.device)
     assert dw.is_contiguous() and dw.dtype == torch.float32 and tuple(dw.shape) == (Cout, ntaps, Cin)
-    check(_lib.lib().bgr_conv_wgrad(ptr(x), N, H, W, Cin, ldx, ptr(gy), Cout, ldy, ntaps,
-                                    int_array(dy), int_array(dx), ptr(dw), stream_ptr()))
+    lib = _lib.lib()
+    lib.bgr_conv_wgrad_workspace.restype = ctypes.c_size_t
+    nbytes = int(lib.bgr_conv_wgrad_workspace(N, H, W, Cin, Cout, ntaps))
+    ws = torch.empty(nbytes // 4, dtype=torch.float32, device=x.device) if nbytes else None
+    check(lib.bgr_conv_wgrad(ptr(x), N, H, W, Cin, ldx, ptr(gy), Cout, ldy, ntaps, int_array(dy), int_array(dx),
+                             ptr(dw), ptr(ws), ctypes.c_size_t(nbytes), stream_ptr()))
     return dw
 
 
@@ -192,20 +217,29 @@ def _rows(t):
     return M, C, ld
 
 
-def bn_stats(x, sums=None):
+def bn_stats(x):
+    """fp32 [rows, 2C] partial rows of (sum x | sum x^2) per channel, one row per thread block."""
     M, C, ld = _rows(x)
-    if sums is None:
-        sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
-    check(_lib.lib().bgr_bn_stats(ptr(x), c_long(M), C, ld, ptr(sums), stream_ptr()))
-    return sums
+    part = torch.empty((BN_MAX_ROWS, 2 * C), dtype=torch.float32, device=x.device)
+    rows = ctypes.c_int(0)
+    check(_lib.lib().bgr_bn_stats(ptr(x), c_long(M), C, ld, ptr(part), ctypes.byref(rows), stream_ptr()))
+    return part[:rows.value]
 
 
-def bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var, num_batches_tracked=None):
-    C = sums.numel() // 2
-    dev = sums.device
+def channel_sums(x):
+    """fp32 [C]: sum over pixels of a bf16 [..., C] tensor (partial rows added in row order in fp64)."""
+    C = x.shape[-1]
+    return bn_stats(x)[:, :C].double().sum(0).float()
+
+
+def bn_finalize(part, M, gamma, beta, eps, momentum, running_mean, running_var, num_batches_tracked=None):
+    """part: the [rows, 2C] partial rows of bn_stats or of a conv epilogue (conv_fprop(want_stats=True))."""
+    assert part.dtype == torch.float32 and part.dim() == 2 and part.is_contiguous()
+    rows, C = part.shape[0], part.shape[1] // 2
+    dev = part.device
     mean, invstd, a, b = (torch.empty(C, dtype=torch.float32, device=dev) for _ in range(4))
-    check(_lib.lib().bgr_bn_finalize(ptr(sums), c_long(M), C, ptr(gamma), ptr(beta), c_float(eps), c_float(momentum),
-                                     ptr(mean), ptr(invstd), ptr(a), ptr(b), ptr(running_mean),
+    check(_lib.lib().bgr_bn_finalize(ptr(part), rows, c_long(M), C, ptr(gamma), ptr(beta), c_float(eps),
+                                     c_float(momentum), ptr(mean), ptr(invstd), ptr(a), ptr(b), ptr(running_mean),
                                      ptr(running_var), ptr(num_batches_tracked), stream_ptr()))
     return mean, invstd, a, b
 
@@ -241,7 +275,7 @@ def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2, g2=None):
         assert (Mo, Co) == (M, C)
     dyh = act_empty(x.shape, x.device)
     dx = act_empty(x.shape, x.device)
-    sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+    sums = torch.empty((BN_MAX_ROWS, 2 * C), dtype=torch.float32, device=x.device)   # partial-row workspace
     coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_bn_backward(ptr(g), ldg, ptr(g2), ldg2, ptr(out) if act else ctypes.c_void_p(0), ldo, ptr(x), ldx,
                                      ptr(mean), ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
@@ -277,8 +311,9 @@ def dw_wgrad_bn(x, a, b, act, gy, slope=0.2):
     N, H, W, C, ldx = _nhwc_view(x)
     _, _, _, _, ldy = _nhwc_view(gy)
     dw = torch.empty((C, 9), dtype=torch.float32, device=x.device)   # the parameter's [C,1,3,3] layout
+    ws = torch.empty(DW_WGRAD_WS_FLOATS, dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_dw_wgrad_bn(ptr(x), N, H, W, C, ldx, ptr(a), ptr(b), int(act), c_float(slope), ptr(gy), ldy,
-                                     ptr(dw), stream_ptr()))
+                                     ptr(dw), ptr(ws), stream_ptr()))
     return dw
 
 
@@ -293,7 +328,7 @@ def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2, 
         assert (M2, C2) == (M, C)
         dyh = act_empty(x.shape, x.device) if want_dyh else None
         dx = act_empty(x.shape, x.device)
-        sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+        sums = torch.empty((BN_MAX_ROWS, 2 * C), dtype=torch.float32, device=x.device)
         coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
         check(_lib.lib().bgr_bn_backward_recompute_dual(ptr(g), ldg, ptr(g2), ldg2, ptr(a), ptr(b), ptr(x), ldx, ptr(mean),
                                                         ptr(invstd), ptr(gamma), int(act), c_float(slope), c_long(M), C,
@@ -301,37 +336,12 @@ def bn_backward_recompute(g, a, b, x, mean, invstd, gamma, act=True, slope=0.2, 
         return dx, dyh, coef[5 * C:7 * C]
     dyh = act_empty(x.shape, x.device) if want_dyh else None   # NULL: pass 2 recomputes it from g and x
     dx = act_empty(x.shape, x.device)
-    sums = torch.empty(2 * C, dtype=torch.float64, device=x.device)
+    sums = torch.empty((BN_MAX_ROWS, 2 * C), dtype=torch.float32, device=x.device)   # partial-row workspace
     coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
     check(_lib.lib().bgr_bn_backward_recompute(ptr(g), ldg, ptr(a), ptr(b), ptr(x), ldx, ptr(mean), ptr(invstd),
                                                ptr(gamma), int(act), c_float(slope), c_long(M), C, ptr(dyh), ptr(dx),
                                                _rows(dx)[2], ptr(sums), ptr(coef), stream_ptr()))
     return dx, dyh, coef[5 * C:7 * C]   # fp32 [dL/dbeta | dL/dgamma]
-
-
-def dw_dgrad_bn_reduce(gy, w9, q, a, b, mean, invstd, act, slope=0.2):
-    """(dyh, sums): the stride-1 depthwise data gradient masked by act'(a*q + b), and the fp64
-    BatchNorm-backward sums of it, from one march (see bgr.h)."""
-    N, H, W, C, ldq = _nhwc_view(q)
-    Ng, Hg, Wg, Cg, ldy = _nhwc_view(gy)
-    assert (Ng, Hg, Wg, Cg) == (N, H, W, C)
-    dyh = act_empty(q.shape, q.device)
-    sums = torch.empty(2 * C, dtype=torch.float64, device=q.device)
-    check(_lib.lib().bgr_dw_dgrad_bn_reduce(ptr(gy), N, H, W, C, ldy, ptr(w9), ptr(q), ldq, ptr(a), ptr(b), ptr(mean),
-                                            ptr(invstd), int(act), c_float(slope), ptr(dyh), _nhwc_view(dyh)[4],
-                                            ptr(sums), stream_ptr()))
-    return dyh, sums
-
-
-def bn_backward_apply(dyh, x, mean, invstd, gamma, sums):
-    """Pass 2 of the BatchNorm backward: (dx, fp32 [dL/dbeta | dL/dgamma])."""
-    M, C, ldx = _rows(x)
-    dx = act_empty(x.shape, x.device)
-    assert _rows(dyh)[2] == _rows(dx)[2]
-    coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
-    check(_lib.lib().bgr_bn_backward_apply(ptr(dyh), ptr(x), ldx, ptr(mean), ptr(invstd), ptr(gamma), ptr(sums),
-                                           c_long(M), C, ptr(dx), _rows(dx)[2], ptr(coef), stream_ptr()))
-    return dx, coef[5 * C:7 * C]
 
 
 def dw_dgrad(gy, w9, stride, dil, in_shape):
@@ -347,7 +357,8 @@ def dw_wgrad(x, gy, stride, dil):
     N, H, W, C, ldx = _nhwc_view(x)
     _, _, _, _, ldy = _nhwc_view(gy)
     dw = torch.empty((C, 9), dtype=torch.float32, device=x.device)   # the parameter's [C,1,3,3] layout
-    check(_lib.lib().bgr_dw_wgrad(ptr(x), N, H, W, C, ldx, ptr(gy), ldy, stride, dil, ptr(dw), stream_ptr()))
+    ws = torch.empty(DW_WGRAD_WS_FLOATS, dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_dw_wgrad(ptr(x), N, H, W, C, ldx, ptr(gy), ldy, stride, dil, ptr(dw), ptr(ws), stream_ptr()))
     return dw
 
 
@@ -388,7 +399,8 @@ def bilinear_bwd(gy, in_shape, H, W, s2d=False):
 def gap_fwd(x):
     N, H, W, C, ld = _nhwc_view(x)
     sums = torch.empty((N, C), dtype=torch.float32, device=x.device)
-    check(_lib.lib().bgr_gap_fwd(ptr(x), N, c_long(H * W), C, ld, ptr(sums), stream_ptr()))
+    ws = torch.empty((GAP_MAX_ROWS, N, C), dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_gap_fwd(ptr(x), N, c_long(H * W), C, ld, ptr(sums), ptr(ws), stream_ptr()))
     return sums
 
 
@@ -404,7 +416,8 @@ def head_fwd(x, w, logits):
     N = x.shape[0]
     K = x.numel() // N
     assert x.is_contiguous() and w.is_contiguous() and w.numel() == K and logits.dtype == torch.float32
-    check(_lib.lib().bgr_head_fwd(ptr(x), ptr(w), N, c_long(K), ptr(logits), stream_ptr()))
+    ws = torch.empty((HEAD_MAX_ROWS, N), dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_head_fwd(ptr(x), ptr(w), N, c_long(K), ptr(logits), ptr(ws), stream_ptr()))
     return logits
 
 
@@ -423,7 +436,9 @@ def l1_loss_grad(a, b, gscale, need_grad=True):
     assert a.shape == b.shape and a.is_contiguous() and b.is_contiguous() and a.dtype == b.dtype == torch.bfloat16
     s = torch.empty((), dtype=torch.float64, device=a.device)
     grad = torch.empty(a.shape, dtype=torch.bfloat16, device=a.device) if need_grad else None
-    check(_lib.lib().bgr_l1_loss_grad(ptr(a), ptr(b), c_long(a.numel()), c_float(gscale), ptr(grad), ptr(s), stream_ptr()))
+    ws = torch.empty(LOSS_MAX_ROWS, dtype=torch.float32, device=a.device)
+    check(_lib.lib().bgr_l1_loss_grad(ptr(a), ptr(b), c_long(a.numel()), c_float(gscale), ptr(grad), ptr(s), ptr(ws),
+                                      stream_ptr()))
     return s, grad
 
 

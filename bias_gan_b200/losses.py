@@ -28,6 +28,19 @@ class GANLoss:
         else:
             raise NotImplementedError("Error, {} loss not implemented".format(mode))
         self._static = None   # (label_for_fake, label_for_real) device buffers once draw_labels() is used
+        self._copied = None   # CUDA event: the last host->device copy out of the pinned staging buffers
+
+    def _staging_free(self):
+        """The pinned staging buffers are rewritten every step: wait until the previous step's asynchronous
+        host->device copies have read them (a host running ahead of graph replays would otherwise hand
+        step i the labels of step i+1)."""
+        if self._copied is not None:
+            self._copied.synchronize()
+
+    def _staging_used(self):
+        if torch.cuda.is_available() and torch.device(self.device).type == "cuda":
+            self._copied = torch.cuda.Event()
+            self._copied.record()
 
     def draw_labels(self):
         """Draw this step's noisy labels and the 5 % swap on the CPU generator — the same three
@@ -40,8 +53,10 @@ class GANLoss:
                 pin = torch.cuda.is_available() and torch.device(self.device).type == "cuda"
                 self._eta_host = torch.empty(eta.shape, pin_memory=pin)
                 self._eta = torch.empty(eta.shape, device=self.device)
+            self._staging_free()
             self._eta_host.copy_(eta)
             self._eta.copy_(self._eta_host, non_blocking=True)
+            self._staging_used()
             return
         label_fake = self.dist_fake.rsample(self.label_fake.shape)
         label_real = self.dist_real.rsample(self.label_real.shape)
@@ -51,9 +66,11 @@ class GANLoss:
             pin = torch.cuda.is_available() and torch.device(self.device).type == "cuda"
             self._host = tuple(torch.empty(self.label_fake.shape, pin_memory=pin) for _ in range(2))
             self._static = tuple(torch.empty_like(self.label_fake) for _ in range(2))
+        self._staging_free()
         for host, dev, val in zip(self._host, self._static, (label_fake, label_real)):
             host.copy_(val)
             dev.copy_(host, non_blocking=True)
+        self._staging_used()
 
     def d_loss(self, logits_real, logits_fake):
         if self.mode == "Wasserstein":

@@ -130,6 +130,19 @@ class numpy_reader(object):
         dev = torch.device("cpu") if self._device < 0 else torch.device("cuda", self._device)
         if out is None:
             out = torch.empty_strided(shape, strides, dtype=_DTYPES[i["dtype"]], device=dev)
+        else:
+            # the C side writes numel * itemsize * n bytes unconditionally: a wrong-sized / wrong-typed
+            # destination (or a file whose shape differs from the parsed one) must fail here, not overrun
+            need = 1
+            for v in shape:
+                need *= v
+            if out.dtype != _DTYPES[i["dtype"]]:
+                raise ValueError("numpy_reader: out has dtype %s, the file holds %s" % (out.dtype, _DTYPES[i["dtype"]]))
+            if out.device != dev and not (out.device.type == dev.type == "cuda" and (out.device.index or 0) == dev.index):
+                raise ValueError("numpy_reader: out lives on %s, the reader delivers to %s" % (out.device, dev))
+            if not out.is_contiguous() or out.numel() < need:
+                raise ValueError("numpy_reader: out must be contiguous with at least %d elements (has %d)"
+                                 % (need, out.numel()))
         arr = (ctypes.c_int64 * n)(*[int(v) for v in ids])
         stream = ctypes.c_void_p(0)
         if self._device >= 0:

@@ -7,14 +7,33 @@ SURVEY F8) and the G phase does not compute D's weight gradients (zeroed by the 
 d_opt.zero_grad()).  Parameters, BN running statistics, losses and RNG draw order after the step
 are identical to the reference-faithful schedule (`lean=False`).
 """
-import torch
-
+import contextlib
 import os
+
+import torch
 
 from . import layouts as L
 
 # one bgr_weights_prepare launch per network and phase instead of per-layer weight copies (A/B switch)
 PACK_WEIGHTS = os.environ.get("BGR_PACK_WEIGHTS", "1") != "0"
+
+
+@contextlib.contextmanager
+def _sync_only(stepped, other):
+    """The backward pass of `stepped`'s update: its gradient buckets start clean, and `other`'s hooks stay
+    silent (the reference schedule back-propagates d_loss into G and g_loss into D; those gradients are
+    discarded, so they must neither be all-reduced nor leave bucket state behind)."""
+    so, oo = getattr(stepped, "grad_sync", None), getattr(other, "grad_sync", None)
+    if so is not None:
+        so.start()
+    was = oo.enabled if oo is not None else None
+    if oo is not None:
+        oo.enabled = False
+    try:
+        yield
+    finally:
+        if oo is not None:
+            oo.enabled = was
 
 
 def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_reg=1.0, w_gp=10.0, lean=True,
@@ -38,7 +57,8 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
             from .deeplab_gan import gradient_penalty
             d_loss = d_loss + w_gp * gradient_penalty(D, fake, real, eta=crit_gan.static_eta())
         d_opt.zero_grad(set_to_none=True)
-        d_loss.backward()
+        with _sync_only(D, G):
+            d_loss.backward()
         if hasattr(D, "grad_sync"):
             D.grad_sync.finish()
         d_opt.step()
@@ -57,7 +77,8 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
             reg_loss = crit_reg(fake, real)
             g_loss = reg_loss if warmup else w_gan * gan_loss + w_reg * reg_loss
             g_opt.zero_grad(set_to_none=True)
-            g_loss.backward()
+            with _sync_only(G, D):
+                g_loss.backward()
         finally:
             if lean:
                 for p in D.parameters():

@@ -36,6 +36,16 @@ extern "C" {
 #define BGR_NCHW 0
 #define BGR_NHWC 1
 
+/* Reductions across thread blocks never use floating-point atomics: a kernel writes one partial row per
+ * block (or split) into a caller-provided workspace and the rows are added in index order, so every
+ * result of this library is independent of block scheduling (bit-identical from run to run).  Workspace
+ * capacities the caller must provide: */
+#define BGR_BN_MAX_ROWS 448            /* BatchNorm partial rows: fp32 [BGR_BN_MAX_ROWS][2*C] */
+#define BGR_DW_WGRAD_WS_FLOATS (1 << 20) /* depthwise weight-gradient partial rows (fp32 elements) */
+#define BGR_GAP_MAX_ROWS 64            /* global-average-pool partial rows: fp32 [64][N][C] */
+#define BGR_HEAD_MAX_ROWS 296          /* linear-head partial rows: fp32 [296][N] */
+#define BGR_LOSS_MAX_ROWS 2368         /* loss partial rows: fp32 [2368] */
+
 const char* bgr_last_error(void);
 int bgr_version(void);
 /* number of CUDA kernels this library has launched in this process */
@@ -105,12 +115,13 @@ int bgr_channel_stats(const void* src, int src_dtype, int src_layout, int B, int
  * stride-1 conv over fields stored as 2x2 space-to-depth blocks (see bgr_stage_normalize). */
 int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const void* w, int ldw,
                    int Cout, int ntaps, const int* dy, const int* dx, void* y, int ldy,
-                   const float* bias, double* bn_sums, void* stream);
+                   const float* bias, float* bn_part, int* bn_rows, void* stream);
 /* ldw: elements between consecutive (cout, tap) rows of w (>= Cin, multiple of 8).  TMA moves whole
  * 128-byte lines: keep ldx, ldy and ldw multiples of 64 elements where the channel count is not
  * (728 -> 768) so that no pixel row straddles a line — measured 1.65x on the 728-channel layers. */
-/* bn_sums (optional, NULL to skip; excludes bias): fp64 [2*Cout], zeroed inside and filled by the
- * conv epilogue with sum_m y and sum_m y^2 of the bf16-rounded outputs — the statistics pass of
+/* bn_part (optional, NULL to skip; excludes bias): fp32 [BGR_BN_MAX_ROWS][2*Cout] workspace; the conv
+ * epilogue writes *bn_rows (HOST int) partial rows of [sum_m y | sum_m y^2] of the bf16-rounded outputs,
+ * one per group of thread blocks, for bgr_bn_finalize to add in row order — the statistics pass of
  * the nn.BatchNorm2d that follows every such conv in the reference (deeplab.py:179,183,334,...)
  * without re-reading y (same contract as bgr_bn_stats). */
 
@@ -120,20 +131,26 @@ int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const v
 int bgr_weight_to_gemm(const float* w, int Cout, int Cin, int taps, int transpose, void* out, int pitch,
                        void* stream);
 
-/* dw[co,t,ci] += sum_{n,h,w} dy_[n,h,w,co] * x[n, h+dy[t], w+dx[t], ci]   (fp32, accumulated:
- * zero dw first).  Same views as bgr_conv_fprop. */
+/* dw[co,t,ci] = sum_{n,h,w} dy_[n,h,w,co] * x[n, h+dy[t], w+dx[t], ci]   (fp32, overwritten).
+ * Same views as bgr_conv_fprop.  The pixel reduction is split over thread blocks; each split writes its
+ * own slab of `ws` (device, 16-byte aligned, at least bgr_conv_wgrad_workspace(...) bytes — 0 when one
+ * split suffices and ws may be NULL) and the slabs are added in split order. */
+size_t bgr_conv_wgrad_workspace(int N, int H, int W, int Cin, int Cout, int ntaps);
 int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx, const void* dy_, int Cout,
-                   int ldy, int ntaps, const int* dy, const int* dx, float* dw, void* stream);
+                   int ldy, int ntaps, const int* dy, const int* dx, float* dw, float* ws, size_t ws_bytes,
+                   void* stream);
 
 /* ---- BatchNorm (training mode) + LeakyReLU + residual (deeplab.py:100,141,179-183,334-338) --
  * Tensors are bf16 [M pixels][C] with pixel strides ld*; C multiple of 8. */
 
-/* sums[0..C) = sum_m x, sums[C..2C) = sum_m x^2 (fp64, zeroed inside). */
-int bgr_bn_stats(const void* x, long M, int C, int ld, double* sums, void* stream);
-/* mean, invstd = 1/sqrt(var_biased+eps), a = gamma*invstd, b = beta - mean*a; running stats
+/* part: fp32 [BGR_BN_MAX_ROWS][2*C] workspace; writes *rows (HOST int) partial rows of
+ * [sum_m x | sum_m x^2], one per thread block. */
+int bgr_bn_stats(const void* x, long M, int C, int ld, float* part, int* rows, void* stream);
+/* The `rows` partial rows of `part` are added in row order in fp64, then:
+ * mean, invstd = 1/sqrt(var_biased+eps), a = gamma*invstd, b = beta - mean*a; running stats
  * updated with `momentum` and the unbiased variance (nn.BatchNorm2d semantics); gamma/beta/
  * running_* may be NULL; num_batches_tracked (device int64, may be NULL) is incremented by one. */
-int bgr_bn_finalize(const double* sums, long M, int C, const float* gamma, const float* beta, float eps,
+int bgr_bn_finalize(const float* part, int rows, long M, int C, const float* gamma, const float* beta, float eps,
                     float momentum, float* mean, float* invstd, float* a, float* b,
                     float* running_mean, float* running_var, long long* num_batches_tracked, void* stream);
 /* out = act(a*x + b [+ res]); act != 0: LeakyReLU(slope). */
@@ -142,13 +159,13 @@ int bgr_bn_apply(const void* x, int ldx, const float* a, const float* b, const v
 /* Backward of bgr_bn_apply o batch statistics.  g: dL/dout; g2 (optional, NULL): a second gradient
  * of the same output, added on load (the block input feeds both the separable convs and the skip /
  * residual path, deeplab.py:137-141); dyh ([M][C], pixel stride ldd) receives
- * g*act'(out), which is also dL/dres; dx (same stride) receives dL/dx; sums (fp64 [2][C]) receives
- * dL/dbeta = sum dyh and dL/dgamma = sum dyh*xhat; coef_ws: fp32 [7][C] workspace whose rows 5 and 6
- * return dL/dbeta and dL/dgamma in fp32. */
+ * g*act'(out), which is also dL/dres; dx (same stride) receives dL/dx; part: fp32
+ * [BGR_BN_MAX_ROWS][2*C] workspace for the per-block partial rows of sum dyh and sum dyh*xhat (added in
+ * row order); coef_ws: fp32 [7][C] workspace whose rows 5 and 6 return dL/dbeta and dL/dgamma. */
 int bgr_bn_backward(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
                     const void* x, int ldx,
                     const float* mean, const float* invstd, const float* gamma, int act, float slope,
-                    long M, int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
+                    long M, int C, void* dyh, void* dx, int ldd, float* part, float* coef_ws,
                     void* stream);
 
 /* Same, for a BatchNorm(+LeakyReLU) whose activated output was never stored because the depthwise
@@ -157,7 +174,7 @@ int bgr_bn_backward(const void* g, int ldg, const void* g2, int ldg2, const void
  * writing and pass 2 re-reading it -- one tensor pass less in each. */
 int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const float* b, const void* x, int ldx,
                               const float* mean, const float* invstd, const float* gamma, int act,
-                              float slope, long M, int C, void* dyh, void* dx, int ldd, double* sums,
+                              float slope, long M, int C, void* dyh, void* dx, int ldd, float* part,
                               float* coef_ws, void* stream);
 
 /* bgr_bn_backward_recompute with a second gradient g2 of the same output (NULL = none), added on load by
@@ -166,24 +183,8 @@ int bgr_bn_backward_recompute(const void* g, int ldg, const float* a, const floa
 int bgr_bn_backward_recompute_dual(const void* g, int ldg, const void* g2, int ldg2, const float* a,
                                    const float* b, const void* x, int ldx, const float* mean,
                                    const float* invstd, const float* gamma, int act, float slope, long M,
-                                   int C, void* dyh, void* dx, int ldd, double* sums, float* coef_ws,
+                                   int C, void* dyh, void* dx, int ldd, float* part, float* coef_ws,
                                    void* stream);
-
-/* Data gradient of a stride-1 depthwise 3x3 conv fused with pass 1 of the backward of the
- * BatchNorm(+LeakyReLU) that produced its input on the fly (bgr_dw_fwd_bn): writes
- * dyh = act'(a*q + b) * dgrad(dy) (bf16, pixel stride ldd) and sums = fp64 [sum dyh | sum dyh*xhat].
- * Replaces, for those layers, bgr_dw_dgrad followed by pass 1 of bgr_bn_backward_recompute
- * (reference: autograd of deeplab.py:66-79 SeparableConv2d_same + nn.BatchNorm2d). */
-int bgr_dw_dgrad_bn_reduce(const void* dy, int N, int H, int W, int C, int ldy, const float* w9,
-                           const void* q, int ldq, const float* a, const float* b, const float* mean,
-                           const float* invstd, int act, float slope, void* dyh, int ldd, double* sums,
-                           void* stream);
-
-/* Pass 2 of the BatchNorm backward from given dyh and sums: dx = gamma*invstd*(dyh - s1/M - xhat*s2/M);
- * coef_ws = fp32 [7][C] workspace, rows 5 and 6 return dL/dbeta and dL/dgamma. */
-int bgr_bn_backward_apply(const void* dyh, const void* x, int ldx, const float* mean, const float* invstd,
-                          const float* gamma, const double* sums, long M, int C, void* dx, int ldd,
-                          float* coef_ws, void* stream);
 
 /* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
  * w: fp32 [9][C] (tap-major); dw: fp32 [C][9] (the parameter's own [C,1,3,3] layout).  Output size ceil(H/stride) x ceil(W/stride). */
@@ -191,8 +192,9 @@ int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* 
                void* y, int ldy, void* stream);
 int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy, const float* w, int stride, int dil,
                  void* dx, int ldx, void* stream);
+/* dw is overwritten; ws: fp32 workspace of BGR_DW_WGRAD_WS_FLOATS elements for the per-block partial rows. */
 int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, const void* dy, int ldy, int stride,
-                 int dil, float* dw, void* stream);
+                 int dil, float* dw, float* ws, void* stream);
 /* Stride-1 dilation-1 depthwise conv of act(a[c]*x + b[c]) (act: 0 affine, 1 LeakyReLU(slope)) with
  * the transform applied on load and zero padding applied after it: BatchNorm2d (+LeakyReLU) followed
  * by SeparableConv2d_same.conv1 (deeplab.py:100-118,75-87) without storing the activated tensor;
@@ -200,7 +202,7 @@ int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, const void*
 int bgr_dw_fwd_bn(const void* x, int N, int H, int W, int C, int ldx, const float* w, const float* a,
                   const float* b, int act, float slope, void* y, int ldy, void* stream);
 int bgr_dw_wgrad_bn(const void* x, int N, int H, int W, int C, int ldx, const float* a, const float* b,
-                    int act, float slope, const void* dy, int ldy, float* dw, void* stream);
+                    int act, float slope, const void* dy, int ldy, float* dw, float* ws, void* stream);
 /* y[n,oy,ox,:] = x[n,2oy,2ox,:] (input of the stride-2 1x1 skip convs, deeplab.py:95) + adjoint. */
 int bgr_subsample2(const void* x, int N, int H, int W, int C, int ldx, void* y, int ldy, void* stream);
 int bgr_subsample2_bwd(const void* dy, int N, int H, int W, int C, int ldy, void* dx, int ldx, void* stream);
@@ -210,22 +212,23 @@ int bgr_subsample2_bwd(const void* dy, int N, int H, int W, int C, int ldy, void
  * [N,H,W,C] (pixel stride ldy) or, s2d != 0, the field layout [N,H/2,W/2,4C]. */
 int bgr_bilinear_fwd(const void* x, int N, int h, int w, int C, int ldx, void* y, int H, int W, int ldy,
                      int s2d, void* stream);
-/* adjoint: gx fp32 dense [N,h,w,C] (zeroed inside) += scatter of gy. */
+/* adjoint, gather form (no atomics): gx fp32 dense [N,h,w,C] is overwritten. */
 int bgr_bilinear_bwd(const void* gy, int N, int h, int w, int C, int H, int W, int ldy, int s2d, float* gx,
                      void* stream);
-/* nn.AdaptiveAvgPool2d(1) (deeplab.py:621): out_sums fp32 [N][C] = sum over P pixels (zeroed
- * inside; caller scales by 1/P).  bwd: dx[n,p,:] = g[n,:]/P (g bf16 [N][C], dx dense). */
-int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* out_sums, void* stream);
+/* nn.AdaptiveAvgPool2d(1) (deeplab.py:621): out_sums fp32 [N][C] = sum over P pixels (caller scales
+ * by 1/P); ws: fp32 [BGR_GAP_MAX_ROWS][N][C].  bwd: dx[n,p,:] = g[n,:]/P (g bf16 [N][C], dx dense). */
+int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* out_sums, float* ws, void* stream);
 int bgr_gap_bwd(const void* g, int N, long P, int C, void* dx, void* stream);
 /* flatten + nn.Linear(K,1) (deeplab_gan.py:32-36): logits[n] += x[n,:].w (logits pre-set to
- * the bias); bwd: dx[n,:] = g[n]*w (NULL to skip), dw = sum_n g[n]*x[n,:] (NULL to skip). */
-int bgr_head_fwd(const void* x, const void* w, int N, long K, float* logits, void* stream);
+ * the bias; ws: fp32 [BGR_HEAD_MAX_ROWS][N]); bwd: dx[n,:] = g[n]*w (NULL to skip),
+ * dw = sum_n g[n]*x[n,:] (NULL to skip). */
+int bgr_head_fwd(const void* x, const void* w, int N, long K, float* logits, float* ws, void* stream);
 int bgr_head_bwd(const float* g, const void* x, const void* w, int N, long K, void* dx, float* dw,
                  void* stream);
-/* nn.L1Loss (train_gan.py:146,281) fused with its gradient: *sum = sum|a-b| (fp64, zeroed
- * inside), grad = sign(a-b)*gscale (bf16, NULL to skip). */
+/* nn.L1Loss (train_gan.py:146,281) fused with its gradient: *sum = sum|a-b| (fp64),
+ * grad = sign(a-b)*gscale (bf16, NULL to skip); ws: fp32 [BGR_LOSS_MAX_ROWS]. */
 int bgr_l1_loss_grad(const void* a, const void* b, long n, float gscale, void* grad, double* sum,
-                     void* stream);
+                     float* ws, void* stream);
 /* field layout (bf16 [N,H/2,W/2,(py,px,c)]) <-> fp32 NCHW, the tensors the training script sees. */
 int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream);
 int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W, void* stream);

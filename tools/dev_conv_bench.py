@@ -61,10 +61,10 @@ for (N, H, W, Cin, Cout, ks, dil) in SHAPES:
     for bn in bns:
         _lib.lib().bgr_debug_conv_block_n(bn)
         t1 = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y))
-        t2 = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y, bn_sums=sums))
+        t2 = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y, want_stats=True))
         if os.environ.get("BGR_DBG"):
             _lib.lib().bgr_debug_conv_mode(int(os.environ["BGR_DBG"]))
-            t2b = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y, bn_sums=sums))
+            t2b = timeit(lambda: K.conv_fprop(x, w, dy, dx, out=y, want_stats=True))
             _lib.lib().bgr_debug_conv_mode(0)
             line += "(dbg %.1f us) " % t2b
         t3 = timeit(lambda: K.conv_fprop(gy, wt, dy, dx, out=gx))
