@@ -7,6 +7,7 @@
 // schedule-independent: per-thread fp32 partials -> one shared-memory slot per (row lane, channel),
 // added in lane order -> one partial row per block in a workspace [rows][2C] -> the finalize /
 // coefficient kernels add the rows in index order in fp64.  No floating-point atomics anywhere.
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 #include "bgr_internal.h"
@@ -86,19 +87,33 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long M, int C, int ld, int 
   block_partial_flush(sh, C, m.R, part);
 }
 
-// Ordered fp64 sum of the partial rows of 32 channels: 8 row lanes (warps) x 32 channels; lane w adds
-// rows w, w+8, ...; the eight lane sums are added in lane order.  Returns true in the threads (warp 0)
-// that hold the result for a valid channel c.
+// Ordered fp64 sum of the partial rows of kRsCh channels: kRsLanes row lanes x kRsCh channels per block;
+// lane w adds rows w, w+kRsLanes, ... (four loads in flight, added in row order); the lane sums are added
+// in lane order.  Returns true in the threads (lane 0) that hold the result for a valid channel c.
+constexpr int kRsCh = 16, kRsLanes = 16;   // 256 threads; grid = ceil(C / 16): 46 blocks at C = 728
 __device__ __forceinline__ bool ordered_row_sums(const float* __restrict__ part, int rows, int C, int* c_out,
                                                  double* s_out, double* q_out) {
-  __shared__ double shd[8][2][32];
-  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
-  const int c = blockIdx.x * 32 + cl;
+  __shared__ double shd[kRsLanes][2][kRsCh];
+  const int cl = threadIdx.x % kRsCh, rl = threadIdx.x / kRsCh;
+  const int c = blockIdx.x * kRsCh + cl;
   double s = 0.0, q = 0.0;
   if (c < C) {
-    for (int r = rl; r < rows; r += 8) {
-      s += double(part[size_t(r) * 2 * C + c]);
-      q += double(part[size_t(r) * 2 * C + C + c]);
+    const float* p = part + c;
+    const size_t st = size_t(2) * C;
+    int r = rl;
+    for (; r + 3 * kRsLanes < rows; r += 4 * kRsLanes) {
+      const float a0 = p[size_t(r) * st], b0 = p[size_t(r) * st + C];
+      const float a1 = p[size_t(r + kRsLanes) * st], b1 = p[size_t(r + kRsLanes) * st + C];
+      const float a2 = p[size_t(r + 2 * kRsLanes) * st], b2 = p[size_t(r + 2 * kRsLanes) * st + C];
+      const float a3 = p[size_t(r + 3 * kRsLanes) * st], b3 = p[size_t(r + 3 * kRsLanes) * st + C];
+      s += double(a0); q += double(b0);
+      s += double(a1); q += double(b1);
+      s += double(a2); q += double(b2);
+      s += double(a3); q += double(b3);
+    }
+    for (; r < rows; r += kRsLanes) {
+      s += double(p[size_t(r) * st]);
+      q += double(p[size_t(r) * st + C]);
     }
   }
   shd[rl][0][cl] = s;
@@ -106,13 +121,13 @@ __device__ __forceinline__ bool ordered_row_sums(const float* __restrict__ part,
   __syncthreads();
   if (rl != 0 || c >= C) return false;
 #pragma unroll
-  for (int w = 1; w < 8; ++w) { s += shd[w][0][cl]; q += shd[w][1][cl]; }
+  for (int w = 1; w < kRsLanes; ++w) { s += shd[w][0][cl]; q += shd[w][1][cl]; }
   *c_out = c; *s_out = s; *q_out = q;
   return true;
 }
 
 // mean / invstd / fused affine (a, b) / running statistics (momentum, unbiased variance) from the
-// partial rows of the statistics pass (bn_stats_kernel or the conv epilogue).  grid = ceil(C/32) x 256.
+// partial rows of the statistics pass (bn_stats_kernel or the conv epilogue).  grid = ceil(C/16) x 256.
 __global__ void __launch_bounds__(256)
 bn_finalize_kernel(const float* __restrict__ part, int rows, long M, int C,
                    const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -409,13 +424,19 @@ bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, co
   }
 }
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
 // grid / block of the (channel group, rows) streaming kernels
 static void rowgroup_launch(long M, int C, int* grid, int* block) {
+  static const int min_rows = env_int("BGR_EW_ROWS", 4), cap = env_int("BGR_EW_CAP", 16);   // tuning knobs
   const int G = C / 8;
   const int R = G >= 256 ? 1 : 256 / G;
   *block = G >= 256 ? 256 : G * R;
-  long blocks = (M + long(R) * 4 - 1) / (long(R) * 4);   // >= 4 rows per thread
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  long blocks = (M + long(R) * min_rows - 1) / (long(R) * min_rows);   // >= min_rows rows per thread
+  if (blocks > long(sm_count()) * cap) blocks = long(sm_count()) * cap;
   *grid = int(blocks < 1 ? 1 : blocks);
 }
 
@@ -432,7 +453,9 @@ static int reduce_grid(long M, int C, int* rows_per_block) {
   long blocks = (M + long(R) * 8 - 1) / (long(R) * 8);  // >= 8 row iterations per thread
   // three CTAs per SM (the register limit) for narrow tensors; two for wide ones, where every extra
   // block costs 2*C fp64 global atomics and the tensors are small anyway
-  const long cap = C <= 256 ? 148 * 3 : 148 * 2;   // one wave at three resident blocks per SM
+  static const int bps_wide = env_int("BGR_RED_BPS_WIDE", 2);   // tuning knob
+  long cap = C <= 256 ? 148 * 3 : 148 * bps_wide;   // one wave at three resident blocks per SM
+  if (cap > BGR_BN_MAX_ROWS) cap = BGR_BN_MAX_ROWS;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   *rows_per_block = int((M + blocks - 1) / blocks);
@@ -463,7 +486,7 @@ extern "C" int bgr_bn_finalize(const float* part, int rows, long M, int C, const
                                float* running_mean, float* running_var, long long* num_batches_tracked,
                                void* stream) {
   if (rows < 1 || rows > BGR_BN_MAX_ROWS) return fail(BGR_ERR_ARG, "bn_finalize: rows out of range");
-  bn_finalize_kernel<<<(C + 31) / 32, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  bn_finalize_kernel<<<(C + kRsCh - 1) / kRsCh, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       part, rows, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var, num_batches_tracked);
   BGR_LAUNCH_OK();
   return BGR_OK;
@@ -506,7 +529,7 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
   else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
   else bn_bwd_reduce_kernel<0><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
   BGR_LAUNCH_OK();
-  bn_bwd_coef_kernel<<<(C + 31) / 32, 256, 0, st>>>(mean, invstd, gamma, part, grid, M, C, coef_ws);
+  bn_bwd_coef_kernel<<<(C + kRsCh - 1) / kRsCh, 256, 0, st>>>(mean, invstd, gamma, part, grid, M, C, coef_ws);
   BGR_LAUNCH_OK();
   int agrid, ablock;
   rowgroup_launch(M, C, &agrid, &ablock);

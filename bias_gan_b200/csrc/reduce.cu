@@ -11,19 +11,21 @@
 namespace bgr {
 
 // out[i] = sum_{r < rows} ws[r * n + i]   (thread per output, rows in order, coalesced across i)
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 sum_rows_kernel(const float* __restrict__ ws, int rows, long n4, float4* __restrict__ out) {
   const long i = long(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   const float4* p = reinterpret_cast<const float4*>(ws) + i;
   float4 acc = p[0];
   int r = 1;
-  for (; r + 1 < rows; r += 2) {   // two loads in flight, added in row order
-    const float4 a = p[long(r) * n4], b = p[long(r + 1) * n4];
+  for (; r + 3 < rows; r += 4) {   // four loads in flight, added in row order
+    const float4 a = p[long(r) * n4], b = p[long(r + 1) * n4], c = p[long(r + 2) * n4], d = p[long(r + 3) * n4];
     acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
     acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+    acc.x += c.x; acc.y += c.y; acc.z += c.z; acc.w += c.w;
+    acc.x += d.x; acc.y += d.y; acc.z += d.z; acc.w += d.w;
   }
-  if (r < rows) {
+  for (; r < rows; ++r) {
     const float4 a = p[long(r) * n4];
     acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
   }
@@ -65,7 +67,7 @@ int launch_sum_rows(const float* ws, int rows, long n, float* out, cudaStream_t 
   if (rows < 1 || n < 1) return fail(BGR_ERR_ARG, "sum_rows: empty reduction");
   if ((n % 4) == 0 && ((uintptr_t(ws) | uintptr_t(out)) & 15) == 0) {
     const long n4 = n / 4;
-    sum_rows_kernel<<<unsigned((n4 + 255) / 256), 256, 0, st>>>(ws, rows, n4, reinterpret_cast<float4*>(out));
+    sum_rows_kernel<<<unsigned((n4 + 127) / 128), 128, 0, st>>>(ws, rows, n4, reinterpret_cast<float4*>(out));
   } else {
     sum_rows_scalar_kernel<<<unsigned((n + 255) / 256), 256, 0, st>>>(ws, rows, n, out);
   }

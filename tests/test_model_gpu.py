@@ -7,14 +7,15 @@ from their fp32 run by ~0.13 rel-L2 at the generator output for these weights (r
 grows ~0.1 %/block through the 20 Xception blocks and is amplified by the decoder).  The bar is
 therefore *relative to that noise floor*, measured in the same test on the same GPU:
 
-    dev(product, fp32 oracle)  <=  1.5 * dev(oracle under bf16 autocast, fp32 oracle) + eps
+    dev(product, fp32 oracle)  <=  1.25 * dev(oracle under bf16 autocast, fp32 oracle) + eps
 
-(1.5: product and autocast oracle are each one draw of amplified rounding noise, and the product's own
-run-to-run spread from fp32-atomic ordering is a few per cent of these deviations; per block the
-product is closer to fp32 than autocast, tools/dev_model_debug.py)
-
-for the generator output, logits, losses and concatenated per-parameter gradients, plus hard
-caps that catch semantic errors (early-trunk activations within 2e-2, gradient cosine >= 0.9).
+for the generator output, losses and concatenated per-parameter gradients (product and autocast oracle
+are each one draw of amplified rounding noise; per block the product is closer to fp32 than autocast,
+tools/dev_model_debug.py), plus hard caps that catch semantic errors (early-trunk activations within
+2e-2, gradient cosines).  The product is run-to-run deterministic (no floating-point atomics,
+tests/test_determinism_gpu.py), so every bound below is a fixed number checked against a reproducible
+value -- no band is derived from a run-to-run spread.  The same checks at the BASELINE shape
+(16 x 768 x 1152) are in tests/test_fullsize_gpu.py.
 """
 import os
 
@@ -87,13 +88,15 @@ def test_generator_forward_backward(setup):
     lr_.backward(); lp_.backward()
     out_a, g_a = _autocast_generator(s)
     floor_out = rel(out_a, out_r)
-    assert rel(out_p, out_r) <= 1.5 * floor_out + 1e-3
-    assert abs(float(lp_) - float(lr_)) <= 2e-2 * abs(float(lr_))
     g_p, g_r = _flat_grads(s["Gp"]), _flat_grads(s["Gr"])
+    print("PARITY G fwd/bwd: out rel product %.4f autocast %.4f | grad rel %.4f / %.4f cos %.4f / %.4f"
+          % (rel(out_p, out_r), floor_out, rel(g_p, g_r), rel(g_a, g_r), cos(g_p, g_r), cos(g_a, g_r)))
+    assert rel(out_p, out_r) <= 1.25 * floor_out + 1e-3
+    assert abs(float(lp_) - float(lr_)) <= 2e-2 * abs(float(lr_))
     # the trunk gradient of G is noisy for *any* bf16 arithmetic (at 64x96 autocast only reaches
     # cosine ~0.4 against fp32, ~0.85 at this size): the bar is the autocast floor plus hard caps.
-    assert rel(g_p, g_r) <= 1.5 * rel(g_a, g_r) + 1e-3
-    assert (1 - cos(g_p, g_r)) <= 1.5 * (1 - cos(g_a, g_r)) + 1e-4
+    assert rel(g_p, g_r) <= 1.25 * rel(g_a, g_r) + 1e-3
+    assert (1 - cos(g_p, g_r)) <= 1.25 * (1 - cos(g_a, g_r)) + 1e-4
     assert cos(g_p, g_r) >= 0.8
     dec_p = torch.cat([p.grad.flatten().double() for n, p in s["Gp"].named_parameters() if n.startswith("model.upsample")])
     dec_r = torch.cat([p.grad.flatten().double() for n, p in s["Gr"].named_parameters() if n.startswith("model.upsample")])
@@ -133,6 +136,10 @@ def test_early_trunk_is_tight(setup):
     assert rel(got["block3"], want["block3"]) <= 2e-2
 
 
+# four logits = four draws of amplified rounding noise; product and autocast are single samples of it
+D_LOGIT_FLOOR_FACTOR = 2.5
+
+
 def test_discriminator_forward_backward(setup):
     s = setup
     tgt = torch.tensor([[0.9], [0.1], [0.85], [0.05]], device=s["dev"])[:B]
@@ -146,11 +153,19 @@ def test_discriminator_forward_backward(setup):
     # 12288-term dot product; product and autocast oracle are each ONE sample of that distribution
     # (per block the product is closer to fp32 than autocast, tools/dev_model_debug.py), so the
     # logit bound is a factor 2.5 of the floor; the gradient bounds below stay at 1.25.
-    assert rel(lo_p, lo_r) <= 2.5 * rel(lo_a, lo_r) + 1e-2
-    assert rel(pr_p, pr_r) <= 2.5 * rel(torch.sigmoid(lo_a), pr_r) + 1e-2
     g_p, g_r = _flat_grads(s["Dp"]), _flat_grads(s["Dr"])
-    assert rel(g_p, g_r) <= 1.5 * rel(g_a, g_r) + 1e-3
-    assert cos(g_p, g_r) >= 0.9 and (1 - cos(g_p, g_r)) <= 2.0 * (1 - cos(g_a, g_r)) + 1e-4
+    print("PARITY D fwd/bwd: logits rel product %.4f autocast %.4f | grad rel %.4f / %.4f cos %.4f / %.4f"
+          % (rel(lo_p, lo_r), rel(lo_a, lo_r), rel(g_p, g_r), rel(g_a, g_r), cos(g_p, g_r), cos(g_a, g_r)))
+    assert rel(lo_p, lo_r) <= D_LOGIT_FLOOR_FACTOR * rel(lo_a, lo_r) + 1e-2
+    assert rel(pr_p, pr_r) <= D_LOGIT_FLOOR_FACTOR * rel(torch.sigmoid(lo_a), pr_r) + 1e-2
+    assert rel(g_p, g_r) <= 1.25 * rel(g_a, g_r) + 1e-3
+    assert cos(g_p, g_r) >= 0.9 and (1 - cos(g_p, g_r)) <= 1.25 * (1 - cos(g_a, g_r)) + 1e-4
+
+
+# |loss - fp32 oracle| / |oracle| of one full G+D step at 256x384, batch 4 (d_loss, g_loss): fixed bounds with
+# head-room over the measured, reproducible values (the PARITY line of this test); the bf16-autocast run of
+# the oracle deviates by the amounts printed beside them
+STEP_LOSS_BOUNDS = (0.15, 0.15)
 
 
 def test_gan_step_matches_oracle_step(setup):
@@ -177,17 +192,19 @@ def test_gan_step_matches_oracle_step(setup):
     with torch.autocast("cuda", dtype=torch.bfloat16):
         dl_a, gl_a, _ = R.gan_step_ref(Ga, Da, opt(Ga), opt(Da), R.GANLossRef("ModifiedMinMax", B, s["dev"]),
                                        s["x"], s["y"].clone())
-    # (the product's own run-to-run spread from fp32-atomic ordering, amplified by the train-mode
-    # trunk, is several per cent of the adversarial losses: see test_graphed_step_matches_eager)
-    assert abs(float(dl_p) - float(dl_r)) <= 3.0 * abs(float(dl_a) - float(dl_r)) + 0.15 * abs(float(dl_r))
-    assert abs(float(gl_p) - float(gl_r)) <= 3.0 * abs(float(gl_a) - float(gl_r)) + 0.15 * abs(float(gl_r))
+    print("PARITY gan_step: d_loss product %.5f autocast %.5f fp32 %.5f | g_loss %.5f / %.5f / %.5f"
+          % (float(dl_p), float(dl_a), float(dl_r), float(gl_p), float(gl_a), float(gl_r)))
+    assert abs(float(dl_p) - float(dl_r)) <= STEP_LOSS_BOUNDS[0] * abs(float(dl_r))
+    assert abs(float(gl_p) - float(gl_r)) <= STEP_LOSS_BOUNDS[1] * abs(float(gl_r))
+    worst = {True: 0.0, False: 0.0}
     for prod, ref, start, check_dir in ((Gp, Gr, s["Gp"], False), (Dp, Dr, s["Dp"], True)):
         if check_dir:  # AdamW's first step is sign-like: compare update directions (D only; the
             # adversarial gradient reaching G through D's input is chaotic in bf16 at test size)
             dp = torch.cat([(p - q).flatten().double() for p, q in zip(prod.parameters(), start.parameters())])
             dr = torch.cat([(p - q).flatten().double() for p, q in zip(ref.parameters(), start.parameters())])
             da = torch.cat([(p - q).flatten().double() for p, q in zip(Da.parameters(), start.parameters())])
-            assert cos(dp, dr) >= 0.85 * cos(da, dr) - 0.03  # as close to fp32 as the bf16-autocast step
+            print("PARITY gan_step: D update direction cos product %.4f autocast %.4f" % (cos(dp, dr), cos(da, dr)))
+            assert cos(dp, dr) >= 0.9 * cos(da, dr)  # as close to fp32 as the bf16-autocast step
         sp, sr = prod.state_dict(), ref.state_dict()
         for k in sp:
             if k.endswith("running_mean") or k.endswith("running_var"):
@@ -195,19 +212,18 @@ def test_gan_step_matches_oracle_step(setup):
                 # everything upstream in their batch statistics (looser, still catches a missing or
                 # doubled momentum update, which changes these vectors by >= 2x)
                 early = any("xception_features." + t in k for t in ("bn1.", "bn2.", "block1.", "block2.", "block3."))
+                worst[early] = max(worst[early], rel(sp[k], sr[k]))
                 assert rel(sp[k], sr[k]) <= (0.1 if early else 0.4), k
             if k.endswith("num_batches_tracked"):
                 assert int(sp[k]) == int(sr[k]), k
+    print("PARITY gan_step: worst BN running-stat rel deviation early %.4f deep %.4f" % (worst[True], worst[False]))
 
 
 def test_graphed_step_matches_eager():
     """step.GraphedGanStep (one CUDA-graph replay per step, labels pre-drawn on the host, cached GEMM
-    weight copies) against the kernel-by-kernel gan_step from the same state.  The 70-layer train-mode
-    network amplifies the last-bit run-to-run differences of fp32 atomics (BatchNorm sums, wgrad) to
-    ~10 % at the losses of this tiny configuration, so: (1) quantities upstream of the amplification
-    (entry-layer BatchNorm running statistics after the step's three D and two G forwards) must agree
-    tightly, (2) the losses must agree within the measured eager run-to-run spread, (3) constructing
-    the graphed step must not advance training, (4) replays must update parameters and Adam state."""
+    weight copies) against the kernel-by-kernel gan_step from the same state: (1) bit-identical losses,
+    parameters and BatchNorm statistics (no atomics: scheduling cannot change a sum), (2) constructing
+    the graphed step must not advance training, (3) replays update parameters and Adam state."""
     import copy
     dev = torch.device("cuda", 0)
     from bias_gan_b200 import kernels as K
@@ -225,15 +241,9 @@ def test_graphed_step_matches_eager():
         D = seed_state(Discriminator(C, input_size=(H, W)), 22).to(dev).train()
         return G, D, opt(G), opt(D)
 
-    def eager():
-        G0, D0, go0, do0 = build()
-        torch.manual_seed(5)
-        dl, gl = gan_step(G0, D0, go0, do0, GANLoss("ModifiedMinMax", B, dev), L1LossField(), xf, yf)
-        return G0, D0, (float(dl), float(gl))
-
-    runs = [eager() for _ in range(5)]   # the range of five draws: three were too few (flaked 1 run in 5)
-    G0, D0, ref = runs[0]
-    spread = [max(abs(r[2][i] - q[2][i]) for r in runs for q in runs) for i in range(2)]
+    G0, D0, go0, do0 = build()
+    torch.manual_seed(5)
+    ref = gan_step(G0, D0, go0, do0, GANLoss("ModifiedMinMax", B, dev), L1LossField(), xf, yf)
     G1, D1, go1, do1 = build()
     before = copy.deepcopy(G1.state_dict())
     torch.manual_seed(5)
@@ -241,16 +251,11 @@ def test_graphed_step_matches_eager():
     for k, v in G1.state_dict().items():
         assert torch.equal(v, before[k]), "constructing the graphed step changed " + k
     assert all(int(st["step"]) == 0 for st in go1.state.values())
-    got = tuple(float(t) for t in gs(xf, yf))
-    for i in range(2):
-        assert abs(got[i] - ref[i]) <= max(4 * spread[i], 3e-2 * abs(ref[i])), (ref, spread, got)
-    # G's entry layers see only the inputs (tight); D's also see the generator's output twice (loose)
-    for m0, m1, rt, at in ((G0.model.xception_features, G1.model.xception_features, 2e-3, 2e-4),
-                           (D0.xception_features, D1.xception_features, 5e-2, 5e-3)):
-        for bn in ("bn1", "bn2"):
-            for stat in ("running_mean", "running_var"):
-                torch.testing.assert_close(getattr(getattr(m1, bn), stat), getattr(getattr(m0, bn), stat), rtol=rt, atol=at)
-            assert int(getattr(m1, bn).num_batches_tracked) == int(getattr(m0, bn).num_batches_tracked)
+    got = gs(xf, yf)
+    assert torch.equal(got[0], ref[0]) and torch.equal(got[1], ref[1]), ([float(t) for t in ref], [float(t) for t in got])
+    for m0, m1 in ((G0, G1), (D0, D1)):
+        for (k, a), b in zip(m0.state_dict().items(), m1.state_dict().values()):
+            assert torch.equal(a, b), k
     assert all(int(st["step"]) == 1 for st in go1.state.values()) and all(int(st["step"]) == 1 for st in do1.state.values())
     moved = max(float((p - before[n]).abs().max()) for n, p in G1.named_parameters())
     assert 5e-5 < moved <= 1.5e-4, moved   # one AdamW step at lr 1e-4

@@ -142,11 +142,9 @@ def test_graphed_step_with_noise_draw_order():
     assert torch.equal(torch.get_rng_state(), rng_eager)
     assert len(G1._noise_slots) == 2
     assert torch.equal(G1._noise_slots[0].dev.cpu(), z1) and torch.equal(G1._noise_slots[1].dev.cpu(), z2)
-    # losses: sanity only -- at this tiny size the train-mode 70-layer net amplifies fp32-atomic ordering
-    # to 10-20 % run to run (test_model_gpu.test_graphed_step_matches_eager measures that spread); the
-    # exact checks are the RNG state and the slot contents above
-    for a, b in ((dl0, dl1), (gl0, gl1)):
-        assert abs(float(a) - float(b)) <= 0.5 * abs(float(a)) + 5e-2, (float(a), float(b))
+    # same state, same labels, same noise planes and no atomics anywhere: the replayed graph reproduces the
+    # kernel-by-kernel step bit for bit
+    assert torch.equal(dl0, dl1) and torch.equal(gl0, gl1), (float(dl0), float(dl1), float(gl0), float(gl1))
     dl2, gl2 = gs(xf, yf)
     assert not torch.equal(G1._noise_slots[0].dev.cpu(), z1)    # fresh noise every replay
     assert all(torch.isfinite(t) for t in (dl2, gl2))

@@ -45,6 +45,11 @@ def test_gradient_penalty_matches_oracle():
     torch.testing.assert_close(Dp.xception_features.bn1.running_mean, Dr.xception_features.bn1.running_mean, rtol=2e-2, atol=2e-3)
 
 
+# relative deviation of (d_loss, g_loss) of one Wasserstein step from the fp32 oracle; measured values on B200
+# (deterministic): see the PARITY line this test prints
+WGAN_STEP_BOUNDS = (0.6, 0.6)
+
+
 def test_wasserstein_step_eager_and_graphed():
     P, R, dev, fake, real, mk = _setup()
     from bias_gan_b200 import kernels as K
@@ -71,7 +76,7 @@ def test_wasserstein_step_eager_and_graphed():
     torch.manual_seed(17)
     dl_r, gl_r, _ = R.gan_step_ref(Gr, Dr, gor, dor, R.GANLossRef("Wasserstein", b, dev), x, y)
     rng = torch.get_rng_state()
-    G0, D0, go0, do0 = build(P, False)
+    G0, D0, go0, do0 = build(P, True)
     torch.manual_seed(17)
     dl0, gl0 = gan_step(G0, D0, go0, do0, GANLoss("Wasserstein", b, dev), L1LossField(), xf, yf)
     assert torch.equal(torch.get_rng_state(), rng)
@@ -83,12 +88,15 @@ def test_wasserstein_step_eager_and_graphed():
     torch.manual_seed(17)
     dl1, gl1 = gs(xf, yf)
     assert torch.equal(torch.get_rng_state(), rng)
-    # tiny-configuration noise (see test_graphed_step_matches_eager): d_loss here is 10 x the gradient penalty,
-    # a mean of (||grad|| - 1)^2 over 2 x 64 x 96 pixels behind a 70-layer train-mode net -- the product's own
-    # run-to-run spread is 8.1 ... 13.6 against the oracle's 13.6 (one run in four left a 35 % band), so only
-    # the scale is held here; the value itself is held at 256x384 in test_gradient_penalty_matches_oracle
-    for got in ((dl0, gl0), (dl1, gl1)):
-        assert 0.3 <= float(got[0]) / float(dl_r) <= 3.0, (float(got[0]), float(dl_r))
-        assert abs(float(got[1]) - float(gl_r)) <= 0.5 * abs(float(gl_r)) + 0.5, (float(got[1]), float(gl_r))
+    # the product is deterministic: graph replay == kernel-by-kernel step, bit for bit
+    assert torch.equal(dl0, dl1) and torch.equal(gl0, gl1), (float(dl0), float(dl1), float(gl0), float(gl1))
+    # against the fp32 oracle.  d_loss here is 10 x the gradient penalty, a mean of (||grad|| - 1)^2 over
+    # 2 x 64 x 96 pixels behind a 70-layer train-mode net in bf16: the bound is the measured, reproducible
+    # value with head-room (WGAN_STEP_BOUNDS); the penalty itself is held against its autocast floor at
+    # 256x384 in test_gradient_penalty_matches_oracle
+    print("PARITY wgan step: d_loss product %.4f oracle %.4f   g_loss product %.4f oracle %.4f"
+          % (float(dl0), float(dl_r), float(gl0), float(gl_r)))
+    assert abs(float(dl0) - float(dl_r)) <= WGAN_STEP_BOUNDS[0] * abs(float(dl_r)), (float(dl0), float(dl_r))
+    assert abs(float(gl0) - float(gl_r)) <= WGAN_STEP_BOUNDS[1] * abs(float(gl_r)), (float(gl0), float(gl_r))
     dl2, gl2 = gs(xf, yf)
     assert all(torch.isfinite(t) for t in (dl2, gl2))
