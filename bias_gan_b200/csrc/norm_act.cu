@@ -451,9 +451,9 @@ static int reduce_grid(long M, int C, int* rows_per_block) {
   const int G = C / 8;
   const int R = G >= 256 ? 1 : 256 / G;
   long blocks = (M + long(R) * 8 - 1) / (long(R) * 8);  // >= 8 row iterations per thread
-  // three CTAs per SM (the register limit) for narrow tensors; two for wide ones, where every extra
-  // block costs 2*C fp64 global atomics and the tensors are small anyway
-  static const int bps_wide = env_int("BGR_RED_BPS_WIDE", 2);   // tuning knob
+  // three CTAs per SM (the register limit): one wave.  (Wide tensors used two while every block cost 2*C fp64
+  // atomics; with partial rows three measure 3-8 % faster at the mid-flow shape, profiles/r02_knob_sweep.txt)
+  static const int bps_wide = env_int("BGR_RED_BPS_WIDE", 3);   // tuning knob
   long cap = C <= 256 ? 148 * 3 : 148 * bps_wide;   // one wave at three resident blocks per SM
   if (cap > BGR_BN_MAX_ROWS) cap = BGR_BN_MAX_ROWS;
   if (blocks > cap) blocks = cap;
@@ -570,4 +570,60 @@ extern "C" int bgr_bn_backward_recompute_dual(const void* g, int ldg, const void
                                               void* stream) {
   return bn_backward_impl(g, ldg, g2, ldg2, nullptr, 0, a, b, x, ldx, mean, invstd, gamma, act ? 2 : 0, slope, M, C, dyh, dx,
                           ldd, part, coef_ws, stream);
+}
+
+// ---------------------------------------------------------------- frozen statistics (eval mode / Identity)
+// dx[m][c] = s[c] * d[m][c]
+__global__ void __launch_bounds__(256)
+scale_rows_kernel(const __nv_bfloat16* __restrict__ d, int ldd, const float* __restrict__ sc,
+                  __nv_bfloat16* __restrict__ dx, int ldx, long M, int C) {
+  const int G = C >> 3;
+  const long total = M * G;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
+    const int g = int(i % G);
+    const long row = i / G;
+    float f[8], sv[8];
+    unpack8(*reinterpret_cast<const uint4*>(d + row * ldd + g * 8), f);
+    load8f(sc + g * 8, sv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= sv[j];
+    *reinterpret_cast<uint4*>(dx + row * ldx + g * 8) = pack8(f);
+  }
+}
+
+// Backward of out = act(a*x + b [+ res]) whose a, b do NOT depend on the batch: nn.BatchNorm2d in eval mode
+// (running statistics; train_gan.py:330-398 validation, freeze_bn) or an Identity normaliser
+// (--disable_batchnorm, train_gan.py:125).  mean / invstd = the frozen statistics (NULL: 0 / 1), gamma may be
+// NULL (1).  dyh = (g [+ g2]) * act'(out) is also dL/dres; dx = gamma*invstd*dyh (dx may alias nothing; NULL
+// when gamma*invstd == 1, then dyh is dL/dx); coef_ws rows 5, 6 = dL/dbeta, dL/dgamma.
+extern "C" int bgr_bn_backward_frozen(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
+                                      const void* x, int ldx, const float* mean, const float* invstd,
+                                      const float* gamma, int act, float slope, long M, int C, void* dyh, void* dx,
+                                      int ldd, float* part, float* coef_ws, void* stream) {
+  BGR_CHECK_C8(C);
+  if (reduce_smem(C) > 48 * 1024) return fail(BGR_ERR_ARG, "bn_backward_frozen: too many channels");
+  if (dyh == nullptr) return fail(BGR_ERR_ARG, "bn_backward_frozen: dyh is required");
+  if (mean == nullptr || invstd == nullptr) return fail(BGR_ERR_ARG, "bn_backward_frozen: mean / invstd vectors are required");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int rpb;
+  const int grid = reduce_grid(M, C, &rpb);
+  const size_t rsm = reduce_smem(C);
+  auto G = static_cast<const __nv_bfloat16*>(g);
+  auto G2 = static_cast<const __nv_bfloat16*>(g2);
+  auto O = static_cast<const __nv_bfloat16*>(out);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto D = static_cast<__nv_bfloat16*>(dyh);
+  if (act) bn_bwd_reduce_kernel<1><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  else bn_bwd_reduce_kernel<0><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  BGR_LAUNCH_OK();
+  bn_bwd_coef_kernel<<<(C + kRsCh - 1) / kRsCh, 256, 0, st>>>(mean, invstd, gamma, part, grid, M, C, coef_ws);
+  BGR_LAUNCH_OK();
+  if (dx != nullptr) {
+    long blocks = (M * (C / 8) + 255) / 256;
+    if (blocks > long(sm_count()) * 16) blocks = long(sm_count()) * 16;
+    scale_rows_kernel<<<int(blocks < 1 ? 1 : blocks), 256, 0, st>>>(D, ldd, coef_ws /* row 0 = gamma*invstd */,
+                                                                    static_cast<__nv_bfloat16*>(dx), ldd, M, C);
+    BGR_LAUNCH_OK();
+  }
+  return BGR_OK;
 }

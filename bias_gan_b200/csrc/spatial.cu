@@ -277,6 +277,56 @@ l1_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __
   }
 }
 
+// Regression losses of the script's flag surface (train_gan.py:141-152,278-281; utils/losses.py:101-112) in one
+// kernel: MODE 0 = L1 |d|, 1 = SmoothL1 (beta), 2 = MSE d^2; optional per-element weights (the masks of
+// --enable_masks, L1LossWeighted): loss = sum w * l(d), grad = w * l'(d) * gscale [* *gscale_dev].
+// ws[blockIdx.x] = this block's share of the sum.
+template <int MODE, bool WEIGHTED>
+__global__ void __launch_bounds__(256)
+reg_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                     const __nv_bfloat16* __restrict__ w, long n8, float gscale, const float* __restrict__ gscale_dev,
+                     float beta, __nv_bfloat16* __restrict__ grad, float* __restrict__ ws) {
+  float acc = 0.f;
+  const float gs = gscale_dev ? gscale * __ldg(gscale_dev) : gscale;
+  const float inv_beta = beta > 0.f ? 1.f / beta : 0.f;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += long(gridDim.x) * blockDim.x) {
+    float x[8], y[8], wt[8], o[8];
+    sp_unpack8(*reinterpret_cast<const uint4*>(a + i * 8), x);
+    sp_unpack8(*reinterpret_cast<const uint4*>(b + i * 8), y);
+    if (WEIGHTED) sp_unpack8(*reinterpret_cast<const uint4*>(w + i * 8), wt);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = x[j] - y[j], ad = fabsf(d);
+      float l, g;
+      if (MODE == 0) {
+        l = ad;
+        g = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+      } else if (MODE == 1) {   // nn.SmoothL1Loss: 0.5 d^2 / beta below beta, |d| - 0.5 beta above
+        const bool quad = ad < beta;
+        l = quad ? 0.5f * d * d * inv_beta : ad - 0.5f * beta;
+        g = quad ? d * inv_beta : (d > 0.f ? 1.f : -1.f);
+      } else {
+        l = d * d;
+        g = 2.f * d;
+      }
+      if (WEIGHTED) { l *= wt[j]; g *= wt[j]; }
+      acc += l;
+      o[j] = g * gs;
+    }
+    if (grad) *reinterpret_cast<uint4*>(grad + i * 8) = sp_pack8(o);
+  }
+  __shared__ float red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    ws[blockIdx.x] = t;
+  }
+}
+
 // ---------------------------------------------------------------- field layout conversions
 // field = bf16 [N, H/2, W/2, (py, px, c)];  nchw = fp32 [N, C, H, W]
 template <bool TO_NCHW>
@@ -430,6 +480,28 @@ extern "C" int bgr_l1_loss_grad(const void* a, const void* b, long n, float gsca
   l1_loss_grad_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(a),
                                               static_cast<const __nv_bfloat16*>(b), n / 8, gscale,
                                               static_cast<__nv_bfloat16*>(grad), ws);
+  BGR_LAUNCH_OK();
+  return launch_sum_rows_block(ws, blocks, 1, nullptr, sum, st);
+}
+
+extern "C" int bgr_reg_loss_grad(const void* a, const void* b, const void* w, long n, int mode, float beta, float gscale,
+                                 const float* gscale_dev, void* grad, double* sum, float* ws, void* stream) {
+  if (n % 8) return fail(BGR_ERR_ARG, "reg_loss: element count must be a multiple of 8");
+  if (mode < 0 || mode > 2) return fail(BGR_ERR_ARG, "reg_loss: mode must be 0 (L1), 1 (SmoothL1) or 2 (MSE)");
+  if (mode == 1 && !(beta > 0.f)) return fail(BGR_ERR_ARG, "reg_loss: SmoothL1 needs beta > 0");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int blocks = sp_grid(n / 8);   // <= BGR_LOSS_MAX_ROWS
+  auto A = static_cast<const __nv_bfloat16*>(a);
+  auto B = static_cast<const __nv_bfloat16*>(b);
+  auto W = static_cast<const __nv_bfloat16*>(w);
+  auto G = static_cast<__nv_bfloat16*>(grad);
+#define BGR_REG_LAUNCH(M)                                                                                     \
+  if (W) reg_loss_grad_kernel<M, true><<<blocks, 256, 0, st>>>(A, B, W, n / 8, gscale, gscale_dev, beta, G, ws); \
+  else reg_loss_grad_kernel<M, false><<<blocks, 256, 0, st>>>(A, B, W, n / 8, gscale, gscale_dev, beta, G, ws)
+  if (mode == 0) { BGR_REG_LAUNCH(0); }
+  else if (mode == 1) { BGR_REG_LAUNCH(1); }
+  else { BGR_REG_LAUNCH(2); }
+#undef BGR_REG_LAUNCH
   BGR_LAUNCH_OK();
   return launch_sum_rows_block(ws, blocks, 1, nullptr, sum, st);
 }

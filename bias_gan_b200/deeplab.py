@@ -26,6 +26,18 @@ def _hold_conv(cin, cout, k, groups=1, bias=False):
     return nn.Conv2d(cin, cout, k, groups=groups, bias=bias)
 
 
+class _Act(nn.Identity):
+    """Place holder of the reference's nn.LeakyReLU(0.2, inplace=True) modules inside nn.Sequential containers:
+    it keeps the `rep.N` / `last_conv.N` indices of the state-dict keys; the activation itself is fused into the
+    neighbouring kernel.  A class of its own so that an Identity *normaliser* (--disable_batchnorm,
+    train_gan.py:125) in the same container is not mistaken for it."""
+
+
+def _is_norm(m):
+    """BatchNorm2d or the Identity normaliser (anything the `normalizer` argument built), not an activation slot."""
+    return F_.is_batchnorm(m) or (isinstance(m, nn.Identity) and not isinstance(m, _Act))
+
+
 class SeparableConv2d_same(nn.Module):
     """fixed_padding + depthwise 3x3 + pointwise 1x1 (deeplab.py:75-87)."""
 
@@ -55,17 +67,17 @@ class Block(nn.Module):
             self.skipbn = normalizer(planes)
         else:
             self.skip = None
-        self.relu = nn.Identity()
+        self.relu = _Act()
         self.stride = stride
         rep = []
         filters = inplanes
         if grow_first:
-            rep += [nn.Identity(), SeparableConv2d_same(inplanes, planes, 3, 1, dilation), normalizer(planes)]
+            rep += [_Act(), SeparableConv2d_same(inplanes, planes, 3, 1, dilation), normalizer(planes)]
             filters = planes
         for _ in range(reps - 1):
-            rep += [nn.Identity(), SeparableConv2d_same(filters, filters, 3, 1, dilation), normalizer(filters)]
+            rep += [_Act(), SeparableConv2d_same(filters, filters, 3, 1, dilation), normalizer(filters)]
         if not grow_first:
-            rep += [nn.Identity(), SeparableConv2d_same(inplanes, planes, 3, 1, dilation), normalizer(planes)]
+            rep += [_Act(), SeparableConv2d_same(inplanes, planes, 3, 1, dilation), normalizer(planes)]
         if not start_with_relu:
             rep = rep[1:]
         if stride != 1:
@@ -88,12 +100,12 @@ class Block(nn.Module):
         while i < len(mods):
             m = mods[i]
             if isinstance(m, SeparableConv2d_same):
-                has_bn = i + 1 < len(mods) and isinstance(mods[i + 1], nn.BatchNorm2d)
-                want = has_bn and mods[i + 1].training
+                has_bn = i + 1 < len(mods) and _is_norm(mods[i + 1])
+                want = has_bn and F_.needs_stats(mods[i + 1])
                 if pending is not None:
                     py, pbn, pact = pending
                     pending = None
-                    if m.stride == 1 and m.dilation == 1 and pbn.training and FUSE_BN_INTO_DEPTHWISE:
+                    if m.stride == 1 and m.dilation == 1 and F_.needs_stats(pbn) and FUSE_BN_INTO_DEPTHWISE:
                         # BatchNorm (+LeakyReLU) applied while the depthwise kernel loads: never stored
                         t = F_.bn_act_depthwise(py, pbn, m.conv1.weight, act=pact)
                         y = F_.conv2d(t, m.pointwise.weight, want_stats=want)
@@ -104,7 +116,7 @@ class Block(nn.Module):
                 if has_bn:
                     bn = mods[i + 1]
                     i += 2
-                    act = i < len(mods) and isinstance(mods[i], nn.Identity)  # the (identity-held) relu
+                    act = i < len(mods) and isinstance(mods[i], _Act)  # the (place-held) relu
                     if act:
                         i += 1
                     pending = (y, bn, act)
@@ -115,7 +127,7 @@ class Block(nn.Module):
             tail_bn = pending  # last rep element is a BN: fuse with the residual add
         if self.skip is not None:
             s_in = F_.subsample2(a_side) if self.stride == 2 else a_side
-            s = F_.conv2d(s_in, self.skip.weight, want_stats=self.skipbn.training)
+            s = F_.conv2d(s_in, self.skip.weight, want_stats=F_.needs_stats(self.skipbn))
             if tail_bn is not None:
                 x = F_.bn_act(tail_bn[0], tail_bn[1], act=False)
             return F_.bn_act(s, self.skipbn, res=x, act=act_out, dual=dual_out)
@@ -139,7 +151,7 @@ class Xception(nn.Module):
         self.inplanes = inplanes
         self.conv1 = nn.Conv2d(inplanes, 128, 3, stride=2, padding=1, bias=False)
         self.bn1 = normalizer(128)
-        self.relu = nn.Identity()
+        self.relu = _Act()
         self.conv2 = nn.Conv2d(128, 128, 3, stride=1, padding=1, bias=False)
         self.bn2 = normalizer(128)
         self.block1 = Block(128, 128, reps=2, stride=2, start_with_relu=False, normalizer=normalizer)
@@ -169,8 +181,8 @@ class Xception(nn.Module):
         """field: bf16 [N, H/2, W/2, 4*inplanes] (2x2 space-to-depth).  Returns (features
         [N,H/16,W/16,2048], low_level [N,H/4,W/4,128]) — both activated, as the reference's
         in-place LeakyReLUs leave them."""
-        x = F_.bn_act(F_.conv_s2d(field, self.conv1.weight, self.bn1.training), self.bn1, act=True)
-        x = F_.bn_act(F_.conv2d(x, self.conv2.weight, want_stats=self.bn2.training), self.bn2, act=True, dual=True)
+        x = F_.bn_act(F_.conv_s2d(field, self.conv1.weight, F_.needs_stats(self.bn1)), self.bn1, act=True)
+        x = F_.bn_act(F_.conv2d(x, self.conv2.weight, want_stats=F_.needs_stats(self.bn2)), self.bn2, act=True, dual=True)
         x = self.block1(x, act_out=True, dual_out=True)
         low = x[0]
         x = self.block2(x, act_out=True, dual_out=True)
@@ -178,9 +190,9 @@ class Xception(nn.Module):
         for i in range(4, 20):
             x = getattr(self, "block%d" % i)(x, act_out=True, dual_out=True)
         x = self.block20(x, act_out=False)
-        x = F_.bn_act(self.conv3(x, self.bn3.training), self.bn3, act=True)
-        x = F_.bn_act(self.conv4(x, self.bn4.training), self.bn4, act=True)
-        x = F_.bn_act(self.conv5(x, self.bn5.training), self.bn5, act=True)
+        x = F_.bn_act(self.conv3(x, F_.needs_stats(self.bn3)), self.bn3, act=True)
+        x = F_.bn_act(self.conv4(x, F_.needs_stats(self.bn4)), self.bn4, act=True)
+        x = F_.bn_act(self.conv5(x, F_.needs_stats(self.bn5)), self.bn5, act=True)
         return x, low
 
 
@@ -204,13 +216,13 @@ class ASPP_module(nn.Module):
         self.atrous_convolution = nn.Conv2d(inplanes, planes, k, padding=0 if rate == 1 else rate,
                                             dilation=rate, bias=False)
         self.bn = normalizer(planes)
-        self.relu = nn.Identity()
+        self.relu = _Act()
         self.rate = rate
         nn.init.kaiming_normal_(self.atrous_convolution.weight)
 
     def forward(self, x):
         return F_.bn_act(F_.conv2d(x, self.atrous_convolution.weight, dilation=self.rate,
-                                   want_stats=self.bn.training), self.bn, act=True)
+                                   want_stats=F_.needs_stats(self.bn)), self.bn, act=True)
 
 
 class InterpolationUpsampler(nn.Module):
@@ -218,8 +230,8 @@ class InterpolationUpsampler(nn.Module):
 
     def __init__(self, n_output, normalizer=nn.BatchNorm2d):
         super().__init__()
-        self.last_conv = nn.Sequential(nn.Conv2d(304, 256, 3, padding=1, bias=False), normalizer(256), nn.Identity(),
-                                       nn.Conv2d(256, 256, 3, padding=1, bias=False), normalizer(256), nn.Identity(),
+        self.last_conv = nn.Sequential(nn.Conv2d(304, 256, 3, padding=1, bias=False), normalizer(256), _Act(),
+                                       nn.Conv2d(256, 256, 3, padding=1, bias=False), normalizer(256), _Act(),
                                        nn.Conv2d(256, n_output, 1))
         _init_decoder(self)
 
@@ -227,8 +239,8 @@ class InterpolationUpsampler(nn.Module):
         x = F_.bilinear(x, int(math.ceil(H / 4)), int(math.ceil(W / 4)))
         x = torch.cat((x, low_level_features), dim=3)
         lc = self.last_conv
-        x = F_.bn_act(F_.conv2d(x, lc[0].weight, want_stats=lc[1].training), lc[1], act=True)
-        x = F_.bn_act(F_.conv2d(x, lc[3].weight, want_stats=lc[4].training), lc[4], act=True)
+        x = F_.bn_act(F_.conv2d(x, lc[0].weight, want_stats=F_.needs_stats(lc[1])), lc[1], act=True)
+        x = F_.bn_act(F_.conv2d(x, lc[3].weight, want_stats=F_.needs_stats(lc[4])), lc[4], act=True)
         x = F_.conv2d(x, lc[6].weight, lc[6].bias)
         return F_.bilinear(x, H, W, s2d=True)
 
@@ -249,9 +261,9 @@ class DeepLabv3_plus(nn.Module):
         self.aspp2 = ASPP_module(2048, 256, rates[1], normalizer)
         self.aspp3 = ASPP_module(2048, 256, rates[2], normalizer)
         self.aspp4 = ASPP_module(2048, 256, rates[3], normalizer)
-        self.relu = nn.Identity()
-        self.global_avg_pool = nn.Sequential(nn.Identity(), nn.Conv2d(2048, 256, 1, bias=False), normalizer(256),
-                                             nn.Identity())
+        self.relu = _Act()
+        self.global_avg_pool = nn.Sequential(_Act(), nn.Conv2d(2048, 256, 1, bias=False), normalizer(256),
+                                             _Act())
         self.conv1 = nn.Conv2d(1280, 256, 1, bias=False)
         self.bn1 = normalizer(256)
         self.conv2 = nn.Conv2d(128, 48, 1, bias=False)
@@ -265,11 +277,11 @@ class DeepLabv3_plus(nn.Module):
         h, w = x.shape[1], x.shape[2]
         x1, x2, x3, x4 = self.aspp1(x), self.aspp2(x), self.aspp3(x), self.aspp4(x)
         gp = self.global_avg_pool
-        x5 = F_.bn_act(F_.conv2d(F_.global_avg_pool(x), gp[1].weight, want_stats=gp[2].training), gp[2], act=True)
+        x5 = F_.bn_act(F_.conv2d(F_.global_avg_pool(x), gp[1].weight, want_stats=F_.needs_stats(gp[2])), gp[2], act=True)
         x5 = F_.bilinear(x5, h, w)
         x = torch.cat((x1, x2, x3, x4, x5), dim=3)
-        x = F_.bn_act(F_.conv2d(x, self.conv1.weight, want_stats=self.bn1.training), self.bn1, act=True)
-        low = F_.bn_act(F_.conv2d(low, self.conv2.weight, want_stats=self.bn2.training), self.bn2, act=True)
+        x = F_.bn_act(F_.conv2d(x, self.conv1.weight, want_stats=F_.needs_stats(self.bn1)), self.bn1, act=True)
+        low = F_.bn_act(F_.conv2d(low, self.conv2.weight, want_stats=F_.needs_stats(self.bn2)), self.bn2, act=True)
         return self.upsample(x, low, H, W)
 
     def freeze_bn(self):

@@ -254,22 +254,67 @@ def bn_act_depthwise(y, bn, dw_weight, act=True):
     sums = None
     if isinstance(y, tuple):
         y, sums = y
-    if not bn.training:
+    if not needs_stats(bn):   # eval mode / Identity normaliser: the unfused pair (both differentiable)
         return depthwise3x3(bn_act(y, bn, act=act), dw_weight)
     return _BNActDepthwise.apply(y, sums, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps, bn.momentum,
                                  act, dw_weight, _nbt(bn))
 
 
 class _AffineAct(torch.autograd.Function):
-    """Eval-mode BatchNorm (running statistics folded into a, b) + activation; forward only."""
+    """out = act(a*y + b [+ res]) with a, b that do not depend on the batch: nn.BatchNorm2d in eval mode
+    (running statistics; validation train_gan.py:330-398, freeze_bn) or an Identity normaliser
+    (--disable_batchnorm, train_gan.py:125: gamma = beta = None, mean 0, invstd 1)."""
 
     @staticmethod
-    def forward(ctx, y, a, b, res, act):
-        return K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
+    def forward(ctx, y, gamma, beta, mean, invstd, res, act, dual):
+        C = y.shape[-1]
+        if gamma is None:
+            a, b = _const_vec(1.0, C, y.device), _const_vec(0.0, C, y.device)
+        else:
+            a = (gamma.detach() * invstd).float().contiguous()
+            b = (beta.detach() - mean * a).float().contiguous()
+        out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
+        ctx.save_for_backward(y, out if act else None, gamma, mean, invstd)
+        ctx.act, ctx.has_res = act, res is not None
+        if dual:
+            return out, out[...]
+        return out
 
     @staticmethod
-    def backward(ctx, g):
-        raise NotImplementedError("eval-mode BatchNorm backward is not on the training hot path")
+    def backward(ctx, g, g2=None):
+        y, out, gamma, mean, invstd = ctx.saved_tensors
+        if g is None:
+            g, g2 = g2, None
+        g = _bf16c(g)
+        g2 = _bf16c(g2) if g2 is not None else None
+        C = y.shape[-1]
+        identity = gamma is None
+        dx, dyh, grads = K.bn_backward_frozen(g, out, y, mean, invstd, gamma, act=ctx.act, slope=SLOPE, g2=g2,
+                                              want_dx=not identity)
+        ggamma = grads[C:] if (not identity and ctx.needs_input_grad[1]) else None
+        gbeta = grads[:C] if (not identity and ctx.needs_input_grad[2]) else None
+        gres = dyh if (ctx.has_res and ctx.needs_input_grad[5]) else None
+        return (dyh if identity else dx), ggamma, gbeta, None, None, gres, None, None
+
+
+_consts = {}
+
+
+def _const_vec(value, C, device):
+    key = (float(value), int(C), str(device))
+    t = _consts.get(key)
+    if t is None:
+        t = _consts[key] = torch.full((C,), float(value), dtype=torch.float32, device=device)
+    return t
+
+
+def is_batchnorm(m):
+    return isinstance(m, torch.nn.modules.batchnorm._BatchNorm)
+
+
+def needs_stats(m):
+    """True when the normaliser after a conv wants that conv's batch statistics (training-mode BatchNorm)."""
+    return is_batchnorm(m) and m.training
 
 
 def _nbt(bn):
@@ -292,13 +337,18 @@ def bn_act(y, bn, res=None, act=True, sums=None, dual=False):
     full-tensor add kernel."""
     if isinstance(y, tuple):
         y, sums = y
+    if not is_batchnorm(bn):      # Identity normaliser (train_gan.py:125): activation / residual only
+        if not isinstance(bn, torch.nn.Identity):
+            raise NotImplementedError("normalizer %s: BatchNorm2d and Identity are built" % type(bn).__name__)
+        C = y.shape[-1]
+        return _AffineAct.apply(y, None, None, _const_vec(0.0, C, y.device), _const_vec(1.0, C, y.device), res, act, dual)
     if bn.training:
         return _BNAct.apply(y, bn.weight, bn.bias, res, bn.running_mean, bn.running_var, bn.eps,
                             bn.momentum, act, sums, _nbt(bn), dual)
-    a = (bn.weight * torch.rsqrt(bn.running_var + bn.eps)).float().contiguous()
-    b = (bn.bias - bn.running_mean * a).float().contiguous()
-    out = _AffineAct.apply(y, a, b, res, act)
-    return (out, out) if dual else out
+    with torch.no_grad():
+        invstd = torch.rsqrt(bn.running_var + bn.eps).float().contiguous()
+        mean = bn.running_mean.float().contiguous()
+    return _AffineAct.apply(y, bn.weight, bn.bias, mean, invstd, res, act, dual)
 
 
 class _Subsample2(torch.autograd.Function):
@@ -400,6 +450,34 @@ class _L1(torch.autograd.Function):
 
 def l1_loss(a, b):
     return _L1.apply(a, b)
+
+
+class _RegLoss(torch.autograd.Function):
+    """The script's regression losses on fields with the gradient produced in the same pass:
+    mean(l(a - b) [* w]) or, normalised, sum(l * w) / (sum(w) + eps) (utils/losses.py:101-112)."""
+
+    @staticmethod
+    def forward(ctx, a, b, weights, mode, beta, count, normalize, eps):
+        n = float(count if count is not None else a.numel())
+        if normalize and weights is not None:   # 1 / (sum w + eps) stays on the device: no host sync, capturable
+            inv = (1.0 / (weights.float().sum() + eps)).reshape(1).float()
+            s, grad = K.reg_loss_grad(a, b, mode, 1.0, weights=weights, beta=beta, gscale_dev=inv,
+                                      need_grad=ctx.needs_input_grad[0])
+            out = (s * inv.double()[0]).float()
+        else:
+            s, grad = K.reg_loss_grad(a, b, mode, 1.0 / n, weights=weights, beta=beta, need_grad=ctx.needs_input_grad[0])
+            out = (s / n).float()
+        ctx.save_for_backward(grad)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return (grad * g.to(grad.dtype)), None, None, None, None, None, None, None
+
+
+def regression_loss(a, b, weights=None, mode=0, beta=1.0, count=None, normalize=False, eps=1e-8):
+    return _RegLoss.apply(a, b, weights, mode, beta, count, normalize, eps)
 
 
 class _ToField(torch.autograd.Function):

@@ -140,14 +140,23 @@ class GPSRODataset(Dataset):
         if self.augmentation_mode is not None:
             raise NotImplementedError("mixing augmentation is not available on the field path")
         B = len(indices)
-        raw_d, raw_l = raw if raw is not None else self._raw_buffers(B)
+        raw = raw if raw is not None else self._raw_buffers(B)
+        raw_d, raw_l = raw[0], raw[1]
         for b, idx in enumerate(indices):
             self._read_one(self.npr_data, "data_in_", idx, out=raw_d[b])
             self._read_one(self.npr_label, "data_out_", idx, out=raw_l[b])
-        out_d, out_l = out if out is not None else (None, None)
+        out_d, out_l = (out[0], out[1]) if out is not None else (None, None)
         ch = list(self.channels)
         x = K.stage_normalize(raw_d, "NCHW", ch, self.data_shift.flatten(), self.data_scale.flatten(), s2d=s2d, out=out_d)
         y = K.stage_normalize(raw_l, "NCHW", ch, self.label_shift.flatten(), self.label_scale.flatten(), s2d=s2d, out=out_l)
+        if self.masks:   # the reference yields (data, label, masks, filename) then (gpsro_dataset.py:172-175)
+            raw_m = raw[2] if len(raw) > 2 else torch.empty_like(raw_d)
+            for b, idx in enumerate(indices):
+                self._read_one(self.npr_mask, "masks_", idx, out=raw_m[b])
+            zero = torch.zeros(len(ch), dtype=torch.float32, device=raw_m.device)
+            m = K.stage_normalize(raw_m, "NCHW", ch, zero, torch.ones_like(zero), s2d=s2d,
+                                  out=out[2] if (out is not None and len(out) > 2) else None)   # masks are not standardised
+            return x, y, m, [self.files[i] for i in indices]
         return x, y, [self.files[i] for i in indices]
 
 
@@ -170,9 +179,12 @@ class PrefetchLoader:
         shp = dataset.shapes[0]
         C, H, W = len(dataset.channels), shp[1], shp[2]
         fshape = (self.B, H // 2, W // 2, 4 * C) if s2d else (self.B, H, W, C)
+        ntens = 3 if dataset.masks else 2     # data, label (, masks): the reference's batch tuple
         self.raw = [dataset._raw_buffers(self.B) for _ in range(nslots)]
-        self.fields = [(torch.empty(fshape, dtype=torch.bfloat16, device=self.dev),
-                        torch.empty(fshape, dtype=torch.bfloat16, device=self.dev)) for _ in range(nslots)]
+        if dataset.masks:
+            self.raw = [r + (torch.empty_like(r[0]),) for r in self.raw]
+        self.fields = [tuple(torch.empty(fshape, dtype=torch.bfloat16, device=self.dev) for _ in range(ntens))
+                       for _ in range(nslots)]
         self.ready = [torch.cuda.Event() for _ in range(nslots)]      # producer -> consumer
         self.released = [None] * nslots                               # consumer -> producer
 
@@ -188,7 +200,7 @@ class PrefetchLoader:
                     if self.released[slot] is not None:
                         self.stream.wait_event(self.released[slot])
                     idx = list(range(i * self.B, (i + 1) * self.B))
-                    _, _, names = self.ds.get_batch_fields(idx, raw=self.raw[slot], out=self.fields[slot], s2d=self.s2d)
+                    names = self.ds.get_batch_fields(idx, raw=self.raw[slot], out=self.fields[slot], s2d=self.s2d)[-1]
                     self.ready[slot].record(self.stream)
                     queue_put((slot, names, None))
             queue_put((None, None, None))
@@ -217,6 +229,5 @@ class PrefetchLoader:
                 ev.record(cur)
                 self.released[old] = ev
                 self.free[old].release()
-            x, y = self.fields[slot]
-            yield x, y, names
+            yield self.fields[slot] + (names,)
         worker.join()

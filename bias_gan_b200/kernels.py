@@ -283,6 +283,27 @@ def bn_backward(g, out, x, mean, invstd, gamma, act=True, slope=0.2, g2=None):
     return dx, dyh, coef[5 * C:7 * C]   # fp32 [dL/dbeta | dL/dgamma]
 
 
+def bn_backward_frozen(g, out, x, mean, invstd, gamma, act=True, slope=0.2, g2=None, want_dx=True):
+    """Backward with frozen statistics (eval-mode BatchNorm / Identity normaliser): (dx or None, dyh,
+    fp32 [dL/dbeta | dL/dgamma])."""
+    M, C, ldx = _rows(x)
+    Mg, Cg, ldg = _rows(g)
+    assert (Mg, Cg) == (M, C)
+    ldg2 = 0
+    if g2 is not None:
+        ldg2 = _rows(g2)[2]
+    ldo = _rows(out)[2] if act else 0
+    dyh = act_empty(x.shape, x.device)
+    dx = act_empty(x.shape, x.device) if want_dx else None
+    part = torch.empty((BN_MAX_ROWS, 2 * C), dtype=torch.float32, device=x.device)
+    coef = torch.empty(7 * C, dtype=torch.float32, device=x.device)
+    check(_lib.lib().bgr_bn_backward_frozen(ptr(g), ldg, ptr(g2), ldg2, ptr(out) if act else ctypes.c_void_p(0), ldo,
+                                            ptr(x), ldx, ptr(mean), ptr(invstd), ptr(gamma), int(act), c_float(slope),
+                                            c_long(M), C, ptr(dyh), ptr(dx), _rows(dyh)[2], ptr(part), ptr(coef),
+                                            stream_ptr()))
+    return dx, dyh, coef[5 * C:7 * C]
+
+
 def dw_fwd(x, w9, stride, dil, out=None):
     N, H, W, C, ldx = _nhwc_view(x)
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
@@ -439,6 +460,21 @@ def l1_loss_grad(a, b, gscale, need_grad=True):
     ws = torch.empty(LOSS_MAX_ROWS, dtype=torch.float32, device=a.device)
     check(_lib.lib().bgr_l1_loss_grad(ptr(a), ptr(b), c_long(a.numel()), c_float(gscale), ptr(grad), ptr(s), ptr(ws),
                                       stream_ptr()))
+    return s, grad
+
+
+def reg_loss_grad(a, b, mode, gscale, weights=None, beta=1.0, gscale_dev=None, need_grad=True):
+    """(sum w*l(a-b) as an fp64 0-d tensor, grad bf16 or None); mode 0 L1, 1 SmoothL1(beta), 2 MSE."""
+    assert a.shape == b.shape and a.is_contiguous() and b.is_contiguous() and a.dtype == b.dtype == torch.bfloat16
+    if weights is not None:
+        assert weights.shape == a.shape and weights.is_contiguous() and weights.dtype == torch.bfloat16
+    if gscale_dev is not None:
+        assert gscale_dev.dtype == torch.float32 and gscale_dev.numel() == 1 and gscale_dev.is_cuda
+    s = torch.empty((), dtype=torch.float64, device=a.device)
+    grad = torch.empty(a.shape, dtype=torch.bfloat16, device=a.device) if need_grad else None
+    ws = torch.empty(LOSS_MAX_ROWS, dtype=torch.float32, device=a.device)
+    check(_lib.lib().bgr_reg_loss_grad(ptr(a), ptr(b), ptr(weights), c_long(a.numel()), int(mode), c_float(beta),
+                                       c_float(gscale), ptr(gscale_dev), ptr(grad), ptr(s), ptr(ws), stream_ptr()))
     return s, grad
 
 

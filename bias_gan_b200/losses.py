@@ -99,3 +99,31 @@ class L1LossField(nn.Module):
 
     def forward(self, fake_field, real_field):
         return F_.l1_loss(fake_field, real_field)
+
+
+class RegressionLossField(nn.Module):
+    """The reconstruction-loss choices of the training script (train_gan.py:141-152) on bf16 fields:
+    kind 'l1' = nn.L1Loss, 'smooth_l1' = nn.SmoothL1Loss, 'l2' = nn.MSELoss; called with a third argument
+    (the masks of --enable_masks, train_gan.py:278-279) it is utils/losses.py:101-112 L1LossWeighted
+    (normalize=False: mean(l * w); normalize=True: sum(l * w) / (sum(w) + eps)) resp. L2LossWeighted.
+    `count` = number of real elements when the fields carry zero padding (odd-sized inputs)."""
+    MODES = {"l1": 0, "smooth_l1": 1, "l2": 2}
+
+    def __init__(self, kind="l1", normalize=False, eps=1e-8, beta=1.0):
+        super().__init__()
+        if kind not in self.MODES:
+            raise NotImplementedError("Error, loss {} not implemented.".format(kind))
+        self.kind, self.normalize, self.eps, self.beta = kind, normalize, eps, beta
+
+    def forward(self, fake_field, real_field, masks_field=None, count=None):
+        return F_.regression_loss(fake_field, real_field, masks_field, self.MODES[self.kind], self.beta, count,
+                                  self.normalize, self.eps)
+
+
+def L1LossWeighted(normalize=False, eps=1e-8, smooth=False):
+    """utils/losses.py:101-112 by name."""
+    return RegressionLossField("smooth_l1" if smooth else "l1", normalize, eps)
+
+
+def L2LossWeighted(normalize=False, eps=1e-8):
+    return RegressionLossField("l2", normalize, eps)

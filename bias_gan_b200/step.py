@@ -37,9 +37,10 @@ def _sync_only(stepped, other):
 
 
 def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_reg=1.0, w_gp=10.0, lean=True,
-             train_discriminator=True, train_generator=True, warmup=False):
-    """inputs / real: bf16 field tensors [N, H/2, W/2, 4C].  Returns (d_loss, g_loss) as 0-d device
-    tensors (no host sync; comm.metric_average decides when to read them)."""
+             train_discriminator=True, train_generator=True, warmup=False, masks=None):
+    """inputs / real: bf16 field tensors [N, H/2, W/2, 4C]; masks (optional, --enable_masks): per-element
+    weights in the same layout, handed to the regression criterion as train_gan.py:278-279 does.  Returns
+    (d_loss, g_loss) as 0-d device tensors (no host sync; comm.metric_average decides when to read them)."""
     d_loss = g_loss = None
     prep = L.prepare_weights if (PACK_WEIGHTS and inputs.is_cuda) else (lambda m: None)
     if train_discriminator:
@@ -74,7 +75,7 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
         try:
             logits_fake, _ = D.forward_field(fake)
             gan_loss = crit_gan.g_loss(logits_fake)
-            reg_loss = crit_reg(fake, real)
+            reg_loss = crit_reg(fake, real, masks) if masks is not None else crit_reg(fake, real)
             g_loss = reg_loss if warmup else w_gan * gan_loss + w_reg * reg_loss
             g_opt.zero_grad(set_to_none=True)
             with _sync_only(G, D):
@@ -108,6 +109,7 @@ class GraphedGanStep:
         self.crit_gan, self.crit_reg, self.step_kw = crit_gan, crit_reg, step_kw
         self.inputs = torch.zeros(field_shape, dtype=torch.bfloat16, device=device)
         self.real = torch.zeros(field_shape, dtype=torch.bfloat16, device=device)
+        self.masks = torch.ones(field_shape, dtype=torch.bfloat16, device=device) if step_kw.pop("use_masks", False) else None
         self.noisy = getattr(G, "noise_dimensions", 0) > 0
         cpu_rng = torch.get_rng_state()
         crit_gan.draw_labels()
@@ -153,15 +155,18 @@ class GraphedGanStep:
         if self.noisy:
             self.G.rewind_noise()
         return gan_step(self.G, self.D, self.g_opt, self.d_opt, self.crit_gan, self.crit_reg, self.inputs, self.real,
-                        **self.step_kw)
+                        masks=self.masks, **self.step_kw)
 
-    def __call__(self, inputs=None, real=None):
-        """One training step.  inputs/real: bf16 fields to copy into the static buffers; pass None
-        when the caller has staged straight into `self.inputs` / `self.real`."""
+    def __call__(self, inputs=None, real=None, masks=None):
+        """One training step.  inputs/real(/masks): bf16 fields to copy into the static buffers; pass None
+        when the caller has staged straight into `self.inputs` / `self.real` (/ `self.masks`, which exists
+        when the step was built with use_masks=True)."""
         if inputs is not None:
             self.inputs.copy_(inputs)
         if real is not None:
             self.real.copy_(real)
+        if masks is not None:
+            self.masks.copy_(masks)
         # host RNG in the reference's order (SURVEY 8c): [G noise] -> label_fake, label_real, swap -> [G noise]
         if self.noisy:
             self.G.redraw_noise(0, 1)

@@ -186,6 +186,15 @@ int bgr_bn_backward_recompute_dual(const void* g, int ldg, const void* g2, int l
                                    int C, void* dyh, void* dx, int ldd, float* part, float* coef_ws,
                                    void* stream);
 
+/* Backward of out = act(a*x + b [+ res]) with FROZEN statistics: nn.BatchNorm2d in eval mode (validation,
+ * train_gan.py:330-398; freeze_bn) or an Identity normaliser (--disable_batchnorm, train_gan.py:125 — mean 0,
+ * invstd 1, gamma NULL).  dyh = (g [+ g2])*act'(out) is also dL/dres; dx = gamma*invstd*dyh (NULL to skip:
+ * dyh then is dL/dx); part / coef_ws as bgr_bn_backward (rows 5, 6 of coef_ws = dL/dbeta, dL/dgamma). */
+int bgr_bn_backward_frozen(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
+                           const void* x, int ldx, const float* mean, const float* invstd, const float* gamma,
+                           int act, float slope, long M, int C, void* dyh, void* dx, int ldd, float* part,
+                           float* coef_ws, void* stream);
+
 /* ---- depthwise 3x3, "fixed padding" (deeplab.py:56,66-72,79), stride 1|2, dilation d --------
  * w: fp32 [9][C] (tap-major); dw: fp32 [C][9] (the parameter's own [C,1,3,3] layout).  Output size ceil(H/stride) x ceil(W/stride). */
 int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, const float* w, int stride, int dil,
@@ -229,6 +238,13 @@ int bgr_head_bwd(const float* g, const void* x, const void* w, int N, long K, vo
  * grad = sign(a-b)*gscale (bf16, NULL to skip); ws: fp32 [BGR_LOSS_MAX_ROWS]. */
 int bgr_l1_loss_grad(const void* a, const void* b, long n, float gscale, void* grad, double* sum,
                      float* ws, void* stream);
+/* The script's regression-loss choices (train_gan.py:141-152,278-281) fused with their gradient: mode 0 =
+ * nn.L1Loss, 1 = nn.SmoothL1Loss(beta), 2 = nn.MSELoss; w (optional, NULL = none): bf16 per-element weights
+ * in the tensors' layout = the masks of --enable_masks (utils/losses.py:101-112 L1LossWeighted).
+ * *sum = sum w*l(a-b) (fp64), grad = w*l'(a-b)*gscale[* *gscale_dev] (bf16, NULL to skip; gscale_dev: optional
+ * DEVICE scalar factor, e.g. 1/(sum(w)+eps) of the normalised variant); ws: fp32 [BGR_LOSS_MAX_ROWS]. */
+int bgr_reg_loss_grad(const void* a, const void* b, const void* w, long n, int mode, float beta, float gscale,
+                      const float* gscale_dev, void* grad, double* sum, float* ws, void* stream);
 /* field layout (bf16 [N,H/2,W/2,(py,px,c)]) <-> fp32 NCHW, the tensors the training script sees. */
 int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream);
 int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W, void* stream);

@@ -394,3 +394,34 @@ def test_gap_head_l1(dev):
     (2.5 * out).backward()
     assert abs(float(out) - float(ref)) < 1e-5 * abs(float(ref))
     assert rel(ap.grad, ar.grad) < 4e-3
+
+
+# --------------------------------------------------------------------------------- regression losses
+@pytest.mark.parametrize("kind", ["l1", "smooth_l1", "l2"])
+@pytest.mark.parametrize("weighted,normalize", [(False, False), (True, False), (True, True)])
+def test_regression_losses_match_the_script_choices(dev, kind, weighted, normalize):
+    """train_gan.py:141-152,278-281: nn.L1Loss / nn.SmoothL1Loss / nn.MSELoss and, with masks,
+    utils/losses.py:101-112 L1LossWeighted (+ its smooth / L2 / normalised variants): value and gradient."""
+    from bias_gan_b200.losses import RegressionLossField
+    g = torch.Generator(device="cpu").manual_seed(4)
+    a = torch.randn(2, 24, 36, 64, generator=g).to(dev).bfloat16()
+    b = (a.float() + 1.5 * torch.randn(2, 24, 36, 64, generator=g).to(dev)).bfloat16()
+    w = (torch.rand(2, 24, 36, 64, generator=g).to(dev) > 0.3).bfloat16() if weighted else None
+    ar = a.float().requires_grad_(True)
+    base = {"l1": F.l1_loss, "smooth_l1": F.smooth_l1_loss, "l2": F.mse_loss}[kind]
+    if weighted:
+        el = base(ar, b.float(), reduction="none") * w.float()
+        ref = el.sum() / (w.float().sum() + 1e-8) if normalize else el.mean()
+    else:
+        ref = base(ar, b.float())
+    ref.backward()
+    ap = a.clone().requires_grad_(True)
+    crit = RegressionLossField(kind, normalize=normalize)
+    out = crit(ap, b, w) if weighted else crit(ap, b)
+    out.backward()
+    assert abs(float(out) - float(ref)) <= 1e-5 * abs(float(ref))
+    assert rel(ap.grad.float(), ar.grad) < 4e-3     # bf16 rounding of the gradient values
+    # the plain L1 case is the kernel the step uses (functional.l1_loss): same value
+    if kind == "l1" and not weighted:
+        from bias_gan_b200 import functional as F_
+        assert abs(float(F_.l1_loss(a, b)) - float(ref)) <= 1e-5 * abs(float(ref))

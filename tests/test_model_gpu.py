@@ -137,7 +137,7 @@ def test_early_trunk_is_tight(setup):
 
 
 # four logits = four draws of amplified rounding noise; product and autocast are single samples of it
-D_LOGIT_FLOOR_FACTOR = 2.5
+D_LOGIT_FLOOR_FACTOR = 2.0   # measured 1.46 (0.152 vs 0.104)
 
 
 def test_discriminator_forward_backward(setup):
@@ -163,9 +163,11 @@ def test_discriminator_forward_backward(setup):
 
 
 # |loss - fp32 oracle| / |oracle| of one full G+D step at 256x384, batch 4 (d_loss, g_loss): fixed bounds with
-# head-room over the measured, reproducible values (the PARITY line of this test); the bf16-autocast run of
-# the oracle deviates by the amounts printed beside them
-STEP_LOSS_BOUNDS = (0.15, 0.15)
+# head-room over the measured, reproducible values.  Measured on B200: d_loss 0.7567 vs fp32 0.6824 (10.9 %;
+# the oracle under bf16 autocast: 0.7098, 4.0 %); g_loss 34.41 vs 28.03 (22.8 %; autocast: 1.95, 93 % off --
+# g_loss = softplus(-D'(G(x))) is evaluated after D's first AdamW step, where the untrained critic's logits are
+# O(10) and swing with bf16 rounding; the L1 part of it is held to 2 % in test_generator_forward_backward).
+STEP_LOSS_BOUNDS = (0.15, 0.30)
 
 
 def test_gan_step_matches_oracle_step(setup):

@@ -45,9 +45,9 @@ def test_gradient_penalty_matches_oracle():
     torch.testing.assert_close(Dp.xception_features.bn1.running_mean, Dr.xception_features.bn1.running_mean, rtol=2e-2, atol=2e-3)
 
 
-# relative deviation of (d_loss, g_loss) of one Wasserstein step from the fp32 oracle; measured values on B200
-# (deterministic): see the PARITY line this test prints
-WGAN_STEP_BOUNDS = (0.6, 0.6)
+# relative deviation of (d_loss, g_loss) of one Wasserstein step from the fp32 oracle.  Measured on B200
+# (deterministic): d_loss 8.510 vs 8.718 (2.4 %), g_loss 13.473 vs 13.603 (1.0 %)
+WGAN_STEP_BOUNDS = (0.08, 0.05)
 
 
 def test_wasserstein_step_eager_and_graphed():
