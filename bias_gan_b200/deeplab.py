@@ -245,16 +245,120 @@ class InterpolationUpsampler(nn.Module):
         return F_.bilinear(x, H, W, s2d=True)
 
 
+def _pad_cout(w, dim=0):
+    """Weight with its output-channel dimension zero-padded to a multiple of 8 (45 -> 48): the kernels move
+    128-bit channel groups; the padded outputs are exact zeros and their gradient rows are dropped by autograd."""
+    C = w.shape[dim]
+    Cp = F_.pad8(C)
+    if Cp == C:
+        return w
+    pad = [0, 0] * (w.dim() - 1 - dim) + [0, Cp - C]
+    return torch.nn.functional.pad(w, pad)
+
+
+def _pad_cin(w, Cp):
+    return w if w.shape[1] == Cp else torch.nn.functional.pad(w, (0, 0, 0, 0, 0, Cp - w.shape[1]))
+
+
+def _init_deconv(mod):
+    gain = nn.init.calculate_gain("leaky_relu", 0.2)
+    for m in mod.modules():
+        if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+            n = m.kernel_size[0] * m.kernel_size[1] * m.out_channels
+            nn.init.normal_(m.weight, mean=0.0, std=gain / math.sqrt(n))
+        elif isinstance(m, nn.BatchNorm2d):
+            nn.init.ones_(m.weight)
+            nn.init.zeros_(m.bias)
+
+
+class _Pool(nn.Identity):
+    """Place holder of nn.AvgPool2d(2, stride=1, padding=p) in the decoder's nn.Sequential containers (no
+    parameters; keeps the indices of the state-dict keys); the pooling runs fused with the LeakyReLU behind it."""
+
+    def __init__(self, padding):
+        super().__init__()
+        self.padding = padding
+
+
+class DeconvUpsampler(nn.Module):
+    """deeplab.py:398-444.  Four ConvTranspose2d(k3, s2) whose paddings / output paddings are hard-wired for the
+    19 x 37 GPSRO fields (2x3 -> 3x6 -> [pool] 2x5 -> 6x11 -> [pool] 5x10 -> 10x19 -> [pool] 9x18 -> 18x36), each
+    followed by normaliser, AvgPool2d(2, 1) and LeakyReLU; state-dict keys deconv1.0.weight, deconv1.1.*, ...
+    as the reference's.  The transposed convs run on the implicit-GEMM kernel (functional._ConvT)."""
+
+    def __init__(self, n_output, normalizer=nn.BatchNorm2d, nn_pooling=True):
+        super().__init__()
+        pool = (lambda: _Pool(0)) if nn_pooling else (lambda: nn.Identity())
+        ct = lambda cin, cout, p, op: nn.ConvTranspose2d(cin, cout, 3, stride=2, padding=p, output_padding=op, bias=False)
+        self.deconv1 = nn.Sequential(ct(256, 256, 1, (0, 1)), normalizer(256), pool(), _Act())
+        self.deconv2 = nn.Sequential(ct(256, 256, 0, (1, 0)), normalizer(256), pool(), _Act())
+        self.conv1 = nn.Sequential(nn.Conv2d(304, 256, 3, padding=1, bias=False), normalizer(256), _Act(),
+                                   nn.Conv2d(256, 256, 3, padding=1, bias=False), normalizer(256), _Act(),
+                                   nn.Conv2d(256, 256, 1))
+        self.deconv3 = nn.Sequential(ct(256, 128, 1, (1, 0)), normalizer(128), pool(), _Act())
+        self.last_deconv = nn.Sequential(ct(128, n_output, 1, (1, 1)))
+        _init_deconv(self)
+
+    @staticmethod
+    def _stage(seq, x):
+        ct, norm, pool = seq[0], seq[1], seq[2]
+        y = F_.conv_transpose2d(x, ct.weight, ct.padding[0], ct.output_padding, want_stats=F_.needs_stats(norm))
+        if isinstance(pool, _Pool):   # normaliser -> AvgPool2d(2, 1) -> LeakyReLU
+            return F_.avgpool2(F_.bn_act(y, norm, act=False), pool.padding, act=True)
+        return F_.bn_act(y, norm, act=True)
+
+    def forward(self, x, low_level_features):
+        x = self._stage(self.deconv2, self._stage(self.deconv1, x))
+        x = torch.cat((x, low_level_features), dim=3)
+        c = self.conv1
+        x = F_.bn_act(F_.conv2d(x, c[0].weight, want_stats=F_.needs_stats(c[1])), c[1], act=True)
+        x = F_.bn_act(F_.conv2d(x, c[3].weight, want_stats=F_.needs_stats(c[4])), c[4], act=True)
+        x = F_.conv2d(x, c[6].weight, c[6].bias)
+        x = self._stage(self.deconv3, x)
+        ld = self.last_deconv[0]
+        return F_.conv_transpose2d(x, _pad_cout(ld.weight, 1), ld.padding[0], ld.output_padding)
+
+
+class UpsamplerExtension(nn.Module):
+    """deeplab.py:466-500: full-resolution two-conv skip from the raw input, joined with the normalised,
+    pooled (18x36 -> 19x37) decoder output."""
+
+    def __init__(self, n_input, n_output, normalizer=nn.BatchNorm2d, nn_pooling=True):
+        super().__init__()
+        self.init_norm = nn.Sequential(normalizer(128), _Pool(1) if nn_pooling else nn.Identity(), _Act())
+        self.conv1 = nn.Sequential(nn.Conv2d(n_input, 64, 3, padding=1, bias=False), normalizer(64), _Act(),
+                                   nn.Conv2d(64, 128, 3, padding=1, bias=False), normalizer(128), _Act())
+        self.conv2 = nn.Sequential(nn.Conv2d(256, 64, 3, padding=1, bias=False), normalizer(64), _Act(),
+                                   nn.Conv2d(64, n_output, 3, padding=1, bias=False))
+        _init_deconv(self)
+
+    def forward(self, inp, x):
+        """inp: the raw generator input as bf16 NHWC [N,H,W,Cp] (channels zero-padded to a multiple of 8)."""
+        a, b = self.conv1, self.conv2
+        skip = F_.bn_act(F_.conv2d(inp, _pad_cin(a[0].weight, inp.shape[-1]), want_stats=F_.needs_stats(a[1])), a[1], act=True)
+        skip = F_.bn_act(F_.conv2d(skip, a[3].weight, want_stats=F_.needs_stats(a[4])), a[4], act=True)
+        n = self.init_norm
+        if isinstance(n[1], _Pool):
+            x = F_.avgpool2(F_.bn_act(x, n[0], act=False), n[1].padding, act=True)
+        else:
+            x = F_.bn_act(x, n[0], act=True)
+        x = torch.cat((x, skip), dim=3)
+        x = F_.bn_act(F_.conv2d(x, b[0].weight, want_stats=F_.needs_stats(b[1])), b[1], act=True)
+        return F_.conv2d(x, _pad_cout(b[3].weight, 0))
+
+
 class DeepLabv3_plus(nn.Module):
-    """deeplab.py:583-684 with upsampler_type='Interpolate' (the only shape-generic one)."""
+    """deeplab.py:583-684: upsampler_type 'Interpolate' (shape-generic), 'Deconv' and 'Deconv1x'
+    (the reference's default / its GAN run script's choice; 19 x 37 fields only, like the reference's)."""
 
     def __init__(self, n_input=3, n_output=21, os=16, upsampler_type="Interpolate", pretrained=False, _print=False,
                  normalizer=nn.BatchNorm2d, nn_pooling=True):
         super().__init__()
-        if upsampler_type != "Interpolate":
-            raise NotImplementedError("upsampler %s: only 'Interpolate' is built (SURVEY §8f rank 3)" % upsampler_type)
+        if upsampler_type not in ("Interpolate", "Deconv", "Deconv1x"):
+            raise NotImplementedError("Error, upsampler {} not implemented.".format(upsampler_type))
         self.upsampler_type = upsampler_type
         self.n_output = n_output
+        self.nn_pooling = nn_pooling
         self.xception_features = Xception(n_input, os, pretrained, normalizer)
         rates = [1, 6, 12, 18] if os == 16 else [1, 12, 24, 36]
         self.aspp1 = ASPP_module(2048, 256, rates[0], normalizer)
@@ -268,11 +372,20 @@ class DeepLabv3_plus(nn.Module):
         self.bn1 = normalizer(256)
         self.conv2 = nn.Conv2d(128, 48, 1, bias=False)
         self.bn2 = normalizer(48)
-        self.upsample = InterpolationUpsampler(n_output, normalizer)
+        if upsampler_type == "Interpolate":
+            self.upsample = InterpolationUpsampler(n_output, normalizer)
+        else:
+            self.upsample = DeconvUpsampler(128 if upsampler_type == "Deconv1x" else n_output, normalizer, nn_pooling)
+            if upsampler_type == "Deconv1x":
+                self.upsample_extension = UpsamplerExtension(n_input, n_output, normalizer, nn_pooling)
+            else:
+                self.final_pool = _Pool(1) if nn_pooling else nn.Identity()
 
-    def forward(self, field):
+    def forward(self, field, hw=None):
+        """field: bf16 [N, ceil(H/2), ceil(W/2), 4*Cp]; hw = the true (H, W) when the field carries a zero row /
+        column (odd sizes).  Returns the output field (same padding convention, channels padded to 8)."""
         N, H2, W2, _ = field.shape
-        H, W = 2 * H2, 2 * W2
+        H, W = hw if hw is not None else (2 * H2, 2 * W2)
         x, low = self.xception_features(field)
         h, w = x.shape[1], x.shape[2]
         x1, x2, x3, x4 = self.aspp1(x), self.aspp2(x), self.aspp3(x), self.aspp4(x)
@@ -282,7 +395,19 @@ class DeepLabv3_plus(nn.Module):
         x = torch.cat((x1, x2, x3, x4, x5), dim=3)
         x = F_.bn_act(F_.conv2d(x, self.conv1.weight, want_stats=F_.needs_stats(self.bn1)), self.bn1, act=True)
         low = F_.bn_act(F_.conv2d(low, self.conv2.weight, want_stats=F_.needs_stats(self.bn2)), self.bn2, act=True)
-        return self.upsample(x, low, H, W)
+        if self.upsampler_type == "Interpolate":
+            if (H | W) & 1:
+                raise NotImplementedError("the Interpolate upsampler is built for even field sizes")
+            return self.upsample(x, low, H, W)
+        x = self.upsample(x, low)
+        if self.upsampler_type == "Deconv1x":      # deeplab.py:676-677
+            x = self.upsample_extension(F_.field_to_nhwc(field, H, W), x)
+        elif isinstance(self.final_pool, _Pool):   # deeplab.py:678-679
+            x = F_.avgpool2(x, self.final_pool.padding, act=False)
+        if (x.shape[1], x.shape[2]) != (H, W):
+            raise RuntimeError("Deconv upsampler produced %dx%d for a %dx%d input (its paddings are hard-wired for "
+                               "19x37 fields, deeplab.py:406-431)" % (x.shape[1], x.shape[2], H, W))
+        return F_.nhwc_to_field(x)
 
     def freeze_bn(self):
         for m in self.modules():

@@ -48,6 +48,9 @@ class Discriminator(nn.Module):
         return logits, torch.sigmoid(logits)
 
     def forward(self, input):
+        N, C, H, W = input.shape
+        if (H | W) & 1 or C % 8:   # the reference's native 45 x 19 x 37 fields: zero-padded field
+            return self.forward_field(F_.to_field_padded(input, F_.pad8(C)))
         return self.forward_field(F_.to_field(input))
 
     def freeze_bn(self):
@@ -78,6 +81,7 @@ class Generator(nn.Module):
         super().__init__()
         self.noise_dimensions = noise_dimensions
         self.n_output = n_output
+        self.n_input = n_input
         self._noise_slots, self._noise_cursor = None, 0
         if noise_type == "Uniform":
             self.dist = torch.distributions.uniform.Uniform(0.0, 1.0)
@@ -88,13 +92,18 @@ class Generator(nn.Module):
         self.model = DeepLabv3_plus(n_input=n_input + noise_dimensions, n_output=n_output, os=os,
                                     upsampler_type=upsampler_type, pretrained=pretrained, normalizer=normalizer)
 
-    def forward_field(self, field):
-        """deeplab_gan.py:85-94.  The noise planes are drawn like the reference's — `dist.rsample`
+    def forward_field(self, field, hw=None):
+        """deeplab_gan.py:85-94.  hw = the true (H, W) of a field that carries a zero row / column (odd sizes).
+        The noise planes are drawn like the reference's — `dist.rsample`
         on the CPU generator, [B, nd, H, W] fp32 — so a seeded run sees the same noise; they join the
         field in one kernel, padded with zero channels to a multiple of 16 so that the 4*(C+nd)
         channels of a block pixel fill whole 128-byte lines for the entry conv's TMA boxes."""
         nd = self.noise_dimensions
         if nd > 0:
+            if hw is not None and hw != (2 * field.shape[1], 2 * field.shape[2]) or (field.shape[-1] // 4) != self.n_input:
+                raise NotImplementedError("noise planes on zero-padded fields (odd sizes or channel counts that are "
+                                          "not multiples of 8) are not built; the reference's GAN run uses "
+                                          "--noise_dimensions 0 there (run_training_gan_coccobello.sh:36)")
             B, H2, W2, C4 = field.shape
             shape = (B, nd, 2 * H2, 2 * W2)
             if self._noise_slots is None:
@@ -108,7 +117,7 @@ class Generator(nn.Module):
                 noise = self._noise_slots[self._noise_cursor].dev
                 self._noise_cursor += 1
             field = F_.append_noise(field, noise, (C4 // 4 + nd + 15) // 16 * 16)
-        return self.model(field)
+        return self.model(field, hw)
 
     def static_noise(self, enable=True):
         """Keep the noise planes in persistent device buffers, one per forward of a step, so that a
@@ -125,6 +134,10 @@ class Generator(nn.Module):
             slot.draw(self.dist)
 
     def forward(self, input_raw):
+        N, C, H, W = input_raw.shape
+        if (H | W) & 1 or C % 8 or self.n_output % 8:   # the reference's native 45 x 19 x 37 fields
+            out = self.forward_field(F_.to_field_padded(input_raw, F_.pad8(C)), hw=(H, W))
+            return F_.from_field_padded(out, self.n_output, H, W)
         return F_.from_field(self.forward_field(F_.to_field(input_raw)), self.n_output)
 
 

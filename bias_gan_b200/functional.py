@@ -528,3 +528,143 @@ def to_field(x_nchw):
 
 def from_field(field, C):
     return _FromField.apply(field, C)
+
+
+# ---------------------------------------------------------------------------------------------
+# Deconv / Deconv1x decoders, odd-sized fields (csrc/deconv.cu)
+# ---------------------------------------------------------------------------------------------
+class _ConvT(torch.autograd.Function):
+    """nn.ConvTranspose2d(kernel 3, stride 2, padding p, output_padding) (deeplab.py:406-431) on the tcgen05
+    implicit-GEMM kernel: out[2i - p + k] += x[i] * w[k] is the stride-1 conv of the zero-stuffed input
+    (z[2i] = x[i]) with tap offsets p - k, so forward, data gradient and weight gradient are the same three
+    launches as every other conv; weight is the module's [Cin, Cout, 3, 3] parameter."""
+
+    @staticmethod
+    def forward(ctx, x, weight, pad, out_pad, want_stats):
+        N, h, w, Cin = x.shape
+        Cout = weight.shape[1]
+        H = (h - 1) * 2 - 2 * pad + 3 + out_pad[0]
+        W = (w - 1) * 2 - 2 * pad + 3 + out_pad[1]
+        dy = [pad - ky for ky in range(3) for _ in range(3)]
+        dx = [pad - kx for _ in range(3) for kx in range(3)]
+        ctx.save_for_backward(x, weight)
+        ctx.set_materialize_grads(False)
+        ctx.cfg = (H, W, dy, dx)
+        z = K.zero_stuff2(x, H, W)
+        wg = L.cached(weight, "convT", lambda t: L._padded_rows(t.permute(1, 2, 3, 0).reshape(Cout, 9, Cin), Cout, 9, Cin))
+        y = K.conv_fprop(z, wg, dy, dx, want_stats=want_stats)
+        if want_stats:
+            ctx.mark_non_differentiable(y[1])
+        return y
+
+    @staticmethod
+    def backward(ctx, g, *unused):
+        if g is None:
+            return None, None, None, None, None
+        x, weight = ctx.saved_tensors
+        H, W, dy, dx = ctx.cfg
+        N, h, w, Cin = x.shape
+        Cout = weight.shape[1]
+        g = _bf16c(g)
+        gx = gw = None
+        if ctx.needs_input_grad[1]:
+            with _side_stream(g):
+                gwg = K.conv_wgrad(K.zero_stuff2(x, H, W), g, dy, dx)            # [Cout, 9, Cin]
+                gw = gwg.reshape(Cout, 3, 3, Cin).permute(3, 0, 1, 2).contiguous()
+        if ctx.needs_input_grad[0]:
+            wt = L.cached(weight, "convT_t", lambda t: L._padded_rows(t.permute(0, 2, 3, 1).reshape(Cin, 9, Cout), Cin, 9, Cout))
+            gz = K.conv_fprop(g, wt, [-v for v in dy], [-v for v in dx])
+            gx = K.zero_stuff2_bwd(gz, h, w)
+        _join(g)
+        return gx, gw, None, None, None
+
+
+def conv_transpose2d(x, weight, padding, output_padding, want_stats=False):
+    return _ConvT.apply(x, weight, int(padding), tuple(output_padding), want_stats)
+
+
+class _AvgPool2(torch.autograd.Function):
+    """nn.AvgPool2d(2, stride=1, padding=pad) followed (act=True) by LeakyReLU(0.2), one kernel each way."""
+
+    @staticmethod
+    def forward(ctx, x, pad, act):
+        y = K.avgpool2_fwd(x, pad, act, SLOPE)
+        ctx.save_for_backward(y if act else None)
+        ctx.cfg = (tuple(x.shape), pad, act)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (y,) = ctx.saved_tensors
+        shape, pad, act = ctx.cfg
+        return K.avgpool2_bwd(_bf16c(g), y, shape, pad, act, SLOPE), None, None
+
+
+def avgpool2(x, pad, act=False):
+    return _AvgPool2.apply(x, int(pad), bool(act))
+
+
+class _NhwcToField(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.hw = (x.shape[1], x.shape[2])
+        return K.nhwc_to_field(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return K.field_to_nhwc(_bf16c(g).contiguous(), *ctx.hw)
+
+
+class _FieldToNhwc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, field, H, W):
+        return K.field_to_nhwc(field, H, W)
+
+    @staticmethod
+    def backward(ctx, g):
+        return K.nhwc_to_field(_bf16c(g)), None, None
+
+
+def nhwc_to_field(x):
+    return _NhwcToField.apply(x)
+
+
+def field_to_nhwc(field, H, W):
+    return _FieldToNhwc.apply(field, H, W)
+
+
+class _ToFieldPadded(torch.autograd.Function):
+    """fp32 NCHW of any size / channel count -> field with Cp channels per sub-pixel, zero padded."""
+
+    @staticmethod
+    def forward(ctx, x, Cp):
+        ctx.cfg = tuple(x.shape)
+        return K.stage_normalize_padded(x.float().contiguous(), None, None, None, Cp)
+
+    @staticmethod
+    def backward(ctx, g):
+        N, C, H, W = ctx.cfg
+        return K.field_to_nchw_padded(_bf16c(g).contiguous(), C, H, W), None
+
+
+class _FromFieldPadded(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, field, C, H, W):
+        ctx.Cp = field.shape[-1] // 4
+        return K.field_to_nchw_padded(field, C, H, W)
+
+    @staticmethod
+    def backward(ctx, g):
+        return K.stage_normalize_padded(g.float().contiguous(), None, None, None, ctx.Cp), None, None, None
+
+
+def to_field_padded(x_nchw, Cp):
+    return _ToFieldPadded.apply(x_nchw, Cp)
+
+
+def from_field_padded(field, C, H, W):
+    return _FromFieldPadded.apply(field, C, H, W)
+
+
+def pad8(C):
+    return (C + 7) // 8 * 8

@@ -513,3 +513,79 @@ def weights_prepare(descs, first_block, ndesc, total_blocks):
     assert first_block.is_cuda and first_block.dtype == torch.int32 and first_block.numel() == ndesc + 1
     check(_lib.lib().bgr_weights_prepare(ptr(descs), ptr(first_block), ndesc, total_blocks, stream_ptr()))
 
+
+
+# ---------------------------------------------------------------------------------------------
+# Deconv / Deconv1x decoders and odd-sized, odd-channel-count fields (csrc/deconv.cu)
+# ---------------------------------------------------------------------------------------------
+def zero_stuff2(x, H, W):
+    """[N,h,w,C] -> [N,H,W,C] with y[:, 2i, 2j] = x[:, i, j] and zeros elsewhere (ConvTranspose2d s2 as a conv)."""
+    N, h, w, C, ldx = _nhwc_view(x)
+    y = act_empty((N, H, W, C), x.device)
+    check(_lib.lib().bgr_zero_stuff2(ptr(x), N, h, w, C, ldx, ptr(y), H, W, _nhwc_view(y)[4], stream_ptr()))
+    return y
+
+
+def zero_stuff2_bwd(gy, h, w):
+    N, H, W, C, ldy = _nhwc_view(gy)
+    gx = act_empty((N, h, w, C), gy.device)
+    check(_lib.lib().bgr_zero_stuff2_bwd(ptr(gy), N, h, w, C, H, W, ldy, ptr(gx), _nhwc_view(gx)[4], stream_ptr()))
+    return gx
+
+
+def avgpool2_fwd(x, pad, act, slope=0.2):
+    """nn.AvgPool2d(2, stride=1, padding=pad) [+ LeakyReLU]."""
+    N, H, W, C, ldx = _nhwc_view(x)
+    y = act_empty((N, H + 2 * pad - 1, W + 2 * pad - 1, C), x.device)
+    check(_lib.lib().bgr_avgpool2_fwd(ptr(x), N, H, W, C, ldx, int(pad), int(act), c_float(slope), ptr(y),
+                                      _nhwc_view(y)[4], stream_ptr()))
+    return y
+
+
+def avgpool2_bwd(gy, yout, in_shape, pad, act, slope=0.2):
+    N, H, W, C = in_shape
+    ldg = _nhwc_view(gy)[4]
+    ldo = _nhwc_view(yout)[4] if act else 0
+    gx = act_empty((N, H, W, C), gy.device)
+    check(_lib.lib().bgr_avgpool2_bwd(ptr(gy), ldg, ptr(yout) if act else ctypes.c_void_p(0), ldo, N, H, W, C, int(pad),
+                                      int(act), c_float(slope), ptr(gx), _nhwc_view(gx)[4], stream_ptr()))
+    return gx
+
+
+def nhwc_to_field(x):
+    """bf16 NHWC [N,H,W,C] -> field [N,ceil(H/2),ceil(W/2),4C] (zero row / column for odd H / W)."""
+    N, H, W, C, ldx = _nhwc_view(x)
+    f = torch.empty((N, (H + 1) // 2, (W + 1) // 2, 4 * C), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().bgr_nhwc_to_field(ptr(x), N, H, W, C, ldx, ptr(f), stream_ptr()))
+    return f
+
+
+def field_to_nhwc(field, H, W):
+    N, H2, W2, C4 = field.shape
+    assert field.is_contiguous() and field.dtype == torch.bfloat16 and H2 == (H + 1) // 2 and W2 == (W + 1) // 2
+    y = act_empty((N, H, W, C4 // 4), field.device)
+    check(_lib.lib().bgr_field_to_nhwc(ptr(field), N, H, W, C4 // 4, ptr(y), _nhwc_view(y)[4], stream_ptr()))
+    return y
+
+
+def stage_normalize_padded(src, channels, shift, scale, Cp):
+    """fp32 NCHW [B,Cf,H,W] of any size -> field [B,ceil(H/2),ceil(W/2),4*Cp], zero beyond the selected
+    channels and beyond H, W; shift / scale fp32 device [C] or both None (plain cast)."""
+    assert src.is_cuda and src.is_contiguous() and src.dim() == 4 and src.dtype == torch.float32
+    B, Cf, H, W = src.shape
+    channels = list(range(Cf)) if channels is None else [int(c) for c in channels]
+    C = len(channels)
+    if shift is not None:
+        assert shift.dtype == scale.dtype == torch.float32 and shift.numel() == scale.numel() == C
+    f = torch.empty((B, (H + 1) // 2, (W + 1) // 2, 4 * Cp), dtype=torch.bfloat16, device=src.device)
+    check(_lib.lib().bgr_stage_normalize_padded(ptr(src), B, Cf, H, W, int_array(channels), C, ptr(shift), ptr(scale),
+                                                ptr(f), int(Cp), stream_ptr()))
+    return f
+
+
+def field_to_nchw_padded(field, C, H, W):
+    N, H2, W2, C4 = field.shape
+    assert field.is_contiguous() and field.dtype == torch.bfloat16 and H2 == (H + 1) // 2 and W2 == (W + 1) // 2
+    out = torch.empty((N, C, H, W), dtype=torch.float32, device=field.device)
+    check(_lib.lib().bgr_field_to_nchw_padded(ptr(field), ptr(out), N, C, C4 // 4, H, W, stream_ptr()))
+    return out

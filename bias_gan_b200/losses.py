@@ -95,10 +95,18 @@ class GANLoss:
 
 
 class L1LossField(nn.Module):
-    """nn.L1Loss (train_gan.py:146) on two fields in the same (space-to-depth bf16) layout."""
+    """nn.L1Loss (train_gan.py:146) on two fields in the same (space-to-depth bf16) layout.
+    elements_per_sample = C*H*W of the real tensors when the fields carry zero padding (odd sizes, channel
+    counts padded to 8): the padding contributes |0 - 0| to the sum and must not count in the mean."""
+
+    def __init__(self, elements_per_sample=None):
+        super().__init__()
+        self.elements_per_sample = elements_per_sample
 
     def forward(self, fake_field, real_field):
-        return F_.l1_loss(fake_field, real_field)
+        if self.elements_per_sample is None:
+            return F_.l1_loss(fake_field, real_field)
+        return F_.regression_loss(fake_field, real_field, None, 0, 1.0, self.elements_per_sample * fake_field.shape[0])
 
 
 class RegressionLossField(nn.Module):

@@ -254,6 +254,33 @@ int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W
 int bgr_field_append_noise(const void* field, const float* noise, void* out, int N, int C, int nd, int Cp,
                            int H, int W, void* stream);
 
+/* ---- Deconv / Deconv1x decoders and odd-sized fields (deeplab.py:398-444,466-500; the reference's native
+ *      45-channel 19x37 GPSRO data) ------------------------------------------------------------------------
+ * nn.ConvTranspose2d(k3, s2, padding p, output_padding) = bgr_conv_fprop over the zero-stuffed input
+ * (y[n,2i,2j,:] = x[n,i,j,:], zeros elsewhere, output size H x W >= 2h-1 x 2w-1) with tap offsets p - k;
+ * bgr_zero_stuff2_bwd is the adjoint gx[n,i,j,:] = gy[n,2i,2j,:]. */
+int bgr_zero_stuff2(const void* x, int N, int h, int w, int C, int ldx, void* y, int H, int W, int ldy, void* stream);
+int bgr_zero_stuff2_bwd(const void* gy, int N, int h, int w, int C, int H, int W, int ldy, void* gx, int ldx,
+                        void* stream);
+/* nn.AvgPool2d(2, stride=1, padding=pad in {0,1}) (count_include_pad: always / 4) followed by LeakyReLU(slope)
+ * when act != 0 (deeplab.py:409-411,478-479,658): [N,H,W,C] -> [N,H+2pad-1,W+2pad-1,C]; bwd is the adjoint
+ * (yout = the stored forward output, needed for act'). */
+int bgr_avgpool2_fwd(const void* x, int N, int H, int W, int C, int ldx, int pad, int act, float slope, void* y,
+                     int ldy, void* stream);
+int bgr_avgpool2_bwd(const void* gy, int ldg, const void* yout, int ldo, int N, int H, int W, int C, int pad, int act,
+                     float slope, void* gx, int ldx, void* stream);
+/* bf16 NHWC [N,H,W,C] <-> field [N,ceil(H/2),ceil(W/2),4C]; odd H / W are padded with a zero row / column (the
+ * stride-2 pad-1 entry conv over the padded field equals the conv over the odd-sized image). */
+int bgr_nhwc_to_field(const void* x, int N, int H, int W, int C, int ldx, void* field, void* stream);
+int bgr_field_to_nhwc(const void* field, int N, int H, int W, int C, void* y, int ldy, void* stream);
+/* fp32 NCHW payload [B,Cf,H,W] of any size -> field with Cp >= C channels per sub-pixel (multiple of 8, <= 64;
+ * zero beyond C, beyond H, W): bf16(scale[i]*(src[channels[i]] - shift[i])) (shift = scale = NULL: plain cast;
+ * channels HOST array or NULL) — the stage step for the 45 x 19 x 37 GPSRO files; and the way back to the
+ * fp32 NCHW tensor the training script sees (first C of Cp channels, H x W real pixels). */
+int bgr_stage_normalize_padded(const float* src, int B, int Cf, int H, int W, const int* channels, int C,
+                               const float* shift, const float* scale, void* field, int Cp, void* stream);
+int bgr_field_to_nchw_padded(const void* field, float* nchw, int B, int C, int Cp, int H, int W, void* stream);
+
 /* Every derived weight copy of a model in one launch (what layouts.py / kernels.weight_to_gemm build one
  * parameter at a time after each optimizer step).  descs / first_block are DEVICE arrays: descriptor d owns
  * blocks [first_block[d], first_block[d+1]) of the 256-thread grid of total_blocks blocks.

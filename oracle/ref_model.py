@@ -5,6 +5,7 @@ bench.py's cpu_baseline / --impl reference legs.  Product code never imports it.
 Restates (state-dict keys identical, so weights interchange with the reference and the product):
   Sep / Blk / XceptionRef     src/deepCam/architecture/gpsro/deeplab.py:75-87, 90-143, 146-278
   Aspp / DeepLabRef           deeplab.py:322-342, 358-381 (Interpolate upsampler), 583-684
+  _Deconv / _Extension        deeplab.py:398-444, 466-500 (Deconv / Deconv1x upsamplers, native 19x37 fields)
   GeneratorRef / DiscriminatorRef   architecture/gpsro/deeplab_gan.py:12-39, 65-94
   GANLossRef                  src/deepCam/utils/losses.py:129-172
   gan_step_ref                src/deepCam/gpsro_train/train_gan.py:244-301 (one G+D step)
@@ -136,9 +137,59 @@ class _Upsample(nn.Module):
         return F.interpolate(x, size=size[2:], mode="bilinear", align_corners=True)
 
 
-class DeepLabRef(nn.Module):
-    def __init__(self, n_input, n_output, os=16):
+class _Deconv(nn.Module):
+    """DeconvUpsampler, deeplab.py:398-444: four ConvTranspose2d k3 s2 whose paddings / output paddings are
+    hard-wired for the 19x37 GPSRO fields (2x3 -> 3x6 -> 6x11 -> 10x19 -> 18x36), each followed by
+    normaliser, AvgPool2d(2, stride 1) and LeakyReLU (the last one bare)."""
+
+    def __init__(self, n_out, nn_pooling=True):
         super().__init__()
+        pool = (lambda: nn.AvgPool2d(2, stride=1, padding=0)) if nn_pooling else (lambda: nn.Identity())
+        act = lambda: nn.LeakyReLU(0.2, inplace=True)
+        self.deconv1 = nn.Sequential(nn.ConvTranspose2d(256, 256, 3, 2, 1, output_padding=(0, 1), bias=False),
+                                     nn.BatchNorm2d(256), pool(), act())
+        self.deconv2 = nn.Sequential(nn.ConvTranspose2d(256, 256, 3, 2, 0, output_padding=(1, 0), bias=False),
+                                     nn.BatchNorm2d(256), pool(), act())
+        self.conv1 = nn.Sequential(nn.Conv2d(304, 256, 3, 1, 1, bias=False), nn.BatchNorm2d(256), act(),
+                                   nn.Conv2d(256, 256, 3, 1, 1, bias=False), nn.BatchNorm2d(256), act(),
+                                   nn.Conv2d(256, 256, 1))
+        self.deconv3 = nn.Sequential(nn.ConvTranspose2d(256, 128, 3, 2, 1, output_padding=(1, 0), bias=False),
+                                     nn.BatchNorm2d(128), pool(), act())
+        self.last_deconv = nn.Sequential(nn.ConvTranspose2d(128, n_out, 3, 2, 1, output_padding=(1, 1), bias=False))
+        gain = nn.init.calculate_gain("leaky_relu", 0.2)
+        for m in self.modules():
+            if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+                nn.init.normal_(m.weight, 0.0, gain / math.sqrt(m.kernel_size[0] * m.kernel_size[1] * m.out_channels))
+
+    def forward(self, x, low, size):
+        x = self.deconv2(self.deconv1(x))
+        x = self.conv1(torch.cat((x, low), 1))
+        return self.last_deconv(self.deconv3(x))
+
+
+class _Extension(nn.Module):
+    """UpsamplerExtension, deeplab.py:466-500: full-resolution skip from the raw input."""
+
+    def __init__(self, n_in, n_out, nn_pooling=True):
+        super().__init__()
+        act = lambda: nn.LeakyReLU(0.2, inplace=True)
+        self.init_norm = nn.Sequential(nn.BatchNorm2d(128),
+                                       nn.AvgPool2d(2, stride=1, padding=1) if nn_pooling else nn.Identity(), act())
+        self.conv1 = nn.Sequential(nn.Conv2d(n_in, 64, 3, 1, 1, bias=False), nn.BatchNorm2d(64), act(),
+                                   nn.Conv2d(64, 128, 3, 1, 1, bias=False), nn.BatchNorm2d(128), act())
+        self.conv2 = nn.Sequential(nn.Conv2d(256, 64, 3, 1, 1, bias=False), nn.BatchNorm2d(64), act(),
+                                   nn.Conv2d(64, n_out, 3, 1, 1, bias=False))
+        _decoder_init(self)
+
+    def forward(self, inp, x):
+        skip = self.conv1(inp)
+        return self.conv2(torch.cat((self.init_norm(x), skip), 1))
+
+
+class DeepLabRef(nn.Module):
+    def __init__(self, n_input, n_output, os=16, upsampler_type="Interpolate"):
+        super().__init__()
+        self.upsampler_type = upsampler_type
         self.xception_features = XceptionRef(n_input, os)
         r = [1, 6, 12, 18] if os == 16 else [1, 12, 24, 36]
         self.aspp1, self.aspp2, self.aspp3, self.aspp4 = (Aspp(2048, 256, k) for k in r)
@@ -147,7 +198,16 @@ class DeepLabRef(nn.Module):
                                              nn.BatchNorm2d(256), nn.LeakyReLU(0.2))
         self.conv1, self.bn1 = nn.Conv2d(1280, 256, 1, bias=False), nn.BatchNorm2d(256)
         self.conv2, self.bn2 = nn.Conv2d(128, 48, 1, bias=False), nn.BatchNorm2d(48)
-        self.upsample = _Upsample(n_output)
+        if upsampler_type == "Interpolate":
+            self.upsample = _Upsample(n_output)
+        elif upsampler_type in ("Deconv", "Deconv1x"):
+            self.upsample = _Deconv(128 if upsampler_type == "Deconv1x" else n_output)
+            if upsampler_type == "Deconv1x":
+                self.upsample_extension = _Extension(n_input, n_output)
+            else:
+                self.final_pool = nn.AvgPool2d(2, stride=1, padding=1)
+        else:
+            raise NotImplementedError("Error, upsampler {} not implemented.".format(upsampler_type))
 
     def forward(self, inp):
         x, low = self.xception_features(inp)
@@ -155,7 +215,12 @@ class DeepLabRef(nn.Module):
         g = F.interpolate(self.global_avg_pool(x), size=x.shape[2:], mode="bilinear", align_corners=True)
         x = self.relu(self.bn1(self.conv1(torch.cat(parts + [g], 1))))
         low = self.relu(self.bn2(self.conv2(low)))
-        return self.upsample(x, low, inp.size())
+        x = self.upsample(x, low, inp.size())
+        if self.upsampler_type == "Deconv1x":     # deeplab.py:676-679
+            x = self.upsample_extension(inp, x)
+        elif self.upsampler_type == "Deconv":
+            x = self.final_pool(x)
+        return x
 
 
 class GeneratorRef(nn.Module):
@@ -163,7 +228,7 @@ class GeneratorRef(nn.Module):
     generator (`dist.rsample((B, nd, H, W))`), moved to the input's device and concatenated after
     the input channels (deeplab_gan.py:88-90)."""
 
-    def __init__(self, n_input, n_output, os=16, noise_type="Normal", noise_dimensions=0):
+    def __init__(self, n_input, n_output, os=16, noise_type="Normal", noise_dimensions=0, upsampler_type="Interpolate"):
         super().__init__()
         self.noise_dimensions = noise_dimensions
         if noise_type == "Uniform":
@@ -172,7 +237,7 @@ class GeneratorRef(nn.Module):
             self.dist = torch.distributions.normal.Normal(0.0, 1.0)
         else:
             raise NotImplementedError("Error, noise type {} not supported.".format(noise_type))
-        self.model = DeepLabRef(n_input + noise_dimensions, n_output, os)
+        self.model = DeepLabRef(n_input + noise_dimensions, n_output, os, upsampler_type)
 
     def forward(self, x):
         if self.noise_dimensions > 0:
@@ -182,10 +247,11 @@ class GeneratorRef(nn.Module):
 
 
 class DiscriminatorRef(nn.Module):
-    def __init__(self, n_input, input_size, os=16):
+    def __init__(self, n_input, input_size=None, os=16):
         super().__init__()
         self.xception_features = XceptionRef(n_input, os)
-        self.linear = nn.Linear(2048 * math.ceil(input_size[0] / os) * math.ceil(input_size[1] / os), 1)
+        feat = 12288 if input_size is None else 2048 * math.ceil(input_size[0] / os) * math.ceil(input_size[1] / os)
+        self.linear = nn.Linear(feat, 1)   # the reference hard-codes 12288 = 2048*2*3 (19x37 fields, deeplab_gan.py:21)
         self.sigmoid = nn.Sigmoid()
         _decoder_init(self)
         nn.init.xavier_uniform_(self.linear.weight, 1.0)

@@ -1,0 +1,148 @@
+"""Deconv / Deconv1x decoders and the reference's native data shape (45 channels x 19 x 37, local batch 4, the
+configuration of its only GAN run script, run_scripts/run_training_gan_coccobello.sh:36-54) on the sm_100a path.
+
+  * ConvTranspose2d(k3, s2, p, output_padding) as zero-stuffing + the tcgen05 implicit-GEMM conv: output, data
+    gradient and weight gradient against torch's conv_transpose2d for the four (p, output_padding) pairs the
+    decoder uses (deeplab.py:406-431);
+  * AvgPool2d(2, 1, pad) (+LeakyReLU) and the padded field conversions: against torch / bit-exact;
+  * whole generator + critic at 45 x 19 x 37 against the fp32 oracle (pinned to the reference's own modules by
+    tests/golden/deconv_golden.pt) AND directly against that golden output.
+"""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "deconv_golden.pt")
+
+
+def rel(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a @ b) / (a.norm() * b.norm() + 1e-30))
+
+
+def nhwc(x):
+    return x.permute(0, 2, 3, 1).contiguous()
+
+
+def nchw(x):
+    return x.permute(0, 3, 1, 2).contiguous()
+
+
+@pytest.fixture(scope="module")
+def dev():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return torch.device("cuda", 0)
+
+
+@pytest.mark.parametrize("h,w,Cin,Cout,p,op", [(2, 3, 256, 256, 1, (0, 1)), (2, 5, 256, 256, 0, (1, 0)),
+                                               (5, 10, 256, 128, 1, (1, 0)), (9, 18, 128, 48, 1, (1, 1)),
+                                               (24, 40, 64, 64, 1, (1, 1))])
+def test_conv_transpose_matches_torch(dev, h, w, Cin, Cout, p, op):
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(2)
+    x = torch.randn(3, Cin, h, w, generator=g).to(dev).bfloat16()
+    wt = (torch.randn(Cin, Cout, 3, 3, generator=g) / (Cin * 9) ** 0.5 * 2).to(dev).bfloat16().float()
+    xr, wr = x.float().requires_grad_(True), wt.clone().requires_grad_(True)
+    ref = F.conv_transpose2d(xr, wr, None, stride=2, padding=p, output_padding=op)
+    gy = torch.randn(ref.shape, generator=g).to(dev).bfloat16()
+    ref.backward(gy.float())
+    xp, wp = nhwc(x).requires_grad_(True), wt.clone().requires_grad_(True)
+    out = F_.conv_transpose2d(xp, wp, p, op)
+    assert tuple(out.shape) == (3, ref.shape[2], ref.shape[3], Cout)
+    out.backward(nhwc(gy))
+    assert rel(nchw(out), ref) < 4e-3
+    assert rel(nchw(xp.grad), xr.grad) < 4e-3
+    assert rel(wp.grad, wr.grad) < 1e-4
+
+
+@pytest.mark.parametrize("pad,act", [(0, True), (1, True), (1, False), (0, False)])
+def test_avgpool2(dev, pad, act):
+    from bias_gan_b200 import functional as F_
+    g = torch.Generator(device="cpu").manual_seed(3)
+    x = torch.randn(2, 128, 6, 11, generator=g).to(dev).bfloat16()
+    xr = x.float().requires_grad_(True)
+    ref = F.avg_pool2d(xr, 2, stride=1, padding=pad)
+    if act:
+        ref = F.leaky_relu(ref, 0.2)
+    gy = torch.randn(ref.shape, generator=g).to(dev).bfloat16()
+    ref.backward(gy.float())
+    xp = nhwc(x).requires_grad_(True)
+    out = F_.avgpool2(xp, pad, act)
+    out.backward(nhwc(gy))
+    assert rel(nchw(out), ref) < 4e-3 and rel(nchw(xp.grad), xr.grad) < 4e-3
+
+
+def test_padded_field_conversions_bit_exact(dev):
+    """45 x 19 x 37 -> field [N,10,19,4*48] and back: a permutation plus zero padding; the standardising variant
+    equals bf16(scale * (x - shift)) exactly (same two-step fp32 arithmetic as the stage kernel)."""
+    from bias_gan_b200 import kernels as K
+    g = torch.Generator(device="cpu").manual_seed(4)
+    x = (torch.randn(2, 45, 19, 37, generator=g) * 3 + 1).to(dev)
+    f = K.stage_normalize_padded(x, None, None, None, 48)
+    assert tuple(f.shape) == (2, 10, 19, 192)
+    want = torch.zeros(2, 20, 38, 48, device=dev, dtype=torch.bfloat16)
+    want[:, :19, :37, :45] = x.permute(0, 2, 3, 1).bfloat16()
+    want_f = want.view(2, 10, 2, 19, 2, 48).permute(0, 1, 3, 2, 4, 5).reshape(2, 10, 19, 192)
+    assert torch.equal(f, want_f)
+    assert torch.equal(K.field_to_nchw_padded(f, 45, 19, 37), x.bfloat16().float())
+    n = K.field_to_nhwc(f, 19, 37)
+    assert torch.equal(n, want[:, :19, :37])
+    assert torch.equal(K.nhwc_to_field(n), f)
+    ch = [44, 0, 3, 17, 9]
+    shift, scale = torch.randn(5, generator=g).to(dev), (0.5 + torch.rand(5, generator=g)).to(dev)
+    fs = K.stage_normalize_padded(x, ch, shift, scale, 8)
+    got = K.field_to_nchw_padded(fs, 5, 19, 37)
+    want_s = (scale.view(1, 5, 1, 1) * (x[:, ch] - shift.view(1, 5, 1, 1))).bfloat16().float()
+    assert torch.equal(got, want_s)
+
+
+@pytest.mark.parametrize("up", ["Deconv", "Deconv1x"])
+def test_native_configuration_against_oracle_and_reference_golden(dev, up):
+    from bias_gan_b200 import deeplab_gan as P
+    from oracle import ref_model as R
+    from oracle.seeded import seed_state, seeded_fields
+    gold = torch.load(GOLD, weights_only=False)
+    m = gold["meta"]
+    B, C, H, W = m["B"], m["C"], m["H"], m["W"]
+    x, y = seeded_fields(7, B, C, H, W)
+    x, y = x.to(dev), y.to(dev)
+    res = {}
+    for name in ("fp32", "autocast", "product"):
+        if name == "product":
+            G = seed_state(P.Generator(C, C, up, "Normal", 0), 11).to(dev).train()
+            D = seed_state(P.Discriminator(C), 12).to(dev).train()
+        else:
+            G = seed_state(R.GeneratorRef(C, C, upsampler_type=up), 11).to(dev).train()
+            D = seed_state(R.DiscriminatorRef(C), 12).to(dev).train()
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=(name == "autocast")):
+            fake = G(x)
+            logits, _ = D(fake)
+        fake, logits = fake.float(), logits.float()
+        loss = F.binary_cross_entropy_with_logits(logits, torch.ones_like(logits)) + F.l1_loss(fake, y)
+        loss.backward()
+        dec = torch.cat([p.grad.flatten().double() for n, p in G.named_parameters() if n.startswith("model.upsample")])
+        res[name] = (fake.detach(), logits.detach().flatten(), float(loss.detach()), dec)
+    f_r, lo_r, l_r, d_r = res["fp32"]
+    f_a, lo_a, l_a, d_a = res["autocast"]
+    f_p, lo_p, l_p, d_p = res["product"]
+    print("PARITY %s 45x19x37: G out rel product %.4f autocast %.4f | vs reference golden %.4f | loss %.4f / %.4f / %.4f | "
+          "decoder-grad cos %.4f / %.4f | logits %s vs %s"
+          % (up, rel(f_p, f_r), rel(f_a, f_r), rel(f_p.cpu(), gold[up]["fake"]), l_p, l_a, l_r, cos(d_p, d_r), cos(d_a, d_r),
+             lo_p.tolist(), lo_r.tolist()))
+    assert tuple(f_p.shape) == (B, C, H, W) and f_p.dtype == torch.float32
+    # the oracle on this GPU reproduces the reference's own output (golden from the reference modules, CPU)
+    assert rel(f_r.cpu(), gold[up]["fake"]) < 1e-3
+    assert rel(f_p, f_r) <= 1.5 * rel(f_a, f_r) + 1e-2
+    assert rel(f_p.cpu(), gold[up]["fake"]) <= 1.5 * rel(f_a, f_r) + 1e-2
+    assert abs(l_p - l_r) <= 1.5 * abs(l_a - l_r) + 3e-2 * abs(l_r)
+    assert cos(d_p, d_r) >= min(0.95, cos(d_a, d_r) - 0.03)

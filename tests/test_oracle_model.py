@@ -129,3 +129,49 @@ def test_gradient_penalty_matches_reference_golden():
     norm, head = gold["grad"]
     assert abs(float(g.double().norm()) - norm) <= 2e-3 * norm
     torch.testing.assert_close(g.flatten()[:8], head, rtol=5e-3, atol=1e-3 * norm / g.numel() ** 0.5)
+
+
+# ---- Deconv / Deconv1x upsamplers at the reference's native 45 x 19 x 37 configuration ------------------
+DECONV_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "deconv_golden.pt")
+
+
+@pytest.mark.parametrize("up", ["Deconv", "Deconv1x"])
+def test_deconv_oracle_matches_reference_golden(up):
+    """oracle/ref_model.py's restatement of DeconvUpsampler / UpsamplerExtension (deeplab.py:398-500) against
+    the vectors the reference's own, unmodified modules produced (tests/golden/make_deconv_golden.py):
+    state-dict keys, generator output, critic logits (Linear(12288,1)), loss and every gradient norm."""
+    gold = torch.load(DECONV_GOLD, weights_only=False)
+    m = gold["meta"]
+    B, C, H, W = m["B"], m["C"], m["H"], m["W"]
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    G = seed_state(R.GeneratorRef(C, C, upsampler_type=up), 11).train()
+    D = seed_state(R.DiscriminatorRef(C), 12).train()
+    assert sorted(G.state_dict()) == gold[up]["g_keys"] and sorted(D.state_dict()) == gold[up]["d_keys"]
+    x, y = seeded_fields(7, B, C, H, W)
+    fake = G(x)
+    logits, _ = D(fake)
+    loss = F.binary_cross_entropy_with_logits(logits, torch.ones_like(logits)) + F.l1_loss(fake, y)
+    loss.backward()
+    torch.testing.assert_close(fake.detach(), gold[up]["fake"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(logits.detach(), gold[up]["logits"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(loss.detach(), gold[up]["loss"], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(G.model.upsample.deconv1[1].running_mean, gold[up]["bn_rm"], rtol=1e-4, atol=1e-6)
+    for n, p in G.named_parameters():
+        norm, head = gold[up]["g_grads"][n]
+        assert abs(float(p.grad.double().norm()) - norm) <= 2e-3 * norm + 1e-9, n
+        torch.testing.assert_close(p.grad.flatten()[:8], head, rtol=5e-3, atol=1e-6 + 1e-3 * norm / max(p.numel(), 1) ** 0.5)
+
+
+@pytest.mark.parametrize("up", ["Deconv", "Deconv1x"])
+def test_product_deconv_state_dict_is_the_references(up):
+    """The product's Generator / Discriminator at the native configuration expose exactly the reference's
+    state-dict keys and shapes (golden g_keys / d_keys come from the reference's own modules), so `.cpt` files
+    interchange; construction needs no GPU."""
+    from bias_gan_b200 import deeplab_gan as P
+    gold = torch.load(DECONV_GOLD, weights_only=False)
+    C = gold["meta"]["C"]
+    G, D = P.Generator(C, C, up, "Normal", 0), P.Discriminator(C)
+    assert sorted(G.state_dict()) == gold[up]["g_keys"] and sorted(D.state_dict()) == gold[up]["d_keys"]
+    Gr = R.GeneratorRef(C, C, upsampler_type=up)
+    for k, v in Gr.state_dict().items():
+        assert tuple(G.state_dict()[k].shape) == tuple(v.shape), k
