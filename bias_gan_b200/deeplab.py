@@ -220,9 +220,10 @@ class ASPP_module(nn.Module):
         self.rate = rate
         nn.init.kaiming_normal_(self.atrous_convolution.weight)
 
-    def forward(self, x):
+    def forward(self, x, slot=None):
+        """slot: the ConcatBuffer slice the activated result is written into (no torch.cat afterwards)."""
         return F_.bn_act(F_.conv2d(x, self.atrous_convolution.weight, dilation=self.rate,
-                                   want_stats=F_.needs_stats(self.bn)), self.bn, act=True)
+                                   want_stats=F_.needs_stats(self.bn)), self.bn, act=True, slot=slot)
 
 
 class InterpolationUpsampler(nn.Module):
@@ -235,9 +236,13 @@ class InterpolationUpsampler(nn.Module):
                                        nn.Conv2d(256, n_output, 1))
         _init_decoder(self)
 
-    def forward(self, x, low_level_features, H, W):
-        x = F_.bilinear(x, int(math.ceil(H / 4)), int(math.ceil(W / 4)))
-        x = torch.cat((x, low_level_features), dim=3)
+    def forward(self, x, low_conv, low_bn, H, W):
+        """low_conv / low_bn: the raw 1x1-reduced low-level features and their normaliser; both halves of the
+        304-channel concat (deeplab.py:377) are written straight into one buffer."""
+        h4, w4 = int(math.ceil(H / 4)), int(math.ceil(W / 4))
+        c_low = (low_conv[0] if isinstance(low_conv, tuple) else low_conv).shape[-1]
+        cb = F_.ConcatBuffer(x.shape[0], h4, w4, (x.shape[-1], c_low), x.device)
+        x = cb.cat([F_.bilinear(x, h4, w4, slot=cb.slot(0)), F_.bn_act(low_conv, low_bn, act=True, slot=cb.slot(1))])
         lc = self.last_conv
         x = F_.bn_act(F_.conv2d(x, lc[0].weight, want_stats=F_.needs_stats(lc[1])), lc[1], act=True)
         x = F_.bn_act(F_.conv2d(x, lc[3].weight, want_stats=F_.needs_stats(lc[4])), lc[4], act=True)
@@ -388,17 +393,20 @@ class DeepLabv3_plus(nn.Module):
         H, W = hw if hw is not None else (2 * H2, 2 * W2)
         x, low = self.xception_features(field)
         h, w = x.shape[1], x.shape[2]
-        x1, x2, x3, x4 = self.aspp1(x), self.aspp2(x), self.aspp3(x), self.aspp4(x)
+        # the five ASPP branches write their 256 channels each into one 1280-channel buffer (deeplab.py:664)
+        cb = F_.ConcatBuffer(N, h, w, (256,) * 5, x.device)
+        parts = [m(x, slot=cb.slot(i)) for i, m in enumerate((self.aspp1, self.aspp2, self.aspp3, self.aspp4))]
         gp = self.global_avg_pool
         x5 = F_.bn_act(F_.conv2d(F_.global_avg_pool(x), gp[1].weight, want_stats=F_.needs_stats(gp[2])), gp[2], act=True)
-        x5 = F_.bilinear(x5, h, w)
-        x = torch.cat((x1, x2, x3, x4, x5), dim=3)
+        parts.append(F_.bilinear(x5, h, w, slot=cb.slot(4)))
+        x = cb.cat(parts)
         x = F_.bn_act(F_.conv2d(x, self.conv1.weight, want_stats=F_.needs_stats(self.bn1)), self.bn1, act=True)
-        low = F_.bn_act(F_.conv2d(low, self.conv2.weight, want_stats=F_.needs_stats(self.bn2)), self.bn2, act=True)
+        low_raw = F_.conv2d(low, self.conv2.weight, want_stats=F_.needs_stats(self.bn2))
         if self.upsampler_type == "Interpolate":
             if (H | W) & 1:
                 raise NotImplementedError("the Interpolate upsampler is built for even field sizes")
-            return self.upsample(x, low, H, W)
+            return self.upsample(x, low_raw, self.bn2, H, W)
+        low = F_.bn_act(low_raw, self.bn2, act=True)
         x = self.upsample(x, low)
         if self.upsampler_type == "Deconv1x":      # deeplab.py:676-677
             x = self.upsample_extension(F_.field_to_nhwc(field, H, W), x)

@@ -175,12 +175,14 @@ class _BNAct(torch.autograd.Function):
     """out = act(BatchNorm_train(y) [+ res]) with batch statistics (nn.BatchNorm2d training mode)."""
 
     @staticmethod
-    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act, sums, nbt, dual):
+    def forward(ctx, y, gamma, beta, res, running_mean, running_var, eps, momentum, act, sums, nbt, dual, slot=None):
         M = y.numel() // y.shape[-1]
         if sums is None:
             sums = K.bn_stats(y)
         mean, invstd, a, b = K.bn_finalize(sums, M, gamma, beta, eps, momentum, running_mean, running_var, nbt)
-        out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
+        out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE, out=slot.view if slot is not None else None)
+        if slot is not None:
+            out = out[...]      # a fresh view object of the concat buffer's channel slice
         ctx.has_res = res is not None
         # without a residual input act' = sign(a*y + b) is recomputed in backward (RECOMPUTE_BN_BWD): the stored
         # output is not read and no dyh tensor makes the round trip between the two passes
@@ -209,7 +211,7 @@ class _BNAct(torch.autograd.Function):
         ggamma = sums[C:] if ctx.needs_input_grad[1] else None
         gbeta = sums[:C] if ctx.needs_input_grad[2] else None
         gres = dyh if (ctx.has_res and ctx.needs_input_grad[3]) else None
-        return dx, ggamma, gbeta, gres, None, None, None, None, None, None, None, None
+        return dx, ggamma, gbeta, gres, None, None, None, None, None, None, None, None, None
 
 
 class _BNActDepthwise(torch.autograd.Function):
@@ -266,14 +268,16 @@ class _AffineAct(torch.autograd.Function):
     (--disable_batchnorm, train_gan.py:125: gamma = beta = None, mean 0, invstd 1)."""
 
     @staticmethod
-    def forward(ctx, y, gamma, beta, mean, invstd, res, act, dual):
+    def forward(ctx, y, gamma, beta, mean, invstd, res, act, dual, slot=None):
         C = y.shape[-1]
         if gamma is None:
             a, b = _const_vec(1.0, C, y.device), _const_vec(0.0, C, y.device)
         else:
             a = (gamma.detach() * invstd).float().contiguous()
             b = (beta.detach() - mean * a).float().contiguous()
-        out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE)
+        out = K.bn_apply(y, a, b, res=res, act=act, slope=SLOPE, out=slot.view if slot is not None else None)
+        if slot is not None:
+            out = out[...]
         ctx.save_for_backward(y, out if act else None, gamma, mean, invstd)
         ctx.act, ctx.has_res = act, res is not None
         if dual:
@@ -294,7 +298,7 @@ class _AffineAct(torch.autograd.Function):
         ggamma = grads[C:] if (not identity and ctx.needs_input_grad[1]) else None
         gbeta = grads[:C] if (not identity and ctx.needs_input_grad[2]) else None
         gres = dyh if (ctx.has_res and ctx.needs_input_grad[5]) else None
-        return (dyh if identity else dx), ggamma, gbeta, None, None, gres, None, None
+        return (dyh if identity else dx), ggamma, gbeta, None, None, gres, None, None, None
 
 
 _consts = {}
@@ -328,7 +332,47 @@ def _nbt(bn):
     return t
 
 
-def bn_act(y, bn, res=None, act=True, sums=None, dual=False):
+class ConcatBuffer:
+    """A channel concatenation written in place: producers (bn_act / bilinear with slot=...) store their result
+    straight into their channel slice of one NHWC buffer (the TMA-store / vector-store epilogues take a pixel
+    stride), `cat()` hands the whole buffer to the consumer, and in backward the consumer's gradient is split
+    into slice *views* -- no copy in either direction (torch.cat((x1, ..., x5), 1) of deeplab.py:664 and :377)."""
+
+    class Slot:
+        def __init__(self, view):
+            self.view = view
+
+    def __init__(self, N, H, W, channels, device):
+        self.channels = list(channels)
+        self.buf = K.act_empty((N, H, W, sum(self.channels)), device)
+        self.offsets = [sum(self.channels[:i]) for i in range(len(self.channels))]
+
+    def slot(self, i):
+        a = self.offsets[i]
+        return ConcatBuffer.Slot(self.buf[..., a:a + self.channels[i]])
+
+    def cat(self, parts):
+        return _CatInPlace.apply(self, *parts)
+
+
+class _CatInPlace(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cb, *parts):
+        for i, p in enumerate(parts):   # every part must already live in its slice
+            want = cb.buf[..., cb.offsets[i]:cb.offsets[i] + cb.channels[i]]
+            if p.data_ptr() != want.data_ptr() or tuple(p.shape) != tuple(want.shape) or p.stride() != want.stride():
+                raise RuntimeError("ConcatBuffer.cat: part %d was not produced into its slot" % i)
+        ctx.cb = cb
+        return cb.buf[...]
+
+    @staticmethod
+    def backward(ctx, g):
+        cb = ctx.cb
+        g = _bf16c(g)
+        return (None,) + tuple(g[..., a:a + c] for a, c in zip(cb.offsets, cb.channels))
+
+
+def bn_act(y, bn, res=None, act=True, sums=None, dual=False, slot=None):
     """`bn` is a torch.nn.BatchNorm2d-compatible module (weight, bias, running_*, eps, momentum).
     `y` may be the (y, sums) pair of a conv called with want_stats=True.
     dual=True returns two handles (out, out') of the same tensor for a result that feeds two paths
@@ -341,14 +385,14 @@ def bn_act(y, bn, res=None, act=True, sums=None, dual=False):
         if not isinstance(bn, torch.nn.Identity):
             raise NotImplementedError("normalizer %s: BatchNorm2d and Identity are built" % type(bn).__name__)
         C = y.shape[-1]
-        return _AffineAct.apply(y, None, None, _const_vec(0.0, C, y.device), _const_vec(1.0, C, y.device), res, act, dual)
+        return _AffineAct.apply(y, None, None, _const_vec(0.0, C, y.device), _const_vec(1.0, C, y.device), res, act, dual, slot)
     if bn.training:
         return _BNAct.apply(y, bn.weight, bn.bias, res, bn.running_mean, bn.running_var, bn.eps,
-                            bn.momentum, act, sums, _nbt(bn), dual)
+                            bn.momentum, act, sums, _nbt(bn), dual, slot)
     with torch.no_grad():
         invstd = torch.rsqrt(bn.running_var + bn.eps).float().contiguous()
         mean = bn.running_mean.float().contiguous()
-    return _AffineAct.apply(y, bn.weight, bn.bias, mean, invstd, res, act, dual)
+    return _AffineAct.apply(y, bn.weight, bn.bias, mean, invstd, res, act, dual, slot)
 
 
 class _Subsample2(torch.autograd.Function):
@@ -368,8 +412,10 @@ def subsample2(x):
 
 class _Bilinear(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, H, W, s2d):
+    def forward(ctx, x, H, W, s2d, slot=None):
         ctx.cfg = (tuple(x.shape), H, W, s2d)
+        if slot is not None:
+            return K.bilinear_fwd(x, H, W, out=slot.view, s2d=s2d)[...]
         return K.bilinear_fwd(x, H, W, s2d=s2d)
 
     @staticmethod
@@ -377,14 +423,14 @@ class _Bilinear(torch.autograd.Function):
         shape, H, W, s2d = ctx.cfg
         g = _bf16c(g)
         if shape[1] == 1 and shape[2] == 1 and not s2d:   # broadcast of a 1x1 map: the adjoint is the pixel sum
-            return K.gap_fwd(g).to(torch.bfloat16).view(shape), None, None, None
-        return K.bilinear_bwd(g, shape, H, W, s2d=s2d).to(torch.bfloat16), None, None, None
+            return K.gap_fwd(g).to(torch.bfloat16).view(shape), None, None, None, None
+        return K.bilinear_bwd(g, shape, H, W, s2d=s2d).to(torch.bfloat16), None, None, None, None
 
 
-def bilinear(x, H, W, s2d=False):
+def bilinear(x, H, W, s2d=False, slot=None):
     """F.interpolate(x, (H, W), mode='bilinear', align_corners=True) on NHWC; s2d=True writes the
-    2x2 space-to-depth field layout [N, H/2, W/2, 4C]."""
-    return _Bilinear.apply(x, H, W, s2d)
+    2x2 space-to-depth field layout [N, H/2, W/2, 4C]; slot = a ConcatBuffer slot to write into."""
+    return _Bilinear.apply(x, H, W, s2d, slot)
 
 
 class _GlobalAvgPool(torch.autograd.Function):

