@@ -8,6 +8,7 @@
 // added in lane order -> one partial row per block in a workspace [rows][2C] -> the finalize /
 // coefficient kernels add the rows in index order in fp64.  No floating-point atomics anywhere.
 #include <cstdlib>
+#include <cooperative_groups.h>
 #include <cuda_bf16.h>
 
 #include "bgr_internal.h"
@@ -215,14 +216,14 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __res
 // a*x + b (the activated tensor was never stored, see bgr_dw_fwd_bn); then `out` carries a and
 // `out + C` ... is unused: a, b come in through `xa`, `xb`.
 template <int ACT>
-__global__ void __launch_bounds__(256, 3)   // 85 registers: three blocks per SM (was 91-96 -> two, latency-bound)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ g2,
-                     int ldg2, const __nv_bfloat16* __restrict__ out,
-                     int ldo, const float* __restrict__ xa, const float* __restrict__ xb,
-                     const __nv_bfloat16* __restrict__ x, int ldx,
-                     const float* __restrict__ mean, const float* __restrict__ invstd,
-                     __nv_bfloat16* __restrict__ dyh, int ldd, long M, int C, int rows_per_block, float slope,
-                     float* __restrict__ part /* [gridDim.x][2][C] */) {
+__device__ __forceinline__ void
+bn_bwd_reduce_body(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ g2,
+                   int ldg2, const __nv_bfloat16* __restrict__ out,
+                   int ldo, const float* __restrict__ xa, const float* __restrict__ xb,
+                   const __nv_bfloat16* __restrict__ x, int ldx,
+                   const float* __restrict__ mean, const float* __restrict__ invstd,
+                   __nv_bfloat16* __restrict__ dyh, int ldd, long M, int C, int rows_per_block, float slope,
+                   float* __restrict__ part /* [gridDim.x][2][C] */) {
   extern __shared__ float sh[];   // [R][2][C]
   const RowGroupMap m(C);
   const long r0 = long(blockIdx.x) * rows_per_block;
@@ -287,13 +288,25 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
   block_partial_flush(sh, C, m.R, part);
 }
 
+template <int ACT>
+__global__ void __launch_bounds__(256, 3)   // 85 registers: three blocks per SM (was 91-96 -> two, latency-bound)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ g2,
+                     int ldg2, const __nv_bfloat16* __restrict__ out,
+                     int ldo, const float* __restrict__ xa, const float* __restrict__ xb,
+                     const __nv_bfloat16* __restrict__ x, int ldx,
+                     const float* __restrict__ mean, const float* __restrict__ invstd,
+                     __nv_bfloat16* __restrict__ dyh, int ldd, long M, int C, int rows_per_block, float slope,
+                     float* __restrict__ part /* [gridDim.x][2][C] */) {
+  bn_bwd_reduce_body<ACT>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
+}
+
 // backward, pass 2: dx = gamma*invstd * (dyh - s1/M - xhat * s2/M), xhat = (x - mean)*invstd.
 // Per-channel fp32 coefficients (c0 = gamma*invstd, k1 = s1/M, k2 = s2/M, mean, invstd) are
 // prepared by a tiny kernel so the streaming pass has no fp64 and only vector loads.
-__global__ void __launch_bounds__(256)
-bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ invstd,
-                   const float* __restrict__ gamma, const float* __restrict__ part, int rows,
-                   long M, int C, float* __restrict__ coef /* [7][C] */) {
+__device__ __forceinline__ void
+bn_bwd_coef_body(const float* __restrict__ mean, const float* __restrict__ invstd,
+                 const float* __restrict__ gamma, const float* __restrict__ part, int rows,
+                 long M, int C, float* __restrict__ coef /* [7][C] */) {
   int c;
   double s1, s2;
   if (!ordered_row_sums(part, rows, C, &c, &s1, &s2)) return;
@@ -304,6 +317,13 @@ bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ inv
   coef[4 * C + c] = invstd[c];
   coef[5 * C + c] = float(s1);   // dL/dbeta
   coef[6 * C + c] = float(s2);   // dL/dgamma
+}
+
+__global__ void __launch_bounds__(256)
+bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ invstd,
+                   const float* __restrict__ gamma, const float* __restrict__ part, int rows,
+                   long M, int C, float* __restrict__ coef /* [7][C] */) {
+  bn_bwd_coef_body(mean, invstd, gamma, part, rows, M, C, coef);
 }
 
 __global__ void __launch_bounds__(256, 4)   // 64 registers (4 bytes of spill): 552 -> 513 us per 453 MB BatchNorm backward
@@ -429,6 +449,130 @@ static int env_int(const char* name, int dflt) {
   return v && *v ? atoi(v) : dflt;
 }
 
+// ---------------------------------------------------------------- backward, all passes in one cooperative launch
+// pass 1 (partial rows) -> grid barrier -> coefficients (blocks 0 .. ceil(C/16)-1) -> grid barrier -> pass 2 over the
+// SAME rows with the same thread mapping, so g and x come back from L2 (a 48x72x728 mid-flow tensor is 40 MB; the
+// three-kernel version paid two more launches and their ramps on 30 us kernels).  dyh == NULL: pass 2 recomputes
+// dyh from g (and g2) and x exactly as pass 1 rounded it; dyh != NULL: pass 1 stores it and pass 2 reads it back.
+template <int ACT>
+__global__ void __launch_bounds__(256, 3)
+bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ g2,
+                    int ldg2, const __nv_bfloat16* __restrict__ out,
+                    int ldo, const float* __restrict__ xa, const float* __restrict__ xb,
+                    const __nv_bfloat16* __restrict__ x, int ldx,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    __nv_bfloat16* __restrict__ dyh, __nv_bfloat16* __restrict__ dx, int ldd, long M, int C,
+                    int rows_per_block, float slope, float* __restrict__ part, float* __restrict__ coef) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  bn_bwd_reduce_body<ACT>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
+  __threadfence();
+  grid.sync();
+  if (int(blockIdx.x) * kRsCh < C) bn_bwd_coef_body(mean, invstd, gamma, part, int(gridDim.x), M, C, coef);
+  __threadfence();
+  grid.sync();
+  const RowGroupMap m(C);
+  const long r0 = long(blockIdx.x) * rows_per_block;
+  const long r1 = min(r0 + rows_per_block, M);
+  for (int gi = threadIdx.x % m.G; gi < m.G; gi += (m.G >= 256 ? 256 : m.G)) {
+    const int r = m.G >= 256 ? 0 : threadIdx.x / m.G;
+    if (r >= m.R) break;
+    // dx = c0*(v - k1 - (x - mu)*k2*is) folded to c0*v + A*x + B
+    float c0[8], A[8], B[8], ca[8], cb[8];
+    {
+      float k1[8], k2[8], mu[8], is[8];
+      load8f(coef + gi * 8, c0);
+      load8f(coef + C + gi * 8, k1);
+      load8f(coef + 2 * C + gi * 8, k2);
+      load8f(coef + 3 * C + gi * 8, mu);
+      load8f(coef + 4 * C + gi * 8, is);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float k2i = k2[j] * is[j];
+        A[j] = -c0[j] * k2i;
+        B[j] = c0[j] * (k2i * mu[j] - k1[j]);
+      }
+    }
+    if (ACT == 2) {
+      load8f(xa + gi * 8, ca);
+      load8f(xb + gi * 8, cb);
+    }
+    auto one = [&](long row, const uint4& du, const uint4& xu, const uint4& ou) {
+      float d[8], xv[8], ov[8];
+      unpack8(du, d);
+      unpack8(xu, xv);
+      if (dyh == nullptr) {   // rebuild the rounded dyh of pass 1
+        if (g2 != nullptr) {
+          float hv[8];
+          unpack8(*reinterpret_cast<const uint4*>(g2 + row * ldg2 + gi * 8), hv);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) d[j] += hv[j];
+        }
+        if (ACT == 1) unpack8(ou, ov);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float v = d[j];
+          if (ACT == 1) v = ov[j] > 0.f ? v : slope * v;
+          if (ACT == 2) v = fmaf(ca[j], xv[j], cb[j]) > 0.f ? v : slope * v;
+          d[j] = __bfloat162float(__float2bfloat16_rn(v));
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = fmaf(c0[j], d[j], fmaf(A[j], xv[j], B[j]));
+      *reinterpret_cast<uint4*>(dx + row * ldd + gi * 8) = pack8(d);
+    };
+    const __nv_bfloat16* src = dyh != nullptr ? dyh : g;
+    const int lds = dyh != nullptr ? ldd : ldg;
+    const bool need_out = (ACT == 1) && dyh == nullptr;
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    long row = r0 + r;
+    for (; row + m.R < r1; row += 2 * m.R) {
+      const long row2 = row + m.R;
+      const uint4 d0 = *reinterpret_cast<const uint4*>(src + row * lds + gi * 8);
+      const uint4 d1 = *reinterpret_cast<const uint4*>(src + row2 * lds + gi * 8);
+      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + gi * 8);
+      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + gi * 8);
+      const uint4 o0 = need_out ? *reinterpret_cast<const uint4*>(out + row * ldo + gi * 8) : z4;
+      const uint4 o1 = need_out ? *reinterpret_cast<const uint4*>(out + row2 * ldo + gi * 8) : z4;
+      one(row, d0, x0, o0);
+      one(row2, d1, x1, o1);
+    }
+    if (row < r1)
+      one(row, *reinterpret_cast<const uint4*>(src + row * lds + gi * 8),
+          *reinterpret_cast<const uint4*>(x + row * ldx + gi * 8),
+          need_out ? *reinterpret_cast<const uint4*>(out + row * ldo + gi * 8) : z4);
+    if (m.G < 256) break;
+  }
+}
+
+// Largest co-resident grid of the fused kernel on the current device (cached per kernel instance and device).
+template <int ACT>
+static int fused_max_grid(size_t smem) {
+  static int cache[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  if (cache[dev] == 0) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bn_bwd_fused_kernel<ACT>, 256, 16 * 1024) != cudaSuccess)
+      per_sm = 0;
+    cache[dev] = per_sm > 0 ? per_sm * sm_count() : -1;
+  }
+  (void)smem;
+  return cache[dev] > 0 ? cache[dev] : 0;
+}
+
+template <int ACT>
+static int launch_bn_bwd_fused(const __nv_bfloat16* G, int ldg, const __nv_bfloat16* G2, int ldg2, const __nv_bfloat16* O,
+                               int ldo, const float* xa, const float* xb, const __nv_bfloat16* X, int ldx,
+                               const float* mean, const float* invstd, const float* gamma, __nv_bfloat16* D,
+                               __nv_bfloat16* DX, int ldd, long M, int C, int rpb, int grid, float slope, float* part,
+                               float* coef, size_t rsm, cudaStream_t st) {
+  void* args[] = {&G, &ldg, &G2, &ldg2, &O, &ldo, &xa, &xb, &X, &ldx, &mean, &invstd, &gamma, &D, &DX, &ldd, &M, &C,
+                  &rpb, &slope, &part, &coef};
+  BGR_CUDA_OK(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_bwd_fused_kernel<ACT>), dim3(grid), dim3(256), args, rsm, st));
+  ++g_launch_count;
+  return BGR_OK;
+}
+
 // grid / block of the (channel group, rows) streaming kernels
 static void rowgroup_launch(long M, int C, int* grid, int* block) {
   static const int min_rows = env_int("BGR_EW_ROWS", 4), cap = env_int("BGR_EW_CAP", 16);   // tuning knobs
@@ -525,6 +669,22 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
   auto O = static_cast<const __nv_bfloat16*>(out);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto D = static_cast<__nv_bfloat16*>(dyh);
+  auto DXp = static_cast<__nv_bfloat16*>(dx);
+  if (D == nullptr && act == 1) return fail(BGR_ERR_ARG, "bn_backward: dyh may be NULL only on the recompute path");
+  // BGR_BN_BWD_FUSED=1: one cooperative launch (pass 1 -> grid barrier -> coefficients -> grid barrier -> pass 2 over
+  // the same rows out of L2).  Measured on B200 and NOT adopted (profiles/r02_bn_backward_fused.txt): the two grid
+  // barriers and the one-wave grid of the second pass (444 x 256 threads instead of 2368 blocks) cost more than
+  // the two saved launches -- 77.8 vs 74.8 us at the 48x72x728 mid-flow shape, 502 vs 474 us at 384x576x128, and
+  // the step 129.5 vs 126.8 ms.  Kept opt-in for re-measurement.
+  static const int use_fused = env_int("BGR_BN_BWD_FUSED", 0);
+  if (use_fused) {
+    const int cap = act == 2 ? fused_max_grid<2>(rsm) : (act ? fused_max_grid<1>(rsm) : fused_max_grid<0>(rsm));
+    if (cap >= grid && grid * kRsCh >= C) {
+      if (act == 2) return launch_bn_bwd_fused<2>(G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, gamma, D, DXp, ldd, M, C, rpb, grid, slope, part, coef_ws, rsm, st);
+      if (act) return launch_bn_bwd_fused<1>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, gamma, D, DXp, ldd, M, C, rpb, grid, slope, part, coef_ws, rsm, st);
+      return launch_bn_bwd_fused<0>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, gamma, D, DXp, ldd, M, C, rpb, grid, slope, part, coef_ws, rsm, st);
+    }
+  }
   if (act == 2) bn_bwd_reduce_kernel<2><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
   else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
   else bn_bwd_reduce_kernel<0><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
@@ -534,11 +694,10 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
   int agrid, ablock;
   rowgroup_launch(M, C, &agrid, &ablock);
   if (D == nullptr) {
-    if (act == 1) return fail(BGR_ERR_ARG, "bn_backward: dyh may be NULL only on the recompute path");
-    bn_bwd_apply_recompute_kernel<<<agrid, ablock, 0, st>>>(G, ldg, G2, ldg2, X, ldx, xa, xb, coef_ws, static_cast<__nv_bfloat16*>(dx),
+    bn_bwd_apply_recompute_kernel<<<agrid, ablock, 0, st>>>(G, ldg, G2, ldg2, X, ldx, xa, xb, coef_ws, DXp,
                                                             ldd, M, C, slope, act == 2);
   } else {
-    bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(D, X, ldx, coef_ws, static_cast<__nv_bfloat16*>(dx), ldd, M, C);
+    bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(D, X, ldx, coef_ws, DXp, ldd, M, C);
   }
   BGR_LAUNCH_OK();
   return BGR_OK;

@@ -220,3 +220,30 @@ def test_against_compiled_reference(filename):
             assert torch.equal(a, b)
             np.testing.assert_array_equal(orc.read_samples(filename, [i], split)[0].reshape(a.shape), a.numpy())
         ref.finalize_file(); ours.finalize_file()
+
+
+@pytest.mark.gpu
+def test_enable_disable_p2p(tmp_path):
+    """numpy_reader.enable_p2p / disable_p2p (numpy_reader.cpp:17-56): all-pairs peer access, idempotent, leaves the
+    current device alone, and the reader still delivers afterwards.  With one visible GPU there are no pairs and
+    both calls succeed; with several, a peer copy between device 0 and 1 must work once enabled."""
+    import torch
+    from bias_gan_b200 import numpy_reader as nr
+    a = np.arange(2 * 3 * 5, dtype=np.float32).reshape(2, 3, 5)
+    f = str(tmp_path / "p2p.npy")
+    np.save(f, a)
+    cur = torch.cuda.current_device()
+    r = nr.numpy_reader(False, 0)
+    r.enable_p2p()
+    r.enable_p2p()          # already enabled pairs are not an error
+    assert torch.cuda.current_device() == cur
+    r.parse(f); r.init_file(f)
+    t = r.get_sample(0)
+    r.finalize_file()
+    assert np.array_equal(t.cpu().numpy(), a)
+    if torch.cuda.device_count() >= 2 and torch.cuda.can_device_access_peer(0, 1):
+        u = t.to("cuda:1")
+        assert np.array_equal(u.cpu().numpy(), a)
+    r.disable_p2p()
+    r.disable_p2p()
+    assert torch.cuda.current_device() == cur
