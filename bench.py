@@ -507,6 +507,9 @@ def main():
     ap.add_argument("--cold", action="store_true", help="ingest: also time a first pass after dropping the page cache")
     ap.add_argument("--no-step", action="store_true", help="ingest: reader + stage only, no training step behind them")
     ap.add_argument("--no-ingest", action="store_true", help="skip the reader legs of the default line")
+    ap.add_argument("--no-grad-sync", action="store_true",
+                    help="control run for the scaling analysis: N ranks, gradient all-reduce disabled (NOT data-parallel "
+                         "training; separates NCCL time from the slowest-GPU power-cap effect)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--faithful", action="store_true", help="reference-faithful schedule (no lean shortcuts)")
     ap.add_argument("--no-graph", action="store_true", help="launch the step kernel by kernel instead of replaying "
@@ -545,6 +548,8 @@ def main():
     D = Discriminator(C, os=16, input_size=(H, W)).to(dev).train()
     if world > 1:
         cm.DistributedModel(G); cm.DistributedModel(D)
+        if args.no_grad_sync:
+            G.grad_sync.enabled = D.grad_sync.enabled = False
     g_opt = torch.optim.AdamW(G.parameters(), lr=1e-4, eps=1e-8, weight_decay=1e-5, fused=True, capturable=True)
     d_opt = torch.optim.AdamW(D.parameters(), lr=1e-4, eps=1e-8, weight_decay=1e-5, fused=True, capturable=True)
     crit_gan, crit_reg = GANLoss("ModifiedMinMax", B, dev), L1LossField()
@@ -697,6 +702,8 @@ def main():
                                    "DeepLabv3+/Xception G (Interpolate) + Xception D, AdamW" % (args.config, H, W, B),
                        "global_batch": B * world, "parallelism": "dp%d" % world,
                        "schedule": "faithful" if args.faithful else "lean (result-identical, SURVEY F8)",
+                       "grad_sync": "DISABLED (control run, not data-parallel training)" if args.no_grad_sync else
+                                    ("bucketed NCCL all-reduce inside the graph" if world > 1 else "single rank"),
                        "launch": "eager" if graphed is None else "one CUDA graph replay per step",
                        "l2": "working set per step (>30 GB) far exceeds the 126 MB L2; no flush needed"},
             "clocks": clocks, "gpu_launches": int(launches),

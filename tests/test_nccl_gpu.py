@@ -90,9 +90,10 @@ def _worker(rank, world, port, q):
     except Exception:  # pragma: no cover
         import traceback
         q.put((rank, traceback.format_exc()))
-    finally:
-        if dist.is_initialized():
-            dist.destroy_process_group()
+        q.close(); q.join_thread()
+        os._exit(1)     # the peer may be blocked in a collective: do not wait for it in destroy_process_group
+    if dist.is_initialized():
+        dist.destroy_process_group()
 
 
 @pytest.mark.timeout(900)
@@ -105,7 +106,15 @@ def test_two_rank_nccl_gradients_and_parameters():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=840) for _ in procs]
-    for p in procs:
-        p.join(timeout=30)
+    res = []
+    try:
+        for _ in procs:
+            res.append(q.get(timeout=600))
+            if res[-1][1] != "ok":      # a failed rank leaves its peer blocked in a collective: stop both now
+                break
+    finally:
+        for p in procs:
+            p.join(timeout=20 if len(res) == 2 and all(r[1] == "ok" for r in res) else 1)
+            if p.is_alive():
+                p.kill()
     assert sorted(res) == [(0, "ok"), (1, "ok")], res
