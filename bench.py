@@ -732,7 +732,9 @@ def main():
         d = tempfile.mkdtemp(prefix="bgr_bench_")
         try:
             _write_gpsro_files(d, args.files or 2 * B)
-            rd = ingest_measure(torch, dev, d, B, step_fn=files_step)
+            # rank 0 alone is here: with several ranks the captured step contains the gradient all-reduce, so the
+            # step-fed leg (e2e.from_files) is measured at N = 1 only; `--config ingest` runs it on every rank
+            rd = ingest_measure(torch, dev, d, B, step_fn=files_step if world == 1 else None)
             rd["host_path"] = host_path_measure(torch, dev, d)
             line["reader"] = rd
             line["reader_gbs"] = rd["reader_gbs"]

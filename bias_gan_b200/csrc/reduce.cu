@@ -32,6 +32,39 @@ sum_rows_kernel(const float* __restrict__ ws, int rows, long n4, float4* __restr
   out[i] = acc;
 }
 
+// Few outputs, many rows (depthwise weight gradients: 9*C outputs, ~70 rows): 32 outputs x 8 row lanes per
+// block; lane w adds rows w, w+8, ... in order, then the lane sums are added in lane order.
+__global__ void __launch_bounds__(256)
+sum_rows_lanes_kernel(const float* __restrict__ ws, int rows, long n4, float4* __restrict__ out) {
+  __shared__ float4 sh[8][32];
+  const int ol = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const long i = long(blockIdx.x) * 32 + ol;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i < n4) {
+    const float4* p = reinterpret_cast<const float4*>(ws) + i;
+    int r = rl;
+    for (; r + 8 < rows; r += 16) {
+      const float4 a = p[long(r) * n4], b = p[long(r + 8) * n4];
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+      acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+    }
+    if (r < rows) {
+      const float4 a = p[long(r) * n4];
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    }
+  }
+  sh[rl][ol] = acc;
+  __syncthreads();
+  if (rl == 0 && i < n4) {
+#pragma unroll
+    for (int w = 1; w < 8; ++w) {
+      const float4 a = sh[w][ol];
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    }
+    out[i] = acc;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 sum_rows_scalar_kernel(const float* __restrict__ ws, int rows, long n, float* __restrict__ out) {
   const long i = long(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -67,7 +100,10 @@ int launch_sum_rows(const float* ws, int rows, long n, float* out, cudaStream_t 
   if (rows < 1 || n < 1) return fail(BGR_ERR_ARG, "sum_rows: empty reduction");
   if ((n % 4) == 0 && ((uintptr_t(ws) | uintptr_t(out)) & 15) == 0) {
     const long n4 = n / 4;
-    sum_rows_kernel<<<unsigned((n4 + 127) / 128), 128, 0, st>>>(ws, rows, n4, reinterpret_cast<float4*>(out));
+    if (rows >= 16 && n4 <= 8192)
+      sum_rows_lanes_kernel<<<unsigned((n4 + 31) / 32), 256, 0, st>>>(ws, rows, n4, reinterpret_cast<float4*>(out));
+    else
+      sum_rows_kernel<<<unsigned((n4 + 127) / 128), 128, 0, st>>>(ws, rows, n4, reinterpret_cast<float4*>(out));
   } else {
     sum_rows_scalar_kernel<<<unsigned((n + 255) / 256), 256, 0, st>>>(ws, rows, n, out);
   }
