@@ -48,4 +48,34 @@ int ensure_dyn_smem_impl(const void* kern, int bytes);
 template <typename K>
 inline int ensure_dyn_smem(K kern, int bytes) { return ensure_dyn_smem_impl(reinterpret_cast<const void*>(kern), bytes); }
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------
+// A step is ~3400 kernels of 20-40 us; each pays its launch latency and prologue (barrier init, TMEM allocation,
+// descriptor prefetch, weight / coefficient loads, index arithmetic) after the previous kernel has drained.  With
+// the programmatic-stream-serialization launch attribute the next kernel's CTAs are scheduled as soon as every CTA
+// of the running kernel has passed pdl_trigger() (or exited), run their prologue on the SMs the tail leaves idle,
+// and block in pdl_wait() until the previous kernel has completed and flushed its memory.  Rules kept by every
+// kernel launched through launch_pdl(): (1) no global-memory write and no read of anything an earlier kernel of
+// the stream may have produced before pdl_wait(); (2) pdl_wait() is executed by every thread that touches global
+// memory afterwards.  Without the attribute (BGR_PDL=0, or a predecessor that is not a kernel) both are no-ops.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
+
 }  // namespace bgr

@@ -1,4 +1,5 @@
 // Error plumbing and the TMA tensor-map encoder shared by all translation units of libbgr.so.
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <utility>
@@ -73,6 +74,14 @@ int sm_count() {
     cache[dev] = n;
   }
   return cache[dev];
+}
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("BGR_PDL");
+    return v && v[0] == '1';    // opt-in until measured
+  }();
+  return on;
 }
 
 int ensure_dyn_smem_impl(const void* kern, int bytes) {

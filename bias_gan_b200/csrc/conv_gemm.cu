@@ -106,6 +106,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // everything above (barrier init, descriptor prefetch, TMEM allocation) touched no global memory: it may
+  // overlap the tail of the previous kernel (programmatic dependent launch, bgr_internal.h)
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -321,6 +325,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // everything above (barrier init, descriptor prefetch, TMEM allocation) touched no global memory: it may
+  // overlap the tail of the previous kernel (programmatic dependent launch, bgr_internal.h)
+  pdl_wait();
+  pdl_trigger();
 
   if (iters > 0) {
     if (warp == 0) {
@@ -444,7 +452,7 @@ static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   auto kern = conv_fprop_kernel<BLOCK_N, STAGES, STATS>;
   if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
   dim3 grid(groups * p.n_tiles);
-  kern<<<grid, 192, smem, st>>>(tmA, tmB, tmO, bias, stats, p);
+  BGR_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(192), smem, st, tmA, tmB, tmO, bias, stats, p));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -488,7 +496,7 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* 
   if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
   const int tiles = ((p.Cout + kBlockM - 1) / kBlockM) * ((p.Cin + BLOCK_N - 1) / BLOCK_N) * p.ntaps;
   dim3 grid(tiles, splits);
-  kern<<<grid, 192, smem, st>>>(tmDY, tmX, dst, p);
+  BGR_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(192), smem, st, tmDY, tmX, dst, p));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

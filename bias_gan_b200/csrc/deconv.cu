@@ -41,6 +41,8 @@ static int dc_grid(long total) {
 __global__ void __launch_bounds__(256)
 zero_stuff2_kernel(const __nv_bfloat16* __restrict__ x, int h, int w, int ldx, __nv_bfloat16* __restrict__ y, int N,
                    int H, int W, int C, int ldy) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3;
   const long total = long(N) * H * W * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -59,6 +61,8 @@ zero_stuff2_kernel(const __nv_bfloat16* __restrict__ x, int h, int w, int ldx, _
 __global__ void __launch_bounds__(256)
 zero_stuff2_bwd_kernel(const __nv_bfloat16* __restrict__ gy, int H, int W, int ldy, __nv_bfloat16* __restrict__ gx,
                        int N, int h, int w, int C, int ldx) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3;
   const long total = long(N) * h * w * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -77,6 +81,8 @@ zero_stuff2_bwd_kernel(const __nv_bfloat16* __restrict__ gy, int H, int W, int l
 __global__ void __launch_bounds__(256)
 avgpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, int C, int ldx, int pad, int act,
                     float slope, __nv_bfloat16* __restrict__ y, int ldy) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3, Ho = H + 2 * pad - 1, Wo = W + 2 * pad - 1;
   const long total = long(N) * Ho * Wo * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -113,6 +119,8 @@ avgpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, in
 __global__ void __launch_bounds__(256)
 avgpool2_bwd_kernel(const __nv_bfloat16* __restrict__ gy, int ldg, const __nv_bfloat16* __restrict__ yout, int ldo,
                     int N, int H, int W, int C, int pad, int act, float slope, __nv_bfloat16* __restrict__ gx, int ldx) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3, Ho = H + 2 * pad - 1, Wo = W + 2 * pad - 1;
   const long total = long(N) * H * W * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -154,6 +162,8 @@ avgpool2_bwd_kernel(const __nv_bfloat16* __restrict__ gy, int ldg, const __nv_bf
 template <bool TO_FIELD>
 __global__ void __launch_bounds__(256)
 nhwc_field_kernel(__nv_bfloat16* __restrict__ nhwc, int ld, __nv_bfloat16* __restrict__ field, int N, int H, int W, int C) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3, Hp = (H + 1) & ~1, Wp = (W + 1) & ~1;
   const long total = long(N) * (TO_FIELD ? Hp : H) * (TO_FIELD ? Wp : W) * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -186,6 +196,8 @@ struct PadStage {
 __global__ void __launch_bounds__(256)
 stage_padded_kernel(const float* __restrict__ src, const float* __restrict__ shift, const float* __restrict__ scale,
                     __nv_bfloat16* __restrict__ field, const __grid_constant__ PadStage p) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int Hp = (p.H + 1) & ~1, Wp = (p.W + 1) & ~1;
   const long total = long(p.B) * Hp * Wp * p.Cp;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -206,6 +218,8 @@ stage_padded_kernel(const float* __restrict__ src, const float* __restrict__ shi
 // nchw[b, c, y, x] = float(field[...]) for c < C
 __global__ void __launch_bounds__(256)
 field_to_nchw_padded_kernel(const __nv_bfloat16* __restrict__ field, float* __restrict__ nchw, int B, int C, int Cp, int H, int W) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int Hp = (H + 1) & ~1, Wp = (W + 1) & ~1;
   const long total = long(B) * C * H * W;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -230,8 +244,8 @@ extern "C" int bgr_zero_stuff2(const void* x, int N, int h, int w, int C, int ld
                                void* stream) {
   DC_CHECK_C8(C);
   if (H < 2 * h - 1 || W < 2 * w - 1) return fail(BGR_ERR_ARG, "zero_stuff2: output smaller than 2*input - 1");
-  zero_stuff2_kernel<<<dc_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), h, w, ldx, static_cast<__nv_bfloat16*>(y), N, H, W, C, ldy);
+  BGR_CUDA_OK(launch_pdl(zero_stuff2_kernel, dim3(dc_grid(long(N) * H * W * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(x), h, w, ldx, static_cast<__nv_bfloat16*>(y), N, H, W, C, ldy));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -240,8 +254,8 @@ extern "C" int bgr_zero_stuff2_bwd(const void* gy, int N, int h, int w, int C, i
                                    void* stream) {
   DC_CHECK_C8(C);
   if (H < 2 * h - 1 || W < 2 * w - 1) return fail(BGR_ERR_ARG, "zero_stuff2: output smaller than 2*input - 1");
-  zero_stuff2_bwd_kernel<<<dc_grid(long(N) * h * w * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(gy), H, W, ldy, static_cast<__nv_bfloat16*>(gx), N, h, w, C, ldx);
+  BGR_CUDA_OK(launch_pdl(zero_stuff2_bwd_kernel, dim3(dc_grid(long(N) * h * w * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(gy), H, W, ldy, static_cast<__nv_bfloat16*>(gx), N, h, w, C, ldx));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -250,9 +264,8 @@ extern "C" int bgr_avgpool2_fwd(const void* x, int N, int H, int W, int C, int l
                                 void* y, int ldy, void* stream) {
   DC_CHECK_C8(C);
   if (pad < 0 || pad > 1 || H + 2 * pad < 2 || W + 2 * pad < 2) return fail(BGR_ERR_ARG, "avgpool2: padding 0 or 1, window must fit");
-  avgpool2_fwd_kernel<<<dc_grid(long(N) * (H + 2 * pad - 1) * (W + 2 * pad - 1) * (C / 8)), 256, 0,
-                        reinterpret_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), N, H, W, C, ldx,
-                                                                  pad, act, slope, static_cast<__nv_bfloat16*>(y), ldy);
+  BGR_CUDA_OK(launch_pdl(avgpool2_fwd_kernel, dim3(dc_grid(long(N) * (H + 2 * pad - 1) * (W + 2 * pad - 1) * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), N, H, W, C, ldx,
+                                                                  pad, act, slope, static_cast<__nv_bfloat16*>(y), ldy));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -262,9 +275,9 @@ extern "C" int bgr_avgpool2_bwd(const void* gy, int ldg, const void* yout, int l
   DC_CHECK_C8(C);
   if (pad < 0 || pad > 1) return fail(BGR_ERR_ARG, "avgpool2: padding 0 or 1");
   if (act && yout == nullptr) return fail(BGR_ERR_ARG, "avgpool2_bwd: the stored output is needed for the activation");
-  avgpool2_bwd_kernel<<<dc_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  BGR_CUDA_OK(launch_pdl(avgpool2_bwd_kernel, dim3(dc_grid(long(N) * H * W * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
       static_cast<const __nv_bfloat16*>(gy), ldg, static_cast<const __nv_bfloat16*>(yout), ldo, N, H, W, C, pad, act,
-      slope, static_cast<__nv_bfloat16*>(gx), ldx);
+      slope, static_cast<__nv_bfloat16*>(gx), ldx));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -272,16 +285,16 @@ extern "C" int bgr_avgpool2_bwd(const void* gy, int ldg, const void* yout, int l
 extern "C" int bgr_nhwc_to_field(const void* x, int N, int H, int W, int C, int ldx, void* field, void* stream) {
   DC_CHECK_C8(C);
   const int Hp = (H + 1) & ~1, Wp = (W + 1) & ~1;
-  nhwc_field_kernel<true><<<dc_grid(long(N) * Hp * Wp * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(x)), ldx, static_cast<__nv_bfloat16*>(field), N, H, W, C);
+  BGR_CUDA_OK(launch_pdl(nhwc_field_kernel<true>, dim3(dc_grid(long(N) * Hp * Wp * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(x)), ldx, static_cast<__nv_bfloat16*>(field), N, H, W, C));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
 extern "C" int bgr_field_to_nhwc(const void* field, int N, int H, int W, int C, void* y, int ldy, void* stream) {
   DC_CHECK_C8(C);
-  nhwc_field_kernel<false><<<dc_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<__nv_bfloat16*>(y), ldy, const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(field)), N, H, W, C);
+  BGR_CUDA_OK(launch_pdl(nhwc_field_kernel<false>, dim3(dc_grid(long(N) * H * W * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<__nv_bfloat16*>(y), ldy, const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(field)), N, H, W, C));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -299,16 +312,16 @@ extern "C" int bgr_stage_normalize_padded(const float* src, int B, int Cf, int H
     p.channels[i] = c;
   }
   const long total = long(B) * ((H + 1) & ~1) * ((W + 1) & ~1) * Cp;
-  stage_padded_kernel<<<dc_grid(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      src, shift, scale, static_cast<__nv_bfloat16*>(field), p);
+  BGR_CUDA_OK(launch_pdl(stage_padded_kernel, dim3(dc_grid(total)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      src, shift, scale, static_cast<__nv_bfloat16*>(field), p));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
 extern "C" int bgr_field_to_nchw_padded(const void* field, float* nchw, int B, int C, int Cp, int H, int W, void* stream) {
   if (Cp % 8 || C < 1 || C > Cp) return fail(BGR_ERR_ARG, "field_to_nchw_padded: 1 <= C <= Cp, Cp multiple of 8");
-  field_to_nchw_padded_kernel<<<dc_grid(long(B) * C * H * W), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(field), nchw, B, C, Cp, H, W);
+  BGR_CUDA_OK(launch_pdl(field_to_nchw_padded_kernel, dim3(dc_grid(long(B) * C * H * W)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(field), nchw, B, C, Cp, H, W));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

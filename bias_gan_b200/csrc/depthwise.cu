@@ -44,6 +44,8 @@ struct DwGeom {
 __global__ void __launch_bounds__(256)
 dw_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
               __nv_bfloat16* __restrict__ y, const DwGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = g.C >> 3;
   const long total = long(g.N) * g.Ho * g.Wo * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -80,6 +82,8 @@ dw_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
 __global__ void __launch_bounds__(256)
 dw_dgrad_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ w,
                 __nv_bfloat16* __restrict__ dx, const DwGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = g.C >> 3;
   const long total = long(g.N) * g.H * g.W * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -123,6 +127,8 @@ dw_dgrad_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ 
 __global__ void __launch_bounds__(256)
 dw_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                 float* __restrict__ ws, const DwGeom g, long pix_per_block) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   extern __shared__ float sh[];  // [9][C]
   for (int i = threadIdx.x; i < 9 * g.C; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
@@ -189,6 +195,8 @@ dw_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 // y[n,oy,ox,:] = x[n,2oy,2ox,:]  /  adjoint: dx = 0 except dx[n,2oy,2ox,:] = dy[n,oy,ox,:]
 __global__ void __launch_bounds__(256)
 subsample2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, const DwGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = g.C >> 3;
   const long total = long(g.N) * g.Ho * g.Wo * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -204,6 +212,8 @@ subsample2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict
 }
 __global__ void __launch_bounds__(256)
 subsample2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, const DwGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = g.C >> 3;
   const long total = long(g.N) * g.H * g.W * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -229,6 +239,8 @@ template <int S, int D, int T, bool REVERSE>
 __global__ void __launch_bounds__(256)
 dw_fwd_strip_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                     __nv_bfloat16* __restrict__ y, const DwGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   constexpr int SPAN = (T - 1) * S + 2 * D + 1;
   const int G = g.C >> 3;
   const int strips = (g.Wo + T - 1) / T;
@@ -501,6 +513,8 @@ __global__ void __launch_bounds__(128, 3)
 dw_march_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                     __nv_bfloat16* __restrict__ y, const DwGeom g, const MarchSched sc,
                     const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ uint2 ring_all[4][kRing][6 * 32];   // [warp][slot][col][lane]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c0 = ((blockIdx.x % sc.cblocks) * 32 + lane) * kCpt;
@@ -639,6 +653,8 @@ __device__ __forceinline__ void march_fwd_s2_item(const __nv_bfloat16* __restric
 __global__ void __launch_bounds__(128, 3)
 dw_march_fwd_s2_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                        __nv_bfloat16* __restrict__ y, const DwGeom g, const MarchSched sc) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ uint2 ring_all[4][kRing][9 * 32];   // [warp][slot][col][lane]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c0 = ((blockIdx.x % sc.cblocks) * 32 + lane) * kCpt;
@@ -674,6 +690,8 @@ dw_march_fwd_s2_kernel(const __nv_bfloat16* __restrict__ x, const float* __restr
 __global__ void __launch_bounds__(256)
 dw_dgrad_s2_kernel(const __nv_bfloat16* __restrict__ gy, const float* __restrict__ w,
                    __nv_bfloat16* __restrict__ dx, const DwGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = g.C >> 3;
   const int Hb = (g.H + 1) >> 1, Wb = (g.W + 1) >> 1;   // 2x2 blocks of dx (= Ho x Wo)
   const long total = long(g.N) * Hb * Wb * G;
@@ -795,6 +813,8 @@ __device__ __forceinline__ void march_wgrad_s2_item(const __nv_bfloat16* __restr
 __global__ void __launch_bounds__(128, 2)
 dw_march_wgrad_s2_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                          float* __restrict__ ws, const DwGeom g, const MarchSched sc) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ float sh[9 * 128];
   extern __shared__ uint2 ring_dyn[];               // [4 warps][kRing][13 * 32]
   for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sh[i] = 0.f;
@@ -915,6 +935,8 @@ __global__ void __launch_bounds__(128, 3)
 dw_march_wgrad_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                       float* __restrict__ ws, const DwGeom g, const MarchSched sc,
                       const float* __restrict__ xa, const float* __restrict__ xb, float slope) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ float sh[9 * 128];                       // [9][128 channels of this block]
   __shared__ uint2 ring_all[4][kRing][10 * 32];       // [warp][slot][6 x cols + 4 dy cols][lane]
   for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sh[i] = 0.f;
@@ -1032,9 +1054,9 @@ static bool launch_fwd_strip(const __nv_bfloat16* x, const float* w, __nv_bfloat
                              cudaStream_t st) {
   const long total = long(g.N) * g.Ho * ((g.Wo + kStripT - 1) / kStripT) * (g.C / 8);
   const int grid = ew_grid(total);
-  if (g.stride == 1 && g.dil == 1) dw_fwd_strip_kernel<1, 1, kStripT, REVERSE><<<grid, 256, 0, st>>>(x, w, y, g);
-  else if (g.stride == 1 && g.dil == 2) dw_fwd_strip_kernel<1, 2, kStripT, REVERSE><<<grid, 256, 0, st>>>(x, w, y, g);
-  else if (g.stride == 2 && g.dil == 1 && !REVERSE) dw_fwd_strip_kernel<2, 1, kStripT, false><<<grid, 256, 0, st>>>(x, w, y, g);
+  if (g.stride == 1 && g.dil == 1) BGR_CUDA_OK(launch_pdl(dw_fwd_strip_kernel<1, 1, kStripT, REVERSE>, dim3(grid), dim3(256), 0, st, x, w, y, g));
+  else if (g.stride == 1 && g.dil == 2) BGR_CUDA_OK(launch_pdl(dw_fwd_strip_kernel<1, 2, kStripT, REVERSE>, dim3(grid), dim3(256), 0, st, x, w, y, g));
+  else if (g.stride == 2 && g.dil == 1 && !REVERSE) BGR_CUDA_OK(launch_pdl(dw_fwd_strip_kernel<2, 1, kStripT, false>, dim3(grid), dim3(256), 0, st, x, w, y, g));
   else return false;
   return true;
 }
@@ -1050,14 +1072,14 @@ extern "C" int bgr_dw_fwd(const void* x, int N, int H, int W, int C, int ldx, co
     MarchSched sc;
     unsigned blocks;
     march_plan(g, &sc, &blocks);
-    dw_march_fwd_kernel<false, 0><<<blocks, 128, 0, st>>>(X, w, Y, g, sc, nullptr, nullptr, 0.f);
+    BGR_CUDA_OK(launch_pdl(dw_march_fwd_kernel<false, 0>, dim3(blocks), dim3(128), 0, st, X, w, Y, g, sc, nullptr, nullptr, 0.f));
   } else if (stride == 2 && dil == 1) {
     MarchSched sc;
     unsigned blocks;
     march_plan_s2(g, &sc, &blocks);
-    dw_march_fwd_s2_kernel<<<blocks, 128, 0, st>>>(X, w, Y, g, sc);
+    BGR_CUDA_OK(launch_pdl(dw_march_fwd_s2_kernel, dim3(blocks), dim3(128), 0, st, X, w, Y, g, sc));
   } else if (!launch_fwd_strip<false>(X, w, Y, g, st))
-    dw_fwd_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, st>>>(X, w, Y, g);
+    BGR_CUDA_OK(launch_pdl(dw_fwd_kernel, dim3(ew_grid(long(N) * g.Ho * g.Wo * (C / 8))), dim3(256), 0, st, X, w, Y, g));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -1078,14 +1100,14 @@ extern "C" int bgr_dw_dgrad(const void* dy, int N, int H, int W, int C, int ldy,
     MarchSched sc;
     unsigned blocks;
     march_plan(r, &sc, &blocks);
-    dw_march_fwd_kernel<true, 0><<<blocks, 128, 0, st>>>(DY, w, DX, r, sc, nullptr, nullptr, 0.f);
+    BGR_CUDA_OK(launch_pdl(dw_march_fwd_kernel<true, 0>, dim3(blocks), dim3(128), 0, st, DY, w, DX, r, sc, nullptr, nullptr, 0.f));
     done = true;
   }
   if (!done && stride == 2 && dil == 1) {
-    dw_dgrad_s2_kernel<<<ew_grid(long(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
+    BGR_CUDA_OK(launch_pdl(dw_dgrad_s2_kernel, dim3(ew_grid(long(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8))), dim3(256), 0, st, DY, w, DX, g));
     done = true;
   }
-  if (!done) dw_dgrad_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, st>>>(DY, w, DX, g);
+  if (!done) BGR_CUDA_OK(launch_pdl(dw_dgrad_kernel, dim3(ew_grid(long(N) * H * W * (C / 8))), dim3(256), 0, st, DY, w, DX, g));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -1108,7 +1130,7 @@ static int launch_march_wgrad(const __nv_bfloat16* x, const __nv_bfloat16* dy, f
   march_plan(g, &sc, &blocks);
   const int rows = int(blocks) / sc.cblocks;
   if (int rc = dw_wgrad_ws_check(rows, g.C)) return rc;
-  dw_march_wgrad_kernel<XF><<<blocks, 128, 0, st>>>(x, dy, ws, g, sc, xa, xb, slope);
+  BGR_CUDA_OK(launch_pdl(dw_march_wgrad_kernel<XF>, dim3(blocks), dim3(128), 0, st, x, dy, ws, g, sc, xa, xb, slope));
   BGR_LAUNCH_OK();
   return dw_wgrad_finish(ws, rows, g.C, dw, st);
 }
@@ -1127,8 +1149,8 @@ extern "C" int bgr_dw_fwd_bn(const void* x, int N, int H, int W, int C, int ldx,
   MarchSched sc;
   unsigned blocks;
   march_plan(g, &sc, &blocks);
-  if (act) dw_march_fwd_kernel<false, 2><<<blocks, 128, 0, st>>>(X, w, Y, g, sc, a, b, slope);
-  else dw_march_fwd_kernel<false, 1><<<blocks, 128, 0, st>>>(X, w, Y, g, sc, a, b, slope);
+  if (act) BGR_CUDA_OK(launch_pdl(dw_march_fwd_kernel<false, 2>, dim3(blocks), dim3(128), 0, st, X, w, Y, g, sc, a, b, slope));
+  else BGR_CUDA_OK(launch_pdl(dw_march_fwd_kernel<false, 1>, dim3(blocks), dim3(128), 0, st, X, w, Y, g, sc, a, b, slope));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -1164,7 +1186,7 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
     march_plan_s2(g, &sc, &blocks, 2);   // 192 registers: two resident blocks per SM
     const int rows = int(blocks) / sc.cblocks;
     if (int rc = dw_wgrad_ws_check(rows, C)) return rc;
-    dw_march_wgrad_s2_kernel<<<blocks, 128, ring_bytes, st>>>(X, DY, ws, g, sc);
+    BGR_CUDA_OK(launch_pdl(dw_march_wgrad_s2_kernel, dim3(blocks), dim3(128), ring_bytes, st, X, DY, ws, g, sc));
     BGR_LAUNCH_OK();
     return dw_wgrad_finish(ws, rows, C, dw, st);
   }
@@ -1179,7 +1201,7 @@ extern "C" int bgr_dw_wgrad(const void* x, int N, int H, int W, int C, int ldx, 
   blocks = (P + ppb - 1) / ppb;
   if (int rc = dw_wgrad_ws_check(blocks, C)) return rc;
   if (int rc = ensure_dyn_smem(dw_wgrad_kernel, 160 * 1024)) return rc;
-  dw_wgrad_kernel<<<int(blocks), 256, 9 * C * sizeof(float), st>>>(X, DY, ws, g, ppb);
+  BGR_CUDA_OK(launch_pdl(dw_wgrad_kernel, dim3(int(blocks)), dim3(256), 9 * C * sizeof(float), st, X, DY, ws, g, ppb));
   BGR_LAUNCH_OK();
   return dw_wgrad_finish(ws, int(blocks), C, dw, st);
 }
@@ -1188,8 +1210,8 @@ extern "C" int bgr_subsample2(const void* x, int N, int H, int W, int C, int ldx
                               void* stream) {
   DwGeom g;
   if (int rc = make_geom(&g, N, H, W, C, 2, 1, ldx, ldy)) return rc;
-  subsample2_kernel<<<ew_grid(long(N) * g.Ho * g.Wo * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+  BGR_CUDA_OK(launch_pdl(subsample2_kernel, dim3(ew_grid(long(N) * g.Ho * g.Wo * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -1198,8 +1220,8 @@ extern "C" int bgr_subsample2_bwd(const void* dy, int N, int H, int W, int C, in
                                   void* stream) {
   DwGeom g;
   if (int rc = make_geom(&g, N, H, W, C, 2, 1, ldx, ldy)) return rc;
-  subsample2_bwd_kernel<<<ew_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), g);
+  BGR_CUDA_OK(launch_pdl(subsample2_bwd_kernel, dim3(ew_grid(long(N) * H * W * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), g));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

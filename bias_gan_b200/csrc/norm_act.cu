@@ -68,6 +68,8 @@ __device__ __forceinline__ void block_partial_flush(const float* sh, int C, int 
 __global__ void __launch_bounds__(256)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long M, int C, int ld, int rows_per_block,
                 float* __restrict__ part /* [gridDim.x][2][C] */) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   extern __shared__ float sh[];  // [R][2][C]
   const RowGroupMap m(C);
   const long r0 = long(blockIdx.x) * rows_per_block;
@@ -136,6 +138,8 @@ bn_finalize_kernel(const float* __restrict__ part, int rows, long M, int C,
                    float* __restrict__ invstd, float* __restrict__ a,
                    float* __restrict__ b, float* __restrict__ running_mean,
                    float* __restrict__ running_var, long long* __restrict__ num_batches) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches) *num_batches += 1;   // nn.BatchNorm2d.num_batches_tracked
   int c;
   double sum, sq;
@@ -165,6 +169,8 @@ __global__ void __launch_bounds__(256)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __restrict__ a,
                 const float* __restrict__ b, const __nv_bfloat16* __restrict__ res, int ldr,
                 __nv_bfloat16* __restrict__ out, int ldo, long M, int C, float slope) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3;
   const int R = G >= 256 ? 1 : 256 / G;
   const int g0 = G >= 256 ? threadIdx.x : threadIdx.x % G;
@@ -297,6 +303,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
                      const float* __restrict__ mean, const float* __restrict__ invstd,
                      __nv_bfloat16* __restrict__ dyh, int ldd, long M, int C, int rows_per_block, float slope,
                      float* __restrict__ part /* [gridDim.x][2][C] */) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   bn_bwd_reduce_body<ACT>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
 }
 
@@ -323,6 +331,8 @@ __global__ void __launch_bounds__(256)
 bn_bwd_coef_kernel(const float* __restrict__ mean, const float* __restrict__ invstd,
                    const float* __restrict__ gamma, const float* __restrict__ part, int rows,
                    long M, int C, float* __restrict__ coef /* [7][C] */) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   bn_bwd_coef_body(mean, invstd, gamma, part, rows, M, C, coef);
 }
 
@@ -330,6 +340,8 @@ __global__ void __launch_bounds__(256, 4)   // 64 registers (4 bytes of spill): 
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* __restrict__ x, int ldx,
                     const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, int ldd, long M,
                     int C) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   // same thread -> (channel group, rows) mapping as bn_apply_kernel: the five coefficient vectors
   // are loaded once per thread instead of once per 16 bytes of data
   const int G = C >> 3;
@@ -379,6 +391,8 @@ bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, co
                               int ldx, const float* __restrict__ xa, const float* __restrict__ xb,
                               const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, int ldd, long M,
                               int C, float slope, int act) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3;
   const int R = G >= 256 ? 1 : 256 / G;
   const int g0 = G >= 256 ? threadIdx.x : threadIdx.x % G;
@@ -619,7 +633,7 @@ extern "C" int bgr_bn_stats(const void* x, long M, int C, int ld, float* part, i
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int rpb;
   const int grid = reduce_grid(M, C, &rpb);
-  bn_stats_kernel<<<grid, 256, reduce_smem(C), st>>>(static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, part);
+  BGR_CUDA_OK(launch_pdl(bn_stats_kernel, dim3(grid), dim3(256), reduce_smem(C), st, static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, part));
   BGR_LAUNCH_OK();
   *rows = grid;
   return BGR_OK;
@@ -630,8 +644,8 @@ extern "C" int bgr_bn_finalize(const float* part, int rows, long M, int C, const
                                float* running_mean, float* running_var, long long* num_batches_tracked,
                                void* stream) {
   if (rows < 1 || rows > BGR_BN_MAX_ROWS) return fail(BGR_ERR_ARG, "bn_finalize: rows out of range");
-  bn_finalize_kernel<<<(C + kRsCh - 1) / kRsCh, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      part, rows, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var, num_batches_tracked);
+  BGR_CUDA_OK(launch_pdl(bn_finalize_kernel, dim3((C + kRsCh - 1) / kRsCh), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      part, rows, M, C, gamma, beta, eps, momentum, mean, invstd, a, b, running_mean, running_var, num_batches_tracked));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -645,10 +659,10 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto R = static_cast<const __nv_bfloat16*>(res);
   auto O = static_cast<__nv_bfloat16*>(out);
-  if (act && res) bn_apply_kernel<true, true><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
-  else if (act) bn_apply_kernel<true, false><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
-  else if (res) bn_apply_kernel<false, true><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
-  else bn_apply_kernel<false, false><<<grid, block, 0, st>>>(X, ldx, a, b, R, ldr, O, ldo, M, C, slope);
+  if (act && res) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<true, true>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
+  else if (act) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<true, false>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
+  else if (res) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<false, true>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
+  else BGR_CUDA_OK(launch_pdl(bn_apply_kernel<false, false>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -685,19 +699,19 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
       return launch_bn_bwd_fused<0>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, gamma, D, DXp, ldd, M, C, rpb, grid, slope, part, coef_ws, rsm, st);
     }
   }
-  if (act == 2) bn_bwd_reduce_kernel<2><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
-  else if (act) bn_bwd_reduce_kernel<1><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
-  else bn_bwd_reduce_kernel<0><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  if (act == 2) BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<2>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
+  else if (act) BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<1>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
+  else BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<0>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
   BGR_LAUNCH_OK();
-  bn_bwd_coef_kernel<<<(C + kRsCh - 1) / kRsCh, 256, 0, st>>>(mean, invstd, gamma, part, grid, M, C, coef_ws);
+  BGR_CUDA_OK(launch_pdl(bn_bwd_coef_kernel, dim3((C + kRsCh - 1) / kRsCh), dim3(256), 0, st, mean, invstd, gamma, part, grid, M, C, coef_ws));
   BGR_LAUNCH_OK();
   int agrid, ablock;
   rowgroup_launch(M, C, &agrid, &ablock);
   if (D == nullptr) {
-    bn_bwd_apply_recompute_kernel<<<agrid, ablock, 0, st>>>(G, ldg, G2, ldg2, X, ldx, xa, xb, coef_ws, DXp,
-                                                            ldd, M, C, slope, act == 2);
+    BGR_CUDA_OK(launch_pdl(bn_bwd_apply_recompute_kernel, dim3(agrid), dim3(ablock), 0, st, G, ldg, G2, ldg2, X, ldx, xa, xb, coef_ws, DXp,
+                                                            ldd, M, C, slope, act == 2));
   } else {
-    bn_bwd_apply_kernel<<<agrid, ablock, 0, st>>>(D, X, ldx, coef_ws, DXp, ldd, M, C);
+    BGR_CUDA_OK(launch_pdl(bn_bwd_apply_kernel, dim3(agrid), dim3(ablock), 0, st, D, X, ldx, coef_ws, DXp, ldd, M, C));
   }
   BGR_LAUNCH_OK();
   return BGR_OK;
@@ -736,6 +750,8 @@ extern "C" int bgr_bn_backward_recompute_dual(const void* g, int ldg, const void
 __global__ void __launch_bounds__(256)
 scale_rows_kernel(const __nv_bfloat16* __restrict__ d, int ldd, const float* __restrict__ sc,
                   __nv_bfloat16* __restrict__ dx, int ldx, long M, int C) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3;
   const long total = M * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -772,16 +788,16 @@ extern "C" int bgr_bn_backward_frozen(const void* g, int ldg, const void* g2, in
   auto O = static_cast<const __nv_bfloat16*>(out);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto D = static_cast<__nv_bfloat16*>(dyh);
-  if (act) bn_bwd_reduce_kernel<1><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
-  else bn_bwd_reduce_kernel<0><<<grid, 256, rsm, st>>>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  if (act) BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<1>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
+  else BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<0>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
   BGR_LAUNCH_OK();
-  bn_bwd_coef_kernel<<<(C + kRsCh - 1) / kRsCh, 256, 0, st>>>(mean, invstd, gamma, part, grid, M, C, coef_ws);
+  BGR_CUDA_OK(launch_pdl(bn_bwd_coef_kernel, dim3((C + kRsCh - 1) / kRsCh), dim3(256), 0, st, mean, invstd, gamma, part, grid, M, C, coef_ws));
   BGR_LAUNCH_OK();
   if (dx != nullptr) {
     long blocks = (M * (C / 8) + 255) / 256;
     if (blocks > long(sm_count()) * 16) blocks = long(sm_count()) * 16;
-    scale_rows_kernel<<<int(blocks < 1 ? 1 : blocks), 256, 0, st>>>(D, ldd, coef_ws /* row 0 = gamma*invstd */,
-                                                                    static_cast<__nv_bfloat16*>(dx), ldd, M, C);
+    BGR_CUDA_OK(launch_pdl(scale_rows_kernel, dim3(int(blocks < 1 ? 1 : blocks)), dim3(256), 0, st, D, ldd, coef_ws /* row 0 = gamma*invstd */,
+                                                                    static_cast<__nv_bfloat16*>(dx), ldd, M, C));
     BGR_LAUNCH_OK();
   }
   return BGR_OK;

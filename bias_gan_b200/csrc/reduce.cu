@@ -13,6 +13,8 @@ namespace bgr {
 // out[i] = sum_{r < rows} ws[r * n + i]   (thread per output, rows in order, coalesced across i)
 __global__ void __launch_bounds__(128)
 sum_rows_kernel(const float* __restrict__ ws, int rows, long n4, float4* __restrict__ out) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const long i = long(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   const float4* p = reinterpret_cast<const float4*>(ws) + i;
@@ -36,6 +38,8 @@ sum_rows_kernel(const float* __restrict__ ws, int rows, long n4, float4* __restr
 // block; lane w adds rows w, w+8, ... in order, then the lane sums are added in lane order.
 __global__ void __launch_bounds__(256)
 sum_rows_lanes_kernel(const float* __restrict__ ws, int rows, long n4, float4* __restrict__ out) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ float4 sh[8][32];
   const int ol = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const long i = long(blockIdx.x) * 32 + ol;
@@ -67,6 +71,8 @@ sum_rows_lanes_kernel(const float* __restrict__ ws, int rows, long n4, float4* _
 
 __global__ void __launch_bounds__(256)
 sum_rows_scalar_kernel(const float* __restrict__ ws, int rows, long n, float* __restrict__ out) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const long i = long(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float acc = 0.f;
@@ -80,6 +86,8 @@ sum_rows_scalar_kernel(const float* __restrict__ ws, int rows, long n, float* __
 __global__ void __launch_bounds__(256)
 sum_rows_block_kernel(const float* __restrict__ ws, int rows, int n, float* __restrict__ out_f32_add,
                       double* __restrict__ out_f64) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ double sh[256];
   const int i = blockIdx.x;
   double acc = 0.0;
@@ -101,11 +109,11 @@ int launch_sum_rows(const float* ws, int rows, long n, float* out, cudaStream_t 
   if ((n % 4) == 0 && ((uintptr_t(ws) | uintptr_t(out)) & 15) == 0) {
     const long n4 = n / 4;
     if (rows >= 16 && n4 <= 8192)
-      sum_rows_lanes_kernel<<<unsigned((n4 + 31) / 32), 256, 0, st>>>(ws, rows, n4, reinterpret_cast<float4*>(out));
+      BGR_CUDA_OK(launch_pdl(sum_rows_lanes_kernel, dim3(unsigned((n4 + 31) / 32)), dim3(256), 0, st, ws, rows, n4, reinterpret_cast<float4*>(out)));
     else
-      sum_rows_kernel<<<unsigned((n4 + 127) / 128), 128, 0, st>>>(ws, rows, n4, reinterpret_cast<float4*>(out));
+      BGR_CUDA_OK(launch_pdl(sum_rows_kernel, dim3(unsigned((n4 + 127) / 128)), dim3(128), 0, st, ws, rows, n4, reinterpret_cast<float4*>(out)));
   } else {
-    sum_rows_scalar_kernel<<<unsigned((n + 255) / 256), 256, 0, st>>>(ws, rows, n, out);
+    BGR_CUDA_OK(launch_pdl(sum_rows_scalar_kernel, dim3(unsigned((n + 255) / 256)), dim3(256), 0, st, ws, rows, n, out));
   }
   BGR_LAUNCH_OK();
   return BGR_OK;
@@ -113,7 +121,7 @@ int launch_sum_rows(const float* ws, int rows, long n, float* out, cudaStream_t 
 
 int launch_sum_rows_block(const float* ws, int rows, int n, float* out_f32_add, double* out_f64, cudaStream_t st) {
   if (rows < 1 || n < 1) return fail(BGR_ERR_ARG, "sum_rows_block: empty reduction");
-  sum_rows_block_kernel<<<n, 256, 0, st>>>(ws, rows, n, out_f32_add, out_f64);
+  BGR_CUDA_OK(launch_pdl(sum_rows_block_kernel, dim3(n), dim3(256), 0, st, ws, rows, n, out_f32_add, out_f64));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

@@ -60,6 +60,8 @@ __device__ __forceinline__ size_t bil_out_index(const BilGeom& g, int n, int y, 
 
 __global__ void __launch_bounds__(256)
 bilinear_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, const BilGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = g.C >> 3;
   const long total = long(g.N) * g.H * g.W * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -91,6 +93,8 @@ bilinear_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restri
 // one and each candidate re-runs bil_coord, so the weights are exactly the forward's.
 __global__ void __launch_bounds__(256)
 bilinear_bwd_gather_kernel(const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx, const BilGeom g) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = g.C >> 3;
   const long total = long(g.N) * g.h * g.w * G;
   const float ry = g.sy > 0.f ? 1.f / g.sy : 0.f, rx = g.sx > 0.f ? 1.f / g.sx : 0.f;   // 0: a single source row / column
@@ -141,6 +145,8 @@ bilinear_bwd_gather_kernel(const __nv_bfloat16* __restrict__ gy, float* __restri
 __global__ void __launch_bounds__(256)
 gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int ld, long P, int C, long pix_per_block,
                float* __restrict__ ws) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   extern __shared__ float sh[];   // [R][C]
   const int n = blockIdx.y;
   const int G = C >> 3;
@@ -173,6 +179,8 @@ gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int ld, long P, int C, long 
 __global__ void __launch_bounds__(256)
 gap_bwd_kernel(const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ dx, long P, int C, int N,
                float inv_p) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int G = C >> 3;
   const long total = long(N) * P * G;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -194,6 +202,8 @@ gap_bwd_kernel(const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ 
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w, long K,
                 float* __restrict__ ws) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int n = blockIdx.y;
   const long K8 = K >> 3;
   float acc = 0.f;
@@ -221,6 +231,8 @@ __global__ void __launch_bounds__(256)
 head_bwd_kernel(const float* __restrict__ g, const __nv_bfloat16* __restrict__ x,
                 const __nv_bfloat16* __restrict__ w, long K, int N, __nv_bfloat16* __restrict__ dx,
                 float* __restrict__ dw) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const long K8 = K >> 3;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < K8; i += long(gridDim.x) * blockDim.x) {
     float wv[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -252,6 +264,8 @@ head_bwd_kernel(const float* __restrict__ g, const __nv_bfloat16* __restrict__ x
 __global__ void __launch_bounds__(256)
 l1_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, long n8,
                     float gscale, __nv_bfloat16* __restrict__ grad, float* __restrict__ ws) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   float acc = 0.f;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += long(gridDim.x) * blockDim.x) {
     float x[8], y[8], o[8];
@@ -286,6 +300,8 @@ __global__ void __launch_bounds__(256)
 reg_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
                      const __nv_bfloat16* __restrict__ w, long n8, float gscale, const float* __restrict__ gscale_dev,
                      float beta, __nv_bfloat16* __restrict__ grad, float* __restrict__ ws) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   float acc = 0.f;
   const float gs = gscale_dev ? gscale * __ldg(gscale_dev) : gscale;
   const float inv_beta = beta > 0.f ? 1.f / beta : 0.f;
@@ -332,6 +348,8 @@ reg_loss_grad_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* _
 template <bool TO_NCHW>
 __global__ void __launch_bounds__(256)
 field_convert_kernel(__nv_bfloat16* __restrict__ field, float* __restrict__ nchw, int N, int C, int H, int W) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const long total = long(N) * C * H * W;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += long(gridDim.x) * blockDim.x) {
@@ -353,6 +371,8 @@ field_convert_kernel(__nv_bfloat16* __restrict__ field, float* __restrict__ nchw
 __global__ void __launch_bounds__(256)
 field_append_noise_kernel(const uint4* __restrict__ field, const float* __restrict__ noise, uint4* __restrict__ out,
                           int N, int C, int nd, int Cp, int H, int W) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int gin = C >> 3, gout = Cp >> 3;
   const long total = long(N) * (H >> 1) * (W >> 1) * 4 * gout;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
@@ -388,9 +408,8 @@ extern "C" int bgr_field_append_noise(const void* field, const float* noise, voi
                                       int H, int W, void* stream) {
   if (C % 8 || Cp % 8 || Cp < C + nd || nd < 1 || (H & 1) || (W & 1))
     return fail(BGR_ERR_ARG, "field_append_noise: need C, Cp multiples of 8, Cp >= C + nd, nd >= 1, even H and W");
-  field_append_noise_kernel<<<sp_grid(long(N) * (H / 2) * (W / 2) * 4 * (Cp / 8)), 256, 0,
-                              reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const uint4*>(field), noise, static_cast<uint4*>(out), N, C, nd, Cp, H, W);
+  BGR_CUDA_OK(launch_pdl(field_append_noise_kernel, dim3(sp_grid(long(N) * (H / 2) * (W / 2) * 4 * (Cp / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const uint4*>(field), noise, static_cast<uint4*>(out), N, C, nd, Cp, H, W));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -408,8 +427,8 @@ extern "C" int bgr_bilinear_fwd(const void* x, int N, int h, int w, int C, int l
                                 int ldy, int s2d, void* stream) {
   BilGeom g;
   if (int rc = make_bil(&g, N, h, w, H, W, C, ldx, ldy, s2d)) return rc;
-  bilinear_fwd_kernel<<<sp_grid(long(N) * H * W * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+  BGR_CUDA_OK(launch_pdl(bilinear_fwd_kernel, dim3(sp_grid(long(N) * H * W * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -422,8 +441,8 @@ extern "C" int bgr_bilinear_bwd(const void* gy, int N, int h, int w, int C, int 
   // always the gather form (no atomics, schedule-independent).  Broadcasts of a 1x1 map (the image-pool
   // branch, deeplab.py:623-624) are summed by the caller with bgr_gap_fwd instead: one thread per source
   // pixel would walk the whole image.
-  bilinear_bwd_gather_kernel<<<sp_grid(long(N) * h * w * (C / 8)), 256, 0, st>>>(
-      static_cast<const __nv_bfloat16*>(gy), gx, g);
+  BGR_CUDA_OK(launch_pdl(bilinear_bwd_gather_kernel, dim3(sp_grid(long(N) * h * w * (C / 8))), dim3(256), 0, st, 
+      static_cast<const __nv_bfloat16*>(gy), gx, g));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -437,16 +456,16 @@ extern "C" int bgr_gap_fwd(const void* x, int N, long P, int C, int ld, float* o
   if (blocks < 1) blocks = 1;
   const long ppb = (P + blocks - 1) / blocks;
   blocks = (P + ppb - 1) / ppb;
-  gap_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, size_t(R) * C * sizeof(float), st>>>(
-      static_cast<const __nv_bfloat16*>(x), ld, P, C, ppb, ws);
+  BGR_CUDA_OK(launch_pdl(gap_fwd_kernel, dim3(unsigned(blocks), unsigned(N)), dim3(256), size_t(R) * C * sizeof(float), st, 
+      static_cast<const __nv_bfloat16*>(x), ld, P, C, ppb, ws));
   BGR_LAUNCH_OK();
   return launch_sum_rows(ws, int(blocks), long(N) * C, out_sums, st);
 }
 
 extern "C" int bgr_gap_bwd(const void* g, int N, long P, int C, void* dx, void* stream) {
   if (C % 8) return fail(BGR_ERR_ARG, "gap: channel count must be a multiple of 8");
-  gap_bwd_kernel<<<sp_grid(long(N) * P * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(g), static_cast<__nv_bfloat16*>(dx), P, C, N, 1.f / float(P));
+  BGR_CUDA_OK(launch_pdl(gap_bwd_kernel, dim3(sp_grid(long(N) * P * (C / 8))), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<const __nv_bfloat16*>(g), static_cast<__nv_bfloat16*>(dx), P, C, N, 1.f / float(P)));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -456,8 +475,8 @@ extern "C" int bgr_head_fwd(const void* x, const void* w, int N, long K, float* 
   long blocks = (K / 8 + 255) / 256;
   if (blocks > BGR_HEAD_MAX_ROWS) blocks = BGR_HEAD_MAX_ROWS;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  head_fwd_kernel<<<dim3(unsigned(blocks), unsigned(N)), 256, 0, st>>>(
-      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, ws);
+  BGR_CUDA_OK(launch_pdl(head_fwd_kernel, dim3(unsigned(blocks), unsigned(N)), dim3(256), 0, st, 
+      static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, ws));
   BGR_LAUNCH_OK();
   return launch_sum_rows_block(ws, int(blocks), N, logits, nullptr, st);
 }
@@ -465,9 +484,9 @@ extern "C" int bgr_head_fwd(const void* x, const void* w, int N, long K, float* 
 extern "C" int bgr_head_bwd(const float* g, const void* x, const void* w, int N, long K, void* dx, float* dw,
                             void* stream) {
   if (K % 8) return fail(BGR_ERR_ARG, "head: K must be a multiple of 8");
-  head_bwd_kernel<<<sp_grid(K / 8), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  BGR_CUDA_OK(launch_pdl(head_bwd_kernel, dim3(sp_grid(K / 8)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
       g, static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(w), K, N,
-      static_cast<__nv_bfloat16*>(dx), dw);
+      static_cast<__nv_bfloat16*>(dx), dw));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -477,9 +496,9 @@ extern "C" int bgr_l1_loss_grad(const void* a, const void* b, long n, float gsca
   if (n % 8) return fail(BGR_ERR_ARG, "l1: element count must be a multiple of 8");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int blocks = sp_grid(n / 8);   // <= BGR_LOSS_MAX_ROWS
-  l1_loss_grad_kernel<<<blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(a),
+  BGR_CUDA_OK(launch_pdl(l1_loss_grad_kernel, dim3(blocks), dim3(256), 0, st, static_cast<const __nv_bfloat16*>(a),
                                               static_cast<const __nv_bfloat16*>(b), n / 8, gscale,
-                                              static_cast<__nv_bfloat16*>(grad), ws);
+                                              static_cast<__nv_bfloat16*>(grad), ws));
   BGR_LAUNCH_OK();
   return launch_sum_rows_block(ws, blocks, 1, nullptr, sum, st);
 }
@@ -495,27 +514,29 @@ extern "C" int bgr_reg_loss_grad(const void* a, const void* b, const void* w, lo
   auto B = static_cast<const __nv_bfloat16*>(b);
   auto W = static_cast<const __nv_bfloat16*>(w);
   auto G = static_cast<__nv_bfloat16*>(grad);
-#define BGR_REG_LAUNCH(M)                                                                                     \
-  if (W) reg_loss_grad_kernel<M, true><<<blocks, 256, 0, st>>>(A, B, W, n / 8, gscale, gscale_dev, beta, G, ws); \
-  else reg_loss_grad_kernel<M, false><<<blocks, 256, 0, st>>>(A, B, W, n / 8, gscale, gscale_dev, beta, G, ws)
-  if (mode == 0) { BGR_REG_LAUNCH(0); }
-  else if (mode == 1) { BGR_REG_LAUNCH(1); }
-  else { BGR_REG_LAUNCH(2); }
+#define BGR_REG_LAUNCH(M)                                                                                               \
+  if (W) { BGR_CUDA_OK(launch_pdl(reg_loss_grad_kernel<M, true>, dim3(blocks), dim3(256), 0, st, A, B, W, n / 8, gscale,   \
+                                  gscale_dev, beta, G, ws)); }                                                           \
+  else { BGR_CUDA_OK(launch_pdl(reg_loss_grad_kernel<M, false>, dim3(blocks), dim3(256), 0, st, A, B, W, n / 8, gscale,    \
+                                gscale_dev, beta, G, ws)); }
+  if (mode == 0) { BGR_REG_LAUNCH(0) }
+  else if (mode == 1) { BGR_REG_LAUNCH(1) }
+  else { BGR_REG_LAUNCH(2) }
 #undef BGR_REG_LAUNCH
   BGR_LAUNCH_OK();
   return launch_sum_rows_block(ws, blocks, 1, nullptr, sum, st);
 }
 
 extern "C" int bgr_field_to_nchw(const void* field, float* nchw, int N, int C, int H, int W, void* stream) {
-  field_convert_kernel<true><<<sp_grid(long(N) * C * H * W), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(field)), nchw, N, C, H, W);
+  BGR_CUDA_OK(launch_pdl(field_convert_kernel<true>, dim3(sp_grid(long(N) * C * H * W)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(field)), nchw, N, C, H, W));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
 
 extern "C" int bgr_nchw_to_field(const float* nchw, void* field, int N, int C, int H, int W, void* stream) {
-  field_convert_kernel<false><<<sp_grid(long(N) * C * H * W), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      static_cast<__nv_bfloat16*>(field), const_cast<float*>(nchw), N, C, H, W);
+  BGR_CUDA_OK(launch_pdl(field_convert_kernel<false>, dim3(sp_grid(long(N) * C * H * W)), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), 
+      static_cast<__nv_bfloat16*>(field), const_cast<float*>(nchw), N, C, H, W));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -530,6 +551,8 @@ namespace bgr {
 // [256][taps] fp32 chunk is read coalesced into shared memory and written tap-major.
 __global__ void __launch_bounds__(256)
 weight_to_gemm_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int Cin, int taps, int pitch) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   extern __shared__ float sh[];   // [256][taps]
   const int co = blockIdx.x, ci0 = blockIdx.y * 256;
   const int n = min(256, pitch - ci0);            // columns to write (zeros beyond Cin)
@@ -546,6 +569,8 @@ weight_to_gemm_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ o
 // 32x32 shared-memory tiles (coalesced on both sides); co in [Cout, pitch) is written as zero.
 __global__ void __launch_bounds__(256)
 weight_to_gemm_t_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int Cout, int J, int pitch) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ float tile[32][33];
   const int j0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
@@ -574,10 +599,10 @@ extern "C" int bgr_weight_to_gemm(const float* w, int Cout, int Cin, int taps, i
     // [Cout][J = Cin*taps] -> [J][pitch]: row j = ci*taps + t is exactly out[ci][t][:]
     const int J = Cin * taps;
     dim3 grid((J + 31) / 32, (pitch + 31) / 32);
-    bgr::weight_to_gemm_t_kernel<<<grid, 256, 0, st>>>(w, O, Cout, J, pitch);
+    BGR_CUDA_OK(launch_pdl(bgr::weight_to_gemm_t_kernel, dim3(grid), dim3(256), 0, st, w, O, Cout, J, pitch));
   } else {
     dim3 grid(Cout, (pitch + 255) / 256);
-    bgr::weight_to_gemm_kernel<<<grid, 256, 256 * taps * sizeof(float), st>>>(w, O, Cin, taps, pitch);
+    BGR_CUDA_OK(launch_pdl(bgr::weight_to_gemm_kernel, dim3(grid), dim3(256), 256 * taps * sizeof(float), st, w, O, Cin, taps, pitch));
   }
   BGR_LAUNCH_OK();
   return BGR_OK;
@@ -591,6 +616,8 @@ extern "C" int bgr_weight_to_gemm(const float* w, int Cout, int Cin, int taps, i
 namespace bgr {
 __global__ void __launch_bounds__(256)
 weights_prepare_kernel(const BgrWeightDesc* __restrict__ descs, const int* __restrict__ first_block, int ndesc) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   __shared__ float sh[256 * 9];   // mode 0: [256][taps <= 9]; mode 1: a 32x33 tile
   int lo = 0, hi = ndesc - 1;
   while (lo < hi) {               // last d with first_block[d] <= blockIdx.x
@@ -643,7 +670,7 @@ weights_prepare_kernel(const BgrWeightDesc* __restrict__ descs, const int* __res
 extern "C" int bgr_weights_prepare(const BgrWeightDesc* descs, const int* first_block, int ndesc, int total_blocks,
                                    void* stream) {
   if (ndesc < 1 || total_blocks < 1) return bgr::fail(BGR_ERR_ARG, "weights_prepare: empty descriptor table");
-  bgr::weights_prepare_kernel<<<total_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(descs, first_block, ndesc);
+  BGR_CUDA_OK(launch_pdl(bgr::weights_prepare_kernel, dim3(total_blocks), dim3(256), 0, reinterpret_cast<cudaStream_t>(stream), descs, first_block, ndesc));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }

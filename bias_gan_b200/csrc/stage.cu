@@ -46,6 +46,8 @@ __global__ void __launch_bounds__(256)
 stage_kernel(const T* __restrict__ src, const float* __restrict__ shift,
              const float* __restrict__ scale, __nv_bfloat16* __restrict__ dst,
              const __grid_constant__ StageParams p) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int groups = p.C >> 3;                 // 8-channel groups
   const int wq = p.w >> 2;                     // 4-pixel quads per row (w % 4 == 0 required)
   const size_t total = size_t(p.B) * p.h * wq * groups;
@@ -121,11 +123,11 @@ static int launch_stage(const void* src, int layout, bool vec, const float* shif
   const T* s = static_cast<const T*>(src);
   __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst);
   if (layout == BGR_NCHW) {
-    if (vec) stage_kernel<T, BGR_NCHW, true><<<blocks, 256, 0, st>>>(s, shift, scale, d, p);
-    else stage_kernel<T, BGR_NCHW, false><<<blocks, 256, 0, st>>>(s, shift, scale, d, p);
+    if (vec) BGR_CUDA_OK(launch_pdl(stage_kernel<T, BGR_NCHW, true>, dim3(blocks), dim3(256), 0, st, s, shift, scale, d, p));
+    else BGR_CUDA_OK(launch_pdl(stage_kernel<T, BGR_NCHW, false>, dim3(blocks), dim3(256), 0, st, s, shift, scale, d, p));
   } else {
-    if (vec) stage_kernel<T, BGR_NHWC, true><<<blocks, 256, 0, st>>>(s, shift, scale, d, p);
-    else stage_kernel<T, BGR_NHWC, false><<<blocks, 256, 0, st>>>(s, shift, scale, d, p);
+    if (vec) BGR_CUDA_OK(launch_pdl(stage_kernel<T, BGR_NHWC, true>, dim3(blocks), dim3(256), 0, st, s, shift, scale, d, p));
+    else BGR_CUDA_OK(launch_pdl(stage_kernel<T, BGR_NHWC, false>, dim3(blocks), dim3(256), 0, st, s, shift, scale, d, p));
   }
   BGR_LAUNCH_OK();
   return BGR_OK;

@@ -69,6 +69,8 @@ __device__ __forceinline__ void acc_store(const AccT<T>& a, double* o) {
 template <typename T>
 __global__ void __launch_bounds__(256)
 stats_plane_kernel(const T* __restrict__ src, long P, long chunk, int splits, double* __restrict__ part) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const long row = blockIdx.y;
   const T* plane = src + row * P;
   const long e0 = long(blockIdx.x) * chunk, e1 = min(e0 + chunk, P);
@@ -106,6 +108,8 @@ stats_plane_kernel(const T* __restrict__ src, long P, long chunk, int splits, do
 template <typename T>
 __global__ void __launch_bounds__(256)
 stats_pixels_kernel(const T* __restrict__ src, long P, int Cf, long chunk, int splits, double* __restrict__ part) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   constexpr int V = 16 / sizeof(T);
   const int G = Cf / V;                                  // vectors per pixel
   const long b = blockIdx.y;
@@ -147,6 +151,8 @@ stats_pixels_kernel(const T* __restrict__ src, long P, int Cf, long chunk, int s
 template <typename T>
 __global__ void __launch_bounds__(256)
 stats_pixels_scalar_kernel(const T* __restrict__ src, long P, int Cf, long chunk, int splits, double* __restrict__ part) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const long row = blockIdx.y, b = row / Cf;
   const int c = int(row % Cf);
   const T* base = src + b * P * Cf + c;
@@ -169,6 +175,8 @@ stats_pixels_scalar_kernel(const T* __restrict__ src, long P, int Cf, long chunk
 // out[b][k][c], k = mean, mean-square, min, max
 __global__ void stats_finalize_kernel(const double* __restrict__ part, int B, int Cf, int splits, double n,
                                       double* __restrict__ out) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * Cf) return;
   const double* p = part + long(i) * splits * 4;
@@ -192,17 +200,17 @@ static int channel_stats_impl(const T* src, int layout, int B, int Cf, long P, i
   if (layout == BGR_NCHW) {
     long chunk = (P + splits - 1) / splits;
     chunk = (chunk + V - 1) / V * V;
-    stats_plane_kernel<T><<<dim3(splits, B * Cf), 256, 0, st>>>(src, P, chunk, splits, part);
+    BGR_CUDA_OK(launch_pdl(stats_plane_kernel<T>, dim3(splits, B * Cf), dim3(256), 0, st, src, P, chunk, splits, part));
   } else {
     const long chunk = (P + splits - 1) / splits;
     const int G = Cf / V;
     const bool vec = Cf % V == 0 && G >= 1 && G <= 32 && (G & (G - 1)) == 0 &&
                      (reinterpret_cast<uintptr_t>(src) & 15) == 0;
-    if (vec) stats_pixels_kernel<T><<<dim3(splits, B), 256, 0, st>>>(src, P, Cf, chunk, splits, part);
-    else stats_pixels_scalar_kernel<T><<<dim3(splits, B * Cf), 256, 0, st>>>(src, P, Cf, chunk, splits, part);
+    if (vec) BGR_CUDA_OK(launch_pdl(stats_pixels_kernel<T>, dim3(splits, B), dim3(256), 0, st, src, P, Cf, chunk, splits, part));
+    else BGR_CUDA_OK(launch_pdl(stats_pixels_scalar_kernel<T>, dim3(splits, B * Cf), dim3(256), 0, st, src, P, Cf, chunk, splits, part));
   }
   BGR_LAUNCH_OK();
-  stats_finalize_kernel<<<(B * Cf + 127) / 128, 128, 0, st>>>(part, B, Cf, splits, double(P), out);
+  BGR_CUDA_OK(launch_pdl(stats_finalize_kernel, dim3((B * Cf + 127) / 128), dim3(128), 0, st, part, B, Cf, splits, double(P), out));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
