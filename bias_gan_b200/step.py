@@ -140,7 +140,14 @@ class GraphedGanStep:
         lib.bgr_launch_count.restype = __import__("ctypes").c_ulonglong
         c0 = lib.bgr_launch_count()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # BGR_GRAPH_PRIORITY=1 captures the critical chain on a HIGH-priority stream while the weight-gradient side
+        # stream (functional._side_stream) keeps the default priority, so that at replay the block scheduler serves
+        # the forward / data-gradient chain first.  Measured on B200 and NOT adopted (profiles/r02_sched_ab.txt):
+        # 127.6 vs 126.3 ms/step -- the deferred weight gradients pile up in front of the optimizer step.
+        cap = None
+        if os.environ.get("BGR_GRAPH_PRIORITY", "0") == "1":
+            cap = torch.cuda.Stream(device=device, priority=-1)
+        with torch.cuda.graph(self.graph, stream=cap):
             self.d_loss, self.g_loss = self._run()
         self.launches_per_step = int(lib.bgr_launch_count() - c0)   # kernels of libbgr.so in the graph
         L.invalidate_cache()
