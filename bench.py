@@ -464,12 +464,12 @@ def conv_traffic(n_launches):
     """DRAM bytes per conv launch from the committed ncu capture of this same step (profiles/):
     measured once per round under ncu, never inside a timed run."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r01_conv_traffic.json")))
+        t = json.load(open(os.path.join(ROOT, "profiles", "r02_conv_traffic.json")))
     except (OSError, ValueError):
         return None, None
     if t.get("launches_per_step") != n_launches:   # the capture is of another schedule: do not quote it
-        return None, "profiles/r01_conv_traffic.json is stale (%s launches per step there)" % t.get("launches_per_step")
-    return t["dram_bytes_per_launch"], "profiles/r01_conv_traffic.json"
+        return None, "profiles/r02_conv_traffic.json is stale (%s launches per step there)" % t.get("launches_per_step")
+    return t["dram_bytes_per_launch"], "profiles/r02_conv_traffic.json"
 
 
 _OUT = None
