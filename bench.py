@@ -33,6 +33,12 @@ METRIC = "GAN train samples/sec (G+D step)"
 CONFIGS = {"baseline": (768, 1152, 8), "hires": (1536, 2304, 4), "ingest": (768, 1152, 8)}
 
 
+def workload_string(config, batch):
+    """The same string in the product arm and the reference arm: it names BASELINE.json's configuration."""
+    return ("%s config: G+D train step (train_gan.py:250-298), 16x%dx%d fields, local batch %d, "
+            "DeepLabv3+/Xception G (Interpolate) + Xception D, AdamW" % (config, H, W, batch))
+
+
 def set_config(name, batch=None):
     """Select the workload; returns the local batch."""
     global H, W, W_MIN
@@ -257,8 +263,11 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3 * b / 2.0, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "%s config: G+D train step, 16x%dx%d fields, batch %d/GPU (reference CPU path, "
-                                   "local batch 2 per step, value per sample)" % (args.config, H, W, b)},
+            "config": {"workload": workload_string(args.config if args.config != "ingest" else "baseline", b),
+                       "global_batch": b * max(1, args.gpus), "parallelism": "dp%d" % max(1, args.gpus),
+                       "reference_arm": "the reference's CPU implementation of the same step on the host cores; BatchNorm "
+                                        "rejects batch 1 and a batch-%d step needs %d x the memory, so one step at local "
+                                        "batch 2 is timed and reported per sample" % (b, b // 2)},
             "cpu_baseline": {"value": v, "unit": "samples/s", "cores": threads, "kind": kind, "sample": sample,
                              "seconds_per_step_of_2": dt},
             "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -698,8 +707,7 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "%s config: G+D train step (train_gan.py:250-298), 16x%dx%d fields, local batch %d, "
-                                   "DeepLabv3+/Xception G (Interpolate) + Xception D, AdamW" % (args.config, H, W, B),
+            "config": {"workload": workload_string(args.config, B),
                        "global_batch": B * world, "parallelism": "dp%d" % world,
                        "schedule": "faithful" if args.faithful else "lean (result-identical, SURVEY F8)",
                        "grad_sync": "DISABLED (control run, not data-parallel training)" if args.no_grad_sync else
