@@ -314,6 +314,21 @@ extern "C" int bgr_reader_init_file(void* handle, const char* filename) {
     return fail(BGR_ERR_RUNTIME,
                 std::string("NumpyReader: failed to open file ") + filename + ": " + strerror(errno));
   posix_fadvise(r->fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+  // The reference re-uses the geometry of the file that was parsed for every file it opens afterwards
+  // (gpsro_dataset.py:133-148).  A LARGER file than the parsed header describes is a file of another shape: its
+  // bytes would be delivered silently mis-shaped, so refuse it.  (A shorter one keeps the reference's
+  // behaviour: IndexError("... file corruption ...") from the read.)
+  if (r->parsed) {
+    struct stat sb;
+    const int64_t expect = r->offset + r->numsample * r->numelem * int64_t(r->typesize);
+    if (fstat(r->fd, &sb) == 0 && int64_t(sb.st_size) > expect + 4096) {
+      close(r->fd);
+      r->fd = -1;
+      return fail(BGR_ERR_RUNTIME, std::string("NumpyReader: ") + filename + " holds " +
+                                       std::to_string(int64_t(sb.st_size)) + " bytes, more than the parsed header describes (" +
+                                       std::to_string(expect) + "): call parse() for files of another shape");
+    }
+  }
   return BGR_OK;
 }
 

@@ -247,3 +247,26 @@ def test_enable_disable_p2p(tmp_path):
     r.disable_p2p()
     r.disable_p2p()
     assert torch.cuda.current_device() == cur
+
+
+def test_init_file_refuses_a_file_of_another_shape(tmp_path):
+    """The geometry of the parsed file is re-used for every file opened afterwards (gpsro_dataset.py:133-148): a
+    larger file cannot be one of the same shape and is refused instead of being delivered mis-shaped; `out=` must
+    match the parsed geometry (dtype, size) or the read is refused before the C side writes."""
+    a, b = np.zeros((4, 8, 8), np.float32), np.zeros((4, 64, 64), np.float32)
+    fa, fb = str(tmp_path / "a.npy"), str(tmp_path / "b.npy")
+    np.save(fa, a); np.save(fb, b)
+    r = nr.numpy_reader(False, -1)
+    r.parse(fa)
+    r.init_file(fa)
+    with pytest.raises(ValueError):
+        r.get_sample(0, out=torch.empty(10))                       # too small
+    with pytest.raises(ValueError):
+        r.get_sample(0, out=torch.empty(4, 8, 8, dtype=torch.float64))   # wrong dtype
+    assert np.array_equal(r.get_sample(0, out=torch.empty(4, 8, 8)).numpy(), a)
+    r.finalize_file()
+    with pytest.raises(RuntimeError, match="more than the parsed header"):
+        r.init_file(fb)
+    r.parse(fb); r.init_file(fb)
+    assert tuple(r.get_sample(0).shape) == (4, 64, 64)
+    r.finalize_file()
