@@ -11,6 +11,9 @@
 #include <cooperative_groups.h>
 #include <cuda_bf16.h>
 
+#include <mutex>
+#include <string>
+
 #include "bgr_internal.h"
 
 namespace bgr {
@@ -636,6 +639,67 @@ extern "C" int bgr_bn_stats(const void* x, long M, int C, int ld, float* part, i
   BGR_CUDA_OK(launch_pdl(bn_stats_kernel, dim3(grid), dim3(256), reduce_smem(C), st, static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, part));
   BGR_LAUNCH_OK();
   *rows = grid;
+  return BGR_OK;
+}
+
+// ---------------------------------------------------------------- bgr_bn_stats without any allocation by anyone
+// The partial rows of the statistics pass live in a file-scope device array instead of a caller-provided workspace,
+// for callers that cannot allocate device memory at all (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  Every GPU that loads this library holds the array (7.0 MiB) until exit.
+// Nothing in it has to start at zero: each of the `rows` blocks overwrites its whole row before the sum reads
+// exactly those rows.  All calls share the array, so two calls that overlap on one GPU (different streams) race.
+static __device__ __align__(256) float g_bn_stats_scratch[size_t(BGR_BN_MAX_ROWS) * 2 * BGR_BN_STATS_STATIC_MAX_C];
+
+namespace bgr {
+// sums[c] = sum over the partial rows (fixed order, fp64) of sum_m x, sums[C + c] = the same of sum_m x^2
+__global__ void __launch_bounds__(256)
+bn_sums_kernel(const float* __restrict__ part, int rows, int C, double* __restrict__ sums) {
+  pdl_wait();      // programmatic dependent launch: see bgr_internal.h
+  pdl_trigger();
+  int c;
+  double s, q;
+  if (!ordered_row_sums(part, rows, C, &c, &s, &q)) return;
+  sums[c] = s;
+  sums[C + c] = q;
+}
+
+// Device address of the scratch array on the CURRENT device.  In host code the array's name is only a host-side
+// stand-in for the symbol, not a device address; cudaGetSymbolAddress resolves it, once per device ordinal, with
+// that device current (it allocates nothing: the array came with the module).
+static int bn_stats_scratch_ptr(float** out) {
+  static std::mutex mu;
+  static float* cache[64] = {nullptr};
+  int dev = 0;
+  BGR_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(BGR_ERR_ARG, "bn_stats_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (cache[dev] == nullptr) {
+    float* ptr = nullptr;
+    BGR_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_bn_stats_scratch));
+    if (ptr == nullptr) return fail(BGR_ERR_CUDA, "bn_stats_static: cudaGetSymbolAddress returned a null address");
+    cache[dev] = ptr;
+  }
+  *out = cache[dev];
+  return BGR_OK;
+}
+}  // namespace bgr
+
+extern "C" int bgr_bn_stats_static(const void* x, long M, int C, int ld, double* sums, void* stream) {
+  BGR_CHECK_C8(C);
+  if (C > BGR_BN_STATS_STATIC_MAX_C)
+    return fail(BGR_ERR_ARG, "bn_stats_static: C = " + std::to_string(C) + " exceeds BGR_BN_STATS_STATIC_MAX_C = " +
+                                 std::to_string(BGR_BN_STATS_STATIC_MAX_C) + " (use bgr_bn_stats with your own workspace)");
+  if (M < 1 || sums == nullptr || x == nullptr) return fail(BGR_ERR_ARG, "bn_stats_static: empty input or missing output");
+  if (reduce_smem(C) > 48 * 1024) return fail(BGR_ERR_ARG, "bn_stats_static: too many channels");
+  float* scratch = nullptr;
+  if (int rc = bn_stats_scratch_ptr(&scratch)) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int rpb;
+  const int grid = reduce_grid(M, C, &rpb);   // <= BGR_BN_MAX_ROWS rows of 2*C floats
+  BGR_CUDA_OK(launch_pdl(bn_stats_kernel, dim3(grid), dim3(256), reduce_smem(C), st, static_cast<const __nv_bfloat16*>(x), M, C, ld, rpb, scratch));
+  BGR_LAUNCH_OK();
+  BGR_CUDA_OK(launch_pdl(bn_sums_kernel, dim3((C + kRsCh - 1) / kRsCh), dim3(256), 0, st, static_cast<const float*>(scratch), grid, C, sums));
+  BGR_LAUNCH_OK();
   return BGR_OK;
 }
 

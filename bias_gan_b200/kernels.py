@@ -589,3 +589,16 @@ def field_to_nchw_padded(field, C, H, W):
     out = torch.empty((N, C, H, W), dtype=torch.float32, device=field.device)
     check(_lib.lib().bgr_field_to_nchw_padded(ptr(field), ptr(out), N, C, C4 // 4, H, W, stream_ptr()))
     return out
+
+
+BN_STATS_STATIC_MAX_C = 2048   # include/bgr.h
+
+
+def bn_stats_static(x, out):
+    """bgr_bn_stats_static: per-channel (sum x | sum x^2) of a bf16 [..., C] view into the caller's fp64 [2C]
+    device tensor `out`; the partial rows live in the library's own static device array, so neither this wrapper
+    nor the entry point allocates anything (not added by the reference: see include/bgr.h)."""
+    M, C, ld = _rows(x)
+    assert out.is_cuda and out.dtype == torch.float64 and out.is_contiguous() and out.numel() == 2 * C
+    check(_lib.lib().bgr_bn_stats_static(ptr(x), c_long(M), C, ld, ptr(out), stream_ptr()))
+    return out

@@ -146,6 +146,16 @@ int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int ldx, const v
 /* part: fp32 [BGR_BN_MAX_ROWS][2*C] workspace; writes *rows (HOST int) partial rows of
  * [sum_m x | sum_m x^2], one per thread block. */
 int bgr_bn_stats(const void* x, long M, int C, int ld, float* part, int* rows, void* stream);
+/* NO COUNTERPART IN THE REFERENCE.  bgr_bn_stats for callers that
+ * cannot allocate device memory at all (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc): the partial rows go to a file-scope device array of the library (fp32
+ * [BGR_BN_MAX_ROWS][2*BGR_BN_STATS_STATIC_MAX_C] = 7.0 MiB, held by every GPU that loads libbgr.so until exit) and the
+ * result is the finished statistics sums[0..C) = sum_m x, sums[C..2C) = sum_m x^2 (DEVICE fp64 [2*C], rows added in
+ * row order).  The call allocates nothing (no cudaMalloc / cudaFree, no library allocator).  C > the maximum is
+ * rejected with BGR_ERR_ARG.  All calls share the one array: calls that overlap on the same GPU race (serialise
+ * them on one stream); no state is carried from one call to the next. */
+#define BGR_BN_STATS_STATIC_MAX_C 2048
+int bgr_bn_stats_static(const void* x, long M, int C, int ld, double* sums, void* stream);
 /* The `rows` partial rows of `part` are added in row order in fp64, then:
  * mean, invstd = 1/sqrt(var_biased+eps), a = gamma*invstd, b = beta - mean*a; running stats
  * updated with `momentum` and the unbiased variance (nn.BatchNorm2d semantics); gamma/beta/
