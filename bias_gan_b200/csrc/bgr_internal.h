@@ -61,8 +61,14 @@ inline int ensure_dyn_smem(K kern, int bytes) { return ensure_dyn_smem_impl(rein
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-bool pdl_enabled();
-template <typename... KArgs, typename... Args>
+// BGR_PDL: 0 / unset = off, 1 = every kernel, 2 = the implicit-GEMM kernels only (their prologue -- barrier init,
+// TMEM allocation, tensor-map prefetch -- is the longest), 3 = every kernel except those.
+int pdl_mode();
+inline bool pdl_enabled(bool gemm = false) {
+  const int m = pdl_mode();
+  return m == 1 || (m == 2 && gemm) || (m == 3 && !gemm);
+}
+template <bool GEMM = false, typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
@@ -71,7 +77,7 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled(GEMM) ? 1 : 0;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);

@@ -76,12 +76,12 @@ int sm_count() {
   return cache[dev];
 }
 
-bool pdl_enabled() {
-  static const bool on = [] {
+int pdl_mode() {
+  static const int mode = [] {
     const char* v = getenv("BGR_PDL");
-    return v && v[0] == '1';    // opt-in until measured
+    return (v && v[0] >= '0' && v[0] <= '3') ? v[0] - '0' : 0;    // opt-in: measured slower (profiles/r02_sched_ab.txt)
   }();
-  return on;
+  return mode;
 }
 
 int ensure_dyn_smem_impl(const void* kern, int bytes) {

@@ -452,7 +452,7 @@ static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   auto kern = conv_fprop_kernel<BLOCK_N, STAGES, STATS>;
   if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
   dim3 grid(groups * p.n_tiles);
-  BGR_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(192), smem, st, tmA, tmB, tmO, bias, stats, p));
+  BGR_CUDA_OK(launch_pdl<true>(kern, dim3(grid), dim3(192), smem, st, tmA, tmB, tmO, bias, stats, p));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -496,7 +496,7 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* 
   if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
   const int tiles = ((p.Cout + kBlockM - 1) / kBlockM) * ((p.Cin + BLOCK_N - 1) / BLOCK_N) * p.ntaps;
   dim3 grid(tiles, splits);
-  BGR_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(192), smem, st, tmDY, tmX, dst, p));
+  BGR_CUDA_OK(launch_pdl<true>(kern, dim3(grid), dim3(192), smem, st, tmDY, tmX, dst, p));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
