@@ -11,7 +11,7 @@
 #include "bgr_internal.h"
 
 #ifndef BGR_DW_FFMA2
-#define BGR_DW_FFMA2 0   // packed fp32 FMAs (FFMA2): measured no faster (fwd) or slower (wgrad, spills)
+#define BGR_DW_FFMA2 1   // packed fp32 FMAs (FFMA2): -16 % instructions in the issue-bound marches; 1-2 % per kernel (r02)
 #endif
 
 namespace bgr {
@@ -388,10 +388,11 @@ __device__ __forceinline__ void dw_load_coef(XfCoef* t, const float* xa, const f
   t->slope = slope;
 }
 
-// Two scalar FMAs.  The packed FFMA2 form was measured twice (before and after the cp.async ring):
-// same time to the microsecond at every trunk shape, as is a ring of 8 rows instead of 4 -- at the
-// mid-flow shape the march is bound by neither issue slots nor load latency but by its fixed ramp
-// (weights, item decode, first ring fill from cold HBM) on 25 us of work.
+// Packed FFMA2 (same rounding as two scalar FMAs: results are bit-identical).  Round 1 measured it as no gain while
+// the marches were bound by their ramp; with the cost-model planner they are issue-bound at the mid-flow shape (ncu:
+// 49 % issue-active at 12 warps per SM, profiles/r02_dw_march_mid_flow_ncu.txt) and 864 FFMA -> 432 FFMA2 removes 16 %
+// of the kernel's instructions: 1-2 % per kernel at every trunk shape, 0.3 ms of the step
+// (profiles/r02_dw_ffma2_ab.txt).  -DBGR_DW_FFMA2=0 restores the scalar form.
 __device__ __forceinline__ float2 fma2s(const float2& a, const float2& b, const float2& c) {
 #if BGR_DW_FFMA2
   return __ffma2_rn(a, b, c);
