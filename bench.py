@@ -410,7 +410,7 @@ def conv_roofline_step(step_fn, torch, K):
     of every conv launch (shapes, pixel strides, taps, epilogue options); each distinct signature is
     then timed alone with CUDA events on the launching stream, L2 flushed before every launch, and
     weighted by its launch count.  (Event pairs around the launches of a live step would time the
-    host: launching 6000 kernels one by one is slower than the GPU runs them.)"""
+    host: launching ~3400 kernels one by one is slower than the GPU runs them.)"""
     sigs = {}
     orig_f, orig_w = K.conv_fprop, K.conv_wgrad
 
@@ -432,7 +432,7 @@ def conv_roofline_step(step_fn, torch, K):
         K.conv_fprop, K.conv_wgrad = orig_f, orig_w
     dev = torch.device("cuda", torch.cuda.current_device())
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
-    by, reps = {}, 3
+    by, reps, table = {}, 3, []
     for (kind, shape, ldx, cout, dy, dx, has_bias, has_stats), count in sigs.items():
         n, h, w_, cin = shape
         x = torch.randn(n, h, w_, max(ldx, cin), device=dev).bfloat16()[..., :cin]
@@ -455,6 +455,10 @@ def conv_roofline_step(step_fn, torch, K):
             e0.record(); fn(); e1.record()
             torch.cuda.synchronize()
             ms += e0.elapsed_time(e1) / reps
+        px_ = n * h * w_
+        table.append((count * ms, count, ms * 1e3, kind, "%dx%dx%d" % (n, h, w_), cin, cout, nt, max(abs(v) for v in dy + dx),
+                      "stats" if has_stats else ("bias" if has_bias else "-"), 2.0 * px_ * cin * cout * nt / (ms * 1e-3) / 1e12,
+                      (2.0 * px_ * (cin + cout) + cout * nt * cin * (2.0 if kind == "fprop" else 4.0)) / (ms * 1e-3) / 1e9))
         a = by.setdefault(kind, [0.0, 0.0, 0, 0.0])
         a[0] += count * 2.0 * n * h * w_ * cin * cout * nt
         a[1] += count * ms
@@ -463,6 +467,15 @@ def conv_roofline_step(step_fn, torch, K):
         px = n * h * w_
         a[3] += count * (2.0 * px * (cin + cout) + cout * nt * cin * (2.0 if kind == "fprop" else 4.0))
         del x, fn
+    path = os.environ.get("BGR_CONV_TABLE")   # per-signature table of the step's implicit-GEMM launches (profiles/)
+    if path:
+        with open(path, "w") as f:
+            f.write("# every distinct implicit-GEMM launch signature of one G+D step, timed alone (CUDA events, L2 flushed), by\n"
+                    "# share of the step's conv time.  GB/s = algorithmic bytes (operands + result once) / time: the HBM-bound\n"
+                    "# signatures are the ones near the measured copy bandwidth, the tensor-bound ones near the bf16 peak.\n")
+            f.write("#  total_ms  count   us/launch  kind   pixels        Cin  Cout taps maxoff epilogue  TFLOP/s    GB/s\n")
+            for r in sorted(table, reverse=True):
+                f.write("%10.3f %6d %11.1f  %-5s  %-12s %5d %5d %4d %6d %-8s %8.1f %7.0f\n" % r)
     flops = sum(v[0] for v in by.values())
     ms = sum(v[1] for v in by.values())
     return flops, ms, sum(v[2] for v in by.values()), \

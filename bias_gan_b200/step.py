@@ -93,7 +93,7 @@ def gan_step(G, D, g_opt, d_opt, crit_gan, crit_reg, inputs, real, w_gan=1.0, w_
 
 
 class GraphedGanStep:
-    """gan_step captured once into a CUDA graph and replayed: the ~6000 kernel launches of a step
+    """gan_step captured once into a CUDA graph and replayed: the ~3400 kernel launches of a step
     (and PyTorch's autograd bookkeeping between them) collapse into one graph launch, so the GPU is
     never waiting for the host.  Inputs are copied (or staged directly, see `inputs`/`real`) into
     static field buffers; the adversarial labels are drawn on the host before each replay

@@ -10,10 +10,11 @@ Restates (state-dict keys identical, so weights interchange with the reference a
   GANLossRef                  src/deepCam/utils/losses.py:129-172
   gan_step_ref                src/deepCam/gpsro_train/train_gan.py:244-301 (one G+D step)
 
-Pinned: tests/test_oracle_model.py checks it against the reference's own modules imported from
-/root/reference (forward, losses and per-parameter gradients) in the build container, and
-against tests/golden/model_golden.pt (generated from the reference modules by
-tests/golden/make_model_golden.py) everywhere.  The arithmetic itself lives in PyTorch ATen
+Pinned: tests/test_oracle_model.py checks it against tests/golden/model_golden.pt, noise_golden.pt, gp_golden.pt and
+deconv_golden.pt -- vectors (outputs, logits, losses, BatchNorm statistics, every per-parameter gradient norm)
+produced by the reference's OWN modules imported from /root/reference in the build container by the committed
+scripts tests/golden/make_*_golden.py.  The test itself never imports the reference (it must run on the GPU box).
+The arithmetic itself lives in PyTorch ATen
 (un-vendored third-party code; the reference pins only the NGC 20.12 container).
 """
 import math
