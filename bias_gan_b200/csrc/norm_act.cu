@@ -40,6 +40,51 @@ __device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
   *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(p + 4);
 }
 
+// ---- packed (float2) forms.  The streaming kernels are issue-bound at the mid-flow shape (40 MB tensors that
+// live in L2), so their inner loops use FFMA2 / FADD2 / FMUL2 on channel pairs, round two values per cvt, and step
+// pointers instead of recomputing 64-bit row offsets.  Every operation is the same IEEE operation as the scalar
+// form it replaced, in the same order per channel: results are bit-identical (checked against the scalar library
+// on B200, tools/dev_bn_bits.py).
+__device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+__device__ __forceinline__ void unpack8p(const uint4& u, float2 (&f)[4]) {
+  f[0] = bf2_to_f2(u.x); f[1] = bf2_to_f2(u.y); f[2] = bf2_to_f2(u.z); f[3] = bf2_to_f2(u.w);
+}
+__device__ __forceinline__ uint32_t pack2rn(const float2& f) {   // two RNE roundings in one cvt.rn.bf16x2.f32
+  __nv_bfloat162 t = __floats2bfloat162_rn(f.x, f.y);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ void load8p(const float* p, float2 (&f)[4]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = make_float2(a.x, a.y); f[1] = make_float2(a.z, a.w);
+  f[2] = make_float2(b.x, b.y); f[3] = make_float2(b.z, b.w);
+}
+// LeakyReLU derivative / value select on a pair: z > 0 ? v : slope * v
+__device__ __forceinline__ float2 leaky_sel(const float2& z, const float2& v, const float2& sl2) {
+  const float2 sv = __fmul2_rn(sl2, v);
+  return make_float2(z.x > 0.f ? v.x : sv.x, z.y > 0.f ? v.y : sv.y);
+}
+
+// ---- per-thread asynchronous row ring.  A thread of these kernels walks 6-60 rows of 16 bytes per tensor; with
+// the loads held in registers (two rows in flight) it is a serial chain of memory round trips -- latency-bound at
+// the mid-flow shape, where a whole 40 MB pass should take 6 us and took 25-35 (fewer instructions changed
+// nothing: profiles/r02_bn_ring.txt).  Rows are therefore fetched kDepth ahead with cp.async into shared-memory
+// slots that only the issuing thread reads back (no barriers, no registers held by loads in flight), the scheme
+// of the depthwise marches.  Slot layout [tensor][slot][thread] x 16 bytes: consecutive threads, consecutive lines.
+__device__ __forceinline__ void bn_cp16(uint4* smem, const void* gmem, bool valid) {
+  const unsigned sa = static_cast<unsigned>(__cvta_generic_to_shared(smem));
+  const int sz = valid ? 16 : 0;   // 0 source bytes: nothing is read
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gmem), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void bn_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bn_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__host__ __device__ constexpr int bn_ring_depth(int ntensors) { return ntensors <= 2 ? 4 : 2; }   // power of two
+static size_t bn_ring_bytes(int ntensors, int threads) {
+  return size_t(ntensors) * bn_ring_depth(ntensors) * threads * sizeof(uint4);
+}
+
 // Thread -> (row lane r, channel group g) mapping shared by the reduction kernels:
 // G = C/8 groups.  If G <= 256 a block covers R = 256/G rows at a time, else each thread loops
 // over groups g = tid, tid+256, ...
@@ -179,42 +224,58 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __res
   const int g0 = G >= 256 ? threadIdx.x : threadIdx.x % G;
   const int r = G >= 256 ? 0 : threadIdx.x / G;
   const long rstep = long(gridDim.x) * R;
+  const float2 sl2 = make_float2(slope, slope);
   for (int g = g0; g < G; g += 256) {
-    float av[8], bv[8];
-    load8f(a + g * 8, av);
-    load8f(b + g * 8, bv);
-    auto one = [&](long row, const uint4& xu, const uint4& ru) {
-      float f[8], rr[8];
-      unpack8(xu, f);
-      if (RES) unpack8(ru, rr);
+    float2 av[4], bv[4];
+    load8p(a + g * 8, av);
+    load8p(b + g * 8, bv);
+    auto one = [&](__nv_bfloat16* dst, const uint4& xu, const uint4& ru) {
+      float2 f[4], rr[4];
+      unpack8p(xu, f);
+      if (RES) unpack8p(ru, rr);
+      uint4 o;
+      uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float v = fmaf(av[j], f[j], bv[j]);
-        if (RES) v += rr[j];
-        if (ACT) v = v > 0.f ? v : slope * v;
-        f[j] = v;
+      for (int j = 0; j < 4; ++j) {
+        float2 v = __ffma2_rn(av[j], f[j], bv[j]);
+        if (RES) v = __fadd2_rn(v, rr[j]);
+        if (ACT) v = leaky_sel(v, v, sl2);
+        ow[j] = pack2rn(v);
       }
-      *reinterpret_cast<uint4*>(out + row * ldo + g * 8) = pack8(f);
+      *reinterpret_cast<uint4*>(dst) = o;
     };
-    long row = long(blockIdx.x) * R + r;
-    for (; row + rstep < M; row += 2 * rstep) {   // two rows in flight per thread
-      const long row2 = row + rstep;
-      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
-      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + g * 8);
-      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
-      if (RES) {
-        r0 = *reinterpret_cast<const uint4*>(res + row * ldr + g * 8);
-        r1 = *reinterpret_cast<const uint4*>(res + row2 * ldr + g * 8);
-      }
-      one(row, x0, r0);
-      one(row2, x1, r1);
+    constexpr int NT = RES ? 2 : 1, DEPTH = bn_ring_depth(NT);
+    extern __shared__ uint4 ring_raw[];
+    uint4* ring = ring_raw + threadIdx.x;
+    const int nthr = blockDim.x;
+    const long row0 = long(blockIdx.x) * R + r;
+    const int n = row0 < M ? int((M - row0 + rstep - 1) / rstep) : 0;   // rows of this thread
+    const __nv_bfloat16* xp = x + row0 * ldx + g * 8;
+    const __nv_bfloat16* rp = RES ? res + row0 * ldr + g * 8 : x;
+    __nv_bfloat16* op = out + row0 * ldo + g * 8;
+    const long xs = rstep * ldx, rs = rstep * ldr, os = rstep * ldo;
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    auto issue = [&](int k) {
+      const bool ok = k < n;
+      const int sl = k & (DEPTH - 1);
+      bn_cp16(ring + sl * nthr, ok ? xp : x, ok);
+      if (RES) bn_cp16(ring + (DEPTH + sl) * nthr, ok ? rp : x, ok);
+      bn_cp_commit();
+      xp += xs;
+      if (RES) rp += rs;
+    };
+#pragma unroll
+    for (int k = 0; k < DEPTH; ++k) issue(k);
+    for (int k = 0; k < n; ++k) {
+      bn_cp_wait<DEPTH - 1>();
+      const int sl = k & (DEPTH - 1);
+      const uint4 xu = ring[sl * nthr];
+      const uint4 ru = RES ? ring[(DEPTH + sl) * nthr] : z4;
+      issue(k + DEPTH);
+      one(op, xu, ru);
+      op += os;
     }
-    if (row < M) {
-      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
-      uint4 r0 = make_uint4(0, 0, 0, 0);
-      if (RES) r0 = *reinterpret_cast<const uint4*>(res + row * ldr + g * 8);
-      one(row, x0, r0);
-    }
+    bn_cp_wait<0>();
   }
 }
 
@@ -224,7 +285,7 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const float* __res
 // ACT: 0 = no activation, 1 = sign of the stored activation output, 2 = sign recomputed from
 // a*x + b (the activated tensor was never stored, see bgr_dw_fwd_bn); then `out` carries a and
 // `out + C` ... is unused: a, b come in through `xa`, `xb`.
-template <int ACT>
+template <int ACT, bool G2>
 __device__ __forceinline__ void
 bn_bwd_reduce_body(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ g2,
                    int ldg2, const __nv_bfloat16* __restrict__ out,
@@ -237,67 +298,99 @@ bn_bwd_reduce_body(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bflo
   const RowGroupMap m(C);
   const long r0 = long(blockIdx.x) * rows_per_block;
   const long r1 = min(r0 + rows_per_block, M);
+  const float2 sl2 = make_float2(slope, slope);
   for (int gi = threadIdx.x % m.G; gi < m.G; gi += (m.G >= 256 ? 256 : m.G)) {
     const int r = m.G >= 256 ? 0 : threadIdx.x / m.G;
     if (r >= m.R) break;
-    float mu[8], s1[8], s2[8], ca[8], cb[8];   // s2 accumulates dyh*(x - mean); invstd is applied once at the end
+    float2 nmu[4], s1[4], s2[4], ca[4], cb[4];   // s2 accumulates dyh*(x - mean); invstd is applied once at the end
+    load8p(mean + gi * 8, nmu);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      mu[j] = mean[gi * 8 + j]; s1[j] = 0.f; s2[j] = 0.f;
-      ca[j] = ACT == 2 ? xa[gi * 8 + j] : 0.f;
-      cb[j] = ACT == 2 ? xb[gi * 8 + j] : 0.f;
+    for (int j = 0; j < 4; ++j) {
+      nmu[j] = make_float2(-nmu[j].x, -nmu[j].y);   // x - mean == x + (-mean), bit for bit
+      s1[j] = s2[j] = make_float2(0.f, 0.f);
     }
-    auto one = [&](long row, const uint4& gu, const uint4& xu, const uint4& ou) {
-      float gv[8], xv[8], ov[8];
-      unpack8(gu, gv);
-      if (g2 != nullptr) {   // second gradient of the same tensor (residual path), summed in fp32
-        float hv[8];
-        unpack8(*reinterpret_cast<const uint4*>(g2 + row * ldg2 + gi * 8), hv);
+    if (ACT == 2) {
+      load8p(xa + gi * 8, ca);
+      load8p(xb + gi * 8, cb);
+    }
+    auto one = [&](__nv_bfloat16* dst, const uint4& gu, const uint4& hu, const uint4& xu, const uint4& ou) {
+      float2 gv[4], xv[4], ov[4];
+      unpack8p(gu, gv);
+      if (G2) {   // second gradient of the same tensor (residual path), summed in fp32
+        float2 hv[4];
+        unpack8p(hu, hv);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) gv[j] += hv[j];
+        for (int j = 0; j < 4; ++j) gv[j] = __fadd2_rn(gv[j], hv[j]);
       }
-      unpack8(xu, xv);
-      if (ACT == 1) unpack8(ou, ov);
+      unpack8p(xu, xv);
+      if (ACT == 1) unpack8p(ou, ov);
+      uint4 o;
+      uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float d = gv[j];
-        if (ACT == 1) d = ov[j] > 0.f ? d : slope * d;
-        if (ACT == 2) d = fmaf(ca[j], xv[j], cb[j]) > 0.f ? d : slope * d;
+      for (int j = 0; j < 4; ++j) {
+        float2 d = gv[j];
+        if (ACT == 1) d = leaky_sel(ov[j], d, sl2);
+        if (ACT == 2) d = leaky_sel(__ffma2_rn(ca[j], xv[j], cb[j]), d, sl2);
         // statistics are taken from the bf16-rounded value pass 2 will read back, so that the
         // mean subtraction cancels exactly (matters when M is tiny, e.g. the image-pool branch)
-        d = __bfloat162float(__float2bfloat16_rn(d));
-        gv[j] = d;
-        s1[j] += d;
-        s2[j] = fmaf(d, xv[j] - mu[j], s2[j]);
+        ow[j] = pack2rn(d);
+        d = bf2_to_f2(ow[j]);
+        s1[j] = __fadd2_rn(s1[j], d);
+        s2[j] = __ffma2_rn(d, __fadd2_rn(xv[j], nmu[j]), s2[j]);
       }
-      if (dyh != nullptr) *reinterpret_cast<uint4*>(dyh + row * ldd + gi * 8) = pack8(gv);
+      if (dst != nullptr) *reinterpret_cast<uint4*>(dst) = o;
     };
     const uint4 z4 = make_uint4(0, 0, 0, 0);
-    long row = r0 + r;
-    for (; row + m.R < r1; row += 2 * m.R) {   // two rows (6 loads) in flight per thread
-      const long row2 = row + m.R;
-      const uint4 g0 = *reinterpret_cast<const uint4*>(g + row * ldg + gi * 8);
-      const uint4 g1 = *reinterpret_cast<const uint4*>(g + row2 * ldg + gi * 8);
-      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + gi * 8);
-      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + gi * 8);
-      const uint4 o0 = ACT == 1 ? *reinterpret_cast<const uint4*>(out + row * ldo + gi * 8) : z4;
-      const uint4 o1 = ACT == 1 ? *reinterpret_cast<const uint4*>(out + row2 * ldo + gi * 8) : z4;
-      one(row, g0, x0, o0);
-      one(row2, g1, x1, o1);
-    }
-    if (row < r1)
-      one(row, *reinterpret_cast<const uint4*>(g + row * ldg + gi * 8),
-          *reinterpret_cast<const uint4*>(x + row * ldx + gi * 8),
-          ACT == 1 ? *reinterpret_cast<const uint4*>(out + row * ldo + gi * 8) : z4);
+    constexpr int NT = 2 + (G2 ? 1 : 0) + (ACT == 1 ? 1 : 0), DEPTH = bn_ring_depth(NT);
+    uint4* ring = reinterpret_cast<uint4*>(sh + size_t(m.R) * 2 * C) + threadIdx.x;   // behind the partial-sum slots
+    const int nthr = blockDim.x;
+    const long row0 = r0 + r;
+    const int n = row0 < r1 ? int((r1 - row0 + m.R - 1) / m.R) : 0;   // rows of this thread: row0, row0 + R, ...
+    const __nv_bfloat16* gp = g + row0 * ldg + gi * 8;
+    const __nv_bfloat16* xp = x + row0 * ldx + gi * 8;
+    const __nv_bfloat16* hp = G2 ? g2 + row0 * ldg2 + gi * 8 : g;
+    const __nv_bfloat16* op = ACT == 1 ? out + row0 * ldo + gi * 8 : g;
+    __nv_bfloat16* dp = dyh != nullptr ? dyh + row0 * ldd + gi * 8 : nullptr;
+    const long gs = long(m.R) * ldg, xs = long(m.R) * ldx, hs = long(m.R) * ldg2, os = long(m.R) * ldo, ds = long(m.R) * ldd;
+    auto issue = [&](int k) {   // row k of this thread -> slot k % DEPTH of every tensor; one group per row
+      const bool ok = k < n;
+      const int sl = k & (DEPTH - 1);
+      bn_cp16(ring + (0 * DEPTH + sl) * nthr, ok ? gp : g, ok);
+      bn_cp16(ring + (1 * DEPTH + sl) * nthr, ok ? xp : g, ok);
+      if (G2) bn_cp16(ring + (2 * DEPTH + sl) * nthr, ok ? hp : g, ok);
+      if (ACT == 1) bn_cp16(ring + ((G2 ? 3 : 2) * DEPTH + sl) * nthr, ok ? op : g, ok);
+      bn_cp_commit();
+      gp += gs; xp += xs;
+      if (G2) hp += hs;
+      if (ACT == 1) op += os;
+    };
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s2[j] *= invstd[gi * 8 + j];
-    block_partial_put(sh, C, r, gi, s1, s2);
+    for (int k = 0; k < DEPTH; ++k) issue(k);
+    for (int k = 0; k < n; ++k) {
+      bn_cp_wait<DEPTH - 1>();   // the oldest outstanding group is row k
+      const int sl = k & (DEPTH - 1);
+      const uint4 gu = ring[(0 * DEPTH + sl) * nthr];
+      const uint4 xu = ring[(1 * DEPTH + sl) * nthr];
+      const uint4 hu = G2 ? ring[(2 * DEPTH + sl) * nthr] : z4;
+      const uint4 ou = ACT == 1 ? ring[((G2 ? 3 : 2) * DEPTH + sl) * nthr] : z4;
+      issue(k + DEPTH);          // refill the slot just read
+      one(dp, gu, hu, xu, ou);
+      if (dp != nullptr) dp += ds;
+    }
+    bn_cp_wait<0>();             // drain the (empty) tail groups before the ring is reused
+    float s1f[8], s2f[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      s1f[2 * j] = s1[j].x; s1f[2 * j + 1] = s1[j].y;
+      s2f[2 * j] = s2[j].x * invstd[gi * 8 + 2 * j]; s2f[2 * j + 1] = s2[j].y * invstd[gi * 8 + 2 * j + 1];
+    }
+    block_partial_put(sh, C, r, gi, s1f, s2f);
     if (m.G < 256) break;
   }
   block_partial_flush(sh, C, m.R, part);
 }
 
-template <int ACT>
+template <int ACT, bool G2>
 __global__ void __launch_bounds__(256, 3)   // 85 registers: three blocks per SM (was 91-96 -> two, latency-bound)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfloat16* __restrict__ g2,
                      int ldg2, const __nv_bfloat16* __restrict__ out,
@@ -308,7 +401,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bf
                      float* __restrict__ part /* [gridDim.x][2][C] */) {
   pdl_wait();      // programmatic dependent launch: see bgr_internal.h
   pdl_trigger();
-  bn_bwd_reduce_body<ACT>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
+  bn_bwd_reduce_body<ACT, G2>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
 }
 
 // backward, pass 2: dx = gamma*invstd * (dyh - s1/M - xhat * s2/M), xhat = (x - mean)*invstd.
@@ -361,39 +454,57 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dyh, const __nv_bfloat16* 
     load8f(coef + 4 * C + g * 8, is);
 #pragma unroll
     for (int j = 0; j < 8; ++j) k2[j] *= is[j];   // (x - mu) * is * k2
-    auto one = [&](long row, const uint4& du, const uint4& xu) {
+    auto one = [&](__nv_bfloat16* dst, const uint4& du, const uint4& xu) {
       float d[8], xv[8];
       unpack8(du, d);
       unpack8(xu, xv);
 #pragma unroll
       for (int j = 0; j < 8; ++j) d[j] = c0[j] * (d[j] - k1[j] - (xv[j] - mu[j]) * k2[j]);
-      *reinterpret_cast<uint4*>(dx + row * ldd + g * 8) = pack8(d);
+      *reinterpret_cast<uint4*>(dst) = pack8(d);
     };
-    long row = long(blockIdx.x) * R + r;
-    for (; row + rstep < M; row += 2 * rstep) {
-      const long row2 = row + rstep;
-      const uint4 d0 = *reinterpret_cast<const uint4*>(dyh + row * ldd + g * 8);
-      const uint4 d1 = *reinterpret_cast<const uint4*>(dyh + row2 * ldd + g * 8);
-      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
-      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + g * 8);
-      one(row, d0, x0);
-      one(row2, d1, x1);
+    constexpr int DEPTH = bn_ring_depth(2);
+    extern __shared__ uint4 ring_raw[];
+    uint4* ring = ring_raw + threadIdx.x;
+    const int nthr = blockDim.x;
+    const long row0 = long(blockIdx.x) * R + r;
+    const int n = row0 < M ? int((M - row0 + rstep - 1) / rstep) : 0;
+    const __nv_bfloat16* dp = dyh + row0 * ldd + g * 8;
+    const __nv_bfloat16* xp = x + row0 * ldx + g * 8;
+    __nv_bfloat16* op = dx + row0 * ldd + g * 8;
+    const long ds = rstep * ldd, xs = rstep * ldx;
+    auto issue = [&](int k) {
+      const bool ok = k < n;
+      const int sl = k & (DEPTH - 1);
+      bn_cp16(ring + sl * nthr, ok ? dp : dyh, ok);
+      bn_cp16(ring + (DEPTH + sl) * nthr, ok ? xp : x, ok);
+      bn_cp_commit();
+      dp += ds; xp += xs;
+    };
+#pragma unroll
+    for (int k = 0; k < DEPTH; ++k) issue(k);
+    for (int k = 0; k < n; ++k) {
+      bn_cp_wait<DEPTH - 1>();
+      const int sl = k & (DEPTH - 1);
+      const uint4 du = ring[sl * nthr];
+      const uint4 xu = ring[(DEPTH + sl) * nthr];
+      issue(k + DEPTH);
+      one(op, du, xu);
+      op += ds;
     }
-    if (row < M)
-      one(row, *reinterpret_cast<const uint4*>(dyh + row * ldd + g * 8),
-          *reinterpret_cast<const uint4*>(x + row * ldx + g * 8));
+    bn_cp_wait<0>();
   }
 }
 
 // Pass 2 without a stored dyh (the BatchNorm whose activation was applied on load, bgr_dw_fwd_bn):
 // dyh = bf16(g * act'(a*x + b)) is recomputed from g and x -- x is read anyway -- exactly as pass 1
 // computed it for the sums, so pass 1 need not write it and this pass need not read it back.
+template <bool ACT, bool G2>
 __global__ void __launch_bounds__(256, 3)
 bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, const __nv_bfloat16* __restrict__ gin2,
                               int ldg2, const __nv_bfloat16* __restrict__ x,
                               int ldx, const float* __restrict__ xa, const float* __restrict__ xb,
                               const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx, int ldd, long M,
-                              int C, float slope, int act) {
+                              int C, float slope) {
   pdl_wait();      // programmatic dependent launch: see bgr_internal.h
   pdl_trigger();
   const int G = C >> 3;
@@ -401,14 +512,15 @@ bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, co
   const int g0 = G >= 256 ? threadIdx.x : threadIdx.x % G;
   const int r = G >= 256 ? 0 : threadIdx.x / G;
   const long rstep = long(gridDim.x) * R;
+  const float2 sl2 = make_float2(slope, slope);
   for (int g = g0; g < G; g += 256) {
     // dx = c0*(v - k1 - (x - mu)*k2*is) folded to c0*v + A*x + B: three coefficient vectors live in
     // registers instead of five (108 -> under 86 registers: a third block per SM; ncu showed the 2-block
     // version latency-bound at 3.6 TB/s where bn_bwd_apply_kernel streams the same bytes at 5.1)
-    float c0[8], A[8], B[8], ca[8], cb[8];
+    float2 c0[4], A[4], B[4], ca[4], cb[4];
     {
-      float k1[8], k2[8], mu[8], is[8];
-      load8f(coef + g * 8, c0);
+      float c0s[8], k1[8], k2[8], mu[8], is[8], As[8], Bs[8];
+      load8f(coef + g * 8, c0s);
       load8f(coef + C + g * 8, k1);
       load8f(coef + 2 * C + g * 8, k2);
       load8f(coef + 3 * C + g * 8, mu);
@@ -416,48 +528,76 @@ bn_bwd_apply_recompute_kernel(const __nv_bfloat16* __restrict__ gin, int ldg, co
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float k2i = k2[j] * is[j];
-        A[j] = -c0[j] * k2i;
-        B[j] = c0[j] * (k2i * mu[j] - k1[j]);
+        As[j] = -c0s[j] * k2i;
+        Bs[j] = c0s[j] * (k2i * mu[j] - k1[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        c0[j] = make_float2(c0s[2 * j], c0s[2 * j + 1]);
+        A[j] = make_float2(As[2 * j], As[2 * j + 1]);
+        B[j] = make_float2(Bs[2 * j], Bs[2 * j + 1]);
       }
     }
-    if (act) {
-      load8f(xa + g * 8, ca);
-      load8f(xb + g * 8, cb);
+    if (ACT) {
+      load8p(xa + g * 8, ca);
+      load8p(xb + g * 8, cb);
     }
-    auto one = [&](long row, const uint4& gu, const uint4& xu) {
-      float d[8], xv[8];
-      unpack8(gu, d);
-      if (gin2 != nullptr) {   // the second gradient of a dual-handle output, summed in fp32 as pass 1 did
-        float hv[8];
-        unpack8(*reinterpret_cast<const uint4*>(gin2 + row * ldg2 + g * 8), hv);
+    auto one = [&](__nv_bfloat16* dst, const uint4& gu, const uint4& hu, const uint4& xu) {
+      float2 d[4], xv[4];
+      unpack8p(gu, d);
+      if (G2) {   // the second gradient of a dual-handle output, summed in fp32 as pass 1 did
+        float2 hv[4];
+        unpack8p(hu, hv);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) d[j] += hv[j];
+        for (int j = 0; j < 4; ++j) d[j] = __fadd2_rn(d[j], hv[j]);
       }
-      unpack8(xu, xv);
+      unpack8p(xu, xv);
+      uint4 o;
+      uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float v = d[j];
-        if (act) {
-          v = fmaf(ca[j], xv[j], cb[j]) > 0.f ? v : slope * v;
-        }
-        if (act || gin2 != nullptr) v = __bfloat162float(__float2bfloat16_rn(v));   // the value pass 1 summed
-        d[j] = fmaf(c0[j], v, fmaf(A[j], xv[j], B[j]));
+      for (int j = 0; j < 4; ++j) {
+        float2 v = d[j];
+        if (ACT) v = leaky_sel(__ffma2_rn(ca[j], xv[j], cb[j]), v, sl2);
+        if (ACT || G2) v = bf2_to_f2(pack2rn(v));   // the value pass 1 summed
+        ow[j] = pack2rn(__ffma2_rn(c0[j], v, __ffma2_rn(A[j], xv[j], B[j])));
       }
-      *reinterpret_cast<uint4*>(dx + row * ldd + g * 8) = pack8(d);
+      *reinterpret_cast<uint4*>(dst) = o;
     };
-    long row = long(blockIdx.x) * R + r;
-    for (; row + rstep < M; row += 2 * rstep) {
-      const long row2 = row + rstep;
-      const uint4 d0 = *reinterpret_cast<const uint4*>(gin + row * ldg + g * 8);
-      const uint4 d1 = *reinterpret_cast<const uint4*>(gin + row2 * ldg + g * 8);
-      const uint4 x0 = *reinterpret_cast<const uint4*>(x + row * ldx + g * 8);
-      const uint4 x1 = *reinterpret_cast<const uint4*>(x + row2 * ldx + g * 8);
-      one(row, d0, x0);
-      one(row2, d1, x1);
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    constexpr int NT = G2 ? 3 : 2, DEPTH = bn_ring_depth(NT);
+    extern __shared__ uint4 ring_raw[];
+    uint4* ring = ring_raw + threadIdx.x;
+    const int nthr = blockDim.x;
+    const long row0 = long(blockIdx.x) * R + r;
+    const int n = row0 < M ? int((M - row0 + rstep - 1) / rstep) : 0;
+    const __nv_bfloat16* gp = gin + row0 * ldg + g * 8;
+    const __nv_bfloat16* hp = G2 ? gin2 + row0 * ldg2 + g * 8 : gin;
+    const __nv_bfloat16* xp = x + row0 * ldx + g * 8;
+    __nv_bfloat16* op = dx + row0 * ldd + g * 8;
+    const long gs = rstep * ldg, hs = rstep * ldg2, xs = rstep * ldx, os = rstep * ldd;
+    auto issue = [&](int k) {
+      const bool ok = k < n;
+      const int sl = k & (DEPTH - 1);
+      bn_cp16(ring + sl * nthr, ok ? gp : gin, ok);
+      bn_cp16(ring + (DEPTH + sl) * nthr, ok ? xp : gin, ok);
+      if (G2) bn_cp16(ring + (2 * DEPTH + sl) * nthr, ok ? hp : gin, ok);
+      bn_cp_commit();
+      gp += gs; xp += xs;
+      if (G2) hp += hs;
+    };
+#pragma unroll
+    for (int k = 0; k < DEPTH; ++k) issue(k);
+    for (int k = 0; k < n; ++k) {
+      bn_cp_wait<DEPTH - 1>();
+      const int sl = k & (DEPTH - 1);
+      const uint4 gu = ring[sl * nthr];
+      const uint4 xu = ring[(DEPTH + sl) * nthr];
+      const uint4 hu = G2 ? ring[(2 * DEPTH + sl) * nthr] : z4;
+      issue(k + DEPTH);
+      one(op, gu, hu, xu);
+      op += os;
     }
-    if (row < M)
-      one(row, *reinterpret_cast<const uint4*>(gin + row * ldg + g * 8),
-          *reinterpret_cast<const uint4*>(x + row * ldx + g * 8));
+    bn_cp_wait<0>();
   }
 }
 
@@ -481,7 +621,8 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ g, int ldg, const __nv_bfl
                     __nv_bfloat16* __restrict__ dyh, __nv_bfloat16* __restrict__ dx, int ldd, long M, int C,
                     int rows_per_block, float slope, float* __restrict__ part, float* __restrict__ coef) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
-  bn_bwd_reduce_body<ACT>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
+  if (g2 != nullptr) bn_bwd_reduce_body<ACT, true>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
+  else bn_bwd_reduce_body<ACT, false>(g, ldg, g2, ldg2, out, ldo, xa, xb, x, ldx, mean, invstd, dyh, ldd, M, C, rows_per_block, slope, part);
   __threadfence();
   grid.sync();
   if (int(blockIdx.x) * kRsCh < C) bn_bwd_coef_body(mean, invstd, gamma, part, int(gridDim.x), M, C, coef);
@@ -569,7 +710,8 @@ static int fused_max_grid(size_t smem) {
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
   if (cache[dev] == 0) {
     int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bn_bwd_fused_kernel<ACT>, 256, 16 * 1024) != cudaSuccess)
+    if (ensure_dyn_smem(bn_bwd_fused_kernel<ACT>, 80 * 1024) != BGR_OK ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bn_bwd_fused_kernel<ACT>, 256, 52 * 1024) != cudaSuccess)
       per_sm = 0;
     cache[dev] = per_sm > 0 ? per_sm * sm_count() : -1;
   }
@@ -591,8 +733,11 @@ static int launch_bn_bwd_fused(const __nv_bfloat16* G, int ldg, const __nv_bfloa
 }
 
 // grid / block of the (channel group, rows) streaming kernels
-static void rowgroup_launch(long M, int C, int* grid, int* block) {
-  static const int min_rows = env_int("BGR_EW_ROWS", 4), cap = env_int("BGR_EW_CAP", 16);   // tuning knobs
+// With the row ring every thread wants a long run of rows (its prefetch depth is only useful on a run), so the
+// grid is ONE resident wave: `cap` blocks per SM (what registers and the ring's shared memory allow).
+static void rowgroup_launch(long M, int C, int* grid, int* block, int cap_default = 4) {
+  static const int min_rows = env_int("BGR_EW_ROWS", 4), cap_env = env_int("BGR_EW_CAP", 0);   // tuning knobs
+  const int cap = cap_env > 0 ? cap_env : cap_default;
   const int G = C / 8;
   const int R = G >= 256 ? 1 : 256 / G;
   *block = G >= 256 ? 256 : G * R;
@@ -719,17 +864,30 @@ extern "C" int bgr_bn_apply(const void* x, int ldx, const float* a, const float*
   BGR_CHECK_C8(C);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int grid, block;
-  rowgroup_launch(M, C, &grid, &block);
+  rowgroup_launch(M, C, &grid, &block, 4);
+  const size_t ring = bn_ring_bytes(res ? 2 : 1, block);   // <= 32 KB
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto R = static_cast<const __nv_bfloat16*>(res);
   auto O = static_cast<__nv_bfloat16*>(out);
-  if (act && res) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<true, true>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
-  else if (act) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<true, false>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
-  else if (res) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<false, true>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
-  else BGR_CUDA_OK(launch_pdl(bn_apply_kernel<false, false>, dim3(grid), dim3(block), 0, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
+  if (act && res) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<true, true>, dim3(grid), dim3(block), ring, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
+  else if (act) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<true, false>, dim3(grid), dim3(block), ring, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
+  else if (res) BGR_CUDA_OK(launch_pdl(bn_apply_kernel<false, true>, dim3(grid), dim3(block), ring, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
+  else BGR_CUDA_OK(launch_pdl(bn_apply_kernel<false, false>, dim3(grid), dim3(block), ring, st, X, ldx, a, b, R, ldr, O, ldo, M, C, slope));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
+
+// pass 1 with the second-gradient flag as a template argument (no per-row branch in the kernel)
+#define BGR_LAUNCH_REDUCE(ACTV, ...)                                                                      \
+  do {                                                                                                    \
+    if (G2 != nullptr) {                                                                                  \
+      if (int rc_ = ensure_dyn_smem(bn_bwd_reduce_kernel<ACTV, true>, 80 * 1024)) return rc_;             \
+      BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<ACTV, true>, __VA_ARGS__));                             \
+    } else {                                                                                              \
+      if (int rc_ = ensure_dyn_smem(bn_bwd_reduce_kernel<ACTV, false>, 80 * 1024)) return rc_;            \
+      BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<ACTV, false>, __VA_ARGS__));                            \
+    }                                                                                                     \
+  } while (0)
 
 static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, const void* out, int ldo,
                             const float* xa, const float* xb,
@@ -741,7 +899,8 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int rpb;
   const int grid = reduce_grid(M, C, &rpb);
-  const size_t rsm = reduce_smem(C);
+  // partial-sum slots + the row ring of pass 1 (g, x [, g2] [, stored output])
+  const size_t rsm = reduce_smem(C) + bn_ring_bytes(2 + (g2 != nullptr ? 1 : 0) + (act == 1 ? 1 : 0), 256);
   auto G = static_cast<const __nv_bfloat16*>(g);
   auto G2 = static_cast<const __nv_bfloat16*>(g2);
   auto O = static_cast<const __nv_bfloat16*>(out);
@@ -763,19 +922,26 @@ static int bn_backward_impl(const void* g, int ldg, const void* g2, int ldg2, co
       return launch_bn_bwd_fused<0>(G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, gamma, D, DXp, ldd, M, C, rpb, grid, slope, part, coef_ws, rsm, st);
     }
   }
-  if (act == 2) BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<2>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
-  else if (act) BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<1>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
-  else BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<0>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
+  if (act == 2) BGR_LAUNCH_REDUCE(2, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, nullptr, 0, xa, xb, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  else if (act) BGR_LAUNCH_REDUCE(1, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  else BGR_LAUNCH_REDUCE(0, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
   BGR_LAUNCH_OK();
   BGR_CUDA_OK(launch_pdl(bn_bwd_coef_kernel, dim3((C + kRsCh - 1) / kRsCh), dim3(256), 0, st, mean, invstd, gamma, part, grid, M, C, coef_ws));
   BGR_LAUNCH_OK();
   int agrid, ablock;
-  rowgroup_launch(M, C, &agrid, &ablock);
+  rowgroup_launch(M, C, &agrid, &ablock, D == nullptr ? 3 : 4);   // 80 / 64 registers per thread
+  const size_t aring = bn_ring_bytes(D == nullptr && G2 != nullptr ? 3 : 2, ablock);   // <= 32 KB
   if (D == nullptr) {
-    BGR_CUDA_OK(launch_pdl(bn_bwd_apply_recompute_kernel, dim3(agrid), dim3(ablock), 0, st, G, ldg, G2, ldg2, X, ldx, xa, xb, coef_ws, DXp,
-                                                            ldd, M, C, slope, act == 2));
+#define BGR_LAUNCH_RECOMPUTE(A_, G_)                                                                                      \
+  BGR_CUDA_OK(launch_pdl(bn_bwd_apply_recompute_kernel<A_, G_>, dim3(agrid), dim3(ablock), aring, st, G, ldg, G2, ldg2, X, ldx, \
+                         xa, xb, coef_ws, DXp, ldd, M, C, slope))
+    if (act == 2 && G2 != nullptr) BGR_LAUNCH_RECOMPUTE(true, true);
+    else if (act == 2) BGR_LAUNCH_RECOMPUTE(true, false);
+    else if (G2 != nullptr) BGR_LAUNCH_RECOMPUTE(false, true);
+    else BGR_LAUNCH_RECOMPUTE(false, false);
+#undef BGR_LAUNCH_RECOMPUTE
   } else {
-    BGR_CUDA_OK(launch_pdl(bn_bwd_apply_kernel, dim3(agrid), dim3(ablock), 0, st, D, X, ldx, coef_ws, DXp, ldd, M, C));
+    BGR_CUDA_OK(launch_pdl(bn_bwd_apply_kernel, dim3(agrid), dim3(ablock), aring, st, D, X, ldx, coef_ws, DXp, ldd, M, C));
   }
   BGR_LAUNCH_OK();
   return BGR_OK;
@@ -846,14 +1012,15 @@ extern "C" int bgr_bn_backward_frozen(const void* g, int ldg, const void* g2, in
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int rpb;
   const int grid = reduce_grid(M, C, &rpb);
-  const size_t rsm = reduce_smem(C);
+  // partial-sum slots + the row ring of pass 1 (g, x [, g2] [, stored output])
+  const size_t rsm = reduce_smem(C) + bn_ring_bytes(2 + (g2 != nullptr ? 1 : 0) + (act ? 1 : 0), 256);
   auto G = static_cast<const __nv_bfloat16*>(g);
   auto G2 = static_cast<const __nv_bfloat16*>(g2);
   auto O = static_cast<const __nv_bfloat16*>(out);
   auto X = static_cast<const __nv_bfloat16*>(x);
   auto D = static_cast<__nv_bfloat16*>(dyh);
-  if (act) BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<1>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
-  else BGR_CUDA_OK(launch_pdl(bn_bwd_reduce_kernel<0>, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part));
+  if (act) BGR_LAUNCH_REDUCE(1, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
+  else BGR_LAUNCH_REDUCE(0, dim3(grid), dim3(256), rsm, st, G, ldg, G2, ldg2, O, ldo, nullptr, nullptr, X, ldx, mean, invstd, D, ldd, M, C, rpb, slope, part);
   BGR_LAUNCH_OK();
   BGR_CUDA_OK(launch_pdl(bn_bwd_coef_kernel, dim3((C + kRsCh - 1) / kRsCh), dim3(256), 0, st, mean, invstd, gamma, part, grid, M, C, coef_ws));
   BGR_LAUNCH_OK();
