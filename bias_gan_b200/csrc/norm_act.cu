@@ -138,10 +138,12 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, long M, int C, int ld, int 
   block_partial_flush(sh, C, m.R, part);
 }
 
-// Ordered fp64 sum of the partial rows of kRsCh channels: kRsLanes row lanes x kRsCh channels per block;
-// lane w adds rows w, w+kRsLanes, ... (four loads in flight, added in row order); the lane sums are added
-// in lane order.  Returns true in the threads (lane 0) that hold the result for a valid channel c.
-constexpr int kRsCh = 16, kRsLanes = 16;   // 256 threads; grid = ceil(C / 16): 46 blocks at C = 728
+// Ordered fp64 sum of the partial rows of kRsCh channels: kRsLanes row lanes x kRsCh channels per block; lane w
+// adds rows w, w + kRsLanes, ... in row order (eight loads in flight: with up to 444 rows this kernel sits on the
+// critical path between the two BatchNorm-backward passes and is pure load latency); the lane sums are combined by
+// a fixed binary tree.  The order depends on nothing but (rows, C): the result is reproducible.  Returns true in
+// the threads (lane 0) that hold the result for a valid channel c.
+constexpr int kRsCh = 8, kRsLanes = 32;   // 256 threads; grid = ceil(C / 8): 91 blocks at C = 728
 __device__ __forceinline__ bool ordered_row_sums(const float* __restrict__ part, int rows, int C, int* c_out,
                                                  double* s_out, double* q_out) {
   __shared__ double shd[kRsLanes][2][kRsCh];
@@ -152,33 +154,47 @@ __device__ __forceinline__ bool ordered_row_sums(const float* __restrict__ part,
     const float* p = part + c;
     const size_t st = size_t(2) * C;
     int r = rl;
-    for (; r + 3 * kRsLanes < rows; r += 4 * kRsLanes) {
-      const float a0 = p[size_t(r) * st], b0 = p[size_t(r) * st + C];
-      const float a1 = p[size_t(r + kRsLanes) * st], b1 = p[size_t(r + kRsLanes) * st + C];
-      const float a2 = p[size_t(r + 2 * kRsLanes) * st], b2 = p[size_t(r + 2 * kRsLanes) * st + C];
-      const float a3 = p[size_t(r + 3 * kRsLanes) * st], b3 = p[size_t(r + 3 * kRsLanes) * st + C];
-      s += double(a0); q += double(b0);
-      s += double(a1); q += double(b1);
-      s += double(a2); q += double(b2);
-      s += double(a3); q += double(b3);
+    for (; r + 7 * kRsLanes < rows; r += 8 * kRsLanes) {
+      float a[8], b[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        a[u] = p[size_t(r + u * kRsLanes) * st];
+        b[u] = p[size_t(r + u * kRsLanes) * st + C];
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { s += double(a[u]); q += double(b[u]); }
     }
-    for (; r < rows; r += kRsLanes) {
-      s += double(p[size_t(r) * st]);
-      q += double(p[size_t(r) * st + C]);
+    if (r < rows) {   // up to seven more rows, again all loads first
+      float a[7], b[7];
+#pragma unroll
+      for (int u = 0; u < 7; ++u) {
+        const bool ok = r + u * kRsLanes < rows;
+        a[u] = ok ? p[size_t(r + u * kRsLanes) * st] : 0.f;
+        b[u] = ok ? p[size_t(r + u * kRsLanes) * st + C] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 7; ++u)
+        if (r + u * kRsLanes < rows) { s += double(a[u]); q += double(b[u]); }
     }
   }
   shd[rl][0][cl] = s;
   shd[rl][1][cl] = q;
   __syncthreads();
-  if (rl != 0 || c >= C) return false;
 #pragma unroll
-  for (int w = 1; w < kRsLanes; ++w) { s += shd[w][0][cl]; q += shd[w][1][cl]; }
-  *c_out = c; *s_out = s; *q_out = q;
+  for (int w = kRsLanes / 2; w > 0; w >>= 1) {   // fixed tree over the row lanes
+    if (rl < w) {
+      shd[rl][0][cl] += shd[rl + w][0][cl];
+      shd[rl][1][cl] += shd[rl + w][1][cl];
+    }
+    __syncthreads();
+  }
+  if (rl != 0 || c >= C) return false;
+  *c_out = c; *s_out = shd[0][0][cl]; *q_out = shd[0][1][cl];
   return true;
 }
 
 // mean / invstd / fused affine (a, b) / running statistics (momentum, unbiased variance) from the
-// partial rows of the statistics pass (bn_stats_kernel or the conv epilogue).  grid = ceil(C/16) x 256.
+// partial rows of the statistics pass (bn_stats_kernel or the conv epilogue).  grid = ceil(C/8) x 256.
 __global__ void __launch_bounds__(256)
 bn_finalize_kernel(const float* __restrict__ part, int rows, long M, int C,
                    const float* __restrict__ gamma, const float* __restrict__ beta,
