@@ -82,6 +82,9 @@ class Generator(nn.Module):
         self.noise_dimensions = noise_dimensions
         self.n_output = n_output
         self.n_input = n_input
+        # true (H, W) of the fields handed to forward_field when they carry a zero row / column (odd sizes, e.g. the
+        # native 19 x 37): a padded field cannot tell its own size.  None = the field is exactly 2*H2 x 2*W2.
+        self.field_hw = None
         self._noise_slots, self._noise_cursor = None, 0
         if noise_type == "Uniform":
             self.dist = torch.distributions.uniform.Uniform(0.0, 1.0)
@@ -98,6 +101,8 @@ class Generator(nn.Module):
         on the CPU generator, [B, nd, H, W] fp32 — so a seeded run sees the same noise; they join the
         field in one kernel, padded with zero channels to a multiple of 16 so that the 4*(C+nd)
         channels of a block pixel fill whole 128-byte lines for the entry conv's TMA boxes."""
+        if hw is None:
+            hw = self.field_hw
         nd = self.noise_dimensions
         if nd > 0:
             if hw is not None and hw != (2 * field.shape[1], 2 * field.shape[2]) or (field.shape[-1] // 4) != self.n_input:
