@@ -752,7 +752,7 @@ def main():
         import tempfile
         d = tempfile.mkdtemp(prefix="bgr_bench_")
         try:
-            _write_gpsro_files(d, args.files or 2 * B)
+            _write_gpsro_files(d, args.files or 4 * B)
             # rank 0 alone is here: with several ranks the captured step contains the gradient all-reduce, so the
             # step-fed leg (e2e.from_files) is measured at N = 1 only; `--config ingest` runs it on every rank
             rd = ingest_measure(torch, dev, d, B, step_fn=files_step if world == 1 else None)
@@ -761,7 +761,7 @@ def main():
             line["reader_gbs"] = rd["reader_gbs"]
             line["e2e"]["from_files"] = rd.get("with_step")
             if not args.no_cpu_baseline:
-                line.setdefault("cpu_baseline", {})["ingest"] = cpu_reader_legs(d, args.files or 2 * B, threads)
+                line.setdefault("cpu_baseline", {})["ingest"] = cpu_reader_legs(d, args.files or 4 * B, threads)
         finally:
             shutil.rmtree(d, ignore_errors=True)
     if not args.no_cpu_baseline:
