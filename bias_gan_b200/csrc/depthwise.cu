@@ -373,8 +373,9 @@ __device__ __forceinline__ void dw_transform(float2 (&v)[2], const XfCoef& t, bo
   for (int p = 0; p < 2; ++p) {
     float2 z = __ffma2_rn(t.a[p], v[p], t.b[p]);
     if (XF == 2) {
-      z.x = fmaxf(z.x, t.slope * z.x);
-      z.y = fmaxf(z.y, t.slope * z.y);
+      const float2 sz = __fmul2_rn(make_float2(t.slope, t.slope), z);
+      z.x = fmaxf(z.x, sz.x);
+      z.y = fmaxf(z.y, sz.y);
     }
     v[p] = inside ? z : make_float2(0.f, 0.f);
   }
@@ -471,12 +472,17 @@ __device__ __forceinline__ void march_fwd_item(const __nv_bfloat16* __restrict__
     march_issue_row<INTERIOR>(slot, xin, it.H, rowstride, colbase, cstep, iy + kRing, cmask,
                               iy + kRing <= it.oy1);   // refill the slot
     cp_async_commit();
-    const unsigned mc = (iy >= 0 && iy < it.H) ? cmask : 0u;
+    // Padding is zero AFTER the transform (the reference pads the activated tensor).  For an interior strip that is a
+    // per-row condition: a row outside the image contributes nothing and is skipped, every other row needs no
+    // per-element select at all (the marches are issue-bound: the selects were a quarter of the transform).
+    const bool rowok = iy >= 0 && iy < it.H;
+    const unsigned mc = rowok ? cmask : 0u;
+    if (!(INTERIOR && XF != 0) || rowok) {
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
       float2 xv[2];
       dw_unpack22(rc[c], xv);
-      dw_transform<XF>(xv, tc, (mc >> c) & 1u);
+      dw_transform<XF>(xv, tc, (INTERIOR && XF != 0) ? true : bool((mc >> c) & 1u));
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int kx = c - j;
@@ -488,6 +494,7 @@ __device__ __forceinline__ void march_fwd_item(const __nv_bfloat16* __restrict__
           prev[j][e] = fma2s(xv[e], wr[6 + kx][e], prev[j][e]);
         }
       }
+    }
     }
     const int oy = iy - 1;
     if (oy >= it.oy0 && oy < it.oy1) {
@@ -897,12 +904,17 @@ __device__ __forceinline__ void march_wgrad_item(const __nv_bfloat16* __restrict
 #pragma unroll
     for (int j = 0; j < 4; ++j) next[j] = slot[(6 + j) * 32];
     issue(slot, iy + kRing);
-    const unsigned mc = (iy >= 0 && iy < it.H) ? cmask : 0u;
+    // Padding is zero AFTER the transform (the reference pads the activated tensor).  For an interior strip that is a
+    // per-row condition: a row outside the image contributes nothing and is skipped, every other row needs no
+    // per-element select at all (the marches are issue-bound: the selects were a quarter of the transform).
+    const bool rowok = iy >= 0 && iy < it.H;
+    const unsigned mc = rowok ? cmask : 0u;
+    if (!(INTERIOR && XF != 0) || rowok) {
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
       float2 xv[2];
       dw_unpack22(rc[c], xv);
-      dw_transform<XF>(xv, tc, (mc >> c) & 1u);
+      dw_transform<XF>(xv, tc, (INTERIOR && XF != 0) ? true : bool((mc >> c) & 1u));
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int kx = c - j;
@@ -918,6 +930,7 @@ __device__ __forceinline__ void march_wgrad_item(const __nv_bfloat16* __restrict
           acc[6 + kx][e] = fma2s(gp[e], xv[e], acc[6 + kx][e]);
         }
       }
+    }
     }
   };
   uint2 d0[4], d1[4], d2[4];
