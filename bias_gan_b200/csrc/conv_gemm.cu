@@ -18,6 +18,7 @@
 
 static int g_force_block_n = 0;   // development switches (bgr_debug_conv_*)
 static int g_conv_dbg = 0;
+static int g_force_ctas = -1;     // -1 = not read yet (BGR_CONV_CTAS), 0 = pick, 1 / 2 = forced
 
 namespace bgr {
 
@@ -51,17 +52,43 @@ struct ConvParams {
 //             for the CTA's life; at the end the four warps are added in warp order and the CTA writes
 //             one partial row (its tiles are a fixed function of blockIdx, so the row is reproducible).
 // ------------------------------------------------------------------------------------------
-template <int BLOCK_N, int STAGES, bool STATS>
-__global__ void __launch_bounds__(192, 1)
+// Development build only (-DBGR_CONV_TIMING, tools/dev_conv_timing.py): where each role of the forward kernel waits.
+#ifdef BGR_CONV_TIMING
+__device__ long long g_conv_timing[512][8];
+#define BGR_T0(v) const long long v = clock64()
+#define BGR_TACC(slot, v) g_conv_timing[blockIdx.x][slot] += clock64() - (v)
+#else
+#define BGR_T0(v)
+#define BGR_TACC(slot, v)
+#endif
+
+// CTAS = 2: the CTA pair variant (cta_group::2).  The two CTAs of a cluster take two neighbouring pixel tiles and
+// the same Cout tile; each stages its own 128 pixels and HALF of the Cout tile's weights (BLOCK_N/2 rows), the
+// leader issues one 256 x BLOCK_N MMA over both shared memories, and each CTA drains its own 128 accumulator rows.
+// Per k-block a CTA then receives 16 KB + BLOCK_N/2 x 128 B instead of 16 KB + BLOCK_N x 128 B: the 1-CTA kernel is
+// bound by what one SM can pull from L2 (profiles/r02_conv_roles.txt), not by the tensor pipe.
+// The pair variant also runs two sets of four epilogue warps (320 threads): one warp per scheduler drains a
+// 128 x 256 tile in ~10 k cycles (instruction latency; measured with -DBGR_CONV_TIMING), longer than the tile's
+// 6144 tensor-pipe cycles at K = 768; set h takes the 64-channel chunks c with c % 2 == h, with its own pair of
+// staging buffers and its own bulk-store groups.
+template <int BLOCK_N, int STAGES, bool STATS, int CTAS = 1>
+__global__ void __launch_bounds__(64 + 128 * CTAS, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmO, const float* __restrict__ bias,
                   float* __restrict__ stats /* [CTA groups][2][Cout] */, const __grid_constant__ ConvParams p) {
   constexpr uint32_t A_BYTES = kBlockM * kBlockK * 2;
-  constexpr uint32_t B_BYTES = BLOCK_N * kBlockK * 2;
+  constexpr uint32_t B_BYTES = (BLOCK_N / CTAS) * kBlockK * 2;   // this CTA's share of the weight tile
   constexpr uint32_t O_BYTES = kBlockM * 64 * 2;       // one 64-channel output chunk
   constexpr uint32_t TMEM_COLS = BLOCK_N > 128 ? 512 : 2 * BLOCK_N;   // allocations are powers of two
-  constexpr uint32_t NEEDED = STAGES * (A_BYTES + B_BYTES) + 2 * O_BYTES + (2 * STAGES + 4) * 8 + 16;
-  static_assert(4 * 2 * BLOCK_N * 4 <= 2 * O_BYTES, "the statistics combine reuses the output staging buffers");
+  constexpr int SETS = CTAS;                           // epilogue warp sets (4 warps each)
+  constexpr int NCHUNK = BLOCK_N / 64;
+  constexpr int MYCH = (NCHUNK + SETS - 1) / SETS;     // chunks one set handles per tile
+  // staging buffers per set: two (write one while the other's store drains), or one for the pair variant, which
+  // spends the shared memory on ring depth instead (its operand feed is latency-bound: 3/4/5 stages wait 58/50/40 %
+  // of the MMA role, profiles/r02_conv_roles.txt) and waits for the previous chunk's store after the TMEM read
+  constexpr int OBUFS = CTAS == 2 ? 1 : 2;
+  constexpr uint32_t NEEDED = STAGES * (A_BYTES + B_BYTES) + SETS * OBUFS * O_BYTES + (2 * STAGES + 4) * 8 + 16;
+  static_assert(4 * 2 * BLOCK_N * 4 <= SETS * OBUFS * O_BYTES, "the statistics combine reuses the output staging buffers");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
@@ -72,7 +99,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* sA = smem;
   uint8_t* sB = sA + STAGES * A_BYTES;
   uint8_t* sO = sB + STAGES * B_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(sO + 2 * O_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sO + SETS * OBUFS * O_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + 2;
@@ -83,8 +110,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   // gridDim.x is a multiple of n_tiles: this CTA keeps one Cout tile (so its BatchNorm partial sums
   // stay in shared memory for the whole kernel) and strides over the pixel tiles; the n_tiles CTAs
   // of one group work on the same activation tile at the same time (shared through L2).
-  const int nt = blockIdx.x % p.n_tiles;
-  const int mt_first = blockIdx.x / p.n_tiles, mt_step = gridDim.x / p.n_tiles;
+  // CTA pairs: unit = the pair, which takes pixel tiles (2k, 2k+1); both CTAs walk the same number of tiles (the
+  // odd one out is a phantom tile past the last image: its loads are zero-filled, its results dropped).
+  const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
+  const int unit = blockIdx.x / CTAS, units = gridDim.x / CTAS;
+  const int nt = unit % p.n_tiles;
+  const int mt_first = (unit / p.n_tiles) * CTAS + int(rank), mt_step = (units / p.n_tiles) * CTAS;
+  const int mt_end = p.m_tiles + int(rank);   // loop bound: the pair's first tile is inside
   const int n0 = nt * BLOCK_N;
 
   if (threadIdx.x == 0) {
@@ -97,13 +129,17 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tfull[b], 1);
-      mbar_init(&tempty[b], 4);
+      mbar_init(&tempty[b], 4 * SETS * CTAS);   // the leader's barrier collects the epilogue warps of both CTAs
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if (warp == 1) {
+    if (CTAS == 2) tmem_alloc2<TMEM_COLS>(tmem_slot);
+    else tmem_alloc<TMEM_COLS>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();   // the peer's barriers exist before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   // everything above (barrier init, descriptor prefetch, TMEM allocation) touched no global memory: it may
@@ -114,7 +150,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0) {
     if (lane == 0) {
       uint32_t it = 0;
-      for (int mt = mt_first; mt < p.m_tiles; mt += mt_step) {
+      BGR_T0(t_role);
+      const uint32_t full0 = CTAS == 2 ? mapa_shared(smem_u32(&full[0]), 0) : 0u;   // the leader's full[] barriers
+      for (int mt = mt_first; mt < mt_end; mt += mt_step) {
         const int tx = mt % p.tiles_x;
         const int ty = (mt / p.tiles_x) % p.tiles_y;
         const int n = mt / (p.tiles_x * p.tiles_y);
@@ -122,7 +160,19 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int t = 0; t < p.ntaps; ++t) {
           for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
             const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-            mbar_wait(&empty[s], ph ^ 1);
+            {
+              BGR_T0(t_w);
+              mbar_wait(&empty[s], ph ^ 1);
+              BGR_TACC(0, t_w);
+            }
+            if (CTAS == 2) {
+              if (rank == 0) mbar_expect_tx(&full[s], 2 * (A_BYTES + B_BYTES));
+              tma_load_5d_2sm(sA + s * A_BYTES, &tmA, full0 + s * 8, kb * kBlockK, 0, x0 + p.dx[t],
+                              y0 + p.dy[t], n);
+              tma_load_3d_2sm(sB + s * B_BYTES, &tmB, full0 + s * 8, kb * kBlockK, t,
+                              n0 + int(rank) * (BLOCK_N / 2));
+              continue;
+            }
             mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
             tma_load_5d(sA + s * A_BYTES, &tmA, &full[s], kb * kBlockK, 0, x0 + p.dx[t],
                         y0 + p.dy[t], n);
@@ -130,69 +180,111 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
         }
       }
+      BGR_TACC(1, t_role);
     }
   } else if (warp == 1) {
+    if (CTAS == 1 || rank == 0) {
     // The whole warp walks the loop (uniform control flow); one elected lane issues.  Per k-block
     // the issuing thread has ~512 tensor-pipe cycles of work to hide behind, so the loop carries
     // running (stage, phase) counters and descriptor low words instead of divisions and rebuilds.
-    constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
+    constexpr uint32_t idesc = umma_idesc_bf16(kBlockM * CTAS, BLOCK_N, 0, 0);
     const uint64_t da0 = umma_desc_sw128(smem_u32(sA), 16, 1024), db0 = umma_desc_sw128(smem_u32(sB), 16, 1024);
     const uint32_t a_hi = uint32_t(da0 >> 32), b_hi = uint32_t(db0 >> 32);
     const uint32_t a_lo0 = uint32_t(da0), b_lo0 = uint32_t(db0);
     uint32_t s = 0, ph = 0, lt = 0;
-    for (int mt = mt_first; mt < p.m_tiles; mt += mt_step, ++lt) {
+    BGR_T0(t_role);
+    for (int mt = mt_first; mt < mt_end; mt += mt_step, ++lt) {
       const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
-      mbar_wait(&tempty[acc], aph ^ 1);
+      {
+        BGR_T0(t_w);
+        if (CTAS == 2) mbar_wait_cluster(&tempty[acc], aph ^ 1);
+        else mbar_wait(&tempty[acc], aph ^ 1);
+        if (lane == 0) BGR_TACC(2, t_w);
+      }
       tc_fence_after();
       const uint32_t d = tmem + acc * BLOCK_N;
       for (int i = 0; i < iters; ++i) {
-        mbar_wait(&full[s], ph);
+        {
+          BGR_T0(t_w);
+          mbar_wait(&full[s], ph);
+          if (lane == 0) BGR_TACC(3, t_w);
+        }
         tc_fence_after();
         if (elect_one_sync()) {
           const uint32_t al = a_lo0 + s * (A_BYTES >> 4), bl = b_lo0 + s * (B_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k)
-            umma_bf16_w(d, al + k * 2, a_hi, bl + k * 2, b_hi, idesc, k ? 1u : uint32_t(i != 0));
-          umma_commit(&empty[s]);
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            if (CTAS == 2) umma_bf16_w2(d, al + k * 2, a_hi, bl + k * 2, b_hi, idesc, k ? 1u : uint32_t(i != 0));
+            else umma_bf16_w(d, al + k * 2, a_hi, bl + k * 2, b_hi, idesc, k ? 1u : uint32_t(i != 0));
+          }
+          if (CTAS == 2) umma_commit2(&empty[s]);
+          else umma_commit(&empty[s]);
         }
         __syncwarp();
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
-      if (elect_one_sync()) umma_commit(&tfull[acc]);
+      if (elect_one_sync()) {
+        if (CTAS == 2) umma_commit2(&tfull[acc]);
+        else umma_commit(&tfull[acc]);
+      }
       __syncwarp();
+    }
+    if (lane == 0) BGR_TACC(4, t_role);
     }
   } else {
     const int q = warp & 3;                  // TMEM lane quadrant this warp may access
     const int row = q * 32 + lane;           // tile row = pixel (row % BW, row / BW) of the rectangle
-    const int epi_tid = threadIdx.x - 64;    // 0..127
+    const int set = (warp - 2) >> 2;         // epilogue warp set (0 when there is one)
+    const int epi_tid = (threadIdx.x - 64) & 127;   // 0..127 within the set
+    uint8_t* const sOset = sO + set * OBUFS * O_BYTES;
     uint8_t* my_row = nullptr;
     uint32_t lt = 0, chunk_ctr = 0;
-    // BatchNorm partial sums of this CTA's Cout tile over this warp's rows: st_*[c*2 + e] <-> channel c*64 + 2*lane + e
-    float st_sum[BLOCK_N / 32], st_sq[BLOCK_N / 32];
+    // BatchNorm partial sums of this CTA's Cout tile over this warp's rows, for the chunks of this warp's set:
+    // st_*[i*2 + e] <-> channel (i*SETS + set)*64 + 2*lane + e
+    float st_sum[2 * MYCH], st_sq[2 * MYCH];
 #pragma unroll
-    for (int i = 0; i < BLOCK_N / 32; ++i) st_sum[i] = st_sq[i] = 0.f;
-    for (int mt = mt_first; mt < p.m_tiles; mt += mt_step, ++lt) {
+    for (int i = 0; i < 2 * MYCH; ++i) st_sum[i] = st_sq[i] = 0.f;
+    const uint32_t tempty0 = CTAS == 2 ? mapa_shared(smem_u32(&tempty[0]), 0) : 0u;
+    BGR_T0(t_role);
+    for (int mt = mt_first; mt < mt_end; mt += mt_step, ++lt) {
       const int tx = mt % p.tiles_x;
       const int ty = (mt / p.tiles_x) % p.tiles_y;
       const int n = mt / (p.tiles_x * p.tiles_y);
       const int x0 = tx * p.BW, y0 = ty * p.BH;
       const bool tile_full = (y0 + p.BH <= p.H) && (x0 + p.BW <= p.W);
       const uint32_t acc = lt & 1, aph = (lt >> 1) & 1;
-      mbar_wait(&tfull[acc], aph);
+      {
+        BGR_T0(t_w);
+        mbar_wait(&tfull[acc], aph);
+        if (threadIdx.x == 64) BGR_TACC(5, t_w);
+      }
       tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < BLOCK_N / 64; ++c) {
+      for (int ci = 0; ci < MYCH; ++ci) {
+        const int c = ci * SETS + set;
+        if (c >= NCHUNK) break;
         const int ch0 = n0 + c * 64;
         if (ch0 >= p.Cout) break;
+        if (CTAS == 2 && mt >= p.m_tiles) break;   // phantom tile of an odd tile count
         if (p.dbg == 2) break;   // timing experiments only (bgr_debug_conv_mode): no epilogue at all
-        uint8_t* buf = sO + (chunk_ctr & 1) * O_BYTES;
-        if (epi_tid == 0) bulk_wait_group_read<1>();   // the store issued two chunks ago has left smem
-        named_bar_sync(1, 128);
+        uint8_t* buf = sOset + (OBUFS == 2 ? (chunk_ctr & 1) * O_BYTES : 0);
+        if (OBUFS == 2) {
+          BGR_T0(t_w);
+          if (epi_tid == 0) bulk_wait_group_read<1>();   // the store issued two chunks ago has left smem
+          named_bar_sync(1 + set, 128);
+          if (threadIdx.x == 64) BGR_TACC(6, t_w);
+        }
         uint32_t v[64];
         const uint32_t taddr = tmem + (uint32_t(q * 32) << 16) + acc * BLOCK_N + c * 64;
         tmem_ld32(taddr, v);
         tmem_ld32(taddr + 32, v + 32);
         tmem_ld_wait();
+        if (OBUFS == 1) {   // the previous chunk's store has left the buffer (and every warp its statistics pass)
+          BGR_T0(t_w);
+          if (epi_tid == 0) bulk_wait_group_read<0>();
+          named_bar_sync(1 + set, 128);
+          if (threadIdx.x == 64) BGR_TACC(6, t_w);
+        }
         if (p.dbg == 3) { ++chunk_ctr; continue; }   // TMEM reads only
         if (bias != nullptr) {
 #pragma unroll
@@ -210,7 +302,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           *reinterpret_cast<uint4*>(my_row + ((j ^ (row & 7)) << 4)) = o;
         }
         fence_proxy_async();
-        named_bar_sync(1, 128);
+        named_bar_sync(1 + set, 128);
         if (epi_tid == 0 && p.dbg != 4) {   // dbg 4: everything but the TMA store
           tma_store_5d(&tmO, buf, ch0, 0, x0, y0, n);
           bulk_commit_group();
@@ -243,30 +335,37 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
             }
           }
-          st_sum[c * 2 + 0] += s0; st_sum[c * 2 + 1] += s1;
-          st_sq[c * 2 + 0] += q0;  st_sq[c * 2 + 1] += q1;
+          st_sum[ci * 2 + 0] += s0; st_sum[ci * 2 + 1] += s1;
+          st_sq[ci * 2 + 0] += q0;  st_sq[ci * 2 + 1] += q1;
         }
         ++chunk_ctr;
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if (CTAS == 2) mbar_arrive_cluster(tempty0 + acc * 8);
+        else mbar_arrive(&tempty[acc]);
+      }
     }
     if (epi_tid == 0) bulk_wait_group_read<0>();
+    if (threadIdx.x == 64) BGR_TACC(7, t_role);
     if (STATS) {
       // The four warps' sums are added in warp order through the (now idle) output staging buffers and the
       // CTA writes partial row mt_first of the [groups][2][Cout] workspace: no atomics, a fixed summation order.
-      named_bar_sync(2, 128);
+      // (every set's stores have left its staging buffers: all sets meet here before set 0's buffers are reused)
+      named_bar_sync(3, 128 * SETS);
       float* comb = reinterpret_cast<float*>(sO);   // [4 warps][2][BLOCK_N]
 #pragma unroll
-      for (int i = 0; i < BLOCK_N / 32; ++i) {   // st_*[c*2 + e] <-> channel c*64 + 2*lane + e
-        const int ch = (i >> 1) * 64 + 2 * lane + (i & 1);
+      for (int i = 0; i < 2 * MYCH; ++i) {
+        const int c = (i >> 1) * SETS + set;
+        if (c >= NCHUNK) break;
+        const int ch = c * 64 + 2 * lane + (i & 1);
         comb[q * 2 * BLOCK_N + ch] = st_sum[i];
         comb[q * 2 * BLOCK_N + BLOCK_N + ch] = st_sq[i];
       }
-      named_bar_sync(2, 128);
+      named_bar_sync(3, 128 * SETS);
       float* prow = stats + size_t(mt_first) * 2 * p.Cout;
-      for (int i = epi_tid; i < 2 * BLOCK_N; i += 128) {
+      for (int i = threadIdx.x - 64; i < 2 * BLOCK_N; i += 128 * SETS) {
         const int half = i / BLOCK_N, ch = i - half * BLOCK_N;
         if (n0 + ch < p.Cout)
           prow[half * p.Cout + n0 + ch] = ((comb[i] + comb[2 * BLOCK_N + i]) + comb[4 * BLOCK_N + i]) + comb[6 * BLOCK_N + i];
@@ -274,6 +373,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   }
   tc_fence_before();
+  if (CTAS == 2) {
+    cluster_sync_all();   // neither CTA leaves while the pair's MMAs or remote arrivals may still touch it
+    if (warp == 1) tmem_dealloc2<TMEM_COLS>(tmem);
+    return;
+  }
   __syncthreads();
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem);
 }
@@ -441,18 +545,36 @@ static int check_conv_args(const void* x, const void* w, const void* y, int Cin,
 
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB per CTA on sm_100
 
-template <int BLOCK_N, int STAGES, bool STATS>
+template <int BLOCK_N, int STAGES, bool STATS, int CTAS = 1>
 static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
                         const float* bias, float* stats, const ConvParams& p, int groups, cudaStream_t st) {
-  constexpr size_t needed = size_t(STAGES) * (kBlockM * kBlockK * 2 + BLOCK_N * kBlockK * 2) +
-                            2 * (kBlockM * 64 * 2) + (2 * STAGES + 4) * 8 + 16;
+  constexpr size_t needed = size_t(STAGES) * (kBlockM * kBlockK * 2 + (BLOCK_N / CTAS) * kBlockK * 2) +
+                            2 * (kBlockM * 64 * 2) + (2 * STAGES + 4) * 8 + 16;   // two staging buffers either way
   // the kernel aligns its window to 1024 B itself and traps if the slack does not suffice
   constexpr size_t smem = needed + 1024 > kMaxDynSmem ? kMaxDynSmem : needed + 1024;
   static_assert(needed <= kMaxDynSmem, "fprop stage ring does not fit");
-  auto kern = conv_fprop_kernel<BLOCK_N, STAGES, STATS>;
+  auto kern = conv_fprop_kernel<BLOCK_N, STAGES, STATS, CTAS>;
   if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
-  dim3 grid(groups * p.n_tiles);
-  BGR_CUDA_OK(launch_pdl<true>(kern, dim3(grid), dim3(192), smem, st, tmA, tmB, tmO, bias, stats, p));
+  dim3 grid(groups * p.n_tiles * CTAS);
+  if (CTAS == 2) {   // CTA pairs: clusters of two along x
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(64 + 128 * CTAS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled(true) ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
+    BGR_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, bias, stats, p));
+  } else {
+    BGR_CUDA_OK(launch_pdl<true>(kern, dim3(grid), dim3(192), smem, st, tmA, tmB, tmO, bias, stats, p));
+  }
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -507,6 +629,38 @@ using namespace bgr;
 
 extern "C" void bgr_debug_conv_block_n(int bn) { g_force_block_n = bn; }
 extern "C" void bgr_debug_conv_mode(int m) { g_conv_dbg = m; }
+extern "C" void bgr_debug_conv_ctas(int c) { g_force_ctas = c; }
+#ifdef BGR_CONV_TIMING
+static int g_force_stages = 0;
+extern "C" void bgr_debug_conv_stages(int s) { g_force_stages = s; }
+// out[512][8] cycles per CTA: producer {wait empty, role}, MMA {wait tempty, wait full, role}, epilogue {wait tfull,
+// wait staging buffer, role}; reset != 0 clears the counters afterwards
+extern "C" int bgr_debug_conv_timing(long long* out, int reset) {
+  BGR_CUDA_OK(cudaDeviceSynchronize());
+  BGR_CUDA_OK(cudaMemcpyFromSymbol(out, g_conv_timing, sizeof(long long) * 512 * 8));
+  if (reset) {
+    void* ptr = nullptr;
+    BGR_CUDA_OK(cudaGetSymbolAddress(&ptr, g_conv_timing));
+    BGR_CUDA_OK(cudaMemset(ptr, 0, sizeof(long long) * 512 * 8));
+  }
+  return BGR_OK;
+}
+#endif
+
+// CTA pairs (cta_group::2) for the forward kernel: 1 = 1-CTA tiles, 2 = pairs.  Pairs pay when the tile is bound
+// by its operand feed, i.e. a 256-wide Cout tile with a long reduction (measured per round of tiles, 1-CTA -> pair:
+// 12 k-blocks 6.37 -> 6.06 us, 24 k-blocks 11.16 -> 10.23 us; 4 k-blocks 4.36 -> 4.34 us; 128-wide tiles never
+// gain and lose at 2 k-blocks, 1.28 -> 2.35 us: there the two CTAs only wait for each other).
+// BGR_CONV_CTAS=1|2 (or bgr_debug_conv_ctas) forces one wherever the pair kernel exists.
+static int pick_ctas(int bn, int m_tiles, int iters) {
+  if (g_force_ctas < 0) {
+    const char* e = getenv("BGR_CONV_CTAS");
+    g_force_ctas = e ? atoi(e) : 0;
+  }
+  if ((bn != 128 && bn != 256) || m_tiles < 2) return 1;
+  if (g_force_ctas == 1 || g_force_ctas == 2) return g_force_ctas;
+  return bn == 256 && iters >= 8 ? 2 : 1;
+}
 
 // Cout tile width: 256 halves the activation re-reads and the shared-memory operand traffic per
 // FLOP, 128 quantises better onto the SMs, 192 sits between: 728 (= 768 padded) output channels at
@@ -548,6 +702,7 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
   for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
   p.dbg = g_conv_dbg;
   const int bn = pick_block_n(p.m_tiles, Cout);
+  const int ctas = pick_ctas(bn, p.m_tiles, p.ntaps * p.kblocks);
   p.n_tiles = (Cout + bn - 1) / bn;
   CUtensorMap tmA, tmB, tmO;
   if (int rc = make_act_map(&tmA, x, N, H, W, Cin, ldx, p.BW, p.BH)) return rc;
@@ -555,23 +710,31 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
   {
     uint64_t dims[3] = {uint64_t(Cin), uint64_t(ntaps), uint64_t(Cout)};
     uint64_t strides[2] = {uint64_t(ldw) * 2, uint64_t(ldw) * ntaps * 2};
-    uint32_t box[3] = {64, 1, uint32_t(bn)};
+    uint32_t box[3] = {64, 1, uint32_t(bn / ctas)};   // a CTA of a pair stages half of the Cout tile
     if (int rc = encode_tmap_bf16(&tmB, w, 3, dims, strides, box)) return rc;
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  int groups = sm_count() / p.n_tiles;   // CTAs per Cout tile
-  if (groups < 1) groups = 1;            // more Cout tiles than SMs: the surplus CTAs queue
-  if (groups > p.m_tiles) groups = p.m_tiles;
+  int groups = (sm_count() / ctas) / p.n_tiles;   // CTAs (or CTA pairs) per Cout tile
+  if (groups < 1) groups = 1;                     // more Cout tiles than SMs: the surplus CTAs queue
+  if (groups > (p.m_tiles + ctas - 1) / ctas) groups = (p.m_tiles + ctas - 1) / ctas;
   if (bn_part != nullptr) {
     if (bias != nullptr) return fail(BGR_ERR_ARG, "conv: fused BatchNorm statistics exclude a bias");
     if (bn_rows == nullptr) return fail(BGR_ERR_ARG, "conv: bn_rows must be given with bn_part");
-    if (groups > BGR_BN_MAX_ROWS) groups = BGR_BN_MAX_ROWS;
-    *bn_rows = groups;
+    if (groups * ctas > BGR_BN_MAX_ROWS) groups = BGR_BN_MAX_ROWS / ctas;
+    *bn_rows = groups * ctas;   // one partial row per CTA of a group
+#ifdef BGR_CONV_TIMING
+    if (ctas == 2 && bn == 256 && g_force_stages == 3) return launch_fprop<256, 3, true, 2>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
+    if (ctas == 2 && bn == 256 && g_force_stages == 4) return launch_fprop<256, 4, true, 2>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
+#endif
+    if (ctas == 2 && bn == 128) return launch_fprop<128, 8, true, 2>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
+    if (ctas == 2) return launch_fprop<256, 6, true, 2>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
     if (bn == 64) return launch_fprop<64, 6, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
     if (bn == 128) return launch_fprop<128, 6, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
     if (bn == 192) return launch_fprop<192, 4, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
     return launch_fprop<256, 4, true>(tmA, tmB, tmO, bias, bn_part, p, groups, st);
   }
+  if (ctas == 2 && bn == 128) return launch_fprop<128, 8, false, 2>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
+  if (ctas == 2) return launch_fprop<256, 6, false, 2>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
   if (bn == 64) return launch_fprop<64, 6, false>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
   if (bn == 128) return launch_fprop<128, 6, false>(tmA, tmB, tmO, bias, nullptr, p, groups, st);
   if (bn == 192) return launch_fprop<192, 4, false>(tmA, tmB, tmO, bias, nullptr, p, groups, st);

@@ -118,6 +118,46 @@ def test_weight_to_gemm_bit_exact(dev, Cout, Cin, k):
         assert float(full[..., Cout:].abs().max()) == 0.0
 
 
+@pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil,use_bias", [
+    (8, 48, 72, 728, 728, 1, 1, False),    # the mid-flow signature: 216 pixel tiles, 3 Cout tiles
+    (1, 48, 72, 728, 728, 1, 1, False),    # 27 pixel tiles: an odd count, the last pair has a phantom tile
+    (3, 17, 23, 256, 256, 3, 1, False),    # ragged pixel tiles, 9 taps
+    (2, 48, 72, 2048, 256, 3, 6, False),   # ASPP: dilated taps, 288 k-blocks per tile
+    (1, 30, 50, 304, 256, 3, 1, True),     # bias epilogue, no statistics
+    (7, 8, 16, 1536, 2048, 1, 1, False),   # 8 Cout tiles, 7 pixel tiles
+    (2, 37, 41, 128, 128, 3, 1, False),    # the 128-wide pair kernel (never picked, kept selectable)
+    (1, 9, 200, 136, 1000, 1, 1, False)])  # ragged Cout tile
+def test_conv_cta_pairs_match_single_cta(dev, N, H, W, Cin, Cout, ks, dil, use_bias):
+    """The CTA-pair forward kernel (cta_group::2: two CTAs share one 256-row MMA, each staging half of the
+    weight tile) against the 1-CTA kernel on the same inputs: outputs bit-identical, the fused BatchNorm partial
+    rows (a different row partition) add up to the same sums and repeat bit for bit."""
+    from bias_gan_b200 import _lib, kernels as K, layouts as L
+    g = torch.Generator(device="cpu").manual_seed(17)
+    x = nhwc(torch.randn(N, Cin, H, W, generator=g).to(dev).bfloat16())
+    w = L.gemm_weight((torch.randn(Cout, Cin, ks, ks, generator=g) / (Cin * ks * ks) ** 0.5).to(dev))
+    bias = torch.randn(Cout, generator=g).to(dev) if use_bias else None
+    dy, dx = K.taps_for(ks, dil)
+    out = {}
+    try:
+        for ctas in (1, 2):
+            _lib.lib().bgr_debug_conv_ctas(ctas)
+            if use_bias:
+                out[ctas] = (K.conv_fprop(x, w, dy, dx, bias=bias), None)
+            else:
+                out[ctas] = K.conv_fprop(x, w, dy, dx, want_stats=True)
+                again = K.conv_fprop(x, w, dy, dx, want_stats=True)
+                assert torch.equal(out[ctas][0], again[0]) and torch.equal(out[ctas][1], again[1])
+    finally:
+        _lib.lib().bgr_debug_conv_ctas(0)
+    assert torch.equal(out[1][0], out[2][0])
+    if not use_bias:
+        s1, s2 = out[1][1].double().sum(0), out[2][1].double().sum(0)
+        # fp32 tile sums added in another order: errors scale with sqrt(M * sum y^2), not with the (cancelling) sum
+        scale = torch.cat([(N * H * W * s1[Cout:]).sqrt(), s1[Cout:]]) + 1e-6
+        assert ((s1 - s2).abs() / scale).max().item() < 1e-5
+        assert out[2][1].shape[0] <= 148
+
+
 @pytest.mark.parametrize("block_n", [0, 128, 192, 256])
 @pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil", [
     (2, 48, 72, 728, 728, 1, 1), (1, 19, 37, 304, 256, 3, 1), (3, 40, 56, 128, 1536, 1, 1), (1, 24, 40, 128, 48, 1, 1),
