@@ -19,6 +19,13 @@
 static int g_force_block_n = 0;   // development switches (bgr_debug_conv_*)
 static int g_conv_dbg = 0;
 static int g_force_ctas = -1;     // -1 = not read yet (BGR_CONV_CTAS), 0 = pick, 1 / 2 = forced
+static int g_force_ctas_read() {
+  if (g_force_ctas < 0) {
+    const char* e = getenv("BGR_CONV_CTAS");
+    g_force_ctas = e ? atoi(e) : 0;
+  }
+  return g_force_ctas;
+}
 
 namespace bgr {
 
@@ -387,13 +394,15 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 // chunks into one 128 x BLOCK_N fp32 tile in TMEM and stores it into the slab of its split
 // (slab 0 = dW itself when there is one split); sum_rows adds the slabs in split order.
 // ------------------------------------------------------------------------------------------
-template <int BLOCK_N, int STAGES>
+// CTAS = 2 (CTA pair, see the forward kernel): the pair owns 256 couts x BLOCK_N cins; each CTA stages its 128
+// couts of dY^T and half of the cins of X^T, and drains its own 128 accumulator rows.
+template <int BLOCK_N, int STAGES, int CTAS = 1>
 __global__ void __launch_bounds__(192, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                   float* __restrict__ dw, const __grid_constant__ ConvParams p) {
   constexpr uint32_t BOX_BYTES = 64 * kBlockK * 2;           // one 64-channel x 64-pixel box
   constexpr uint32_t A_BYTES = (kBlockM / 64) * BOX_BYTES;   // dY^T : 128 couts
-  constexpr uint32_t B_BYTES = (BLOCK_N / 64) * BOX_BYTES;   // X^T  : BLOCK_N cins
+  constexpr uint32_t B_BYTES = (BLOCK_N / CTAS / 64) * BOX_BYTES;   // X^T  : this CTA's share of BLOCK_N cins
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
@@ -406,10 +415,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tiles = (p.Cin + BLOCK_N - 1) / BLOCK_N;
-  const int t = blockIdx.x % p.ntaps;
-  const int nt = (blockIdx.x / p.ntaps) % n_tiles;
-  const int mt = blockIdx.x / (p.ntaps * n_tiles);
-  const int m0 = mt * kBlockM, n0 = nt * BLOCK_N;
+  const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
+  const int unit = blockIdx.x / CTAS;   // the tile (of a CTA or of a pair)
+  const int t = unit % p.ntaps;
+  const int nt = (unit / p.ntaps) % n_tiles;
+  const int mt = unit / (p.ntaps * n_tiles);
+  const int m0 = (mt * CTAS + int(rank)) * kBlockM, n0 = nt * BLOCK_N;   // this CTA's couts; the tile's cins
   const int c_begin = blockIdx.y * p.chunks_per_split;
   const int c_end = min(c_begin + p.chunks_per_split, p.total_chunks);
   const int iters = max(c_end - c_begin, 0);
@@ -424,9 +435,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<BLOCK_N>(tmem_slot);
+  if (warp == 1) {
+    if (CTAS == 2) tmem_alloc2<BLOCK_N>(tmem_slot);
+    else tmem_alloc<BLOCK_N>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   // everything above (barrier init, descriptor prefetch, TMEM allocation) touched no global memory: it may
@@ -437,6 +452,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
   if (iters > 0) {
     if (warp == 0) {
       if (lane == 0) {
+        const uint32_t full0 = CTAS == 2 ? mapa_shared(smem_u32(&full[0]), 0) : 0u;   // the leader's full[] barriers
         for (int it = 0; it < iters; ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
@@ -446,6 +462,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
           const int cy = (c / p.tiles_x) % p.tiles_y;
           const int n = c / (p.tiles_x * p.tiles_y);
           const int x0 = cx * p.BW, y0 = cy * p.BH;
+          if (CTAS == 2) {
+            if (rank == 0) mbar_expect_tx(&full[s], 2 * (A_BYTES + B_BYTES));
+#pragma unroll
+            for (int b = 0; b < kBlockM / 64; ++b)
+              tma_load_5d_2sm(sA + s * A_BYTES + b * BOX_BYTES, &tmDY, full0 + s * 8, m0 + b * 64, 0, x0, y0, n);
+#pragma unroll
+            for (int b = 0; b < BLOCK_N / 2 / 64; ++b)
+              tma_load_5d_2sm(sB + s * B_BYTES + b * BOX_BYTES, &tmX, full0 + s * 8,
+                              n0 + int(rank) * (BLOCK_N / 2) + b * 64, 0, x0 + p.dx[t], y0 + p.dy[t], n);
+            continue;
+          }
           mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
 #pragma unroll
           for (int b = 0; b < kBlockM / 64; ++b)
@@ -458,7 +485,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
         }
       }
     } else if (warp == 1) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM, BLOCK_N, 1, 1);
+      if (CTAS == 1 || rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBlockM * CTAS, BLOCK_N, 1, 1);
       const uint64_t da0 = umma_desc_sw128(smem_u32(sA), BOX_BYTES, 1024), db0 = umma_desc_sw128(smem_u32(sB), BOX_BYTES, 1024);
       const uint32_t a_hi = uint32_t(da0 >> 32), b_hi = uint32_t(db0 >> 32);
       const uint32_t a_lo0 = uint32_t(da0), b_lo0 = uint32_t(db0);
@@ -469,15 +497,22 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
         if (elect_one_sync()) {
           const uint32_t al = a_lo0 + s * (A_BYTES >> 4), bl = b_lo0 + s * (B_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k)  // 16 pixel rows = 2048 B per MMA
-            umma_bf16_w(tmem, al + k * 128, a_hi, bl + k * 128, b_hi, idesc, k ? 1u : uint32_t(it != 0));
-          umma_commit(&empty[s]);
+          for (int k = 0; k < kBlockK / 16; ++k) {  // 16 pixel rows = 2048 B per MMA
+            if (CTAS == 2) umma_bf16_w2(tmem, al + k * 128, a_hi, bl + k * 128, b_hi, idesc, k ? 1u : uint32_t(it != 0));
+            else umma_bf16_w(tmem, al + k * 128, a_hi, bl + k * 128, b_hi, idesc, k ? 1u : uint32_t(it != 0));
+          }
+          if (CTAS == 2) umma_commit2(&empty[s]);
+          else umma_commit(&empty[s]);
         }
         __syncwarp();
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
-      if (elect_one_sync()) umma_commit(tmem_full);
+      if (elect_one_sync()) {
+        if (CTAS == 2) umma_commit2(tmem_full);
+        else umma_commit(tmem_full);
+      }
       __syncwarp();
+      }
     } else {
       const int q = warp & 3;
       mbar_wait(tmem_full, 0);
@@ -500,6 +535,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
     }
   }
   tc_fence_before();
+  if (CTAS == 2) {
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc2<BLOCK_N>(tmem);
+    return;
+  }
   __syncthreads();
   if (warp == 1) tmem_dealloc<BLOCK_N>(tmem);
 }
@@ -545,6 +585,26 @@ static int check_conv_args(const void* x, const void* w, const void* y, int Cin,
 
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB per CTA on sm_100
 
+// Launch with clusters of two CTAs along x (CTA pairs); gemm-class programmatic dependent launch as launch_pdl<true>.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pairs(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled(true) ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 template <int BLOCK_N, int STAGES, bool STATS, int CTAS = 1>
 static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
                         const float* bias, float* stats, const ConvParams& p, int groups, cudaStream_t st) {
@@ -556,22 +616,8 @@ static int launch_fprop(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   auto kern = conv_fprop_kernel<BLOCK_N, STAGES, STATS, CTAS>;
   if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
   dim3 grid(groups * p.n_tiles * CTAS);
-  if (CTAS == 2) {   // CTA pairs: clusters of two along x
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid;
-    cfg.blockDim = dim3(64 + 128 * CTAS);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[2];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled(true) ? 1 : 0;
-    cfg.attrs = attr;
-    cfg.numAttrs = 2;
-    BGR_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, bias, stats, p));
+  if (CTAS == 2) {
+    BGR_CUDA_OK(launch_pairs(kern, dim3(grid), dim3(64 + 128 * CTAS), smem, st, tmA, tmB, tmO, bias, stats, p));
   } else {
     BGR_CUDA_OK(launch_pdl<true>(kern, dim3(grid), dim3(192), smem, st, tmA, tmB, tmO, bias, stats, p));
   }
@@ -591,10 +637,20 @@ static int wgrad_block_n(int Cin) {
 // Split the pixel reduction over `splits` CTAs per tile.  Every split costs a prologue and a
 // Cout x Cin pass of fp32 stores + one re-read through L2 (about 32 chunks' worth of MMA time), and the
 // grid runs in rounds of one CTA per SM: take the split count with the cheapest schedule.
+// CTA pairs for the weight gradient: 256 couts per pair, so only where that pads no worse than 128-cout tiles, with
+// the wide Cin tile (the feed-bound one).  BGR_CONV_CTAS / bgr_debug_conv_ctas force 1 or 2 where the shape allows.
+static int wgrad_ctas(int Cout, int Cin) {
+  const int forced = g_force_ctas_read();
+  if (wgrad_block_n(Cin) != 256 || Cout < 256) return 1;
+  if (forced == 1 || forced == 2) return forced;
+  return (Cout + 255) / 256 * 2 == (Cout + 127) / 128 ? 2 : 1;
+}
+
 static int wgrad_splits(int Cout, int Cin, int ntaps, int total_chunks, int* chunks_per_split) {
   const int bn = wgrad_block_n(Cin);
-  const int tiles = ((Cout + kBlockM - 1) / kBlockM) * ((Cin + bn - 1) / bn) * ntaps;
-  const int sms = sm_count();
+  const int ctas = wgrad_ctas(Cout, Cin);
+  const int tiles = ((Cout + kBlockM * ctas - 1) / (kBlockM * ctas)) * ((Cin + bn - 1) / bn) * ntaps;
+  const int sms = sm_count() / ctas;   // CTAs or CTA pairs that run at once
   int splits = 1;
   long best = -1;
   for (int sp = 1; sp <= 64 && sp <= total_chunks; ++sp) {
@@ -609,16 +665,18 @@ static int wgrad_splits(int Cout, int Cin, int ntaps, int total_chunks, int* chu
   return (total_chunks + *chunks_per_split - 1) / *chunks_per_split;
 }
 
-template <int BLOCK_N, int STAGES>
+template <int BLOCK_N, int STAGES, int CTAS = 1>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, float* dst, int splits,
                         const ConvParams& p, cudaStream_t st) {
-  constexpr size_t smem = size_t(STAGES) * ((kBlockM + BLOCK_N) * kBlockK * 2) +
+  constexpr size_t smem = size_t(STAGES) * ((kBlockM + BLOCK_N / CTAS) * kBlockK * 2) +
                           (2 * STAGES + 1) * 8 + 16 + 1024;
-  auto kern = conv_wgrad_kernel<BLOCK_N, STAGES>;
+  static_assert(smem <= kMaxDynSmem, "wgrad stage ring does not fit");
+  auto kern = conv_wgrad_kernel<BLOCK_N, STAGES, CTAS>;
   if (int rc = ensure_dyn_smem(kern, int(smem))) return rc;
-  const int tiles = ((p.Cout + kBlockM - 1) / kBlockM) * ((p.Cin + BLOCK_N - 1) / BLOCK_N) * p.ntaps;
-  dim3 grid(tiles, splits);
-  BGR_CUDA_OK(launch_pdl<true>(kern, dim3(grid), dim3(192), smem, st, tmDY, tmX, dst, p));
+  const int tiles = ((p.Cout + kBlockM * CTAS - 1) / (kBlockM * CTAS)) * ((p.Cin + BLOCK_N - 1) / BLOCK_N) * p.ntaps;
+  dim3 grid(tiles * CTAS, splits);
+  if (CTAS == 2) BGR_CUDA_OK(launch_pairs(kern, dim3(grid), dim3(192), smem, st, tmDY, tmX, dst, p));
+  else BGR_CUDA_OK(launch_pdl<true>(kern, dim3(grid), dim3(192), smem, st, tmDY, tmX, dst, p));
   BGR_LAUNCH_OK();
   return BGR_OK;
 }
@@ -653,10 +711,7 @@ extern "C" int bgr_debug_conv_timing(long long* out, int reset) {
 // gain and lose at 2 k-blocks, 1.28 -> 2.35 us: there the two CTAs only wait for each other).
 // BGR_CONV_CTAS=1|2 (or bgr_debug_conv_ctas) forces one wherever the pair kernel exists.
 static int pick_ctas(int bn, int m_tiles, int iters) {
-  if (g_force_ctas < 0) {
-    const char* e = getenv("BGR_CONV_CTAS");
-    g_force_ctas = e ? atoi(e) : 0;
-  }
+  g_force_ctas_read();
   if ((bn != 128 && bn != 256) || m_tiles < 2) return 1;
   if (g_force_ctas == 1 || g_force_ctas == 2) return g_force_ctas;
   return bn == 256 && iters >= 8 ? 2 : 1;
@@ -780,6 +835,7 @@ extern "C" int bgr_conv_wgrad(const void* x, int N, int H, int W, int Cin, int l
   const int bn = wgrad_block_n(Cin);
   int rc;
   if (bn == 64) rc = launch_wgrad<64, 6>(tmDY, tmX, dst, splits, p, st);
+  else if (bn == 256 && wgrad_ctas(Cout, Cin) == 2) rc = launch_wgrad<256, 6, 2>(tmDY, tmX, dst, splits, p, st);
   else if (bn == 256) rc = launch_wgrad<256, 4>(tmDY, tmX, dst, splits, p, st);
   else rc = launch_wgrad<128, 6>(tmDY, tmX, dst, splits, p, st);
   if (rc != BGR_OK || splits == 1) return rc;

@@ -158,6 +158,36 @@ def test_conv_cta_pairs_match_single_cta(dev, N, H, W, Cin, Cout, ks, dil, use_b
         assert out[2][1].shape[0] <= 148
 
 
+@pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil", [
+    (8, 48, 72, 728, 728, 1, 1),     # mid-flow: 3 x 3 pair tiles, 8 pixel splits
+    (1, 48, 72, 728, 728, 1, 1),
+    (2, 17, 23, 256, 256, 3, 1),     # ragged pixel chunks, 9 taps
+    (2, 48, 72, 2048, 256, 3, 6),    # ASPP: dilated taps
+    (3, 9, 20, 264, 1000, 1, 1),     # ragged Cout (1000 = 3.9 pair tiles) and Cin (264) tiles
+    (1, 30, 50, 304, 256, 3, 1)])
+def test_conv_wgrad_cta_pairs_match_single_cta(dev, N, H, W, Cin, Cout, ks, dil):
+    """The CTA-pair weight-gradient kernel (256 couts per pair, half of the Cin tile staged per CTA) against the
+    1-CTA kernel: same values up to the fp32 order of the pixel splits, both bit-identical on repeats, and the
+    centre tap against an fp64 product of the same bf16 operands."""
+    from bias_gan_b200 import _lib, kernels as K
+    g = torch.Generator(device="cpu").manual_seed(23)
+    x = nhwc(torch.randn(N, Cin, H, W, generator=g).to(dev).bfloat16())
+    gy = nhwc(torch.randn(N, Cout, H, W, generator=g).to(dev).bfloat16())
+    dy, dx = K.taps_for(ks, dil)
+    out = {}
+    try:
+        for ctas in (1, 2):
+            _lib.lib().bgr_debug_conv_ctas(ctas)
+            out[ctas] = K.conv_wgrad(x, gy, dy, dx).clone()
+            assert torch.equal(out[ctas], K.conv_wgrad(x, gy, dy, dx))
+    finally:
+        _lib.lib().bgr_debug_conv_ctas(0)
+    scale = out[1].abs().max().item()
+    assert (out[1] - out[2]).abs().max().item() <= 2e-5 * scale
+    ref = gy.double().reshape(-1, Cout).t() @ x.double().reshape(-1, Cin)
+    assert (out[2][:, len(dy) // 2].double() - ref).abs().max().item() <= 3e-5 * ref.abs().max().item()
+
+
 @pytest.mark.parametrize("block_n", [0, 128, 192, 256])
 @pytest.mark.parametrize("N,H,W,Cin,Cout,ks,dil", [
     (2, 48, 72, 728, 728, 1, 1), (1, 19, 37, 304, 256, 3, 1), (3, 40, 56, 128, 1536, 1, 1), (1, 24, 40, 128, 48, 1, 1),
