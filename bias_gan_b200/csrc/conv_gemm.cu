@@ -708,13 +708,14 @@ extern "C" int bgr_debug_conv_timing(long long* out, int reset) {
 // CTA pairs (cta_group::2) for the forward kernel: 1 = 1-CTA tiles, 2 = pairs.  Pairs pay when the tile is bound
 // by its operand feed, i.e. a 256-wide Cout tile with a long reduction (measured per round of tiles, 1-CTA -> pair:
 // 12 k-blocks 6.37 -> 6.06 us, 24 k-blocks 11.16 -> 10.23 us; 4 k-blocks 4.36 -> 4.34 us; 128-wide tiles never
-// gain and lose at 2 k-blocks, 1.28 -> 2.35 us: there the two CTAs only wait for each other).
+// gain and lose at 2 k-blocks, 1.28 -> 2.35 us: there the two CTAs only wait for each other; at 4 k-blocks pairs
+// gain only when several Cout tiles re-read the pixel tile, 256 -> 728 at 96 x 144: 92.9 -> 82.1 us).
 // BGR_CONV_CTAS=1|2 (or bgr_debug_conv_ctas) forces one wherever the pair kernel exists.
-static int pick_ctas(int bn, int m_tiles, int iters) {
+static int pick_ctas(int bn, int m_tiles, int iters, int n_tiles) {
   g_force_ctas_read();
   if ((bn != 128 && bn != 256) || m_tiles < 2) return 1;
   if (g_force_ctas == 1 || g_force_ctas == 2) return g_force_ctas;
-  return bn == 256 && iters >= 8 ? 2 : 1;
+  return bn == 256 && (iters >= 8 || (iters >= 4 && n_tiles >= 2)) ? 2 : 1;
 }
 
 // Cout tile width: 256 halves the activation re-reads and the shared-memory operand traffic per
@@ -757,8 +758,8 @@ extern "C" int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int l
   for (int t = 0; t < ntaps; ++t) { p.dy[t] = dy[t]; p.dx[t] = dx[t]; }
   p.dbg = g_conv_dbg;
   const int bn = pick_block_n(p.m_tiles, Cout);
-  const int ctas = pick_ctas(bn, p.m_tiles, p.ntaps * p.kblocks);
   p.n_tiles = (Cout + bn - 1) / bn;
+  const int ctas = pick_ctas(bn, p.m_tiles, p.ntaps * p.kblocks, p.n_tiles);
   CUtensorMap tmA, tmB, tmO;
   if (int rc = make_act_map(&tmA, x, N, H, W, Cin, ldx, p.BW, p.BH)) return rc;
   if (int rc = make_act_map(&tmO, y, N, H, W, Cout, ldy, p.BW, p.BH)) return rc;
