@@ -63,7 +63,7 @@ struct ConvParams {
 #ifdef BGR_CONV_TIMING
 __device__ long long g_conv_timing[512][8];
 #define BGR_T0(v) const long long v = clock64()
-#define BGR_TACC(slot, v) g_conv_timing[blockIdx.x][slot] += clock64() - (v)
+#define BGR_TACC(slot, v) g_conv_timing[blockIdx.y * gridDim.x + blockIdx.x][slot] += clock64() - (v)
 #else
 #define BGR_T0(v)
 #define BGR_TACC(slot, v)
@@ -453,10 +453,15 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
     if (warp == 0) {
       if (lane == 0) {
         const uint32_t full0 = CTAS == 2 ? mapa_shared(smem_u32(&full[0]), 0) : 0u;   // the leader's full[] barriers
+        BGR_T0(t_role);
         for (int it = 0; it < iters; ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
-          mbar_wait(&empty[s], ph ^ 1);
+          {
+            BGR_T0(t_w);
+            mbar_wait(&empty[s], ph ^ 1);
+            BGR_TACC(0, t_w);
+          }
           const int c = c_begin + it;
           const int cx = c % p.tiles_x;
           const int cy = (c / p.tiles_x) % p.tiles_y;
@@ -483,6 +488,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
             tma_load_5d(sB + s * B_BYTES + b * BOX_BYTES, &tmX, &full[s], n0 + b * 64, 0,
                         x0 + p.dx[t], y0 + p.dy[t], n);
         }
+        BGR_TACC(1, t_role);
       }
     } else if (warp == 1) {
       if (CTAS == 1 || rank == 0) {
@@ -491,8 +497,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
       const uint32_t a_hi = uint32_t(da0 >> 32), b_hi = uint32_t(db0 >> 32);
       const uint32_t a_lo0 = uint32_t(da0), b_lo0 = uint32_t(db0);
       uint32_t s = 0, ph = 0;
+      BGR_T0(t_role);
       for (int it = 0; it < iters; ++it) {   // warp-uniform; one elected lane issues (see fprop)
-        mbar_wait(&full[s], ph);
+        {
+          BGR_T0(t_w);
+          mbar_wait(&full[s], ph);
+          if (lane == 0) BGR_TACC(3, t_w);
+        }
         tc_fence_after();
         if (elect_one_sync()) {
           const uint32_t al = a_lo0 + s * (A_BYTES >> 4), bl = b_lo0 + s * (B_BYTES >> 4);
@@ -512,10 +523,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
         else umma_commit(tmem_full);
       }
       __syncwarp();
+      if (lane == 0) BGR_TACC(4, t_role);
       }
     } else {
       const int q = warp & 3;
+      BGR_T0(t_role);
       mbar_wait(tmem_full, 0);
+      if (threadIdx.x == 64) BGR_TACC(5, t_role);
       tc_fence_after();
       const int co = m0 + q * 32 + lane;
       float* drow = dw + size_t(blockIdx.y) * p.slab_elems + (size_t(co) * p.ntaps + t) * p.Cin + n0;
@@ -532,6 +546,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
                                                                       __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
         }
       }
+      if (threadIdx.x == 64) BGR_TACC(7, t_role);
     }
   }
   tc_fence_before();
