@@ -119,6 +119,10 @@ int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const v
 /* ldw: elements between consecutive (cout, tap) rows of w (>= Cin, multiple of 8).  TMA moves whole
  * 128-byte lines: keep ldx, ldy and ldw multiples of 64 elements where the channel count is not
  * (728 -> 768) so that no pixel row straddles a line — measured 1.65x on the 728-channel layers. */
+/* Wide, deep layers (Cout tile 256 with >= 8 k-blocks, or >= 4 and several Cout tiles) run as CTA pairs
+ * (tcgen05.mma.cta_group::2, clusters of two CTAs); results are bit-identical to the 1-CTA kernel.  The
+ * environment variable BGR_CONV_CTAS=1 keeps every layer on the 1-CTA kernels (2 forces pairs wherever the pair
+ * kernel exists); same for bgr_conv_wgrad. */
 /* bn_part (optional, NULL to skip; excludes bias): fp32 [BGR_BN_MAX_ROWS][2*Cout] workspace; the conv
  * epilogue writes *bn_rows (HOST int) partial rows of [sum_m y | sum_m y^2] of the bf16-rounded outputs,
  * one per group of thread blocks, for bgr_bn_finalize to add in row order — the statistics pass of
