@@ -823,6 +823,45 @@ static void wgrad_geometry(ConvParams* p, int N, int H, int W, int Cin, int Cout
   p->slab_elems = long(Cout) * ntaps * Cin;
 }
 
+// Launch plan of the implicit-GEMM kernels for one layer signature, from the same pick functions the launches use
+// (no device work; with no device the SM count falls back to 148).  kind 0 = bgr_conv_fprop, 1 = bgr_conv_wgrad.
+extern "C" int bgr_conv_plan(int kind, int N, int H, int W, int Cin, int Cout, int ntaps, int with_stats, int* out8) {
+  if (out8 == nullptr || ntaps < 1 || ntaps > kMaxTaps || N < 1 || H < 1 || W < 1 || Cin < 8 || Cout < 8)
+    return fail(BGR_ERR_ARG, "conv_plan: bad arguments");
+  for (int i = 0; i < 8; ++i) out8[i] = 0;
+  if (kind == 0) {
+    int BW, BH;
+    pick_rect(H, W, kBlockM, &BW, &BH);
+    const int m_tiles = N * ((W + BW - 1) / BW) * ((H + BH - 1) / BH);
+    const int kblocks = (Cin + kBlockK - 1) / kBlockK;
+    const int bn = pick_block_n(m_tiles, Cout);
+    const int n_tiles = (Cout + bn - 1) / bn;
+    const int ctas = pick_ctas(bn, m_tiles, ntaps * kblocks, n_tiles);
+    int groups = (sm_count() / ctas) / n_tiles;   // as in bgr_conv_fprop
+    if (groups < 1) groups = 1;
+    if (groups > (m_tiles + ctas - 1) / ctas) groups = (m_tiles + ctas - 1) / ctas;
+    if (with_stats && groups * ctas > BGR_BN_MAX_ROWS) groups = BGR_BN_MAX_ROWS / ctas;
+    out8[0] = bn; out8[1] = ctas; out8[2] = n_tiles; out8[3] = groups; out8[4] = m_tiles;
+    out8[5] = ((m_tiles + ctas - 1) / ctas + groups - 1) / groups;   // rounds of tiles
+    out8[6] = with_stats ? groups * ctas : 0;                        // BatchNorm partial rows
+    out8[7] = groups * n_tiles * ctas;                               // grid
+    return BGR_OK;
+  }
+  if (kind == 1) {
+    ConvParams p{};
+    wgrad_geometry(&p, N, H, W, Cin, Cout, ntaps);
+    int cps = 0;
+    const int splits = wgrad_splits(Cout, Cin, ntaps, p.total_chunks, &cps);
+    const int bn = wgrad_block_n(Cin), ctas = wgrad_ctas(Cout, Cin);
+    const int tiles = ((Cout + kBlockM * ctas - 1) / (kBlockM * ctas)) * ((Cin + bn - 1) / bn) * ntaps;
+    out8[0] = bn; out8[1] = ctas; out8[2] = tiles; out8[3] = splits; out8[4] = cps; out8[5] = p.total_chunks;
+    out8[6] = tiles * ctas * splits;   // grid (CTAs)
+    out8[7] = splits > 1 ? 1 : 0;      // needs the slab workspace
+    return BGR_OK;
+  }
+  return fail(BGR_ERR_ARG, "conv_plan: kind must be 0 (fprop) or 1 (wgrad)");
+}
+
 extern "C" size_t bgr_conv_wgrad_workspace(int N, int H, int W, int Cin, int Cout, int ntaps) {
   if (ntaps < 1 || ntaps > kMaxTaps) return 0;
   ConvParams p{};

@@ -129,6 +129,13 @@ int bgr_conv_fprop(const void* x, int N, int H, int W, int Cin, int ldx, const v
  * the nn.BatchNorm2d that follows every such conv in the reference (deeplab.py:179,183,334,...)
  * without re-reading y (same contract as bgr_bn_stats). */
 
+/* Launch plan of the implicit-GEMM kernels for one layer signature (host only, no device work; for tests and for
+ * sizing workspaces; no counterpart in the reference).  kind 0 (bgr_conv_fprop): out8 = {Cout tile width, CTAs per
+ * tile (2 = cta_group::2 pair), Cout tiles, CTA groups, pixel tiles, rounds of tiles, BatchNorm partial rows (0
+ * without with_stats), grid}.  kind 1 (bgr_conv_wgrad): out8 = {Cin tile width, CTAs per tile, tiles, pixel splits,
+ * chunks per split, 64-pixel chunks, grid, 1 if the slab workspace is needed}. */
+int bgr_conv_plan(int kind, int N, int H, int W, int Cin, int Cout, int ntaps, int with_stats, int* out8);
+
 /* fp32 master weight [Cout][Cin][taps] (nn.Conv2d.weight) -> the bf16 operand bgr_conv_fprop reads:
  * [Cout][taps][pitch] (transpose = 0) or, for the data gradient, [Cin][taps][pitch] with Cout
  * innermost (transpose = 1); pitch >= inner dimension, padding written as zeros. */
